@@ -1,0 +1,135 @@
+/* ipkgpu.h -- C ABI of the B200 (sm_100a) phylo-k-mer database build.
+ *
+ * Drop-in boundary for ONE path of phylo42/IPK: what `ipk::build(...)` (ipk/include/db_builder.h:22-29, called
+ * from ipk/src/main.cpp:182-198) computes between "posterior matrices are available" and "k-mers are handed to
+ * save_phylo_kmer in filter-value order" (ipk/src/db_builder.cpp:182-338).  The reference has no FFI of its own;
+ * these entry points are what a maintainer would bind from db_builder.cpp.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function returns 0 on success or a negative
+ * IPKGPU_E* code and never throws; the message for the last failure of a context is ipkgpu_last_error().
+ * A context is bound to one CUDA device and one stream; calls on one context must not overlap in time.
+ * There is NO CPU fallback: without a usable CUDA device ipkgpu_create() fails with IPKGPU_ENODEV.
+ */
+#ifndef IPKGPU_H
+#define IPKGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IPKGPU_OK        0
+#define IPKGPU_EINVAL   -1   /* bad argument (k, sigma, bits, null pointer, key does not fit 64 bits ...) */
+#define IPKGPU_ENODEV   -2   /* no CUDA device / device is not sm_100 */
+#define IPKGPU_ENOMEM   -3   /* device or pinned-host memory exhausted (emitted volume is data dependent) */
+#define IPKGPU_ECUDA    -4   /* any other CUDA runtime failure */
+
+#define IPKGPU_FILTER_MIF0   0   /* ipk::filter_type::mif0   (ipk/include/filter.h:12-18) */
+#define IPKGPU_FILTER_RANDOM 1   /* ipk::filter_type::random */
+
+typedef struct ipkgpu_ctx ipkgpu_ctx;
+
+/* Replaces the arguments of ipk::build that matter to the computation (db_builder.h:22-29):
+ * `proba_matrix& matrix` + `ghost_mapping` + `ar::mapping` + ghost_strategy collapse into (logp, node_branch):
+ * the caller lists the ghost nodes it wants explored (is_ghost, db_builder.cpp:495-507; root skipped, :535-539)
+ * in processing order; equal branch ids form one branch group (group_ghost_ids, :524-553). */
+typedef struct ipkgpu_input
+{
+    const float*    logp;          /* [n_nodes][width][sigma] fp32 log10 posteriors, site-major like
+                                      ipk::matrix (window.h:23,67); host memory, or device memory if logp_on_device */
+    const uint32_t* node_branch;   /* [n_nodes] post-order id of the ORIGINAL node (db_builder.cpp:613-618); host */
+    uint32_t n_nodes;
+    uint32_t width;                /* alignment columns W; windows per node = W-k+1 (window.cpp:159-197) */
+    uint32_t sigma;                /* i2l::seq_traits::alphabet_size: 4 (DNA) or 20 (amino acids); 2..32 accepted */
+    uint32_t bits;                 /* i2l::bit_length<seq_type>(): 2 or 5 (pk_compute.cpp:99,103) */
+    uint32_t k;                    /* k-mer size; k*bits + ceil(log2(#groups)) must fit 64 bits */
+    float    log_threshold;        /* log10(score_threshold(omega,k)), db_builder.cpp:640 -- computed by the caller */
+    float    threshold;            /* score_threshold(omega,k) as score_type, db_builder.cpp:260 (MIF0 only) */
+    uint32_t total_num_groups;     /* original_tree.get_node_count(), db_builder.cpp:261 (MIF0 only) */
+    int32_t  filter;               /* IPKGPU_FILTER_* */
+    int32_t  logp_on_device;       /* 0: logp is a host pointer (copied H2D inside the call); 1: device pointer */
+} ipkgpu_input;
+
+typedef struct ipkgpu_stats
+{
+    uint64_t n_windows;            /* n_nodes * (W-k+1) */
+    uint64_t n_emitted;            /* candidates DCLA would emit over all windows (pk_compute.cpp:105) */
+    uint64_t n_entries;            /* unique (k-mer, branch) after the per-branch max (branch_group.cpp:88-101) */
+    uint64_t n_kmers;              /* distinct k-mers */
+    uint32_t n_groups;             /* branch groups */
+    uint32_t sort_passes;          /* radix passes of the merge sort */
+    uint32_t enum_launches;        /* enumeration launches (2 when the first attempt overflowed its buffer) */
+    uint32_t kernel_launches;      /* all kernels of this library launched by the call */
+    float ms_h2d, ms_prefix, ms_enumerate, ms_sort, ms_merge, ms_filter, ms_order, ms_d2h, ms_total;  /* CUDA events */
+    uint64_t h2d_bytes, d2h_bytes;
+} ipkgpu_stats;
+
+/* The database in the order db_builder.cpp:323-332 serializes it: k-mers by ascending filter value (ties: ascending
+ * key), each with its (branch, score) entries in branch-group processing order (db_builder.cpp:685-693).
+ * Arrays are owned by the context and stay valid until the next ipkgpu_build / ipkgpu_free_result / ipkgpu_destroy. */
+typedef struct ipkgpu_result
+{
+    uint64_t n_kmers, n_entries;
+    const uint64_t* keys;          /* [n_kmers]   i2l::phylo_kmer::key_type */
+    const float*    fv;            /* [n_kmers]   kmer_fv::filter_value */
+    const uint64_t* offsets;       /* [n_kmers+1] CSR offsets into branch/score */
+    const uint32_t* branch;        /* [n_entries] pkdb_value::branch (post-order id) */
+    const float*    score;         /* [n_entries] pkdb_value::score (log10) */
+    int32_t on_device;             /* 1: the five arrays are device pointers; 0: pinned host memory */
+    ipkgpu_stats stats;
+} ipkgpu_result;
+
+/* i2l::score_threshold(omega, k) = (omega / sigma)^k evaluated in score_type (float) arithmetic, and the
+ * log10 of it that explore_group compares against (db_builder.cpp:260,640).  Host-only helper so that every caller
+ * (C++ host, Python harness, oracle drivers) feeds the kernels the same two constants.  UNVERIFIED(i2l): the
+ * submodule source is absent; float powf / log10f is what the call sites' types imply. */
+void ipkgpu_score_threshold(float omega, uint32_t sigma, uint32_t k, float* threshold, float* log_threshold);
+
+/* device: CUDA ordinal.  stream: a cudaStream_t to run on (e.g. the caller's timing stream), or NULL for a private one. */
+int  ipkgpu_create(ipkgpu_ctx** out, int device, void* stream);
+void ipkgpu_destroy(ipkgpu_ctx* ctx);
+const char* ipkgpu_last_error(const ipkgpu_ctx* ctx);      /* ctx may be NULL: message of the last failed create */
+void* ipkgpu_stream(const ipkgpu_ctx* ctx);                /* the cudaStream_t all work of ctx is ordered on */
+int  ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes);   /* cap on device scratch; 0 = 85% of free memory */
+
+/* The whole path: H2D (if needed) -> best_prefix -> enumerate -> sort + per-branch max -> CSR by k-mer -> filter
+ * values -> order by filter value -> gather (-> D2H unless result_on_device).  Blocking. */
+int  ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out);
+void ipkgpu_free_result(ipkgpu_ctx* ctx, ipkgpu_result* res);
+
+/* ---- stage-level entry points (parity tests; multi-GPU build, where the caller runs the exchange) ---------------- */
+
+/* matrix::preprocess (window.cpp:16-27) for every node: B_out[n_nodes][W+1] (host). */
+int  ipkgpu_best_prefix(ipkgpu_ctx* ctx, const ipkgpu_input* in, float* B_out);
+
+/* `for window in to_windows(m,k): DCLA(window,k).run(eps)` (db_builder.cpp:645-649) for every node, unmerged.
+ * Writes up to cap records (any order) to the HOST arrays and the true total to *n_out. */
+int  ipkgpu_enumerate(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint64_t cap,
+                      uint32_t* node_out, uint32_t* window_out, uint64_t* key_out, float* score_out, uint64_t* n_out);
+
+/* Stage 1 of one rank: enumerate + per-branch max over this rank's nodes (the rank's branch groups are numbered
+ * group_base, group_base+1, ... in order of first appearance).  Leaves the unique records on the device as
+ * composite keys  (kmer << group_bits) | global group index  with their scores; chunks are sorted by (kmer, group).
+ * *n_out = their number.  stats may be NULL. */
+int  ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out,
+                   ipkgpu_stats* stats);
+/* Buckets the stage-1 records by owner = mix64(kmer) % n_parts, stably, into caller-provided DEVICE buffers of n_out
+ * records (the send buffers of the all-to-all); counts[n_parts] (host) receives the bucket sizes. */
+int  ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys, float* d_scores, uint64_t* counts);
+/* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
+ * values -> order.  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
+ * chunks_group_ordered != 0 promises that the records are a concatenation of chunks in ascending group ranges, each
+ * sorted by (kmer, group) -- what the all-to-all of stably partitioned stage-1 records delivers -- so that a stable
+ * sort on the k-mer bits alone suffices; 0 sorts on all key_bits + group_bits.
+ * group_branch[n_groups_total] (host) maps global group index -> branch id. */
+int  ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t n, uint32_t group_bits,
+                   const uint32_t* group_branch, uint32_t n_groups_total, uint32_t key_bits,
+                   float threshold, uint32_t total_num_groups, int32_t filter, int32_t chunks_group_ordered,
+                   int result_on_device, ipkgpu_result* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IPKGPU_H */

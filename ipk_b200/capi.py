@@ -1,0 +1,306 @@
+"""ctypes binding of the C ABI in include/ipkgpu.h (libipkgpu.so, sm_100a).
+
+This is plumbing only: every entry point below forwards to the CUDA library.  There is no CPU fallback -- if the
+shared library is missing or no B200 is visible the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libipkgpu.so")
+
+FILTER_MIF0 = 0
+FILTER_RANDOM = 1
+
+ERRORS = {0: "OK", -1: "EINVAL", -2: "ENODEV", -3: "ENOMEM", -4: "ECUDA"}
+
+
+class IpkGpuError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libipkgpu {ERRORS.get(code, code)}: {message}")
+        self.code = code
+
+
+class Input(C.Structure):
+    _fields_ = [
+        ("logp", C.c_void_p),
+        ("node_branch", C.c_void_p),
+        ("n_nodes", C.c_uint32),
+        ("width", C.c_uint32),
+        ("sigma", C.c_uint32),
+        ("bits", C.c_uint32),
+        ("k", C.c_uint32),
+        ("log_threshold", C.c_float),
+        ("threshold", C.c_float),
+        ("total_num_groups", C.c_uint32),
+        ("filter", C.c_int32),
+        ("logp_on_device", C.c_int32),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n_windows", C.c_uint64),
+        ("n_emitted", C.c_uint64),
+        ("n_entries", C.c_uint64),
+        ("n_kmers", C.c_uint64),
+        ("n_groups", C.c_uint32),
+        ("sort_passes", C.c_uint32),
+        ("enum_launches", C.c_uint32),
+        ("kernel_launches", C.c_uint32),
+        ("ms_h2d", C.c_float),
+        ("ms_prefix", C.c_float),
+        ("ms_enumerate", C.c_float),
+        ("ms_sort", C.c_float),
+        ("ms_merge", C.c_float),
+        ("ms_filter", C.c_float),
+        ("ms_order", C.c_float),
+        ("ms_d2h", C.c_float),
+        ("ms_total", C.c_float),
+        ("h2d_bytes", C.c_uint64),
+        ("d2h_bytes", C.c_uint64),
+    ]
+
+    def as_dict(self) -> dict:
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class Result(C.Structure):
+    _fields_ = [
+        ("n_kmers", C.c_uint64),
+        ("n_entries", C.c_uint64),
+        ("keys", C.c_void_p),
+        ("fv", C.c_void_p),
+        ("offsets", C.c_void_p),
+        ("branch", C.c_void_p),
+        ("score", C.c_void_p),
+        ("on_device", C.c_int32),
+        ("stats", Stats),
+    ]
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen libipkgpu.so (built in-tree by __graft_entry__.build()).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(nvcc, sm_100a). ipk_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    P = C.POINTER
+    lib.ipkgpu_create.argtypes = [P(C.c_void_p), C.c_int, C.c_void_p]
+    lib.ipkgpu_create.restype = C.c_int
+    lib.ipkgpu_destroy.argtypes = [C.c_void_p]
+    lib.ipkgpu_destroy.restype = None
+    lib.ipkgpu_last_error.argtypes = [C.c_void_p]
+    lib.ipkgpu_last_error.restype = C.c_char_p
+    lib.ipkgpu_stream.argtypes = [C.c_void_p]
+    lib.ipkgpu_stream.restype = C.c_void_p
+    lib.ipkgpu_set_workspace_limit.argtypes = [C.c_void_p, C.c_uint64]
+    lib.ipkgpu_set_workspace_limit.restype = C.c_int
+    lib.ipkgpu_build.argtypes = [C.c_void_p, P(Input), C.c_int, P(Result)]
+    lib.ipkgpu_build.restype = C.c_int
+    lib.ipkgpu_free_result.argtypes = [C.c_void_p, P(Result)]
+    lib.ipkgpu_free_result.restype = None
+    lib.ipkgpu_best_prefix.argtypes = [C.c_void_p, P(Input), C.c_void_p]
+    lib.ipkgpu_best_prefix.restype = C.c_int
+    lib.ipkgpu_enumerate.argtypes = [C.c_void_p, P(Input), C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     P(C.c_uint64)]
+    lib.ipkgpu_enumerate.restype = C.c_int
+    lib.ipkgpu_stage1.argtypes = [C.c_void_p, P(Input), C.c_uint32, C.c_uint32, P(C.c_uint64), P(Stats)]
+    lib.ipkgpu_stage1.restype = C.c_int
+    lib.ipkgpu_stage1_partition.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, P(C.c_uint64)]
+    lib.ipkgpu_stage1_partition.restype = C.c_int
+    lib.ipkgpu_stage2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
+                                  C.c_uint32, C.c_float, C.c_uint32, C.c_int32, C.c_int32, C.c_int, P(Result)]
+    lib.ipkgpu_stage2.restype = C.c_int
+    lib.ipkgpu_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, P(C.c_float), P(C.c_float)]
+    lib.ipkgpu_score_threshold.restype = None
+    _lib = lib
+    return lib
+
+
+def score_threshold(omega: float, sigma: int, k: int) -> tuple[float, float]:
+    """(threshold, log10 threshold) as the library's host helper computes them (float powf / log10f)."""
+    t, lt = C.c_float(0), C.c_float(0)
+    load().ipkgpu_score_threshold(omega, sigma, k, C.byref(t), C.byref(lt))
+    return float(t.value), float(lt.value)
+
+
+def _ptr(a) -> int:
+    """address of a numpy array / torch tensor / raw int"""
+    if a is None:
+        return 0
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    raise TypeError(type(a))
+
+
+@dataclass
+class PhyloKmerDB:
+    """What db_builder.cpp:323-332 hands to save_phylo_kmer, k-mer by k-mer, as CSR arrays (host numpy copies)."""
+    keys: np.ndarray       # u64 [n_kmers], ascending filter value (ties: ascending key)
+    fv: np.ndarray         # f32 [n_kmers]
+    offsets: np.ndarray    # u64 [n_kmers+1]
+    branch: np.ndarray     # u32 [n_entries]
+    score: np.ndarray      # f32 [n_entries]
+    stats: dict = field(default_factory=dict)
+
+    @property
+    def n_kmers(self) -> int:
+        return int(self.keys.shape[0])
+
+    @property
+    def n_entries(self) -> int:
+        return int(self.branch.shape[0])
+
+
+def _view(addr, n, dtype):
+    if n == 0 or not addr:
+        return np.zeros(0, dtype=dtype)
+    nbytes = n * np.dtype(dtype).itemsize
+    buf = (C.c_char * nbytes).from_address(addr)
+    return np.frombuffer(buf, dtype=dtype, count=n)
+
+
+def make_input(logp, node_branch: np.ndarray, width: int, sigma: int, bits: int, k: int, log_threshold: float,
+               threshold: float, total_num_groups: int, filter: int = FILTER_MIF0) -> tuple[Input, tuple]:
+    """logp: numpy [n_nodes, W, sigma] float32 (host) or a CUDA torch tensor of that shape."""
+    node_branch = np.ascontiguousarray(node_branch, dtype=np.uint32)
+    n_nodes = int(node_branch.shape[0])
+    on_device = 0
+    if isinstance(logp, np.ndarray):
+        if logp.dtype != np.float32 or not logp.flags.c_contiguous:
+            raise ValueError("logp must be C-contiguous float32")
+        if logp.size != n_nodes * width * sigma:
+            raise ValueError("logp has the wrong number of elements")
+    else:
+        import torch
+        if logp.dtype != torch.float32 or not logp.is_contiguous():
+            raise ValueError("logp must be a contiguous float32 tensor")
+        if logp.numel() != n_nodes * width * sigma:
+            raise ValueError("logp has the wrong number of elements")
+        on_device = 1 if logp.is_cuda else 0
+    inp = Input(_ptr(logp), _ptr(node_branch), n_nodes, width, sigma, bits, k, log_threshold, threshold,
+                total_num_groups, filter, on_device)
+    return inp, (logp, node_branch)      # keep-alive
+
+
+class Context:
+    """One ipkgpu_ctx: one CUDA device, one stream."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._lib = load()
+        self._h = C.c_void_p()
+        rc = self._lib.ipkgpu_create(C.byref(self._h), device, C.c_void_p(stream or 0))
+        if rc != 0:
+            raise IpkGpuError(rc, (self._lib.ipkgpu_last_error(None) or b"").decode())
+        self.device = device
+
+    def close(self):
+        if self._h:
+            self._lib.ipkgpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise IpkGpuError(rc, (self._lib.ipkgpu_last_error(self._h) or b"").decode())
+
+    @property
+    def stream(self) -> int:
+        return int(self._lib.ipkgpu_stream(self._h) or 0)
+
+    def set_workspace_limit(self, nbytes: int):
+        self._check(self._lib.ipkgpu_set_workspace_limit(self._h, nbytes))
+
+    # ---- whole path ------------------------------------------------------------------------------------------------
+    def build_raw(self, inp: Input, result_on_device: bool = False) -> Result:
+        res = Result()
+        self._check(self._lib.ipkgpu_build(self._h, C.byref(inp), 1 if result_on_device else 0, C.byref(res)))
+        return res
+
+    @staticmethod
+    def to_db(res: Result) -> PhyloKmerDB:
+        if res.on_device:
+            raise ValueError("result lives on the device")
+        nk, ne = int(res.n_kmers), int(res.n_entries)
+        return PhyloKmerDB(_view(res.keys, nk, np.uint64).copy(), _view(res.fv, nk, np.float32).copy(),
+                           _view(res.offsets, nk + 1, np.uint64).copy() if nk or res.offsets else np.zeros(1, np.uint64),
+                           _view(res.branch, ne, np.uint32).copy(), _view(res.score, ne, np.float32).copy(),
+                           res.stats.as_dict())
+
+    def build(self, logp, node_branch, width, sigma, bits, k, log_threshold, threshold, total_num_groups,
+              filter=FILTER_MIF0) -> PhyloKmerDB:
+        inp, keep = make_input(logp, node_branch, width, sigma, bits, k, log_threshold, threshold, total_num_groups, filter)
+        res = self.build_raw(inp, False)
+        del keep
+        return self.to_db(res)
+
+    # ---- stage-level -----------------------------------------------------------------------------------------------
+    def best_prefix(self, logp, node_branch, width, sigma, bits, k) -> np.ndarray:
+        inp, keep = make_input(logp, node_branch, width, sigma, bits, k, 0.0, 0.0, 0)
+        out = np.empty((inp.n_nodes, width + 1), dtype=np.float32)
+        self._check(self._lib.ipkgpu_best_prefix(self._h, C.byref(inp), out.ctypes.data))
+        del keep
+        return out
+
+    def enumerate(self, logp, node_branch, width, sigma, bits, k, log_threshold, cap: int):
+        """-> (n_total, node[u32], window[u32], key[u64], score[f32]) with min(n_total, cap) records, any order"""
+        inp, keep = make_input(logp, node_branch, width, sigma, bits, k, log_threshold, 0.0, 0)
+        node = np.empty(cap, np.uint32)
+        win = np.empty(cap, np.uint32)
+        key = np.empty(cap, np.uint64)
+        score = np.empty(cap, np.float32)
+        n = C.c_uint64(0)
+        self._check(self._lib.ipkgpu_enumerate(self._h, C.byref(inp), cap, node.ctypes.data, win.ctypes.data,
+                                               key.ctypes.data, score.ctypes.data, C.byref(n)))
+        del keep
+        m = min(int(n.value), cap)
+        return int(n.value), node[:m], win[:m], key[:m], score[:m]
+
+    def stage1(self, inp: Input, group_base: int, group_bits: int) -> tuple[int, dict]:
+        n = C.c_uint64(0)
+        st = Stats()
+        self._check(self._lib.ipkgpu_stage1(self._h, C.byref(inp), group_base, group_bits, C.byref(n), C.byref(st)))
+        return int(n.value), st.as_dict()
+
+    def stage1_partition(self, n_parts: int, d_keys, d_scores) -> np.ndarray:
+        counts = np.zeros(n_parts, np.uint64)
+        self._check(self._lib.ipkgpu_stage1_partition(self._h, n_parts, _ptr(d_keys), _ptr(d_scores),
+                                                      counts.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return counts
+
+    def stage2(self, d_keys, d_scores, n: int, group_bits: int, group_branch: np.ndarray, key_bits: int, threshold: float,
+               total_num_groups: int, filter: int = FILTER_MIF0, chunks_group_ordered: bool = True,
+               result_on_device: bool = False) -> Result:
+        group_branch = np.ascontiguousarray(group_branch, dtype=np.uint32)
+        res = Result()
+        self._check(self._lib.ipkgpu_stage2(self._h, _ptr(d_keys), _ptr(d_scores), n, group_bits, group_branch.ctypes.data,
+                                            int(group_branch.shape[0]), key_bits, threshold, total_num_groups, filter,
+                                            1 if chunks_group_ordered else 0, 1 if result_on_device else 0, C.byref(res)))
+        return res

@@ -1,0 +1,163 @@
+// common.cuh -- context, error plumbing and device scratch management of libipkgpu (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdarg>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include "../../include/ipkgpu.h"
+
+namespace ipkgpu
+{
+    struct error
+    {
+        int code;
+        std::string what;
+    };
+
+    [[noreturn]] inline void fail(int code, const char* fmt, ...)
+    {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        throw error{ code, buf };
+    }
+
+#define IPK_CUDA(expr)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t e_ = (expr);                                                                             \
+        if (e_ != cudaSuccess)                                                                               \
+            ::ipkgpu::fail(e_ == cudaErrorMemoryAllocation ? IPKGPU_ENOMEM : IPKGPU_ECUDA, "%s failed: %s (%s:%d)", \
+                           #expr, cudaGetErrorString(e_), __FILE__, __LINE__);                               \
+    } while (0)
+
+    /// Grow-only device buffer, reused across builds so that steady-state calls do no cudaMalloc.
+    struct dbuf
+    {
+        void* p = nullptr;
+        size_t cap = 0;
+        template<class T> T* as() const { return static_cast<T*>(p); }
+    };
+
+    /// Grow-only pinned host buffer (results handed back to the caller live here).
+    struct hbuf
+    {
+        void* p = nullptr;
+        size_t cap = 0;
+        template<class T> T* as() const { return static_cast<T*>(p); }
+    };
+
+    constexpr int NUM_SMS_B200 = 148;
+}
+
+struct ipkgpu_ctx
+{
+    int device = 0;
+    int num_sms = ipkgpu::NUM_SMS_B200;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint64_t workspace_limit = 0;      // 0 = 85 % of free memory, evaluated per build
+    size_t dev_bytes = 0;              // bytes currently held by dbufs
+    std::string last_error;
+    uint32_t launches = 0;             // kernels launched by the current call
+
+    // device scratch
+    ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
+    ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
+    ipkgpu::dbuf dbg_node, dbg_win;
+    ipkgpu::dbuf u_keys, u_scores;                 // unique (kmer,group) records, composite keys
+    ipkgpu::dbuf kmer_keys, kmer_offs, ent_branch, ent_score, fv, ord_keys_a, ord_keys_b, ord_vals_a, ord_vals_b;
+    ipkgpu::dbuf out_keys, out_fv, out_offs, out_branch, out_score, out_cnt;
+    // stage-1 state kept for ipkgpu_stage1_partition
+    uint64_t s1_n = 0;
+    uint32_t s1_group_bits = 0;
+    uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
+    // pinned host staging
+    ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score;
+
+    std::vector<cudaEvent_t> events;
+
+    void reserve(ipkgpu::dbuf& b, size_t bytes)
+    {
+        if (bytes <= b.cap) return;
+        if (b.p) { cudaFree(b.p); dev_bytes -= b.cap; b.p = nullptr; b.cap = 0; }
+        // round up a little so that slowly growing inputs do not realloc on every call
+        size_t want = bytes + bytes / 16 + 256;
+        cudaError_t e = cudaMalloc(&b.p, want);
+        if (e != cudaSuccess) { want = bytes; e = cudaMalloc(&b.p, want); }
+        if (e != cudaSuccess)
+        {
+            cudaGetLastError();
+            b.p = nullptr;
+            ipkgpu::fail(IPKGPU_ENOMEM, "device allocation of %zu bytes failed (%s); %zu bytes already held",
+                         bytes, cudaGetErrorString(e), dev_bytes);
+        }
+        b.cap = want;
+        dev_bytes += want;
+    }
+    /// grow while preserving the first keep_bytes (accumulators that are appended to batch after batch)
+    void reserve_keep(ipkgpu::dbuf& b, size_t bytes, size_t keep_bytes)
+    {
+        if (bytes <= b.cap) return;
+        if (!b.p || keep_bytes == 0) { reserve(b, bytes); return; }
+        ipkgpu::dbuf nb;
+        reserve(nb, std::max(bytes, b.cap * 2));
+        cudaError_t e = cudaMemcpyAsync(nb.p, b.p, keep_bytes, cudaMemcpyDeviceToDevice, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) { release(nb); ipkgpu::fail(IPKGPU_ECUDA, "device copy while growing a buffer failed: %s", cudaGetErrorString(e)); }
+        release(b);
+        b = nb;
+    }
+    void release(ipkgpu::dbuf& b)
+    {
+        if (b.p) { cudaFree(b.p); dev_bytes -= b.cap; }
+        b.p = nullptr; b.cap = 0;
+    }
+    void reserve_host(ipkgpu::hbuf& b, size_t bytes)
+    {
+        if (bytes <= b.cap) return;
+        if (b.p) cudaFreeHost(b.p);
+        b.p = nullptr; b.cap = 0;
+        size_t want = bytes + bytes / 16 + 256;
+        cudaError_t e = cudaMallocHost(&b.p, want);
+        if (e != cudaSuccess)
+        {
+            cudaGetLastError();
+            b.p = nullptr;
+            ipkgpu::fail(IPKGPU_ENOMEM, "pinned host allocation of %zu bytes failed (%s)", want, cudaGetErrorString(e));
+        }
+        b.cap = want;
+    }
+    cudaEvent_t event(size_t i)
+    {
+        while (events.size() <= i)
+        {
+            cudaEvent_t e;
+            IPK_CUDA(cudaEventCreate(&e));
+            events.push_back(e);
+        }
+        return events[i];
+    }
+};
+
+namespace ipkgpu
+{
+    inline void check_launch(ipkgpu_ctx* ctx, const char* name)
+    {
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) fail(IPKGPU_ECUDA, "launch of %s failed: %s", name, cudaGetErrorString(e));
+        ctx->launches++;
+    }
+    inline uint32_t ceil_log2(uint64_t x)
+    {
+        uint32_t b = 0;
+        while ((1ull << b) < x) ++b;
+        return b;
+    }
+    template<class T> inline T div_up(T a, T b) { return (a + b - 1) / b; }
+}

@@ -1,0 +1,780 @@
+// ipkgpu.cu -- C-ABI implementation (include/ipkgpu.h) of the B200 phylo-k-mer database build.  sm_100a only.
+//
+// Pipeline of one build (reference: db_builder::run, ipk/src/db_builder.cpp:182-338):
+//   H2D posteriors -> K1 best_prefix -> [per batch of branch groups: K2 enumerate -> radix sort on (kmer|group) ->
+//   segmented max (K3)] -> (regroup sort, only when there were several batches / an exchange) -> CSR by k-mer (K3')
+//   -> K4 filter values -> K5 order by filter value -> K6 gather -> D2H.
+// There is no CPU fallback anywhere in this file: every stage is a kernel from the .cuh files next to it.
+#include "common.cuh"
+#include "enumerate.cuh"
+#include "radix_sort.cuh"
+#include "merge.cuh"
+#include "filter.cuh"
+
+#include <cmath>
+#include <numeric>
+#include <unordered_map>
+
+using namespace ipkgpu;
+
+namespace
+{
+    thread_local std::string g_create_error;
+
+    /// group_ghost_ids (db_builder.cpp:524-553): groups in order of first appearance of the branch id; plus the
+    /// node order the enumeration launches in (nodes sorted by group, stable).
+    struct group_tables
+    {
+        std::vector<uint32_t> node_group, group_branch, node_order, group_first_slot;   // group_first_slot[g..n_groups]
+    };
+
+    group_tables make_groups(const uint32_t* node_branch, uint32_t n_nodes, uint32_t group_base)
+    {
+        group_tables t;
+        t.node_group.resize(n_nodes);
+        std::unordered_map<uint32_t, uint32_t> index;
+        index.reserve(n_nodes * 2 + 1);
+        for (uint32_t n = 0; n < n_nodes; ++n)
+        {
+            auto it = index.find(node_branch[n]);
+            if (it == index.end())
+            {
+                it = index.emplace(node_branch[n], uint32_t(t.group_branch.size())).first;
+                t.group_branch.push_back(node_branch[n]);
+            }
+            t.node_group[n] = it->second;
+        }
+        const uint32_t n_groups = uint32_t(t.group_branch.size());
+        t.group_first_slot.assign(n_groups + 1, 0);
+        for (uint32_t n = 0; n < n_nodes; ++n) t.group_first_slot[t.node_group[n] + 1]++;
+        for (uint32_t g = 0; g < n_groups; ++g) t.group_first_slot[g + 1] += t.group_first_slot[g];
+        t.node_order.resize(n_nodes);
+        std::vector<uint32_t> cursor(t.group_first_slot.begin(), t.group_first_slot.end() - 1);
+        for (uint32_t n = 0; n < n_nodes; ++n) t.node_order[cursor[t.node_group[n]]++] = n;
+        for (auto& g : t.node_group) g += group_base;
+        return t;
+    }
+
+    void validate(const ipkgpu_input* in)
+    {
+        if (!in) fail(IPKGPU_EINVAL, "input is null");
+        if (in->n_nodes && (!in->logp || !in->node_branch)) fail(IPKGPU_EINVAL, "logp / node_branch is null");
+        if (in->sigma < 2 || in->sigma > 32) fail(IPKGPU_EINVAL, "sigma = %u outside [2, 32]", in->sigma);
+        if (in->bits < 1 || in->bits > 8 || (1u << in->bits) < in->sigma)
+            fail(IPKGPU_EINVAL, "bits = %u cannot encode %u states", in->bits, in->sigma);
+        if (in->k < 1 || in->k > uint32_t(MAX_K)) fail(IPKGPU_EINVAL, "k = %u outside [1, %d]", in->k, MAX_K);
+        if (in->k * in->bits > 63) fail(IPKGPU_EINVAL, "k * bits = %u does not fit the 64-bit k-mer key", in->k * in->bits);
+        if (in->filter != IPKGPU_FILTER_MIF0 && in->filter != IPKGPU_FILTER_RANDOM) fail(IPKGPU_EINVAL, "unknown filter %d", in->filter);
+        if (uint64_t(in->n_nodes) * (uint64_t(in->width) + 1) > 0xffffffffull) fail(IPKGPU_EINVAL, "n_nodes * width too large");
+    }
+
+    struct stage_timer
+    {
+        ipkgpu_ctx* ctx;
+        size_t next = 0;
+        explicit stage_timer(ipkgpu_ctx* c) : ctx(c) {}
+        size_t mark()
+        {
+            cudaEvent_t e = ctx->event(next);
+            IPK_CUDA(cudaEventRecord(e, ctx->stream));
+            return next++;
+        }
+        float ms(size_t a, size_t b)
+        {
+            float t = 0;
+            IPK_CUDA(cudaEventElapsedTime(&t, ctx->event(a), ctx->event(b)));
+            return t;
+        }
+    };
+
+    size_t free_device_bytes()
+    {
+        size_t f = 0, t = 0;
+        IPK_CUDA(cudaMemGetInfo(&f, &t));
+        return f;
+    }
+
+    /// device pointer to the posteriors (copying them in when they are on the host) + group tables on the device
+    const float* stage_inputs(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& t, ipkgpu_stats* st)
+    {
+        const size_t logp_bytes = size_t(in->n_nodes) * in->width * in->sigma * sizeof(float);
+        const float* d_logp = in->logp;
+        if (!in->logp_on_device)
+        {
+            ctx->reserve(ctx->logp, logp_bytes);
+            IPK_CUDA(cudaMemcpyAsync(ctx->logp.p, in->logp, logp_bytes, cudaMemcpyHostToDevice, ctx->stream));
+            d_logp = ctx->logp.as<float>();
+            if (st) st->h2d_bytes += logp_bytes;
+        }
+        const size_t nb = size_t(in->n_nodes) * 4;
+        ctx->reserve(ctx->node_group, nb);
+        ctx->reserve(ctx->node_order, nb);
+        ctx->reserve(ctx->group_branch, t.group_branch.size() * 4 + 4);
+        IPK_CUDA(cudaMemcpyAsync(ctx->node_group.p, t.node_group.data(), nb, cudaMemcpyHostToDevice, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(ctx->node_order.p, t.node_order.data(), nb, cudaMemcpyHostToDevice, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(ctx->group_branch.p, t.group_branch.data(), t.group_branch.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        if (st) st->h2d_bytes += 2 * nb + t.group_branch.size() * 4;
+        // the host vectors above are pageable: the copies are staged synchronously by the runtime, safe to drop after
+        return d_logp;
+    }
+
+    /// K1: matrix::preprocess for every node (window.cpp:16-27)
+    void run_best_prefix(ipkgpu_ctx* ctx, const float* d_logp, const ipkgpu_input* in)
+    {
+        const uint64_t cols = uint64_t(in->n_nodes) * in->width;
+        ctx->reserve(ctx->colmax, cols * 4 + 4);
+        ctx->reserve(ctx->bestpref, uint64_t(in->n_nodes) * (in->width + 1) * 4 + 4);
+        if (in->n_nodes == 0) return;
+        if (cols)
+        {
+            const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(cols, 256), uint64_t(ctx->num_sms) * 16));
+            k1a_colmax<<<grid, 256, 0, ctx->stream>>>(d_logp, ctx->colmax.as<float>(), in->n_nodes, in->width, in->sigma);
+            check_launch(ctx, "k1a_colmax");
+        }
+        k1b_prefix<<<div_up<uint32_t>(in->n_nodes, 64), 64, 0, ctx->stream>>>(ctx->colmax.as<float>(), ctx->bestpref.as<float>(), in->n_nodes, in->width);
+        check_launch(ctx, "k1b_prefix");
+    }
+}
+
+namespace
+{
+    struct enum_launch
+    {
+        uint32_t slot_begin, slot_end;     // launch slots (positions in node_order)
+        uint32_t group_sub, group_bits;    // batch-local group field
+        uint64_t cap;
+        uint64_t* out_keys; float* out_scores;
+        uint32_t* out_node = nullptr; uint32_t* out_win = nullptr;     // debug
+        bool debug = false;
+    };
+
+    /// K2 over a range of launch slots.  counters[0] must have been zeroed; node_counts zeroed by the caller if used.
+    void launch_enumerate(ipkgpu_ctx* ctx, const float* d_logp, const ipkgpu_input* in, const enum_program& P, const enum_launch& L,
+                          bool with_node_counts)
+    {
+        if (in->width < in->k || L.slot_end <= L.slot_begin) return;
+        enum_args A;
+        memset(&A, 0, sizeof A);
+        A.logp = d_logp;
+        A.B = ctx->bestpref.as<float>();
+        A.node_order = ctx->node_order.as<uint32_t>();
+        A.node_group = ctx->node_group.as<uint32_t>();
+        A.out_keys = L.out_keys;
+        A.out_scores = L.out_scores;
+        A.out_node = L.out_node;
+        A.out_win = L.out_win;
+        A.counter = ctx->counters.as<unsigned long long>();
+        A.node_counts = with_node_counts ? ctx->node_counts.as<unsigned long long>() : nullptr;
+        A.cap = L.cap;
+        A.slot_base = L.slot_begin;
+        A.group_sub = L.group_sub;
+        A.n_nodes = in->n_nodes; A.W = in->width; A.sigma = in->sigma; A.bits = in->bits;
+        A.group_bits = L.group_bits;
+        A.nwin = in->width - in->k + 1;
+        A.tiles_per_node = div_up<uint32_t>(A.nwin, ENUM_THREADS);
+        A.log_threshold = in->log_threshold;
+        // TMA bulk copies need 16-byte aligned source, destination and size
+        A.use_tma = ((in->sigma * 4) % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_logp) & 15) == 0);
+        const uint64_t grid = uint64_t(L.slot_end - L.slot_begin) * A.tiles_per_node;
+        if (grid > 0x7fffffffull) fail(IPKGPU_EINVAL, "enumeration grid of %llu tiles is too large", (unsigned long long)grid);
+        const size_t smem = enum_smem_bytes(int(in->k), int(in->sigma), L.debug);
+        if (L.debug)
+        {
+            IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            k2_enumerate<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P);
+        }
+        else
+        {
+            IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            k2_enumerate<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P);
+        }
+        check_launch(ctx, "k2_enumerate");
+    }
+
+    uint64_t read_u64(ipkgpu_ctx* ctx, const void* d)
+    {
+        uint64_t v = 0;
+        IPK_CUDA(cudaMemcpyAsync(&v, d, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        return v;
+    }
+
+    struct merge_out
+    {
+        uint64_t n_records = 0, n_kmers = 0;
+    };
+
+    /// K3 on n sorted records (keys, scores): segmented max over equal composite keys, compaction, and -- when
+    /// `csr` -- the CSR by k-mer (K3').  Unique records go to (u_keys, u_scores) + u_off when `unique`.
+    merge_out run_merge(ipkgpu_ctx* ctx, const uint64_t* keys, const float* scores, uint64_t n, uint32_t group_bits,
+                        uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr)
+    {
+        merge_out r;
+        if (n == 0) return r;
+        const uint32_t tiles = uint32_t(div_up<uint64_t>(n, MG_TILE));
+        ctx->reserve(ctx->block_counts, size_t(tiles) * 8);
+        ctx->reserve(ctx->counters, 64);
+        uint32_t* rc = ctx->block_counts.as<uint32_t>();
+        uint32_t* kc = rc + tiles;
+        mg_count<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, n, group_bits, rc, kc);
+        check_launch(ctx, "mg_count");
+        unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;
+        exclusive_scan_u32(ctx, rc, rc, tiles, ctx->scan_tmp, totals);
+        exclusive_scan_u32(ctx, kc, kc, tiles, ctx->scan_tmp, totals + 1);
+        uint64_t h[2];
+        IPK_CUDA(cudaMemcpyAsync(h, totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        r.n_records = h[0];
+        r.n_kmers = h[1];
+        if (unique)
+        {
+            ctx->reserve_keep(ctx->u_keys, (u_off + r.n_records) * 8, u_off * 8);
+            ctx->reserve_keep(ctx->u_scores, (u_off + r.n_records) * 4, u_off * 4);
+        }
+        if (csr)
+        {
+            ctx->reserve(ctx->kmer_keys, r.n_kmers * 8 + 8);
+            ctx->reserve(ctx->kmer_offs, (r.n_kmers + 1) * 8);
+            ctx->reserve(ctx->ent_branch, r.n_records * 4 + 4);
+            ctx->reserve(ctx->ent_score, r.n_records * 4 + 4);
+        }
+        mg_write<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, scores, n, group_bits, out_group_bits, group_add, rc, kc,
+                                                        unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr,
+                                                        unique ? ctx->u_scores.as<float>() + u_off : nullptr,
+                                                        ctx->group_branch.as<uint32_t>(),
+                                                        csr ? ctx->kmer_keys.as<uint64_t>() : nullptr, ctx->kmer_offs.as<uint64_t>(),
+                                                        ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>());
+        check_launch(ctx, "mg_write");
+        if (csr)
+            IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + r.n_kmers, &r.n_records, 8, cudaMemcpyHostToDevice, ctx->stream));
+        return r;
+    }
+}
+
+namespace
+{
+    struct stage1_out
+    {
+        uint64_t n_emitted = 0, n_unique = 0, n_kmers = 0;
+        uint32_t n_groups = 0, sort_passes = 0, enum_launches = 0, n_batches = 0;
+        bool csr_done = false;             // single batch: the CSR by k-mer was written together with the max-merge
+        float ms_h2d = 0, ms_prefix = 0, ms_enumerate = 0, ms_sort = 0, ms_merge = 0;
+    };
+
+    uint64_t device_budget(ipkgpu_ctx* ctx)
+    {
+        if (ctx->workspace_limit) return ctx->workspace_limit;
+        const size_t reusable = ctx->keys_a.cap + ctx->keys_b.cap + ctx->vals_a.cap + ctx->vals_b.cap + ctx->u_keys.cap + ctx->u_scores.cap;
+        return uint64_t(double(free_device_bytes() + reusable) * 0.85);
+    }
+
+    /// Stage 1 of one rank: K1, then per batch of branch groups K2 -> sort -> K3.
+    /// With want_csr and a single batch the CSR by k-mer comes out of the same K3 pass; otherwise the unique
+    /// records are left in ctx->u_keys/u_scores as (kmer << group_bits) | global group, batch after batch.
+    stage1_out run_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& T, uint32_t group_base, uint32_t group_bits,
+                          bool want_csr, ipkgpu_stats* st, stage_timer& tm)
+    {
+        stage1_out o;
+        o.n_groups = uint32_t(T.group_branch.size());
+        const uint32_t key_bits = in->k * in->bits;
+        if (key_bits + group_bits > 64) fail(IPKGPU_EINVAL, "k*bits + group bits = %u exceeds 64", key_bits + group_bits);
+        const size_t eh = tm.mark();
+        const float* d_logp = stage_inputs(ctx, in, T, st);
+        const size_t e0 = tm.mark();
+        run_best_prefix(ctx, d_logp, in);
+        const size_t e1 = tm.mark();
+        ctx->reserve(ctx->counters, 64);
+        ctx->reserve(ctx->node_counts, size_t(in->n_nodes) * 8 + 8);
+        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+        IPK_CUDA(cudaMemsetAsync(ctx->node_counts.p, 0, size_t(in->n_nodes) * 8 + 8, ctx->stream));
+        ctx->s1_n = 0;
+        if (in->n_nodes == 0 || in->width < in->k)
+        {
+            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+            o.ms_h2d = tm.ms(eh, e0);
+            o.ms_prefix = tm.ms(e0, e1);
+            return o;
+        }
+
+        const enum_program P = make_enum_program(int(in->k));
+        const uint64_t n_windows = uint64_t(in->n_nodes) * (in->width - in->k + 1);
+        const uint64_t budget = device_budget(ctx);
+        const uint64_t batch_cap = std::max<uint64_t>(1 << 16, std::min<uint64_t>(budget / 2 / 24, 0xfff00000ull));
+        uint64_t cap0 = ctx->hint_emitted ? ctx->hint_emitted + ctx->hint_emitted / 16 + 4096 : std::max<uint64_t>(1 << 20, 64 * n_windows);
+        cap0 = std::min(cap0, batch_cap);
+
+        struct batch { uint32_t g0, g1; uint64_t n; };
+        std::vector<batch> batches;
+        const uint32_t all_bits = ceil_log2(o.n_groups);
+
+        ctx->reserve(ctx->keys_a, cap0 * 8);
+        ctx->reserve(ctx->vals_a, cap0 * 4);
+        enum_launch L{ 0, in->n_nodes, group_base, all_bits, cap0, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
+        launch_enumerate(ctx, d_logp, in, P, L, true);
+        o.enum_launches = 1;
+        o.n_emitted = read_u64(ctx, ctx->counters.p);
+        ctx->hint_emitted = o.n_emitted;
+        bool first_valid = o.n_emitted <= cap0;
+        if (first_valid) batches.push_back({ 0, o.n_groups, o.n_emitted });
+        else
+        {
+            // the first attempt overflowed its buffer: it still counted every node exactly -> plan batches of whole groups
+            std::vector<unsigned long long> counts(in->n_nodes);
+            IPK_CUDA(cudaMemcpyAsync(counts.data(), ctx->node_counts.p, size_t(in->n_nodes) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+            uint32_t g0 = 0;
+            uint64_t acc = 0;
+            for (uint32_t g = 0; g < o.n_groups; ++g)
+            {
+                uint64_t c = 0;
+                for (uint32_t s = T.group_first_slot[g]; s < T.group_first_slot[g + 1]; ++s) c += counts[s];
+                if (c > batch_cap)
+                    fail(IPKGPU_ENOMEM, "branch group %u alone emits %llu phylo-k-mers, above the per-batch capacity of %llu records "
+                         "(device budget %llu bytes)", g, (unsigned long long)c, (unsigned long long)batch_cap, (unsigned long long)budget);
+                if (acc + c > batch_cap) { batches.push_back({ g0, g, acc }); g0 = g; acc = 0; }
+                acc += c;
+            }
+            batches.push_back({ g0, o.n_groups, acc });
+        }
+        size_t e_prev = tm.mark();
+        o.ms_h2d = tm.ms(eh, e0);
+        o.ms_prefix = tm.ms(e0, e1);
+        float ms_enum = 0, ms_sort = 0, ms_merge = 0;
+        if (!first_valid) { IPK_CUDA(cudaEventSynchronize(ctx->event(e_prev))); ms_enum += tm.ms(e1, e_prev); }
+        bool timed_first = false;
+        o.n_batches = uint32_t(batches.size());
+        const bool single = batches.size() == 1;
+        uint64_t u_off = 0;
+        for (const batch& b : batches)
+        {
+            uint32_t bbits = all_bits;
+            size_t ea = e_prev;
+            if (!first_valid)
+            {
+                bbits = ceil_log2(b.g1 - b.g0);
+                ctx->reserve(ctx->keys_a, b.n * 8 + 8);
+                ctx->reserve(ctx->vals_a, b.n * 4 + 4);
+                IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 8, ctx->stream));
+                ea = tm.mark();
+                enum_launch Lb{ T.group_first_slot[b.g0], T.group_first_slot[b.g1], group_base + b.g0, bbits, b.n,
+                                ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
+                launch_enumerate(ctx, d_logp, in, P, Lb, false);
+                o.enum_launches++;
+            }
+            else if (!timed_first) { ea = e1; timed_first = true; }
+            const size_t eb = tm.mark();
+            ctx->reserve(ctx->keys_b, b.n * 8 + 8);
+            ctx->reserve(ctx->vals_b, b.n * 4 + 4);
+            uint32_t passes = 0;
+            const bool in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
+                                               ctx->vals_b.as<uint32_t>(), b.n, key_bits + bbits, ctx->hist, ctx->scan_tmp, &passes);
+            o.sort_passes += passes;
+            const size_t ec = tm.mark();
+            const uint64_t* sk = in_b ? ctx->keys_b.as<uint64_t>() : ctx->keys_a.as<uint64_t>();
+            const float* sv = in_b ? ctx->vals_b.as<float>() : ctx->vals_a.as<float>();
+            const bool csr = single && want_csr;
+            const merge_out m = run_merge(ctx, sk, sv, b.n, bbits, group_bits, group_base + b.g0, !csr, u_off, csr);
+            if (csr) { o.csr_done = true; o.n_kmers = m.n_kmers; }
+            u_off += m.n_records;
+            const size_t ed = tm.mark();
+            IPK_CUDA(cudaEventSynchronize(ctx->event(ed)));
+            ms_enum += tm.ms(ea, eb); ms_sort += tm.ms(eb, ec); ms_merge += tm.ms(ec, ed);
+            e_prev = ed;
+        }
+        o.n_unique = u_off;
+        o.ms_enumerate = ms_enum; o.ms_sort = ms_sort; o.ms_merge = ms_merge;
+        ctx->s1_n = o.csr_done ? 0 : u_off;
+        ctx->s1_group_bits = group_bits;
+        return o;
+    }
+}
+
+namespace
+{
+    struct stage2_params
+    {
+        uint32_t group_bits, key_bits, total_num_groups;
+        float threshold;
+        int32_t filter;
+    };
+
+    /// K4 -> K5 -> K6 on the CSR in ctx (kmer_keys / kmer_offs / ent_branch / ent_score) and hand-over of the result.
+    void finish_from_csr(ipkgpu_ctx* ctx, uint64_t n_kmers, uint64_t n_entries, const stage2_params& sp, int result_on_device,
+                         ipkgpu_result* out, stage_timer& tm)
+    {
+        if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard", (unsigned long long)n_entries);
+        ipkgpu_stats& st = out->stats;
+        const size_t e0 = tm.mark();
+        ctx->reserve(ctx->fv, n_kmers * 4 + 4);
+        ctx->reserve(ctx->out_keys, n_kmers * 8 + 8);
+        ctx->reserve(ctx->out_fv, n_kmers * 4 + 4);
+        ctx->reserve(ctx->out_offs, (n_kmers + 1) * 8);
+        ctx->reserve(ctx->out_cnt, n_kmers * 4 + 4);
+        ctx->reserve(ctx->out_branch, n_entries * 4 + 4);
+        ctx->reserve(ctx->out_score, n_entries * 4 + 4);
+        size_t e1 = e0, e2 = e0;
+        if (n_kmers)
+        {
+            const uint32_t grid = uint32_t(div_up<uint64_t>(n_kmers, 256));
+            if (sp.filter == IPKGPU_FILTER_MIF0)
+            {
+                k4_mif0<<<grid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers,
+                                                       sp.total_num_groups, sp.threshold, ctx->fv.as<float>());
+                check_launch(ctx, "k4_mif0");
+            }
+            else
+            {
+                k4_random<<<grid, 256, 0, ctx->stream>>>(n_kmers, ctx->fv.as<float>());
+                check_launch(ctx, "k4_random");
+            }
+            e1 = tm.mark();
+            // K5: stable sort on the 32-bit order-preserving image of fv; k-mers are in ascending key order, so ties keep it
+            ctx->reserve(ctx->ord_keys_a, n_kmers * 8); ctx->reserve(ctx->ord_keys_b, n_kmers * 8);
+            ctx->reserve(ctx->ord_vals_a, n_kmers * 4); ctx->reserve(ctx->ord_vals_b, n_kmers * 4);
+            k5_order_keys<<<grid, 256, 0, ctx->stream>>>(ctx->fv.as<float>(), n_kmers, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>());
+            check_launch(ctx, "k5_order_keys");
+            const bool in_b = radix_sort_pairs(ctx, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>(), ctx->ord_keys_b.as<uint64_t>(),
+                                               ctx->ord_vals_b.as<uint32_t>(), n_kmers, 32, ctx->hist, ctx->scan_tmp);
+            const uint32_t* perm = in_b ? ctx->ord_vals_b.as<uint32_t>() : ctx->ord_vals_a.as<uint32_t>();
+            // K6
+            k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
+                                                           n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>());
+            check_launch(ctx, "k6_gather_heads");
+            exclusive_scan_u32(ctx, ctx->out_cnt.as<uint32_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, ctx->scan_tmp);
+            k6_gather_entries<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, n_entries,
+                                                             ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>(),
+                                                             ctx->out_offs.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>());
+            check_launch(ctx, "k6_gather_entries");
+            e2 = tm.mark();
+        }
+        else
+        {
+            IPK_CUDA(cudaMemsetAsync(ctx->out_offs.p, 0, 8, ctx->stream));
+            e1 = e2 = tm.mark();
+        }
+        out->n_kmers = n_kmers;
+        out->n_entries = n_entries;
+        out->on_device = result_on_device ? 1 : 0;
+        size_t e3 = e2;
+        if (result_on_device)
+        {
+            out->keys = ctx->out_keys.as<uint64_t>(); out->fv = ctx->out_fv.as<float>(); out->offsets = ctx->out_offs.as<uint64_t>();
+            out->branch = ctx->out_branch.as<uint32_t>(); out->score = ctx->out_score.as<float>();
+        }
+        else
+        {
+            ctx->reserve_host(ctx->h_keys, n_kmers * 8 + 8); ctx->reserve_host(ctx->h_fv, n_kmers * 4 + 4);
+            ctx->reserve_host(ctx->h_offs, (n_kmers + 1) * 8);
+            ctx->reserve_host(ctx->h_branch, n_entries * 4 + 4); ctx->reserve_host(ctx->h_score, n_entries * 4 + 4);
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_keys.p, ctx->out_keys.p, n_kmers * 8, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_fv.p, ctx->out_fv.p, n_kmers * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_offs.p, ctx->out_offs.p, (n_kmers + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->out_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_score.p, ctx->out_score.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            st.d2h_bytes += n_kmers * 12 + (n_kmers + 1) * 8 + n_entries * 8;
+            e3 = tm.mark();
+            out->keys = ctx->h_keys.as<uint64_t>(); out->fv = ctx->h_fv.as<float>(); out->offsets = ctx->h_offs.as<uint64_t>();
+            out->branch = ctx->h_branch.as<uint32_t>(); out->score = ctx->h_score.as<float>();
+        }
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        st.ms_filter = tm.ms(e0, e1);
+        st.ms_order = tm.ms(e1, e2);
+        st.ms_d2h = tm.ms(e2, e3);
+        st.n_kmers = n_kmers;
+        st.n_entries = n_entries;
+    }
+
+    /// Stage 2 on unique records (composite keys with the GLOBAL group field): regroup by k-mer -> CSR -> finish.
+    /// (keys, scores) are overwritten (they are one side of the sort's ping-pong).
+    void run_stage2(ipkgpu_ctx* ctx, uint64_t* keys, float* scores, uint64_t n, bool group_ordered, const stage2_params& sp,
+                    int result_on_device, ipkgpu_result* out, stage_timer& tm)
+    {
+        const size_t e0 = tm.mark();
+        const uint64_t* sk = keys;
+        const float* sv = scores;
+        if (n)
+        {
+            ctx->reserve(ctx->keys_b, n * 8 + 8);
+            ctx->reserve(ctx->vals_b, n * 4 + 4);
+            uint32_t passes = 0;
+            // chunks that arrive in group order, each sorted by (kmer, group): a STABLE sort on the k-mer bits alone regroups them
+            const bool in_b = group_ordered
+                ? radix_sort_pairs(ctx, keys, reinterpret_cast<uint32_t*>(scores), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(), n,
+                                   sp.key_bits, ctx->hist, ctx->scan_tmp, &passes, sp.group_bits)
+                : radix_sort_pairs(ctx, keys, reinterpret_cast<uint32_t*>(scores), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(), n,
+                                   sp.key_bits + sp.group_bits, ctx->hist, ctx->scan_tmp, &passes, 0);
+            out->stats.sort_passes += passes;
+            if (in_b) { sk = ctx->keys_b.as<uint64_t>(); sv = ctx->vals_b.as<float>(); }
+        }
+        const size_t e1 = tm.mark();
+        const merge_out m = run_merge(ctx, sk, sv, n, sp.group_bits, sp.group_bits, 0, false, 0, true);
+        if (n == 0)
+        {
+            ctx->reserve(ctx->kmer_offs, 8);
+            IPK_CUDA(cudaMemsetAsync(ctx->kmer_offs.p, 0, 8, ctx->stream));
+        }
+        const size_t e2 = tm.mark();
+        finish_from_csr(ctx, m.n_kmers, m.n_records, sp, result_on_device, out, tm);
+        out->stats.ms_sort += tm.ms(e0, e1);
+        out->stats.ms_merge += tm.ms(e1, e2);
+    }
+
+    template<class F> int guarded(ipkgpu_ctx* ctx, F&& f)
+    {
+        try
+        {
+            if (!ctx) return IPKGPU_EINVAL;
+            IPK_CUDA(cudaSetDevice(ctx->device));
+            ctx->launches = 0;
+            f();
+            return IPKGPU_OK;
+        }
+        catch (const error& e) { if (ctx) ctx->last_error = e.what; cudaGetLastError(); return e.code; }
+        catch (const std::bad_alloc&) { if (ctx) ctx->last_error = "host allocation failed"; return IPKGPU_ENOMEM; }
+        catch (const std::exception& e) { if (ctx) ctx->last_error = e.what(); return IPKGPU_ECUDA; }
+        catch (...) { if (ctx) ctx->last_error = "unknown failure"; return IPKGPU_ECUDA; }
+    }
+}
+
+// =====================================================================================================================
+// C ABI
+// =====================================================================================================================
+extern "C"
+{
+
+void ipkgpu_score_threshold(float omega, uint32_t sigma, uint32_t k, float* threshold, float* log_threshold)
+{
+    const float t = powf(omega / float(sigma), float(k));
+    if (threshold) *threshold = t;
+    if (log_threshold) *log_threshold = log10f(t);
+}
+
+int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
+{
+    if (!out) return IPKGPU_EINVAL;
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+    {
+        cudaGetLastError();
+        g_create_error = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                         " (libipkgpu has no CPU fallback)";
+        return IPKGPU_ENODEV;
+    }
+    if (device < 0 || device >= n_dev) { g_create_error = "device ordinal out of range"; return IPKGPU_EINVAL; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10)
+    {
+        cudaGetLastError();
+        g_create_error = "device is not sm_100 (this library is built for sm_100a only)";
+        return IPKGPU_ENODEV;
+    }
+    ipkgpu_ctx* ctx = new (std::nothrow) ipkgpu_ctx();
+    if (!ctx) { g_create_error = "host allocation failed"; return IPKGPU_ENOMEM; }
+    ctx->device = device;
+    ctx->num_sms = prop.multiProcessorCount;
+    cudaSetDevice(device);
+    if (stream) ctx->stream = static_cast<cudaStream_t>(stream);
+    else
+    {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess)
+        {
+            g_create_error = "cudaStreamCreate failed";
+            delete ctx;
+            return IPKGPU_ECUDA;
+        }
+        ctx->own_stream = true;
+    }
+    *out = ctx;
+    return IPKGPU_OK;
+}
+
+void ipkgpu_destroy(ipkgpu_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ipkgpu::dbuf* all[] = { &ctx->logp, &ctx->colmax, &ctx->bestpref, &ctx->node_group, &ctx->node_order, &ctx->group_branch, &ctx->counters,
+                            &ctx->node_counts, &ctx->keys_a, &ctx->keys_b, &ctx->vals_a, &ctx->vals_b, &ctx->hist, &ctx->scan_tmp,
+                            &ctx->block_counts, &ctx->block_offs, &ctx->dbg_node, &ctx->dbg_win, &ctx->u_keys, &ctx->u_scores,
+                            &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
+                            &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
+                            &ctx->out_score, &ctx->out_cnt };
+    for (auto* b : all) ctx->release(*b);
+    ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score };
+    for (auto* b : hall) if (b->p) cudaFreeHost(b->p);
+    for (auto e : ctx->events) cudaEventDestroy(e);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* ipkgpu_last_error(const ipkgpu_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+void* ipkgpu_stream(const ipkgpu_ctx* ctx) { return ctx ? static_cast<void*>(ctx->stream) : nullptr; }
+
+int ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes)
+{
+    if (!ctx) return IPKGPU_EINVAL;
+    ctx->workspace_limit = bytes;
+    return IPKGPU_OK;
+}
+
+int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out)
+{
+    return guarded(ctx, [&] {
+        validate(in);
+        if (!out) fail(IPKGPU_EINVAL, "result is null");
+        memset(out, 0, sizeof *out);
+        stage_timer tm(ctx);
+        const size_t t0 = tm.mark();
+        const group_tables T = make_groups(in->node_branch, in->n_nodes, 0);
+        const uint32_t n_groups = uint32_t(T.group_branch.size());
+        const uint32_t group_bits = ceil_log2(n_groups);
+        const stage2_params sp{ group_bits, in->k * in->bits, in->total_num_groups, in->threshold, in->filter };
+        ipkgpu_stats& st = out->stats;
+        st.n_windows = in->width >= in->k ? uint64_t(in->n_nodes) * (in->width - in->k + 1) : 0;
+        st.n_groups = n_groups;
+        const stage1_out s1 = run_stage1(ctx, in, T, 0, group_bits, true, &st, tm);
+        st.n_emitted = s1.n_emitted;
+        st.sort_passes = s1.sort_passes;
+        st.enum_launches = s1.enum_launches;
+        st.ms_h2d = s1.ms_h2d; st.ms_prefix = s1.ms_prefix; st.ms_enumerate = s1.ms_enumerate; st.ms_sort = s1.ms_sort; st.ms_merge = s1.ms_merge;
+        if (s1.csr_done) finish_from_csr(ctx, s1.n_kmers, s1.n_unique, sp, result_on_device, out, tm);
+        else run_stage2(ctx, ctx->u_keys.as<uint64_t>(), ctx->u_scores.as<float>(), s1.n_unique, true, sp, result_on_device, out, tm);
+        const size_t t1 = tm.mark();
+        IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
+        st.ms_total = tm.ms(t0, t1);
+        st.kernel_launches = ctx->launches;
+    });
+}
+
+void ipkgpu_free_result(ipkgpu_ctx* ctx, ipkgpu_result* res)
+{
+    (void)ctx;
+    if (res) { res->keys = nullptr; res->fv = nullptr; res->offsets = nullptr; res->branch = nullptr; res->score = nullptr; res->n_kmers = res->n_entries = 0; }
+}
+
+}   // extern "C"
+
+// ---- stage-level entry points ---------------------------------------------------------------------------------------
+extern "C"
+{
+
+int ipkgpu_best_prefix(ipkgpu_ctx* ctx, const ipkgpu_input* in, float* B_out)
+{
+    return guarded(ctx, [&] {
+        validate(in);
+        if (!B_out) fail(IPKGPU_EINVAL, "B_out is null");
+        const group_tables T = make_groups(in->node_branch, in->n_nodes, 0);
+        const float* d_logp = stage_inputs(ctx, in, T, nullptr);
+        run_best_prefix(ctx, d_logp, in);
+        IPK_CUDA(cudaMemcpyAsync(B_out, ctx->bestpref.p, size_t(in->n_nodes) * (in->width + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int ipkgpu_enumerate(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint64_t cap,
+                     uint32_t* node_out, uint32_t* window_out, uint64_t* key_out, float* score_out, uint64_t* n_out)
+{
+    return guarded(ctx, [&] {
+        validate(in);
+        if (!n_out || (cap && (!node_out || !window_out || !key_out || !score_out))) fail(IPKGPU_EINVAL, "output pointer is null");
+        const group_tables T = make_groups(in->node_branch, in->n_nodes, 0);
+        const float* d_logp = stage_inputs(ctx, in, T, nullptr);
+        run_best_prefix(ctx, d_logp, in);
+        ctx->reserve(ctx->counters, 64);
+        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+        ctx->reserve(ctx->keys_a, cap * 8 + 8); ctx->reserve(ctx->vals_a, cap * 4 + 4);
+        ctx->reserve(ctx->dbg_node, cap * 4 + 4); ctx->reserve(ctx->dbg_win, cap * 4 + 4);
+        *n_out = 0;
+        if (in->n_nodes == 0 || in->width < in->k) return;
+        const enum_program P = make_enum_program(int(in->k));
+        enum_launch L{ 0, in->n_nodes, 0, 0, cap, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>(),
+                       ctx->dbg_node.as<uint32_t>(), ctx->dbg_win.as<uint32_t>(), true };
+        launch_enumerate(ctx, d_logp, in, P, L, false);
+        const uint64_t n = read_u64(ctx, ctx->counters.p);
+        *n_out = n;
+        const uint64_t m = std::min(n, cap);
+        IPK_CUDA(cudaMemcpyAsync(key_out, ctx->keys_a.p, m * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(score_out, ctx->vals_a.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(node_out, ctx->dbg_node.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(window_out, ctx->dbg_win.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out, ipkgpu_stats* stats)
+{
+    return guarded(ctx, [&] {
+        validate(in);
+        if (!n_out) fail(IPKGPU_EINVAL, "n_out is null");
+        ipkgpu_stats st;
+        memset(&st, 0, sizeof st);
+        stage_timer tm(ctx);
+        const size_t t0 = tm.mark();
+        const group_tables T = make_groups(in->node_branch, in->n_nodes, group_base);
+        if (group_base + T.group_branch.size() > (1ull << group_bits) && !(group_bits >= 32))
+            fail(IPKGPU_EINVAL, "group_base %u + %zu groups do not fit %u group bits", group_base, T.group_branch.size(), group_bits);
+        const stage1_out s1 = run_stage1(ctx, in, T, group_base, group_bits, false, &st, tm);
+        const size_t t1 = tm.mark();
+        IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
+        *n_out = s1.n_unique;
+        st.n_windows = in->width >= in->k ? uint64_t(in->n_nodes) * (in->width - in->k + 1) : 0;
+        st.n_emitted = s1.n_emitted; st.n_entries = s1.n_unique; st.n_groups = s1.n_groups;
+        st.sort_passes = s1.sort_passes; st.enum_launches = s1.enum_launches;
+        st.ms_h2d = s1.ms_h2d; st.ms_prefix = s1.ms_prefix; st.ms_enumerate = s1.ms_enumerate; st.ms_sort = s1.ms_sort; st.ms_merge = s1.ms_merge;
+        st.ms_total = tm.ms(t0, t1);
+        st.kernel_launches = ctx->launches;
+        if (stats) *stats = st;
+    });
+}
+
+int ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys, float* d_scores, uint64_t* counts)
+{
+    return guarded(ctx, [&] {
+        if (n_parts < 1 || n_parts > RS_RADIX) fail(IPKGPU_EINVAL, "n_parts = %u outside [1, %d]", n_parts, RS_RADIX);
+        if (!counts) fail(IPKGPU_EINVAL, "counts is null");
+        const uint64_t n = ctx->s1_n;
+        for (uint32_t p = 0; p < n_parts; ++p) counts[p] = 0;
+        if (n == 0) return;
+        if (!d_keys || !d_scores) fail(IPKGPU_EINVAL, "send buffer is null");
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed one shard's 2^32-1 limit", (unsigned long long)n);
+        const digit_owner own{ ctx->s1_group_bits, n_parts };
+        radix_pass(ctx, ctx->u_keys.as<uint64_t>(), ctx->u_scores.as<uint32_t>(), d_keys, reinterpret_cast<uint32_t*>(d_scores), n,
+                   own, ctx->hist, ctx->scan_tmp);
+        // bucket sizes: the scanned digit-major table holds the start of digit d's first tile at [d * n_tiles]
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
+        std::vector<uint32_t> starts(n_parts);
+        IPK_CUDA(cudaMemcpy2DAsync(starts.data(), 4, ctx->hist.p, size_t(n_tiles) * 4, 4, n_parts, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t p = 0; p < n_parts; ++p) counts[p] = (p + 1 < n_parts ? starts[p + 1] : n) - starts[p];
+    });
+}
+
+int ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t n, uint32_t group_bits,
+                  const uint32_t* group_branch, uint32_t n_groups_total, uint32_t key_bits,
+                  float threshold, uint32_t total_num_groups, int32_t filter, int32_t chunks_group_ordered,
+                  int result_on_device, ipkgpu_result* out)
+{
+    return guarded(ctx, [&] {
+        if (!out) fail(IPKGPU_EINVAL, "result is null");
+        if (n && (!d_keys || !d_scores)) fail(IPKGPU_EINVAL, "record buffer is null");
+        if (!group_branch && n_groups_total) fail(IPKGPU_EINVAL, "group_branch is null");
+        if (key_bits + group_bits > 64 || key_bits == 0) fail(IPKGPU_EINVAL, "key_bits %u + group_bits %u outside (0, 64]", key_bits, group_bits);
+        if (filter != IPKGPU_FILTER_MIF0 && filter != IPKGPU_FILTER_RANDOM) fail(IPKGPU_EINVAL, "unknown filter %d", filter);
+        memset(out, 0, sizeof *out);
+        stage_timer tm(ctx);
+        const size_t t0 = tm.mark();
+        ctx->reserve(ctx->group_branch, size_t(n_groups_total) * 4 + 4);
+        IPK_CUDA(cudaMemcpyAsync(ctx->group_branch.p, group_branch, size_t(n_groups_total) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        const stage2_params sp{ group_bits, key_bits, total_num_groups, threshold, filter };
+        run_stage2(ctx, d_keys, d_scores, n, chunks_group_ordered != 0, sp, result_on_device, out, tm);
+        const size_t t1 = tm.mark();
+        IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
+        out->stats.ms_total = tm.ms(t0, t1);
+        out->stats.n_groups = n_groups_total;
+        out->stats.kernel_launches = ctx->launches;
+    });
+}
+
+}   // extern "C"

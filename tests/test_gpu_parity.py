@@ -1,0 +1,159 @@
+"""-m gpu: the CUDA path (through the C ABI, libipkgpu.so) against the oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+import oraclelib as O
+from parity import assert_db_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _thr(omega, sigma, k):
+    from ipk_b200 import capi as libipkgpu
+    return libipkgpu.score_threshold(omega, sigma, k)
+
+
+def _synth(n_taxa, W, sigma, seed=42, params=None):
+    from ipk_b200 import synth
+    return synth.posteriors(n_taxa, W, sigma, seed=seed, params=params)
+
+
+def _rand_posteriors(rng, n_nodes, W, sigma, peaked=0.7, zeros=True):
+    """independent columns; a share of exact zeros (-inf) and exactly uniform columns"""
+    p = rng.dirichlet(np.ones(sigma) * 0.3, size=(n_nodes, W))
+    sharp = rng.random((n_nodes, W)) < peaked
+    top = rng.integers(0, sigma, size=(n_nodes, W))
+    eps = 10.0 ** (-rng.uniform(1, 4, size=(n_nodes, W)))
+    q = p * eps[..., None]
+    np.put_along_axis(q, top[..., None], 0.0, axis=2)
+    q = q / np.maximum(q.sum(axis=2, keepdims=True), 1e-300) * eps[..., None]
+    np.put_along_axis(q, top[..., None], (1.0 - eps)[..., None], axis=2)
+    p = np.where(sharp[..., None], q, p)
+    p = np.round(p, 9)
+    if zeros:
+        uni = rng.random((n_nodes, W)) < 0.02
+        p = np.where(uni[..., None], 1.0 / sigma, p)
+    with np.errstate(divide="ignore"):
+        return np.log10(p.astype(np.float32)).astype(np.float32)
+
+
+@pytest.mark.parametrize("sigma,bits,W", [(4, 2, 257), (20, 5, 131), (4, 2, 9700)])
+def test_best_prefix_bitexact(ctx, sigma, bits, W):
+    rng = np.random.default_rng(1)
+    logp = _rand_posteriors(rng, 5, W, sigma)
+    nb = np.arange(5, dtype=np.uint32)
+    B = ctx.best_prefix(logp, nb, W, sigma, bits, 3)
+    for n in range(5):
+        want = O.best_prefix(logp[n], sigma)
+        assert np.array_equal(B[n].view(np.uint32), want.view(np.uint32))
+
+
+ENUM_CASES = [
+    # sigma, bits, k, omega, W, n_nodes
+    (4, 2, 1, 1.5, 40, 3), (4, 2, 2, 1.5, 40, 3), (4, 2, 3, 1.5, 50, 3), (4, 2, 5, 1.5, 140, 4), (4, 2, 7, 2.0, 300, 4),
+    (4, 2, 8, 1.5, 300, 4), (4, 2, 10, 1.5, 400, 3), (4, 2, 12, 1.5, 300, 2), (4, 2, 14, 2.0, 300, 2), (4, 2, 10, 1.5, 10, 2),
+    (4, 2, 10, 1.5, 9, 2), (4, 2, 6, 1.5, 129 + 5, 2), (4, 2, 6, 1.5, 128 + 5, 2), (20, 5, 3, 1.5, 90, 3), (20, 5, 4, 10.0, 150, 3),
+    (20, 5, 6, 1.5, 60, 2),
+]
+
+
+@pytest.mark.parametrize("sigma,bits,k,omega,W,n_nodes", ENUM_CASES)
+def test_enumerate_per_window(ctx, sigma, bits, k, omega, W, n_nodes):
+    """every (node, window, k-mer, score) the reference's DCLA emits, bit-exact scores"""
+    rng = np.random.default_rng(100 * k + sigma + W)
+    logp = _rand_posteriors(rng, n_nodes, W, sigma, peaked=0.85 if k > 8 or sigma == 20 else 0.6)
+    thr, lthr = _thr(omega, sigma, k)
+    nb = np.arange(n_nodes, dtype=np.uint32)
+    wn, ww, wk, ws = [], [], [], []
+    for n in range(n_nodes):
+        w, key, sc = O.enumerate_node(logp[n], sigma, bits, k, lthr)
+        wn.append(np.full(len(w), n, np.uint32)); ww.append(w); wk.append(key); ws.append(sc)
+    wn, ww, wk, ws = O.canonical_windows(np.concatenate(wn), np.concatenate(ww), np.concatenate(wk), np.concatenate(ws))
+    cap = max(len(wk), 1)
+    n_total, gn, gw, gk, gs = ctx.enumerate(logp, nb, W, sigma, bits, k, lthr, cap)
+    assert n_total == len(wk)
+    gn, gw, gk, gs = O.canonical_windows(gn, gw, gk, gs)
+    assert np.array_equal(gn, wn) and np.array_equal(gw, ww) and np.array_equal(gk, wk)
+    assert np.array_equal(gs.view(np.uint32), ws.view(np.uint32))
+
+
+def test_enumerate_cap_overflow_counts_everything(ctx):
+    rng = np.random.default_rng(5)
+    logp = _rand_posteriors(rng, 3, 200, 4, peaked=0.5)
+    thr, lthr = _thr(1.5, 4, 8)
+    nb = np.arange(3, dtype=np.uint32)
+    n_total, *_ = ctx.enumerate(logp, nb, 200, 4, 2, 8, lthr, 1 << 20)
+    n2, gn, gw, gk, gs = ctx.enumerate(logp, nb, 200, 4, 2, 8, lthr, 100)
+    assert n2 == n_total and len(gk) == 100
+
+
+BUILD_CASES = [
+    # name, n_taxa, W, sigma, bits, k, omega
+    ("dna_k7_o2", 24, 220, 4, 2, 7, 2.0), ("dna_k8", 24, 220, 4, 2, 8, 1.5), ("dna_k10", 16, 200, 4, 2, 10, 1.5),
+    ("dna_k12", 8, 150, 4, 2, 12, 1.5), ("aa_k4_o10", 12, 120, 20, 5, 4, 10.0), ("aa_k6", 4, 60, 20, 5, 6, 1.5),
+    ("dna_k14_o2", 6, 400, 4, 2, 14, 2.0),
+]
+
+
+@pytest.mark.parametrize("name,n_taxa,W,sigma,bits,k,omega", BUILD_CASES)
+@pytest.mark.parametrize("filt", [0, 1])
+def test_build_matches_oracle(ctx, name, n_taxa, W, sigma, bits, k, omega, filt):
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    want = O.build(logp, nb, W, sigma, bits, k, lthr, thr, T, filt, 8)
+    got = ctx.build(logp, nb, W, sigma, bits, k, lthr, thr, T, filt)
+    assert got.stats["n_emitted"] == want.n_emitted
+    assert_db_equal(got, want, exact_fv=(filt == 1))
+
+
+def test_build_interleaved_groups_and_singletons(ctx):
+    """ghost nodes of one branch need not be adjacent; a branch may have one ghost only (--inner-only/--outer-only)"""
+    logp, nb = _synth(10, 150, 4)
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(len(nb))[: len(nb) - 5]
+    logp2 = np.ascontiguousarray(logp[perm]); nb2 = nb[perm]
+    thr, lthr = _thr(1.5, 4, 8)
+    want = O.build(logp2, nb2, 150, 4, 2, 8, lthr, thr, 19, 0, 4)
+    got = ctx.build(logp2, nb2, 150, 4, 2, 8, lthr, thr, 19, 0)
+    assert_db_equal(got, want)
+
+
+def test_build_empty_and_short(ctx):
+    thr, lthr = _thr(1.5, 4, 8)
+    z = ctx.build(np.zeros((0, 10, 4), np.float32), np.zeros(0, np.uint32), 10, 4, 2, 8, lthr, thr, 1, 0)
+    assert z.n_kmers == 0 and z.n_entries == 0
+    logp, nb = _synth(4, 7, 4)      # W < k: no windows
+    z = ctx.build(logp, nb, 7, 4, 2, 8, lthr, thr, 7, 0)
+    assert z.n_kmers == 0 and z.stats["n_windows"] == 0
+    # nothing clears an impossible threshold
+    logp, nb = _synth(4, 50, 4)
+    z = ctx.build(logp, nb, 50, 4, 2, 8, 0.5, 3.0, 7, 0)
+    assert z.n_kmers == 0 and z.stats["n_emitted"] == 0
+
+
+def test_build_batched_equals_single(ctx):
+    """a tiny workspace forces the overflow -> count -> batch path; the database must not change"""
+    from ipk_b200 import capi as libipkgpu
+    logp, nb = _synth(24, 200, 4)
+    thr, lthr = _thr(1.5, 4, 8)
+    want = ctx.build(logp, nb, 200, 4, 2, 8, lthr, thr, 47, 0)
+    c2 = libipkgpu.Context(0)
+    try:
+        c2.set_workspace_limit(24 * 2 * (1 << 16))      # batch capacity = 65536 records
+        got = c2.build(logp, nb, 200, 4, 2, 8, lthr, thr, 47, 0)
+        assert got.stats["enum_launches"] > 2
+        assert_db_equal(got, want, exact_fv=True)
+    finally:
+        c2.close()
+
+
+def test_invalid_arguments(ctx):
+    from ipk_b200.capi import IpkGpuError
+    logp, nb = _synth(4, 50, 4)
+    with pytest.raises(IpkGpuError):
+        ctx.build(logp, nb, 50, 4, 2, 33, -1.0, 0.1, 7, 0)        # k*bits > 63
+    with pytest.raises(IpkGpuError):
+        ctx.build(logp, nb, 50, 4, 1, 8, -1.0, 0.1, 7, 0)         # 1 bit cannot encode 4 states
+    with pytest.raises(IpkGpuError):
+        ctx.build(logp, nb, 50, 4, 2, 8, -1.0, 0.1, 7, 7)         # unknown filter
