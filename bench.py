@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py -- phylo-k-mer database build throughput on B200 (BASELINE.json metric) and the reference CPU arm.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...          (one rank per GPU; strong scaling: the SAME database)
+
+A step = one complete build of the workload's database: posteriors -> enumerate -> per-branch max-merge -> regroup by
+k-mer -> MIF0 filter values -> order by filter value (db_builder::run stages 1+2, ipk/src/db_builder.cpp:182-290).
+  value  phylo-k-mers/s = stored (k-mer, branch) entries / device time, posteriors already resident in HBM, result left
+         in HBM.
+  e2e    same metric through the C ABI with HOST buffers: pinned posteriors -> H2D -> build -> D2H of the database.
+Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "phylo-k-mers/s"
+DEFAULT_WORKLOAD = "cfg3_16s_10k"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("IPK_BENCH_WORKLOAD", DEFAULT_WORKLOAD))
+    ap.add_argument("--cpu-sample-branches", type=int, default=0, help="branch groups in the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--seed", type=int, default=42)
+    return ap.parse_args()
+
+
+def peaks():
+    """roofline denominator: measured copy bandwidth (MEASURED_PEAKS.json), else the profiling recipe's fallback"""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md, clocks line)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); power.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own object code (oracle/_ref, kind "reference") or the plain-C restatement (kind "port").
+# The only place outside tests/ and smoke() where oracle/ is executed -- as the thing timed, never on the GPU path.
+# ---------------------------------------------------------------------------------------------------------------------
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_build_sample(wl, seed, b0, b1, threads):
+    """one CPU build over branch groups [b0, b1) of the workload; returns (n_entries, n_emitted, seconds, kind)"""
+    import oraclelib as O
+    from ipk_b200 import capi, synth
+    logp, nb = synth.posteriors(wl.n_taxa, wl.width, wl.sigma, seed=seed, branch_begin=b0, branch_end=b1)
+    thr, lthr = capi.score_threshold(wl.omega, wl.sigma, wl.k)
+    filt = 0 if wl.filter == "mif0" else 1
+    t = time.perf_counter()
+    if O.have_ref(wl.sigma):
+        db, kind = O.ref_build(logp, nb, wl.width, wl.sigma, wl.k, lthr, thr, wl.n_tree_nodes, filt, threads), "reference"
+    else:
+        db, kind = O.build(logp, nb, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt, threads), "port"
+    dt = time.perf_counter() - t
+    return db.n_entries, db.n_emitted, dt, kind
+
+
+def cpu_sample_size(wl, seed, threads, target_s, forced=0):
+    """branch groups in the bounded sample: probe with one group per thread, scale to ~target_s seconds"""
+    if forced:
+        return min(forced, wl.n_branches)
+    probe = min(max(threads, 4), wl.n_branches)
+    _, _, dt, _ = cpu_build_sample(wl, seed, 0, probe, threads)
+    n = int(probe * max(target_s / max(dt, 1e-3), 1.0))
+    n = max(probe, n - n % max(threads, 1))
+    return min(n, wl.n_branches)
+
+
+def cpu_baseline(wl, seed, target_s=15.0, forced=0):
+    threads = host_cores()
+    nb = cpu_sample_size(wl, seed, threads, target_s, forced)
+    n_entries, n_emitted, dt, kind = cpu_build_sample(wl, seed, 0, nb, threads)
+    return {"value": n_entries / dt, "unit": METRIC, "cores": threads, "kind": kind,
+            "sample": f"branch groups [0,{nb}) of {wl.n_branches} ({2 * nb} ghost matrices, {2 * nb * (wl.width - wl.k + 1)} windows): "
+                      f"{n_entries} entries, {n_emitted} emitted in {dt:.2f} s; OpenMP over branch groups "
+                      f"(the loop db_builder.cpp:602-605 once marked parallel), in-RAM stages 1+2, no serialization"}
+
+
+def workload_config(wl, n_gpus):
+    return {"workload": wl.name, "n_taxa": wl.n_taxa, "alignment_columns": wl.width, "k": wl.k, "omega": wl.omega,
+            "states": wl.sigma, "filter": wl.filter, "branch_groups": wl.n_branches, "ghost_matrices": wl.n_ghost_nodes,
+            "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", all-to-all by k-mer hash" if n_gpus > 1 else "")}
+
+
+def run_reference(args):
+    from ipk_b200 import synth
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    wl = synth.WORKLOADS[args.workload]
+    threads = host_cores()
+    per_step = max(3.0, min(20.0, 150.0 / max(args.steps + args.warmup, 1)))
+    nb = cpu_sample_size(wl, args.seed, threads, per_step, args.cpu_sample_branches)
+    for _ in range(args.warmup):
+        cpu_build_sample(wl, args.seed, 0, nb, threads)
+    tot_t, tot_e, kind, n_emitted = 0.0, 0, "port", 0
+    for _ in range(args.steps):
+        n_entries, n_emitted, dt, kind = cpu_build_sample(wl, args.seed, 0, nb, threads)
+        tot_t += dt; tot_e += n_entries
+    value = tot_e / tot_t
+    sample = (f"each step = branch groups [0,{nb}) of {wl.n_branches} ({2 * nb * (wl.width - wl.k + 1)} windows, {tot_e // max(args.steps, 1)} entries, "
+              f"{n_emitted} emitted); reference pk_compute.cpp/window.cpp object code + restated put/unsafe_insert/MIF0, "
+              f"OpenMP over branch groups on {threads} threads")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, args.gpus),
+            "cpu_baseline": {"value": value, "unit": METRIC, "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    g.build(only_missing=True)
+    from ipk_b200 import capi, synth
+    from ipk_b200 import dist as ipkdist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- ipk_b200 has no CPU path (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    wl = synth.WORKLOADS[args.workload]
+    thr, lthr = capi.score_threshold(wl.omega, wl.sigma, wl.k)
+    filt = capi.FILTER_MIF0 if wl.filter == "mif0" else capi.FILTER_RANDOM
+    b0, b1 = ipkdist.split_branches(wl.n_branches, world)[rank]
+
+    # ---- inputs: this rank's ghost matrices, generated straight into pinned host memory, plus a resident device copy
+    n_nodes = 2 * (b1 - b0)
+    h_logp = torch.empty((n_nodes, wl.width, wl.sigma), dtype=torch.float32, pin_memory=True)
+    _, node_branch = synth.posteriors(wl.n_taxa, wl.width, wl.sigma, seed=args.seed, branch_begin=b0, branch_end=b1, out=h_logp.numpy())
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    d_logp = h_logp.to(dev, non_blocking=True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
+    ctx = capi.Context(local_rank, stream.cuda_stream)
+    inp_dev, keep1 = capi.make_input(d_logp, node_branch, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt)
+    inp_host, keep2 = capi.make_input(h_logp.numpy(), node_branch, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt)
+    table = ipkdist.exchange_group_table(node_branch, dev) if world > 1 else None
+    key_bits = wl.k * wl.bits
+
+    def step(host: bool):
+        """one build; returns (n_entries of this rank's shard, n_kmers, stats dict, d2h bytes, launches)"""
+        inp = inp_host if host else inp_dev
+        if world == 1:
+            res = ctx.build_raw(inp, result_on_device=not host)
+            st = res.stats.as_dict()
+            return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), int(st["kernel_launches"]), 0
+        res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table)
+        st = res.stats.as_dict()
+        st1 = info["stage1"]
+        for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):
+            st[k_] = st1[k_]
+        st["ms_sort"] += st1["ms_sort"]; st["ms_merge"] += st1["ms_merge"]; st["sort_passes"] += st1["sort_passes"]
+        launches = int(st["kernel_launches"]) + int(st1["kernel_launches"]) + 1
+        return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), launches, info["n_sent_remote"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(host: bool, steps: int, profile: bool):
+        """K steps, each bracketed by CUDA events on the launching stream; L2 flushed between steps (untimed)"""
+        tot_ms, last = 0.0, None
+        if profile:
+            ctx.kernel_profile(True)
+        barrier()
+        for _ in range(steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world > 1:
+                dist.barrier()
+            e0.record(stream)
+            last = step(host)
+            e1.record(stream)
+            e1.synchronize()
+            tot_ms += e0.elapsed_time(e1)
+        barrier()
+        rows = ctx.kernel_profile_rows() if profile else []
+        if profile:
+            ctx.kernel_profile(False)
+        return tot_ms, last, rows
+
+    def reduce_max(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def reduce_sum(x: int) -> int:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return int(t.item())
+
+    # ---- warm-up (both paths: sizes every grow-only buffer, pins the result staging, settles clocks)
+    for _ in range(args.warmup):
+        step(False)
+    step(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_dev, last_dev, rows = timed(False, args.steps, True)
+    ms_e2e, last_e2e, _ = timed(True, args.steps, False)
+    clocks = sampler.stop() if rank == 0 else None
+
+    ms_dev, ms_e2e = reduce_max(ms_dev), reduce_max(ms_e2e)
+    n_entries = reduce_sum(last_dev[0]); n_kmers = reduce_sum(last_dev[1])
+    st = last_dev[2]
+    n_emitted = reduce_sum(int(st["n_emitted"]))
+    h2d = reduce_sum(int(last_e2e[2]["h2d_bytes"])); d2h = reduce_sum(last_e2e[3])
+    launches = last_dev[4] * args.steps
+    sent_remote = reduce_sum(last_dev[5])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel: algorithmic bytes (summed by the library at each launch site, DESIGN.md
+    # kernel table) / device time measured live with CUDA events around every launch of the timed region
+    peak, peak_kind = peaks()
+    rows.sort(key=lambda r: -r["ms"])
+    kernels = [{"kernel": r["kernel"], "launches": r["launches"], "ms": round(r["ms"], 4),
+                "algo_gbs": round(r["bytes"] / max(r["ms"], 1e-9) * 1e-6, 1), "share": round(r["ms"] / max(ms_dev, 1e-9), 4)} for r in rows]
+    roofline = None
+    if rows:
+        top = rows[0]
+        achieved = top["bytes"] / max(top["ms"], 1e-9) * 1e-6              # GB/s
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                for t in json.load(f):
+                    if t.get("kernel") == top["kernel"] and t.get("workload") == wl.name:
+                        traffic = t.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        roofline = {"bound": "hbm", "kernel": top["kernel"], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                    "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_kind,
+                    "launches_per_step": top["launches"] // max(args.steps, 1),
+                    "algo_bytes_per_launch": top["bytes"] // max(top["launches"], 1),
+                    "ms_per_launch": round(top["ms"] / max(top["launches"], 1), 4),
+                    "share_of_step": round(top["ms"] / max(ms_dev, 1e-9), 4)}
+    # whole-path roofline as north_star defines it: emitted-plus-sorted bytes over HBM vs all-to-all bytes over NVLink
+    passes = int(st["sort_passes"])
+    path_bytes = sum(r["bytes"] for r in rows) / max(args.steps, 1)
+    t_hbm = path_bytes / world / (peak * 1e9)
+    t_nvl = (12.0 * sent_remote / world) / 770e9 if world > 1 else 0.0
+    t_bound = max(t_hbm, t_nvl)
+    value = n_entries * args.steps / (ms_dev * 1e-3)
+    e2e_value = n_entries * args.steps / (ms_e2e * 1e-3)
+    line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {**workload_config(wl, world), "seed": args.seed, "l2": "flushed between steps (256 MiB write)",
+                       "timing": "CUDA events on the launching stream, per step, summed; max over ranks"},
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps, "build_time_s": ms_e2e / args.steps * 1e-3},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "path_roofline": {"algo_bytes_per_step": int(path_bytes), "t_hbm_ms": round(t_hbm * 1e3, 3), "t_nvlink_ms": round(t_nvl * 1e3, 3),
+                              "frac": round(t_bound / (ms_dev / args.steps * 1e-3), 4), "nvlink_peak_gbs": 770.0},
+            "counts": {"windows": wl.n_windows, "emitted": n_emitted, "entries": n_entries, "kmers": n_kmers, "sort_passes": passes,
+                       "emitted_per_s": n_emitted * args.steps / (ms_dev * 1e-3)},
+            "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order")},
+            "kernels": kernels}
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline(wl, args.seed, 15.0, args.cpu_sample_branches)
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -94,6 +94,14 @@ const char* ipkgpu_last_error(const ipkgpu_ctx* ctx);      /* ctx may be NULL: m
 void* ipkgpu_stream(const ipkgpu_ctx* ctx);                /* the cudaStream_t all work of ctx is ordered on */
 int  ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes);   /* cap on device scratch; 0 = 85% of free memory */
 
+/* Per-kernel device timing (measurement aid; no reference counterpart).  While enabled, every kernel launch of ctx is
+ * bracketed by CUDA events on ctx's stream; rows accumulate per kernel name until the next ipkgpu_kernel_profile().
+ * ipkgpu_kernel_profile_get(index) -> name, launches, summed device ms, summed ALGORITHMIC bytes (DESIGN.md kernel
+ * table); returns IPKGPU_EINVAL once index is past the last row. */
+int  ipkgpu_kernel_profile(ipkgpu_ctx* ctx, int enable);
+int  ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name, size_t name_cap, uint32_t* launches,
+                               double* ms, uint64_t* bytes);
+
 /* The whole path: H2D (if needed) -> best_prefix -> enumerate -> sort + per-branch max -> CSR by k-mer -> filter
  * values -> order by filter value -> gather (-> D2H unless result_on_device).  Blocking. */
 int  ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out);

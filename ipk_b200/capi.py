@@ -107,6 +107,10 @@ def load() -> C.CDLL:
     lib.ipkgpu_stream.restype = C.c_void_p
     lib.ipkgpu_set_workspace_limit.argtypes = [C.c_void_p, C.c_uint64]
     lib.ipkgpu_set_workspace_limit.restype = C.c_int
+    lib.ipkgpu_kernel_profile.argtypes = [C.c_void_p, C.c_int]
+    lib.ipkgpu_kernel_profile.restype = C.c_int
+    lib.ipkgpu_kernel_profile_get.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_size_t, P(C.c_uint32), P(C.c_double), P(C.c_uint64)]
+    lib.ipkgpu_kernel_profile_get.restype = C.c_int
     lib.ipkgpu_build.argtypes = [C.c_void_p, P(Input), C.c_int, P(Result)]
     lib.ipkgpu_build.restype = C.c_int
     lib.ipkgpu_free_result.argtypes = [C.c_void_p, P(Result)]
@@ -237,6 +241,19 @@ class Context:
 
     def set_workspace_limit(self, nbytes: int):
         self._check(self._lib.ipkgpu_set_workspace_limit(self._h, nbytes))
+
+    def kernel_profile(self, enable: bool = True):
+        """start (and reset) / stop per-kernel CUDA-event timing"""
+        self._check(self._lib.ipkgpu_kernel_profile(self._h, 1 if enable else 0))
+
+    def kernel_profile_rows(self) -> list[dict]:
+        rows, i = [], 0
+        name = C.create_string_buffer(64)
+        n, ms, b = C.c_uint32(0), C.c_double(0), C.c_uint64(0)
+        while self._lib.ipkgpu_kernel_profile_get(self._h, i, name, 64, C.byref(n), C.byref(ms), C.byref(b)) == 0:
+            rows.append(dict(kernel=name.value.decode(), launches=int(n.value), ms=float(ms.value), bytes=int(b.value)))
+            i += 1
+        return rows
 
     # ---- whole path ------------------------------------------------------------------------------------------------
     def build_raw(self, inp: Input, result_on_device: bool = False) -> Result:

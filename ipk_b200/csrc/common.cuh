@@ -82,6 +82,50 @@ struct ipkgpu_ctx
 
     std::vector<cudaEvent_t> events;
 
+    // optional per-kernel timing (ipkgpu_kernel_profile): one event after every launch of the current call
+    struct kprof_mark { const char* name; uint64_t bytes; };
+    struct kprof_row { std::string name; uint32_t launches = 0; double ms = 0; uint64_t bytes = 0; };
+    bool kprof_on = false;
+    std::vector<cudaEvent_t> kprof_events;
+    std::vector<kprof_mark> kprof_marks;       // kprof_marks[i] ended at kprof_events[i]; [0] = start of the call
+    std::vector<kprof_row> kprof_rows;         // accumulated since the last reset
+
+    void kprof_push(const char* name, uint64_t bytes)
+    {
+        if (!kprof_on) return;
+        const size_t i = kprof_marks.size();
+        while (kprof_events.size() <= i)
+        {
+            cudaEvent_t e;
+            IPK_CUDA(cudaEventCreate(&e));
+            kprof_events.push_back(e);
+        }
+        IPK_CUDA(cudaEventRecord(kprof_events[i], stream));
+        kprof_marks.push_back({ name, bytes });
+    }
+    void kprof_add_bytes(const char* name, uint64_t bytes)
+    {
+        for (size_t i = kprof_marks.size(); i-- > 0;)
+            if (kprof_marks[i].name && !strcmp(kprof_marks[i].name, name)) { kprof_marks[i].bytes += bytes; return; }
+    }
+    /// fold the marks of the finished call into kprof_rows (stream must be idle)
+    void kprof_collect()
+    {
+        if (!kprof_on || kprof_marks.empty()) { kprof_marks.clear(); return; }
+        IPK_CUDA(cudaEventSynchronize(kprof_events[kprof_marks.size() - 1]));
+        for (size_t i = 1; i < kprof_marks.size(); ++i)
+        {
+            if (!kprof_marks[i].name) continue;            // a separator (host work / copies before it are not a kernel's)
+            float ms = 0;
+            IPK_CUDA(cudaEventElapsedTime(&ms, kprof_events[i - 1], kprof_events[i]));
+            kprof_row* row = nullptr;
+            for (auto& r : kprof_rows) if (r.name == kprof_marks[i].name) { row = &r; break; }
+            if (!row) { kprof_rows.push_back({}); row = &kprof_rows.back(); row->name = kprof_marks[i].name; }
+            row->launches++; row->ms += ms; row->bytes += kprof_marks[i].bytes;
+        }
+        kprof_marks.clear();
+    }
+
     void reserve(ipkgpu::dbuf& b, size_t bytes)
     {
         if (bytes <= b.cap) return;
@@ -147,12 +191,24 @@ struct ipkgpu_ctx
 
 namespace ipkgpu
 {
-    inline void check_launch(ipkgpu_ctx* ctx, const char* name)
+    /// call right after a kernel launch; algo_bytes = algorithmic DRAM bytes of that launch (kernel table)
+    inline void check_launch(ipkgpu_ctx* ctx, const char* name, uint64_t algo_bytes = 0)
     {
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) fail(IPKGPU_ECUDA, "launch of %s failed: %s", name, cudaGetErrorString(e));
         ctx->launches++;
+        ctx->kprof_push(name, algo_bytes);
     }
+    /// call right BEFORE a kernel launch that follows copies / memsets / host waits, so that those are not billed to it
+    inline void kprof_fence(ipkgpu_ctx* ctx) { ctx->kprof_push(nullptr, 0); }
+/// fence + launch + check: IPK_LAUNCH(ctx, "name", algorithmic_bytes, kernel<<<grid, block, smem, stream>>>(args...));
+#define IPK_LAUNCH(ctx_, name_, bytes_, ...)                 \
+    do {                                                     \
+        ::ipkgpu::kprof_fence(ctx_);                         \
+        __VA_ARGS__;                                         \
+        ::ipkgpu::check_launch(ctx_, name_, bytes_);         \
+    } while (0)
+
     inline uint32_t ceil_log2(uint64_t x)
     {
         uint32_t b = 0;

@@ -25,7 +25,6 @@ namespace ipkgpu
     constexpr int ENUM_THREADS = 128;        // windows per CTA tile
     constexpr int ENUM_WARPS = ENUM_THREADS / 32;
     constexpr int MAX_K = 32;
-    constexpr int MAX_SLOTS = 16;            // 2 per tree depth, depth <= 7
     constexpr int STAGE_CAP = 96;            // per-warp staging records; flushed when fewer than 32 slots remain
     constexpr float PRUNE_MARGIN = 1e-3f;
 
@@ -34,21 +33,20 @@ namespace ipkgpu
     {
         int k, n_eps_ops, n_nodes;
         struct { uint8_t dst, src, hi, lo; } eps_ops[2 * MAX_K];      // eps[dst] = eps[src] - (B[s+hi] - B[s+lo])
-        uint8_t leaf_eps[MAX_K];                                      // eps index of leaf p
-        uint8_t leaf_slot[MAX_K];                                     // partial-sum slot leaf p writes
+        uint8_t leaf_eps[MAX_K];                                      // tree-node id of leaf p (indexes eps[] and val[])
         uint8_t merge_begin[MAX_K + 1];                               // merges completed by placing position p
-        struct { uint8_t eps, src, dst, pad; } merges[MAX_K];         // S = slot[src] + slot[src+1]; check; slot[dst] = S
+        struct { uint8_t id, left; } merges[MAX_K];                   // S = val[left] + val[left+1]; check S > eps[id]; val[id] = S
     };
 
     namespace detail
     {
-        inline void build_node(enum_program& P, int j, int h, int depth, int side, int id, int& next_id, int& n_merges)
+        // Every tree node owns one partial-sum cell val[id]: a depth-first search revisits earlier positions, so a
+        // cell may not be recycled between subtrees (the left operand of a merge must survive the backtracking).
+        inline void build_node(enum_program& P, int j, int h, int id, int& next_id, int& n_merges)
         {
-            if (depth * 2 + 1 >= MAX_SLOTS) fail(IPKGPU_EINVAL, "k too large: split tree deeper than %d", MAX_SLOTS / 2 - 1);
             if (h == 1)
             {
                 P.leaf_eps[j] = uint8_t(id);
-                P.leaf_slot[j] = uint8_t(depth * 2 + side);
                 P.merge_begin[j] = uint8_t(n_merges);
                 return;
             }
@@ -58,10 +56,10 @@ namespace ipkgpu
             a.dst = uint8_t(l); a.src = uint8_t(id); a.hi = uint8_t(j + h); a.lo = uint8_t(j + hl);
             auto& b = P.eps_ops[P.n_eps_ops++];   // :55  eps_r = eps - rms(j, h/2)
             b.dst = uint8_t(r); b.src = uint8_t(id); b.hi = uint8_t(j + hl); b.lo = uint8_t(j);
-            build_node(P, j, hl, depth + 1, 0, l, next_id, n_merges);
-            build_node(P, j + hl, h - hl, depth + 1, 1, r, next_id, n_merges);
+            build_node(P, j, hl, l, next_id, n_merges);
+            build_node(P, j + hl, h - hl, r, next_id, n_merges);
             auto& m = P.merges[n_merges++];
-            m.eps = uint8_t(id); m.src = uint8_t((depth + 1) * 2); m.dst = uint8_t(depth * 2 + side); m.pad = 0;
+            m.id = uint8_t(id); m.left = uint8_t(l);                  // right child = l + 1
         }
     }
 
@@ -72,7 +70,7 @@ namespace ipkgpu
         memset(&P, 0, sizeof P);
         P.k = k;
         int next_id = 1, n_merges = 0;
-        detail::build_node(P, 0, k, 0, 0, 0, next_id, n_merges);
+        detail::build_node(P, 0, k, 0, next_id, n_merges);
         P.merge_begin[k] = uint8_t(n_merges);
         P.n_nodes = next_id;
         return P;
@@ -154,14 +152,14 @@ namespace ipkgpu
     /// Dynamic shared memory layout (floats unless noted), NC = ENUM_THREADS + k - 1 columns:
     ///   sval [sigma][NCP]   column states' scores, descending          NCP = NC rounded up to a multiple of 4
     ///   bs   [NCP+4]        B[n][s0 .. s0+NC]
-    ///   pt   [4k+MAX_SLOTS-1... ][ENUM_THREADS]  per-thread arrays, index-major => bank = lane, never conflicts
+    ///   pt   [6k][ENUM_THREADS]  per-thread arrays (eps 2k, lim k, ps k, val 2k), index-major => bank = lane, never conflicts
     ///        (aliased, before the DFS starts, by the raw TMA-staged tile [NC][sigma])
     ///   stage keys u64 [ENUM_WARPS][STAGE_CAP], scores f32 [...], (DEBUG: win u32 [...])
     ///   sidx u8 [sigma][NCP]
     inline size_t enum_smem_bytes(int k, int sigma, bool debug)
     {
         const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
-        size_t pt = size_t(4 * k + MAX_SLOTS) * ENUM_THREADS * 4;
+        size_t pt = size_t(6 * k) * ENUM_THREADS * 4;
         size_t raw = size_t(NC) * sigma * 4;
         size_t b = 0;
         b += size_t(sigma) * NCP * 4;                 // sval
@@ -181,8 +179,8 @@ namespace ipkgpu
     {
         extern __shared__ __align__(128) unsigned char smem_raw[];
         __shared__ __align__(8) unsigned long long mbar;
-        __shared__ uint32_t s_pos[MAX_K];      // per position: leaf eps idx | leaf slot << 8 | merge begin << 16 | merge end << 24
-        __shared__ uint32_t s_merge[MAX_K];    // per merge: eps idx | src slot << 8 | dst slot << 16
+        __shared__ uint32_t s_pos[MAX_K];      // per position: leaf node id | merge begin << 16 | merge end << 24
+        __shared__ uint32_t s_merge[MAX_K];    // per merge: node id | left child id << 8
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma);
@@ -196,7 +194,7 @@ namespace ipkgpu
         float* sval = reinterpret_cast<float*>(smem_raw);
         float* bs = sval + sigma * NCP;
         float* pt = bs + NCP + 4;
-        const size_t pt_bytes = size_t(4 * k + MAX_SLOTS) * ENUM_THREADS * 4, raw_bytes = size_t(NC) * sigma * 4;
+        const size_t pt_bytes = size_t(6 * k) * ENUM_THREADS * 4, raw_bytes = size_t(NC) * sigma * 4;
         size_t off = (size_t(sigma) * NCP * 4 + size_t(NCP + 4) * 4 + (pt_bytes > raw_bytes ? pt_bytes : raw_bytes) + 15) & ~size_t(15);
         unsigned long long* st_keys = reinterpret_cast<unsigned long long*>(smem_raw + off) + warp * STAGE_CAP;
         off += size_t(ENUM_WARPS) * STAGE_CAP * 8;
@@ -210,9 +208,8 @@ namespace ipkgpu
         if (tid < MAX_K)
         {
             // lanes sit at different depths of their searches: keep the tree tables where divergent reads are cheap
-            s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.leaf_slot[tid]) << 8 |
-                                    uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
-            s_merge[tid] = uint32_t(P.merges[tid].eps) | uint32_t(P.merges[tid].src) << 8 | uint32_t(P.merges[tid].dst) << 16;
+            s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
+            s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
         }
         // ---- stage the tile: ncols*sigma contiguous floats of logp[node][s0..] ------------------------------------
         const float* gsrc = A.logp + (uint64_t(node) * A.W + s0) * sigma;
@@ -289,7 +286,7 @@ namespace ipkgpu
         float* EPS = pt + tid;                                   // [n_nodes <= 2k-1]   EPS[i*ENUM_THREADS]
         float* LIM = pt + (2 * k) * ENUM_THREADS + tid;          // [k]
         float* PS = pt + (3 * k) * ENUM_THREADS + tid;           // [k]
-        float* SLOT = pt + (4 * k) * ENUM_THREADS + tid;         // [MAX_SLOTS]
+        float* VAL = pt + (4 * k) * ENUM_THREADS + tid;          // [n_nodes <= 2k-1]   partial sum of tree node i
         bool active = tid < nwin_tile;
         if (active)
         {
@@ -339,15 +336,15 @@ namespace ipkgpu
                 }
                 if (ok)
                 {
-                    SLOT[((pi >> 8) & 0xff) * ENUM_THREADS] = v;
+                    VAL[(pi & 0xff) * ENUM_THREADS] = v;
                     S = v;
                     for (uint32_t m = (pi >> 16) & 0xff; m < (pi >> 24); ++m)
                     {
                         const uint32_t mg = s_merge[m];
-                        const uint32_t src = (mg >> 8) & 0xff;
-                        S = __fadd_rn(SLOT[src * ENUM_THREADS], SLOT[(src + 1) * ENUM_THREADS]);         // pk_compute.cpp:90
+                        const uint32_t left = mg >> 8;
+                        S = __fadd_rn(VAL[left * ENUM_THREADS], VAL[(left + 1) * ENUM_THREADS]);         // pk_compute.cpp:90
                         if (!(S > EPS[(mg & 0xff) * ENUM_THREADS])) { ok = false; break; }                // :91 `score <= eps` => drop
-                        SLOT[(mg >> 16) * ENUM_THREADS] = S;
+                        VAL[(mg & 0xff) * ENUM_THREADS] = S;
                     }
                 }
                 if (ok)

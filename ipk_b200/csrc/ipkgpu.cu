@@ -128,11 +128,11 @@ namespace
         if (cols)
         {
             const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(cols, 256), uint64_t(ctx->num_sms) * 16));
-            k1a_colmax<<<grid, 256, 0, ctx->stream>>>(d_logp, ctx->colmax.as<float>(), in->n_nodes, in->width, in->sigma);
-            check_launch(ctx, "k1a_colmax");
+            IPK_LAUNCH(ctx, "k1a_colmax", cols * (in->sigma + 1) * 4,
+                       k1a_colmax<<<grid, 256, 0, ctx->stream>>>(d_logp, ctx->colmax.as<float>(), in->n_nodes, in->width, in->sigma));
         }
-        k1b_prefix<<<div_up<uint32_t>(in->n_nodes, 64), 64, 0, ctx->stream>>>(ctx->colmax.as<float>(), ctx->bestpref.as<float>(), in->n_nodes, in->width);
-        check_launch(ctx, "k1b_prefix");
+        IPK_LAUNCH(ctx, "k1b_prefix", cols * 8 + uint64_t(in->n_nodes) * 4,
+                   k1b_prefix<<<div_up<uint32_t>(in->n_nodes, 64), 64, 0, ctx->stream>>>(ctx->colmax.as<float>(), ctx->bestpref.as<float>(), in->n_nodes, in->width));
     }
 }
 
@@ -178,17 +178,19 @@ namespace
         const uint64_t grid = uint64_t(L.slot_end - L.slot_begin) * A.tiles_per_node;
         if (grid > 0x7fffffffull) fail(IPKGPU_EINVAL, "enumeration grid of %llu tiles is too large", (unsigned long long)grid);
         const size_t smem = enum_smem_bytes(int(in->k), int(in->sigma), L.debug);
+        // algorithmic bytes: the posterior columns and prefix sums of the launched nodes; the emitted records are added by
+        // the caller once the count is known (kprof_add_bytes)
+        const uint64_t in_bytes = uint64_t(L.slot_end - L.slot_begin) * (uint64_t(in->width) * in->sigma + in->width + 1) * 4;
         if (L.debug)
         {
             IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            k2_enumerate<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P);
+            IPK_LAUNCH(ctx, "k2_enumerate", in_bytes, k2_enumerate<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P));
         }
         else
         {
             IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            k2_enumerate<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P);
+            IPK_LAUNCH(ctx, "k2_enumerate", in_bytes, k2_enumerate<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P));
         }
-        check_launch(ctx, "k2_enumerate");
     }
 
     uint64_t read_u64(ipkgpu_ctx* ctx, const void* d)
@@ -216,8 +218,7 @@ namespace
         ctx->reserve(ctx->counters, 64);
         uint32_t* rc = ctx->block_counts.as<uint32_t>();
         uint32_t* kc = rc + tiles;
-        mg_count<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, n, group_bits, rc, kc);
-        check_launch(ctx, "mg_count");
+        IPK_LAUNCH(ctx, "mg_count", n * 8, mg_count<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, n, group_bits, rc, kc));
         unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;
         exclusive_scan_u32(ctx, rc, rc, tiles, ctx->scan_tmp, totals);
         exclusive_scan_u32(ctx, kc, kc, tiles, ctx->scan_tmp, totals + 1);
@@ -238,13 +239,13 @@ namespace
             ctx->reserve(ctx->ent_branch, r.n_records * 4 + 4);
             ctx->reserve(ctx->ent_score, r.n_records * 4 + 4);
         }
-        mg_write<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, scores, n, group_bits, out_group_bits, group_add, rc, kc,
-                                                        unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr,
-                                                        unique ? ctx->u_scores.as<float>() + u_off : nullptr,
-                                                        ctx->group_branch.as<uint32_t>(),
-                                                        csr ? ctx->kmer_keys.as<uint64_t>() : nullptr, ctx->kmer_offs.as<uint64_t>(),
-                                                        ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>());
-        check_launch(ctx, "mg_write");
+        IPK_LAUNCH(ctx, "mg_write", n * 12 + (unique ? r.n_records * 12 : 0) + (csr ? r.n_records * 8 + r.n_kmers * 16 : 0),
+                   mg_write<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, scores, n, group_bits, out_group_bits, group_add, rc, kc,
+                                                                   unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr,
+                                                                   unique ? ctx->u_scores.as<float>() + u_off : nullptr,
+                                                                   ctx->group_branch.as<uint32_t>(),
+                                                                   csr ? ctx->kmer_keys.as<uint64_t>() : nullptr, ctx->kmer_offs.as<uint64_t>(),
+                                                                   ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>()));
         if (csr)
             IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + r.n_kmers, &r.n_records, 8, cudaMemcpyHostToDevice, ctx->stream));
         return r;
@@ -313,6 +314,7 @@ namespace
         launch_enumerate(ctx, d_logp, in, P, L, true);
         o.enum_launches = 1;
         o.n_emitted = read_u64(ctx, ctx->counters.p);
+        ctx->kprof_add_bytes("k2_enumerate", 12 * std::min(o.n_emitted, cap0));
         ctx->hint_emitted = o.n_emitted;
         bool first_valid = o.n_emitted <= cap0;
         if (first_valid) batches.push_back({ 0, o.n_groups, o.n_emitted });
@@ -359,6 +361,7 @@ namespace
                 enum_launch Lb{ T.group_first_slot[b.g0], T.group_first_slot[b.g1], group_base + b.g0, bbits, b.n,
                                 ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
                 launch_enumerate(ctx, d_logp, in, P, Lb, false);
+                ctx->kprof_add_bytes("k2_enumerate", 12 * b.n);
                 o.enum_launches++;
             }
             else if (!timed_first) { ea = e1; timed_first = true; }
@@ -418,33 +421,32 @@ namespace
             const uint32_t grid = uint32_t(div_up<uint64_t>(n_kmers, 256));
             if (sp.filter == IPKGPU_FILTER_MIF0)
             {
-                k4_mif0<<<grid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers,
-                                                       sp.total_num_groups, sp.threshold, ctx->fv.as<float>());
-                check_launch(ctx, "k4_mif0");
+                IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,
+                           k4_mif0<<<grid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers,
+                                                                  sp.total_num_groups, sp.threshold, ctx->fv.as<float>()));
             }
             else
             {
-                k4_random<<<grid, 256, 0, ctx->stream>>>(n_kmers, ctx->fv.as<float>());
-                check_launch(ctx, "k4_random");
+                IPK_LAUNCH(ctx, "k4_random", n_kmers * 4, k4_random<<<grid, 256, 0, ctx->stream>>>(n_kmers, ctx->fv.as<float>()));
             }
             e1 = tm.mark();
             // K5: stable sort on the 32-bit order-preserving image of fv; k-mers are in ascending key order, so ties keep it
             ctx->reserve(ctx->ord_keys_a, n_kmers * 8); ctx->reserve(ctx->ord_keys_b, n_kmers * 8);
             ctx->reserve(ctx->ord_vals_a, n_kmers * 4); ctx->reserve(ctx->ord_vals_b, n_kmers * 4);
-            k5_order_keys<<<grid, 256, 0, ctx->stream>>>(ctx->fv.as<float>(), n_kmers, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>());
-            check_launch(ctx, "k5_order_keys");
+            IPK_LAUNCH(ctx, "k5_order_keys", n_kmers * 16,
+                       k5_order_keys<<<grid, 256, 0, ctx->stream>>>(ctx->fv.as<float>(), n_kmers, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>()));
             const bool in_b = radix_sort_pairs(ctx, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>(), ctx->ord_keys_b.as<uint64_t>(),
                                                ctx->ord_vals_b.as<uint32_t>(), n_kmers, 32, ctx->hist, ctx->scan_tmp);
             const uint32_t* perm = in_b ? ctx->ord_vals_b.as<uint32_t>() : ctx->ord_vals_a.as<uint32_t>();
             // K6
-            k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
-                                                           n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>());
-            check_launch(ctx, "k6_gather_heads");
+            IPK_LAUNCH(ctx, "k6_gather_heads", n_kmers * 44,
+                       k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
+                                                                      n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>()));
             exclusive_scan_u32(ctx, ctx->out_cnt.as<uint32_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, ctx->scan_tmp);
-            k6_gather_entries<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, n_entries,
-                                                             ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>(),
-                                                             ctx->out_offs.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>());
-            check_launch(ctx, "k6_gather_entries");
+            IPK_LAUNCH(ctx, "k6_gather_entries", n_kmers * 32 + n_entries * 16,
+                       k6_gather_entries<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, n_entries,
+                                                                        ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>(),
+                                                                        ctx->out_offs.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>()));
             e2 = tm.mark();
         }
         else
@@ -526,7 +528,9 @@ namespace
             if (!ctx) return IPKGPU_EINVAL;
             IPK_CUDA(cudaSetDevice(ctx->device));
             ctx->launches = 0;
+            ctx->kprof_marks.clear();
             f();
+            ctx->kprof_collect();
             return IPKGPU_OK;
         }
         catch (const error& e) { if (ctx) ctx->last_error = e.what; cudaGetLastError(); return e.code; }
@@ -611,6 +615,26 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
 
 const char* ipkgpu_last_error(const ipkgpu_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
 void* ipkgpu_stream(const ipkgpu_ctx* ctx) { return ctx ? static_cast<void*>(ctx->stream) : nullptr; }
+
+int ipkgpu_kernel_profile(ipkgpu_ctx* ctx, int enable)
+{
+    if (!ctx) return IPKGPU_EINVAL;
+    ctx->kprof_on = enable != 0;
+    ctx->kprof_rows.clear();
+    ctx->kprof_marks.clear();
+    return IPKGPU_OK;
+}
+
+int ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name, size_t name_cap, uint32_t* launches, double* ms, uint64_t* bytes)
+{
+    if (!ctx || index >= ctx->kprof_rows.size()) return IPKGPU_EINVAL;
+    const auto& r = ctx->kprof_rows[index];
+    if (name && name_cap) { strncpy(name, r.name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+    if (launches) *launches = r.launches;
+    if (ms) *ms = r.ms;
+    if (bytes) *bytes = r.bytes;
+    return IPKGPU_OK;
+}
 
 int ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes)
 {

@@ -125,12 +125,9 @@ namespace ipkgpu
         if (tiles > 0x7fffffffull) fail(IPKGPU_EINVAL, "scan of %llu elements is too large", (unsigned long long)n);
         ctx->reserve(tmp, tiles * 4);
         uint32_t* sums = tmp.as<uint32_t>();
-        scan_tile_sums<<<uint32_t(tiles), SCAN_THREADS, 0, ctx->stream>>>(in, sums, n);
-        check_launch(ctx, "scan_tile_sums");
-        scan_small<<<1, SCAN_THREADS, 0, ctx->stream>>>(sums, uint32_t(tiles), d_total);
-        check_launch(ctx, "scan_small");
-        scan_downsweep<<<uint32_t(tiles), SCAN_THREADS, 0, ctx->stream>>>(in, out, sums, n);
-        check_launch(ctx, "scan_downsweep");
+        IPK_LAUNCH(ctx, "scan_tile_sums", n * 4, scan_tile_sums<<<uint32_t(tiles), SCAN_THREADS, 0, ctx->stream>>>(in, sums, n));
+        IPK_LAUNCH(ctx, "scan_small", tiles * 8, scan_small<<<1, SCAN_THREADS, 0, ctx->stream>>>(sums, uint32_t(tiles), d_total));
+        IPK_LAUNCH(ctx, "scan_downsweep", n * 8, scan_downsweep<<<uint32_t(tiles), SCAN_THREADS, 0, ctx->stream>>>(in, out, sums, n));
     }
 
     // ------------------------------------------------------------------------------------------------------------
@@ -276,11 +273,9 @@ namespace ipkgpu
         const uint64_t table_n = uint64_t(n_tiles) * RS_RADIX;
         ctx->reserve(table, table_n * 4);
         uint32_t* tab = table.as<uint32_t>();
-        rs_histogram<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, tab, n, n_tiles, digit);
-        check_launch(ctx, "rs_histogram");
+        IPK_LAUNCH(ctx, "rs_histogram", n * 8 + table_n * 4, rs_histogram<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, tab, n, n_tiles, digit));
         exclusive_scan_u32(ctx, tab, tab, table_n, scan_tmp);
-        rs_scatter<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, tab, n, n_tiles, digit);
-        check_launch(ctx, "rs_scatter");
+        IPK_LAUNCH(ctx, "rs_scatter", n * 24 + table_n * 4, rs_scatter<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, tab, n, n_tiles, digit));
     }
 
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);

@@ -1,0 +1,135 @@
+"""Multi-GPU database build: one process per GPU, partition by branch group, ONE all-to-all by k-mer hash.
+
+Reference counterpart: none -- the reference is single-threaded (ipk/src/db_builder.cpp:602-605).  The shape is the one
+its on-disk mode already has: k-mer space split into batches by key (branch_group.cpp:104-107, db_builder.cpp:654)
+and a final N-way merge by filter value (merge_stage2, db_builder.cpp:392-458).
+
+Per rank r of G:
+  stage 1   enumerate + per-branch max over the rank's own branch groups        (ipkgpu_stage1; no communication)
+  partition bucket the unique records by owner = mix64(kmer) % G, stably          (ipkgpu_stage1_partition)
+  exchange  counts all-gather, then one all-to-all-v of (u64 key, f32 score)     (NCCL over NVLink)
+  stage 2   regroup by k-mer, filter values, order by filter value               (ipkgpu_stage2)
+The final database is the G-way merge of the shards by (filter value, key): `merge_shards`.
+
+All device work goes through a context object exposing stage1 / stage1_partition / stage2 (ipk_b200.capi.Context);
+this module is only the torch.distributed plumbing around it and never computes on the records itself.
+"""
+from __future__ import annotations
+
+import heapq
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def split_branches(n_branches: int, world: int) -> list[tuple[int, int]]:
+    """contiguous blocks of the branch-group processing order, sizes differing by at most one"""
+    base, extra = divmod(n_branches, world)
+    out, b = [], 0
+    for r in range(world):
+        e = b + base + (1 if r < extra else 0)
+        out.append((b, e))
+        b = e
+    return out
+
+
+def local_groups(node_branch: np.ndarray) -> np.ndarray:
+    """branch ids in order of first appearance (group_ghost_ids, db_builder.cpp:524-553)"""
+    nb = np.asarray(node_branch, dtype=np.uint32)
+    _, first = np.unique(nb, return_index=True)
+    return nb[np.sort(first)]
+
+
+@dataclass
+class GroupTable:
+    group_base: int            # global index of this rank's first group
+    group_bits: int            # bits of the global group field
+    group_branch: np.ndarray   # [total groups] global group index -> branch id
+
+
+def exchange_group_table(node_branch: np.ndarray, device, group=None) -> GroupTable:
+    """every rank learns how many groups the ranks before it own and the full group -> branch table"""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    mine = local_groups(node_branch).astype(np.int64)
+    counts = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(counts, torch.tensor([len(mine)], dtype=torch.int64, device=device), group=group)
+    counts = [int(c.item()) for c in counts]
+    cap = max(max(counts), 1)
+    pad = torch.zeros(cap, dtype=torch.int64, device=device)
+    pad[: len(mine)] = torch.from_numpy(mine).to(device)
+    parts = [torch.zeros(cap, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    table = np.concatenate([p[:c].cpu().numpy() for p, c in zip(parts, counts)]).astype(np.uint32)
+    total = int(sum(counts))
+    bits = 0
+    while (1 << bits) < total:
+        bits += 1
+    return GroupTable(int(sum(counts[:rank])), bits, table)
+
+
+def exchange_records(send_keys: torch.Tensor, send_scores: torch.Tensor, counts: np.ndarray, group=None):
+    """all-to-all-v of the partitioned records.  counts[p] = records this rank sends to rank p (bucket order).
+    Returns (recv_keys, recv_scores, recv_counts); chunks arrive in source-rank order = ascending group ranges."""
+    world = dist.get_world_size(group)
+    dev = send_keys.device
+    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device=dev)
+    rows = [torch.zeros(world, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)
+    matrix = torch.stack(rows).cpu().numpy()                 # matrix[src][dst]
+    rank = dist.get_rank(group)
+    recv_counts = matrix[:, rank].astype(np.int64)
+    n_recv = int(recv_counts.sum())
+    recv_keys = torch.empty(max(n_recv, 1), dtype=send_keys.dtype, device=dev)[:n_recv]
+    recv_scores = torch.empty(max(n_recv, 1), dtype=send_scores.dtype, device=dev)[:n_recv]
+    in_split, out_split = [int(c) for c in counts], [int(c) for c in recv_counts]
+    n_send = int(sum(in_split))
+    dist.all_to_all_single(recv_keys, send_keys[:n_send], out_split, in_split, group=group)
+    dist.all_to_all_single(recv_scores, send_scores[:n_send], out_split, in_split, group=group)
+    return recv_keys, recv_scores, recv_counts
+
+
+def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: float, total_num_groups: int, filter: int,
+                  device, result_on_device: bool = False, group=None, table: GroupTable | None = None):
+    """The whole multi-GPU path for this rank.  ctx: ipk_b200.capi.Context (or anything with its stage methods);
+    inp: the rank's ipkgpu_input (its own ghost nodes only).  Returns (stage-2 result, info dict)."""
+    world = dist.get_world_size(group)
+    if table is None:
+        table = exchange_group_table(node_branch, device, group)
+    n_unique, st1 = ctx.stage1(inp, table.group_base, table.group_bits)
+    send_keys = torch.empty(max(n_unique, 1), dtype=torch.int64, device=device)
+    send_scores = torch.empty(max(n_unique, 1), dtype=torch.float32, device=device)
+    counts = ctx.stage1_partition(world, send_keys, send_scores)
+    recv_keys, recv_scores, recv_counts = exchange_records(send_keys, send_scores, counts, group)
+    del send_keys, send_scores
+    n_recv = int(recv_counts.sum())
+    res = ctx.stage2(recv_keys, recv_scores, n_recv, table.group_bits, table.group_branch, key_bits, threshold,
+                     total_num_groups, filter, True, result_on_device)
+    info = dict(stage1=st1, n_unique_local=int(n_unique), n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
+                n_received=n_recv, keep=(recv_keys, recv_scores))
+    return res, info
+
+
+def merge_shards(shards):
+    """G-way merge of per-rank databases (each in ascending (fv, key) order) into one, the shape of merge_stage2
+    (db_builder.cpp:392-458).  shards: objects with keys / fv / offsets / branch / score numpy arrays.
+    Host-side, run while serializing; returns the five arrays of the merged database."""
+    heads = []
+    for s, d in enumerate(shards):
+        if len(d.keys):
+            heads.append((float(d.fv[0]), int(d.keys[0]), s, 0))
+    heapq.heapify(heads)
+    keys, fv, cnt, br, sc = [], [], [], [], []
+    while heads:
+        f, k, s, i = heapq.heappop(heads)
+        d = shards[s]
+        a, b = int(d.offsets[i]), int(d.offsets[i + 1])
+        keys.append(k); fv.append(f); cnt.append(b - a); br.append(d.branch[a:b]); sc.append(d.score[a:b])
+        if i + 1 < len(d.keys):
+            heapq.heappush(heads, (float(d.fv[i + 1]), int(d.keys[i + 1]), s, i + 1))
+    offsets = np.zeros(len(keys) + 1, np.uint64)
+    offsets[1:] = np.cumsum(np.asarray(cnt, dtype=np.uint64)) if keys else 0
+    return (np.asarray(keys, np.uint64), np.asarray(fv, np.float32), offsets,
+            np.concatenate(br).astype(np.uint32) if br else np.zeros(0, np.uint32),
+            np.concatenate(sc).astype(np.float32) if sc else np.zeros(0, np.float32))
