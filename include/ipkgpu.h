@@ -64,6 +64,8 @@ typedef struct ipkgpu_stats
     uint32_t kernel_launches;      /* all kernels of this library launched by the call */
     float ms_h2d, ms_prefix, ms_enumerate, ms_sort, ms_merge, ms_filter, ms_order, ms_d2h, ms_total;  /* CUDA events */
     uint64_t h2d_bytes, d2h_bytes;
+    uint64_t n_tiles;              /* (node, 128-window) tiles enumerated */
+    uint64_t n_deferred_tiles;     /* ... of which the depth-first kernel handled (list pool overflow, k == 1, mode 1) */
 } ipkgpu_stats;
 
 /* The database in the order db_builder.cpp:323-332 serializes it: k-mers by ascending filter value (ties: ascending
@@ -93,6 +95,11 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx);
 const char* ipkgpu_last_error(const ipkgpu_ctx* ctx);      /* ctx may be NULL: message of the last failed create */
 void* ipkgpu_stream(const ipkgpu_ctx* ctx);                /* the cudaStream_t all work of ctx is ordered on */
 int  ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes);   /* cap on device scratch; 0 = 85% of free memory */
+
+/* Enumeration strategy (no reference counterpart; the output is identical either way).  mode 0: list-join kernel, the
+ * depth-first kernel takes the tiles whose lists overflow the shared-memory pool; mode 1: depth-first kernel only.
+ * pool_cap: list-pool capacity in 8-byte elements (0 = default for the alphabet, at most 65000). */
+int  ipkgpu_set_enumeration(ipkgpu_ctx* ctx, int mode, uint32_t pool_cap);
 
 /* Per-kernel device timing (measurement aid; no reference counterpart).  While enabled, every kernel launch of ctx is
  * bracketed by CUDA events on ctx's stream; rows accumulate per kernel name until the next ipkgpu_kernel_profile().

@@ -64,6 +64,8 @@ class Stats(C.Structure):
         ("ms_total", C.c_float),
         ("h2d_bytes", C.c_uint64),
         ("d2h_bytes", C.c_uint64),
+        ("n_tiles", C.c_uint64),
+        ("n_deferred_tiles", C.c_uint64),
     ]
 
     def as_dict(self) -> dict:
@@ -107,6 +109,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_stream.restype = C.c_void_p
     lib.ipkgpu_set_workspace_limit.argtypes = [C.c_void_p, C.c_uint64]
     lib.ipkgpu_set_workspace_limit.restype = C.c_int
+    lib.ipkgpu_set_enumeration.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
+    lib.ipkgpu_set_enumeration.restype = C.c_int
     lib.ipkgpu_kernel_profile.argtypes = [C.c_void_p, C.c_int]
     lib.ipkgpu_kernel_profile.restype = C.c_int
     lib.ipkgpu_kernel_profile_get.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_size_t, P(C.c_uint32), P(C.c_double), P(C.c_uint64)]
@@ -241,6 +245,10 @@ class Context:
 
     def set_workspace_limit(self, nbytes: int):
         self._check(self._lib.ipkgpu_set_workspace_limit(self._h, nbytes))
+
+    def set_enumeration(self, mode: int = 0, pool_cap: int = 0):
+        """0: list-join kernel + depth-first kernel on deferred tiles; 1: depth-first only.  pool_cap 0 = default."""
+        self._check(self._lib.ipkgpu_set_enumeration(self._h, mode, pool_cap))
 
     def kernel_profile(self, enable: bool = True):
         """start (and reset) / stop per-kernel CUDA-event timing"""

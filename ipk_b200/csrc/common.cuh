@@ -69,7 +69,11 @@ struct ipkgpu_ctx
     // device scratch
     ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
     ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
-    ipkgpu::dbuf dbg_node, dbg_win;
+    ipkgpu::dbuf dbg_node, dbg_win, deferred;
+    int enum_mode = 0;                 // 0: list-join kernel + depth-first kernel on deferred tiles; 1: depth-first only
+    uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet
+    uint64_t last_tiles = 0, last_deferred_tiles = 0;   // of the current call
+    uint64_t enum_join_emitted = 0;    // records the join kernel of the last enumeration launch emitted
     ipkgpu::dbuf u_keys, u_scores;                 // unique (kmer,group) records, composite keys
     ipkgpu::dbuf kmer_keys, kmer_offs, ent_branch, ent_score, fv, ord_keys_a, ord_keys_b, ord_vals_a, ord_vals_b;
     ipkgpu::dbuf out_keys, out_fv, out_offs, out_branch, out_score, out_cnt;

@@ -145,6 +145,9 @@ namespace ipkgpu
         uint32_t n_nodes, W, sigma, bits, group_bits, tiles_per_node, nwin;
         float log_threshold;
         int use_tma;
+        const uint32_t* tile_list;    // depth-first kernel: blockIdx.x -> tile index (null: identity)
+        uint32_t* deferred_tiles;     // join kernel: tiles it hands to the depth-first kernel; their number is counter[1]
+        uint32_t pool_cap;            // join kernel: list-pool capacity in elements (<= 65535)
     };
 
     __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
@@ -173,44 +176,16 @@ namespace ipkgpu
         return b + 16;
     }
 
-    template<bool DEBUG>
-    __global__ void __launch_bounds__(ENUM_THREADS)
-    k2_enumerate(const __grid_constant__ enum_args A, const __grid_constant__ enum_program P)
+    /// Common prologue of both enumeration kernels: the tile's ncols*sigma contiguous floats of logp[node][s0..] go to
+    /// `raw` (one 1-D TMA bulk copy when alignment allows), the prefix sums B[n][s0 .. s0+ncols] to `bs`, and every
+    /// column's states are ordered by descending score into sval / sidx (ties by state index).
+    /// Ends WITHOUT a barrier: callers __syncthreads() before reusing `raw` or reading sval.
+    __device__ __forceinline__ void stage_tile(const enum_args& A, uint32_t node, uint32_t s0, int ncols, int NCP, float* raw, float* bs,
+                                               float* sval, uint8_t* sidx, unsigned long long* mbar_p)
     {
-        extern __shared__ __align__(128) unsigned char smem_raw[];
-        __shared__ __align__(8) unsigned long long mbar;
-        __shared__ uint32_t s_pos[MAX_K];      // per position: leaf node id | merge begin << 16 | merge end << 24
-        __shared__ uint32_t s_merge[MAX_K];    // per merge: node id | left child id << 8
-
-        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-        const int k = P.k, sigma = int(A.sigma);
-        const uint32_t lslot = A.slot_base + blockIdx.x / A.tiles_per_node;
-        const uint32_t node = A.node_order[lslot];
-        const uint32_t s0 = (blockIdx.x % A.tiles_per_node) * ENUM_THREADS;
-        const int nwin_tile = int(min(uint32_t(ENUM_THREADS), A.nwin - s0));
-        const int ncols = nwin_tile + k - 1;
-        const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
-
-        float* sval = reinterpret_cast<float*>(smem_raw);
-        float* bs = sval + sigma * NCP;
-        float* pt = bs + NCP + 4;
-        const size_t pt_bytes = size_t(6 * k) * ENUM_THREADS * 4, raw_bytes = size_t(NC) * sigma * 4;
-        size_t off = (size_t(sigma) * NCP * 4 + size_t(NCP + 4) * 4 + (pt_bytes > raw_bytes ? pt_bytes : raw_bytes) + 15) & ~size_t(15);
-        unsigned long long* st_keys = reinterpret_cast<unsigned long long*>(smem_raw + off) + warp * STAGE_CAP;
-        off += size_t(ENUM_WARPS) * STAGE_CAP * 8;
-        float* st_scores = reinterpret_cast<float*>(smem_raw + off) + warp * STAGE_CAP;
-        off += size_t(ENUM_WARPS) * STAGE_CAP * 4;
-        uint32_t* st_win = nullptr;
-        if (DEBUG) { st_win = reinterpret_cast<uint32_t*>(smem_raw + off) + warp * STAGE_CAP; off += size_t(ENUM_WARPS) * STAGE_CAP * 4; }
-        uint8_t* sidx = smem_raw + off;
-        float* raw = pt;                                   // aliased: consumed before the per-thread arrays are written
-
-        if (tid < MAX_K)
-        {
-            // lanes sit at different depths of their searches: keep the tree tables where divergent reads are cheap
-            s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
-            s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
-        }
+        const int tid = threadIdx.x;
+        const int sigma = int(A.sigma);
+        unsigned long long& mbar = *mbar_p;
         // ---- stage the tile: ncols*sigma contiguous floats of logp[node][s0..] ------------------------------------
         const float* gsrc = A.logp + (uint64_t(node) * A.W + s0) * sigma;
         const uint32_t tile_bytes = uint32_t(ncols) * sigma * 4;
@@ -280,6 +255,48 @@ namespace ipkgpu
                 }
             }
         }
+    }
+
+    template<bool DEBUG>
+    __global__ void __launch_bounds__(ENUM_THREADS)
+    k2_enumerate(const __grid_constant__ enum_args A, const __grid_constant__ enum_program P)
+    {
+        extern __shared__ __align__(128) unsigned char smem_raw[];
+        __shared__ __align__(8) unsigned long long mbar;
+        __shared__ uint32_t s_pos[MAX_K];      // per position: leaf node id | merge begin << 16 | merge end << 24
+        __shared__ uint32_t s_merge[MAX_K];    // per merge: node id | left child id << 8
+
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const int k = P.k, sigma = int(A.sigma);
+        const uint32_t tile = A.tile_list ? A.tile_list[blockIdx.x] : blockIdx.x;
+        const uint32_t lslot = A.slot_base + tile / A.tiles_per_node;
+        const uint32_t node = A.node_order[lslot];
+        const uint32_t s0 = (tile % A.tiles_per_node) * ENUM_THREADS;
+        const int nwin_tile = int(min(uint32_t(ENUM_THREADS), A.nwin - s0));
+        const int ncols = nwin_tile + k - 1;
+        const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
+
+        float* sval = reinterpret_cast<float*>(smem_raw);
+        float* bs = sval + sigma * NCP;
+        float* pt = bs + NCP + 4;
+        const size_t pt_bytes = size_t(6 * k) * ENUM_THREADS * 4, raw_bytes = size_t(NC) * sigma * 4;
+        size_t off = (size_t(sigma) * NCP * 4 + size_t(NCP + 4) * 4 + (pt_bytes > raw_bytes ? pt_bytes : raw_bytes) + 15) & ~size_t(15);
+        unsigned long long* st_keys = reinterpret_cast<unsigned long long*>(smem_raw + off) + warp * STAGE_CAP;
+        off += size_t(ENUM_WARPS) * STAGE_CAP * 8;
+        float* st_scores = reinterpret_cast<float*>(smem_raw + off) + warp * STAGE_CAP;
+        off += size_t(ENUM_WARPS) * STAGE_CAP * 4;
+        uint32_t* st_win = nullptr;
+        if (DEBUG) { st_win = reinterpret_cast<uint32_t*>(smem_raw + off) + warp * STAGE_CAP; off += size_t(ENUM_WARPS) * STAGE_CAP * 4; }
+        uint8_t* sidx = smem_raw + off;
+        float* raw = pt;                                   // aliased: consumed before the per-thread arrays are written
+
+        if (tid < MAX_K)
+        {
+            // lanes sit at different depths of their searches: keep the tree tables where divergent reads are cheap
+            s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
+            s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
+        }
+        stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar);
         __syncthreads();      // raw fully consumed; pt may now be written
 
         // ---- per-thread tables (index-major in shared memory) ------------------------------------------------------

@@ -7,6 +7,7 @@
 // There is no CPU fallback anywhere in this file: every stage is a kernel from the .cuh files next to it.
 #include "common.cuh"
 #include "enumerate.cuh"
+#include "join.cuh"
 #include "radix_sort.cuh"
 #include "merge.cuh"
 #include "filter.cuh"
@@ -148,7 +149,19 @@ namespace
         bool debug = false;
     };
 
-    /// K2 over a range of launch slots.  counters[0] must have been zeroed; node_counts zeroed by the caller if used.
+    uint64_t read_u64(ipkgpu_ctx* ctx, const void* d);
+
+    /// default list-pool capacity of the join kernel (elements of 8 bytes): DNA-sized alphabets keep three CTAs per SM,
+    /// larger alphabets get most of the SM's shared memory
+    uint32_t default_pool_cap(const ipkgpu_input* in)
+    {
+        const uint32_t want = in->sigma <= 4 ? 6144u : 20000u;
+        return std::max(want, join_min_pool(int(in->k), int(in->sigma)));
+    }
+
+    /// K2 over a range of launch slots: the list-join kernel, then the depth-first kernel on the tiles it deferred
+    /// (every tile when k == 1 or ctx->enum_mode == 1).  counters[0] must have been zeroed; node_counts zeroed by the
+    /// caller if used.  Blocks until the join kernel's deferred count is known.
     void launch_enumerate(ipkgpu_ctx* ctx, const float* d_logp, const ipkgpu_input* in, const enum_program& P, const enum_launch& L,
                           bool with_node_counts)
     {
@@ -177,19 +190,55 @@ namespace
         A.use_tma = ((in->sigma * 4) % 16 == 0) && ((reinterpret_cast<uintptr_t>(d_logp) & 15) == 0);
         const uint64_t grid = uint64_t(L.slot_end - L.slot_begin) * A.tiles_per_node;
         if (grid > 0x7fffffffull) fail(IPKGPU_EINVAL, "enumeration grid of %llu tiles is too large", (unsigned long long)grid);
-        const size_t smem = enum_smem_bytes(int(in->k), int(in->sigma), L.debug);
-        // algorithmic bytes: the posterior columns and prefix sums of the launched nodes; the emitted records are added by
-        // the caller once the count is known (kprof_add_bytes)
+        // algorithmic bytes: the posterior columns and prefix sums of the launched nodes; the emitted records are added
+        // once their number is known (kprof_add_bytes)
         const uint64_t in_bytes = uint64_t(L.slot_end - L.slot_begin) * (uint64_t(in->width) * in->sigma + in->width + 1) * 4;
+
+        uint64_t n_deferred = grid;
+        ctx->enum_join_emitted = 0;
+        const bool use_join = in->k >= 2 && ctx->enum_mode != 1;
+        if (use_join)
+        {
+            const join_program J = make_join_program(int(in->k));
+            A.pool_cap = std::min<uint32_t>(65000u, std::max(ctx->pool_cap ? ctx->pool_cap : default_pool_cap(in), join_min_pool(int(in->k), int(in->sigma))));
+            ctx->reserve(ctx->deferred, grid * 4);
+            A.deferred_tiles = ctx->deferred.as<uint32_t>();
+            IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
+            const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap, L.debug).total;
+            if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
+            if (L.debug)
+            {
+                IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+                IPK_LAUNCH(ctx, "k2_join", in_bytes, k2_join<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+            }
+            else
+            {
+                IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+                IPK_LAUNCH(ctx, "k2_join", in_bytes, k2_join<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+            }
+            uint64_t h[2] = { 0, 0 };
+            IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+            ctx->kprof_add_bytes("k2_join", 12 * std::min<uint64_t>(h[0], L.cap));
+            n_deferred = h[1];
+            ctx->enum_join_emitted = h[0];
+            ctx->last_deferred_tiles += n_deferred;
+            ctx->last_tiles += grid;
+            A.tile_list = ctx->deferred.as<uint32_t>();
+        }
+        if (!use_join) { ctx->last_deferred_tiles += grid; ctx->last_tiles += grid; }
+        if (n_deferred == 0) return;
+        const size_t smem = enum_smem_bytes(int(in->k), int(in->sigma), L.debug);
+        const uint64_t dfs_in_bytes = use_join ? n_deferred * uint64_t(ENUM_THREADS + in->k) * (in->sigma + 1) * 4 : in_bytes;
         if (L.debug)
         {
             IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            IPK_LAUNCH(ctx, "k2_enumerate", in_bytes, k2_enumerate<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P));
+            IPK_LAUNCH(ctx, "k2_enumerate", dfs_in_bytes, k2_enumerate<true><<<uint32_t(n_deferred), ENUM_THREADS, smem, ctx->stream>>>(A, P));
         }
         else
         {
             IPK_CUDA(cudaFuncSetAttribute(k2_enumerate<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            IPK_LAUNCH(ctx, "k2_enumerate", in_bytes, k2_enumerate<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P));
+            IPK_LAUNCH(ctx, "k2_enumerate", dfs_in_bytes, k2_enumerate<false><<<uint32_t(n_deferred), ENUM_THREADS, smem, ctx->stream>>>(A, P));
         }
     }
 
@@ -314,7 +363,7 @@ namespace
         launch_enumerate(ctx, d_logp, in, P, L, true);
         o.enum_launches = 1;
         o.n_emitted = read_u64(ctx, ctx->counters.p);
-        ctx->kprof_add_bytes("k2_enumerate", 12 * std::min(o.n_emitted, cap0));
+        ctx->kprof_add_bytes("k2_enumerate", 12 * (std::min(o.n_emitted, cap0) - std::min(ctx->enum_join_emitted, cap0)));
         ctx->hint_emitted = o.n_emitted;
         bool first_valid = o.n_emitted <= cap0;
         if (first_valid) batches.push_back({ 0, o.n_groups, o.n_emitted });
@@ -361,7 +410,6 @@ namespace
                 enum_launch Lb{ T.group_first_slot[b.g0], T.group_first_slot[b.g1], group_base + b.g0, bbits, b.n,
                                 ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
                 launch_enumerate(ctx, d_logp, in, P, Lb, false);
-                ctx->kprof_add_bytes("k2_enumerate", 12 * b.n);
                 o.enum_launches++;
             }
             else if (!timed_first) { ea = e1; timed_first = true; }
@@ -528,6 +576,7 @@ namespace
             if (!ctx) return IPKGPU_EINVAL;
             IPK_CUDA(cudaSetDevice(ctx->device));
             ctx->launches = 0;
+            ctx->last_tiles = ctx->last_deferred_tiles = 0;
             ctx->kprof_marks.clear();
             f();
             ctx->kprof_collect();
@@ -601,7 +650,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     ipkgpu::dbuf* all[] = { &ctx->logp, &ctx->colmax, &ctx->bestpref, &ctx->node_group, &ctx->node_order, &ctx->group_branch, &ctx->counters,
                             &ctx->node_counts, &ctx->keys_a, &ctx->keys_b, &ctx->vals_a, &ctx->vals_b, &ctx->hist, &ctx->scan_tmp,
-                            &ctx->block_counts, &ctx->block_offs, &ctx->dbg_node, &ctx->dbg_win, &ctx->u_keys, &ctx->u_scores,
+                            &ctx->block_counts, &ctx->block_offs, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt };
@@ -615,6 +664,14 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
 
 const char* ipkgpu_last_error(const ipkgpu_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
 void* ipkgpu_stream(const ipkgpu_ctx* ctx) { return ctx ? static_cast<void*>(ctx->stream) : nullptr; }
+
+int ipkgpu_set_enumeration(ipkgpu_ctx* ctx, int mode, uint32_t pool_cap)
+{
+    if (!ctx || mode < 0 || mode > 1 || pool_cap > 65000u) return IPKGPU_EINVAL;
+    ctx->enum_mode = mode;
+    ctx->pool_cap = pool_cap;
+    return IPKGPU_OK;
+}
 
 int ipkgpu_kernel_profile(ipkgpu_ctx* ctx, int enable)
 {
@@ -669,6 +726,7 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
         st.ms_total = tm.ms(t0, t1);
         st.kernel_launches = ctx->launches;
+        st.n_tiles = ctx->last_tiles; st.n_deferred_tiles = ctx->last_deferred_tiles;
     });
 }
 
@@ -749,6 +807,7 @@ int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, 
         st.ms_h2d = s1.ms_h2d; st.ms_prefix = s1.ms_prefix; st.ms_enumerate = s1.ms_enumerate; st.ms_sort = s1.ms_sort; st.ms_merge = s1.ms_merge;
         st.ms_total = tm.ms(t0, t1);
         st.kernel_launches = ctx->launches;
+        st.n_tiles = ctx->last_tiles; st.n_deferred_tiles = ctx->last_deferred_tiles;
         if (stats) *stats = st;
     });
 }

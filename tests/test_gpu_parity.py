@@ -57,8 +57,21 @@ ENUM_CASES = [
 ]
 
 
+# enumeration strategies (include/ipkgpu.h: ipkgpu_set_enumeration): the list-join kernel with its default pool, the
+# depth-first kernel alone, and the join kernel with a pool so small that many tiles are deferred to the depth-first one
+ENUM_MODES = {"join": (0, 0), "dfs": (1, 0), "join_tiny_pool": (0, 1)}
+
+
+@pytest.fixture(params=list(ENUM_MODES))
+def mode(request, ctx):
+    m, pool = ENUM_MODES[request.param]
+    ctx.set_enumeration(m, pool)
+    yield request.param
+    ctx.set_enumeration(0, 0)
+
+
 @pytest.mark.parametrize("sigma,bits,k,omega,W,n_nodes", ENUM_CASES)
-def test_enumerate_per_window(ctx, sigma, bits, k, omega, W, n_nodes):
+def test_enumerate_per_window(ctx, mode, sigma, bits, k, omega, W, n_nodes):
     """every (node, window, k-mer, score) the reference's DCLA emits, bit-exact scores"""
     rng = np.random.default_rng(100 * k + sigma + W)
     logp = _rand_posteriors(rng, n_nodes, W, sigma, peaked=0.85 if k > 8 or sigma == 20 else 0.6)
@@ -97,7 +110,7 @@ BUILD_CASES = [
 
 @pytest.mark.parametrize("name,n_taxa,W,sigma,bits,k,omega", BUILD_CASES)
 @pytest.mark.parametrize("filt", [0, 1])
-def test_build_matches_oracle(ctx, name, n_taxa, W, sigma, bits, k, omega, filt):
+def test_build_matches_oracle(ctx, mode, name, n_taxa, W, sigma, bits, k, omega, filt):
     logp, nb = _synth(n_taxa, W, sigma)
     thr, lthr = _thr(omega, sigma, k)
     T = 2 * n_taxa - 1
@@ -105,6 +118,10 @@ def test_build_matches_oracle(ctx, name, n_taxa, W, sigma, bits, k, omega, filt)
     got = ctx.build(logp, nb, W, sigma, bits, k, lthr, thr, T, filt)
     assert got.stats["n_emitted"] == want.n_emitted
     assert_db_equal(got, want, exact_fv=(filt == 1))
+    if mode == "dfs":
+        assert got.stats["n_deferred_tiles"] == got.stats["n_tiles"] > 0
+    elif mode == "join" and sigma == 4:
+        assert got.stats["n_deferred_tiles"] < got.stats["n_tiles"]       # the fast path really ran
 
 
 def test_build_interleaved_groups_and_singletons(ctx):
@@ -157,3 +174,53 @@ def test_invalid_arguments(ctx):
         ctx.build(logp, nb, 50, 4, 1, 8, -1.0, 0.1, 7, 0)         # 1 bit cannot encode 4 states
     with pytest.raises(IpkGpuError):
         ctx.build(logp, nb, 50, 4, 2, 8, -1.0, 0.1, 7, 7)         # unknown filter
+
+
+import glob
+import os
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "enum_*.npz"))), ids=lambda p: os.path.basename(p)[:-4])
+def test_enumerate_matches_reference_fixture(ctx, mode, path):
+    """the committed fixtures were produced by the reference's own object code (tests/golden/make_golden.py)"""
+    import hashlib
+    f = np.load(path)
+    logp, sigma, bits, k, W = f["logp"], int(f["sigma"]), int(f["bits"]), int(f["k"]), int(f["W"])
+    nb = np.arange(logp.shape[0], dtype=np.uint32)
+    n_total, gn, gw, gk, gs = ctx.enumerate(logp, nb, W, sigma, bits, k, float(f["log_threshold"]), max(int(f["n_records"]), 1))
+    assert n_total == int(f["n_records"])
+    gn, gw, gk, gs = O.canonical_windows(gn, gw, gk, gs)
+    h = hashlib.sha256()
+    h.update(gn.astype("<u4").tobytes()); h.update(gw.astype("<u4").tobytes())
+    h.update(gk.astype("<u8").tobytes()); h.update(gs.view(np.uint32).astype("<u4").tobytes())
+    assert h.hexdigest() == str(f["sha256"])
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "build_*.npz"))), ids=lambda p: os.path.basename(p)[:-4])
+def test_build_matches_reference_fixture(ctx, mode, path):
+    f = np.load(path)
+    got = ctx.build(f["logp"], f["node_branch"], int(f["W"]), int(f["sigma"]), int(f["bits"]), int(f["k"]), float(f["log_threshold"]),
+                    float(f["threshold"]), int(f["total_num_groups"]), 0)
+    assert got.stats["n_emitted"] == int(f["n_emitted"])
+    ek, eb, es = O.db_entries(got)
+    assert np.array_equal(ek, f["entry_key"]) and np.array_equal(eb, f["entry_branch"])
+    assert np.array_equal(es.view(np.uint32), f["entry_score"].view(np.uint32))
+    o = np.argsort(got.keys, kind="stable")
+    np.testing.assert_allclose(got.fv[o], f["kmer_fv"], rtol=2e-5, atol=1e-12)
+    assert np.array_equal(got.offsets[-1:], f["offsets"][-1:])
+
+
+@pytest.mark.parametrize("name", ["cfg2_dna_1k", "cfg3_16s_10k", "cfg5_viral", "cfg4_aa_2k", "cfg1_d652_k7"])
+def test_workload_sample_matches_oracle(ctx, mode, name):
+    """a few branch groups of each BASELINE workload at its real width (calibrated, sharply peaked posteriors)"""
+    from ipk_b200 import synth
+    w = synth.WORKLOADS[name]
+    nbr = 3 if w.width < 5000 else 1
+    logp, nb = synth.posteriors(w.n_taxa, w.width, w.sigma, seed=42, branch_begin=50, branch_end=50 + nbr)
+    thr, lthr = _thr(w.omega, w.sigma, w.k)
+    want = O.build(logp, nb, w.width, w.sigma, w.bits, w.k, lthr, thr, w.n_tree_nodes, 0, 8)
+    got = ctx.build(logp, nb, w.width, w.sigma, w.bits, w.k, lthr, thr, w.n_tree_nodes, 0)
+    assert got.stats["n_emitted"] == want.n_emitted
+    assert_db_equal(got, want)
