@@ -8,36 +8,64 @@
 
 namespace ipkgpu
 {
-    /// filter.cpp:20-23: std::min(std::pow(10, log_score), 1.0) evaluated in double, returned as score_type (float)
+    /// filter.cpp:20-23: std::min(std::pow(10, log_score), 1.0) evaluated in double, returned as score_type (float).
+    /// exp10 (<= 1 ulp in fp64) stands in for pow(10, x); after the rounding to float the two agree (FV_RTOL covers the rest).
     __device__ __forceinline__ float logscore_to_score(float log_score)
     {
-        const double p = pow(10.0, double(log_score));
+        const double p = exp10(double(log_score));
         return float(p < 1.0 ? p : 1.0);
     }
     __device__ __forceinline__ double shannon(double x) { return -x * log2(x); }    // filter.cpp:55-58
 
-    /// One thread per k-mer; entries are visited in stored (group processing) order, as filter.cpp:78-82,101-108 does,
-    /// so the fp64 accumulation order is the reference's.
-    __global__ void k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores, uint64_t n_kmers,
-                            uint32_t total_num_groups, float threshold, float* __restrict__ fv)
+    __device__ __forceinline__ double shfl_f64(unsigned mask, double v, int src, int width)
     {
-        const uint64_t q = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
-        if (q >= n_kmers) return;
+        int lo = __double2loint(v), hi = __double2hiint(v);
+        lo = __shfl_sync(mask, lo, src, width);
+        hi = __shfl_sync(mask, hi, src, width);
+        return __hiloint2double(hi, lo);
+    }
+
+    /// G lanes per k-mer (G = 1, 4, 8 or 32, chosen by the host from the mean entries per k-mer).  The transcendental
+    /// work (exp10, log2, the divisions) is spread over the lanes, G entries at a time; the two fp64 running sums are then
+    /// advanced in the reference's order -- entries are visited in stored (group processing) order, as
+    /// filter.cpp:78-82,101-108 does -- by broadcasting the lanes' terms one after the other.
+    template<int G>
+    __global__ void __launch_bounds__(256) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores, uint64_t n_kmers,
+                                                   uint32_t total_num_groups, float threshold, float* __restrict__ fv)
+    {
+        const uint64_t q = (blockIdx.x * uint64_t(blockDim.x) + threadIdx.x) / G;
+        if (q >= n_kmers) return;                                    // whole groups leave together
+        const int gl = int(threadIdx.x) & (G - 1), lane = int(threadIdx.x) & 31;
+        const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
         const uint64_t a = offs[q], b = offs[q + 1];
         double score_sum = 0;
-        for (uint64_t i = a; i < b; ++i) score_sum = __dadd_rn(score_sum, double(logscore_to_score(scores[i])));
+        for (uint64_t base = a; base < b; base += G)
+        {
+            const uint64_t i = base + gl;
+            const float x = i < b ? logscore_to_score(scores[i]) : 0.0f;
+            const int cnt = int(min(uint64_t(G), b - base));
+            if (G == 1) score_sum = __dadd_rn(score_sum, double(x));
+            else for (int j = 0; j < cnt; ++j) score_sum = __dadd_rn(score_sum, double(__shfl_sync(gmask, x, j, G)));
+        }
         score_sum = __dadd_rn(score_sum, __dmul_rn(double(uint64_t(total_num_groups) - (b - a)), double(threshold)));   // :86
         const double weighted_threshold = double(threshold) / score_sum;
         const double target_threshold = shannon(weighted_threshold);
         double HcBw1 = __dmul_rn(double(total_num_groups), target_threshold);                                            // :93
-        for (uint64_t i = a; i < b; ++i)
+        for (uint64_t base = a; base < b; base += G)
         {
-            const double weighted_score = double(logscore_to_score(scores[i])) / score_sum;
-            const double target_value = shannon(weighted_score);
-            HcBw1 = __dadd_rn(__dsub_rn(HcBw1, target_threshold), target_value);                                         // :107
+            const uint64_t i = base + gl;
+            double target_value = 0;
+            if (i < b)
+            {
+                const double weighted_score = double(logscore_to_score(scores[i])) / score_sum;
+                target_value = shannon(weighted_score);
+            }
+            const int cnt = int(min(uint64_t(G), b - base));
+            if (G == 1) HcBw1 = __dadd_rn(__dsub_rn(HcBw1, target_threshold), target_value);                             // :107
+            else for (int j = 0; j < cnt; ++j) HcBw1 = __dadd_rn(__dsub_rn(HcBw1, target_threshold), shfl_f64(gmask, target_value, j, G));
         }
         const double Hc = log2(double(total_num_groups));
-        fv[q] = float(__dmul_rn(score_sum, __dsub_rn(HcBw1, Hc)));                                                       // :115
+        if (gl == 0) fv[q] = float(__dmul_rn(score_sum, __dsub_rn(HcBw1, Hc)));                                          // :115
     }
 
     __device__ __forceinline__ uint64_t mulmod31(uint64_t a, uint64_t b) { return (a * b) % 2147483647ull; }
@@ -87,20 +115,23 @@ namespace ipkgpu
         out_cnt[i] = uint32_t(kmer_offs[src + 1] - kmer_offs[src]);
     }
 
-    /// entries of k-mer perm[i] move to [out_offs32[i], +cnt); also widens the offsets to u64 (+ the final sentinel)
-    __global__ void k6_gather_entries(const uint32_t* __restrict__ perm, const uint64_t* __restrict__ kmer_offs,
-                                      const uint32_t* __restrict__ out_offs32, uint64_t n, uint64_t n_entries,
-                                      const uint32_t* __restrict__ ent_branch, const float* __restrict__ ent_score,
-                                      uint64_t* __restrict__ out_offs, uint32_t* __restrict__ out_branch, float* __restrict__ out_score)
+    /// entries of k-mer perm[i] move to [out_offs32[i], +cnt), G lanes per k-mer; also widens the offsets to u64 (+ the final sentinel)
+    template<int G>
+    __global__ void __launch_bounds__(256) k6_gather_entries(const uint32_t* __restrict__ perm, const uint64_t* __restrict__ kmer_offs,
+                                                             const uint32_t* __restrict__ out_offs32, uint64_t n, uint64_t n_entries,
+                                                             const uint32_t* __restrict__ ent_branch, const float* __restrict__ ent_score,
+                                                             uint64_t* __restrict__ out_offs, uint32_t* __restrict__ out_branch, float* __restrict__ out_score)
     {
-        const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
-        if (i == 0) out_offs[n] = n_entries;
+        const uint64_t t = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        const uint64_t i = t / G;
+        const int gl = int(threadIdx.x) & (G - 1);
+        if (t == 0) out_offs[n] = n_entries;
         if (i >= n) return;
         const uint32_t src = perm[i];
         const uint64_t a = kmer_offs[src], cnt = kmer_offs[src + 1] - a;
         const uint64_t o = out_offs32[i];
-        out_offs[i] = o;
-        for (uint64_t j = 0; j < cnt; ++j)
+        if (gl == 0) out_offs[i] = o;
+        for (uint64_t j = gl; j < cnt; j += G)
         {
             out_branch[o + j] = ent_branch[a + j];
             out_score[o + j] = ent_score[a + j];

@@ -204,7 +204,7 @@ namespace
             ctx->reserve(ctx->deferred, grid * 4);
             A.deferred_tiles = ctx->deferred.as<uint32_t>();
             IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
-            const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap, L.debug).total;
+            const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
             if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
             if (L.debug)
             {
@@ -449,6 +449,13 @@ namespace
         int32_t filter;
     };
 
+    /// lanes that share one k-mer in K4 / K6: short entry lists keep one thread per k-mer, long ones get a lane group
+    int lanes_per_kmer(uint64_t n_kmers, uint64_t n_entries)
+    {
+        const double avg = n_kmers ? double(n_entries) / double(n_kmers) : 0.0;
+        return avg < 2.0 ? 1 : avg < 8.0 ? 4 : avg < 512.0 ? 8 : 32;
+    }
+
     /// K4 -> K5 -> K6 on the CSR in ctx (kmer_keys / kmer_offs / ent_branch / ent_score) and hand-over of the result.
     void finish_from_csr(ipkgpu_ctx* ctx, uint64_t n_kmers, uint64_t n_entries, const stage2_params& sp, int result_on_device,
                          ipkgpu_result* out, stage_timer& tm)
@@ -469,9 +476,14 @@ namespace
             const uint32_t grid = uint32_t(div_up<uint64_t>(n_kmers, 256));
             if (sp.filter == IPKGPU_FILTER_MIF0)
             {
-                IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,
-                           k4_mif0<<<grid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers,
-                                                                  sp.total_num_groups, sp.threshold, ctx->fv.as<float>()));
+                // lanes per k-mer, from the mean number of entries per k-mer
+                const int G = lanes_per_kmer(n_kmers, n_entries);
+                const uint32_t ggrid = uint32_t(div_up<uint64_t>(n_kmers * uint64_t(G), 256));
+#define IPK_MIF0(G_) IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,                                                          \
+                                k4_mif0<G_><<<ggrid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers, \
+                                                                            sp.total_num_groups, sp.threshold, ctx->fv.as<float>()))
+                if (G == 1) IPK_MIF0(1); else if (G == 4) IPK_MIF0(4); else if (G == 8) IPK_MIF0(8); else IPK_MIF0(32);
+#undef IPK_MIF0
             }
             else
             {
@@ -491,10 +503,16 @@ namespace
                        k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
                                                                       n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>()));
             exclusive_scan_u32(ctx, ctx->out_cnt.as<uint32_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, ctx->scan_tmp);
-            IPK_LAUNCH(ctx, "k6_gather_entries", n_kmers * 32 + n_entries * 16,
-                       k6_gather_entries<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, n_entries,
-                                                                        ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>(),
-                                                                        ctx->out_offs.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>()));
+            {
+                const int G = lanes_per_kmer(n_kmers, n_entries);
+                const uint32_t ggrid = uint32_t(div_up<uint64_t>(n_kmers * uint64_t(G), 256));
+#define IPK_GATHER(G_) IPK_LAUNCH(ctx, "k6_gather_entries", n_kmers * 32 + n_entries * 16,                                                  \
+                                  k6_gather_entries<G_><<<ggrid, 256, 0, ctx->stream>>>(perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_cnt.as<uint32_t>(), \
+                                      n_kmers, n_entries, ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>(),                     \
+                                      ctx->out_offs.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>()))
+                if (G == 1) IPK_GATHER(1); else if (G == 4) IPK_GATHER(4); else if (G == 8) IPK_GATHER(8); else IPK_GATHER(32);
+#undef IPK_GATHER
+            }
             e2 = tm.mark();
         }
         else

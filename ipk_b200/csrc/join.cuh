@@ -96,61 +96,143 @@ namespace ipkgpu
         return J;
     }
 
+
     // ----------------------------------------------------------------------------------------------------------
     // shared-memory layout of k2_join (NC = ENUM_THREADS + k - 1 local columns, NCP = NC rounded up to 4):
+    //   pool  u64 [pool_cap]            list elements: fp32 score bits << 32 | key   (the raw TMA-staged tile aliases its start)
     //   sval  f32 [sigma][NCP]          column states' scores, descending
     //   bs    f32 [NCP+4]               B[n][s0 .. s0+NC]
     //   eps   f32 [2k][ENUM_THREADS]    eps of every tree node for every window of the tile (index-major)
+    //   gthr  f32 [NCP]                 g_h(c) of the family being built
+    //   wbase u32 [ENUM_THREADS+1]      exclusive scan of the windows' output counts
+    //   rbase u32 [ENUM_THREADS+1]      exclusive scan of the windows' row counts (rows = left elements with a non-empty row)
     //   fcnt  u16 [n_fam][NCP]          length of G_h(c)
     //   foff  u16 [n_fam][NCP]          its start in the pool
-    //   gthr  f32 [NCP]                 g_h(c) of the family being built
-    //   pool_score f32 [pool_cap], pool_key u32 [pool_cap]     (the raw TMA-staged tile aliases the pool's start)
-    //   stage keys u64 [ENUM_WARPS][STAGE_CAP], scores f32 [...], (DEBUG: win u32 [...])
-    //   sidx  u8 [sigma][NCP]
+    //   wnr   u16 [ENUM_THREADS]        |L_right(s)|
+    //   queue u16 [NCP]                 columns whose list is built by a whole warp (long lists)
+    //   sidx  u8  [sigma][NCP]
     // ----------------------------------------------------------------------------------------------------------
     struct join_layout
     {
-        size_t sval, bs, eps, fcnt, foff, gthr, pool_score, pool_key, st_keys, st_scores, st_win, sidx, total;
+        size_t pool, sval, bs, eps, gthr, wbase, rbase, fcnt, foff, wnr, queue, sidx, total;
     };
 
-    __host__ __device__ inline join_layout make_join_layout(int k, int sigma, int n_fam, uint32_t pool_cap, bool debug)
+    __host__ __device__ inline join_layout make_join_layout(int k, int sigma, int n_fam, uint32_t pool_cap)
     {
         const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
         join_layout L;
         size_t b = 0;
+        L.pool = b; b += size_t(pool_cap) * 8;
         L.sval = b; b += size_t(sigma) * NCP * 4;
         L.bs = b; b += size_t(NCP + 4) * 4;
         L.eps = b; b += size_t(2 * k) * ENUM_THREADS * 4;
+        L.gthr = b; b += size_t(NCP) * 4;
+        L.wbase = b; b += size_t(ENUM_THREADS + 1) * 4;
+        L.rbase = b; b += size_t(ENUM_THREADS + 1) * 4;
         L.fcnt = b; b += size_t(n_fam) * NCP * 2;
         L.foff = b; b += size_t(n_fam) * NCP * 2;
-        b = (b + 3) & ~size_t(3);
-        L.gthr = b; b += size_t(NCP) * 4;
-        b = (b + 15) & ~size_t(15);
-        L.pool_score = b; b += size_t(pool_cap) * 4;
-        L.pool_key = b; b += size_t(pool_cap) * 4;
-        b = (b + 15) & ~size_t(15);
-        L.st_keys = b; b += size_t(ENUM_WARPS) * STAGE_CAP * 8;
-        L.st_scores = b; b += size_t(ENUM_WARPS) * STAGE_CAP * 4;
-        L.st_win = b; if (debug) b += size_t(ENUM_WARPS) * STAGE_CAP * 4;
+        L.wnr = b; b += size_t(ENUM_THREADS) * 2;
+        L.queue = b; b += size_t(NCP) * 2;
         L.sidx = b; b += size_t(sigma) * NCP;
-        L.total = b + 16;
+        L.total = ((b + 15) & ~size_t(15)) + 16;
         return L;
     }
 
     /// smallest pool the raw tile fits in (it is staged over the pool's start before any list exists)
     inline uint32_t join_min_pool(int k, int sigma) { return uint32_t((size_t(ENUM_THREADS + k - 1) * sigma * 4 + 7) / 8 + 16); }
 
-    /// insertion sort of one list by descending score (lists are short; the owner thread sorts its own list)
-    __device__ __forceinline__ void sort_list_desc(float* ps, uint32_t* pk, int n)
+    constexpr int JOIN_SMALL_LIST = 24;      // lists up to this length are filled and insertion-sorted by their owner thread
+
+    __device__ __forceinline__ unsigned long long el_pack(float s, uint32_t key) { return (unsigned long long)__float_as_uint(s) << 32 | key; }
+    __device__ __forceinline__ float el_score(unsigned long long e) { return __uint_as_float(uint32_t(e >> 32)); }
+    __device__ __forceinline__ uint32_t el_key(unsigned long long e) { return uint32_t(e); }
+
+    /// insertion sort of one list by descending score (short lists; the owner thread sorts its own list)
+    __device__ __forceinline__ void sort_list_desc(unsigned long long* p, int n)
     {
         for (int a = 1; a < n; ++a)
         {
-            const float s = ps[a];
-            const uint32_t kk = pk[a];
+            const unsigned long long e = p[a];
+            const float s = el_score(e);
             int b = a;
-            while (b > 0 && ps[b - 1] < s) { ps[b] = ps[b - 1]; pk[b] = pk[b - 1]; --b; }
-            ps[b] = s; pk[b] = kk;
+            while (b > 0 && el_score(p[b - 1]) < s) { p[b] = p[b - 1]; --b; }
+            p[b] = e;
         }
+    }
+
+    /// One warp sorts p[0..n) by descending score in shared memory: bitonic network in its mirrored form (every
+    /// comparison moves the larger element to the lower index), so the virtual -inf padding above n never moves.
+    __device__ __forceinline__ void warp_sort_desc(unsigned long long* p, int n, int lane)
+    {
+        int pw = 1;
+        while (pw < n) pw <<= 1;
+        const int half = pw >> 1;
+        for (int size = 2; size <= pw; size <<= 1)
+        {
+            const int hs = size >> 1;
+            for (int t = lane; t < half; t += 32)
+            {
+                const int blk = t / hs, j = t - blk * hs;
+                const int lo = blk * size + j, hi = blk * size + size - 1 - j;
+                if (hi < n)
+                {
+                    const unsigned long long a = p[lo], b = p[hi];
+                    if (el_score(b) > el_score(a)) { p[lo] = b; p[hi] = a; }
+                }
+            }
+            __syncwarp();
+            for (int d = hs >> 1; d >= 1; d >>= 1)
+            {
+                for (int t = lane; t < half; t += 32)
+                {
+                    const int lo = (t / d) * 2 * d + (t % d), hi = lo + d;
+                    if (hi < n)
+                    {
+                        const unsigned long long a = p[lo], b = p[hi];
+                        if (el_score(b) > el_score(a)) { p[lo] = b; p[hi] = a; }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+
+    /// number of leading elements b of the descending list q[0..n) with fl(sa + S(b)) > thr  (fp32 addition is monotone,
+    /// so they form a prefix)
+    __device__ __forceinline__ int row_length(const unsigned long long* q, int n, float sa, float thr)
+    {
+        int lo = 0, hi = n;                     // invariant: elements < lo pass, elements >= hi fail
+        while (lo < hi)
+        {
+            const int mid = (lo + hi) >> 1;
+            if (__fadd_rn(sa, el_score(q[mid])) > thr) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+    }
+
+    __device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v, int lane)
+    {
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += t;
+        }
+        return v;
+    }
+
+    /// lane that owns output o of a batch: the last lane whose exclusive offset is <= o (incl = inclusive scan of the
+    /// per-lane row lengths; rows of length 0 are skipped automatically)
+    __device__ __forceinline__ int owner_lane(uint32_t incl, uint32_t o)
+    {
+        int lo = 0;                              // first lane with incl > o
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1)
+        {
+            const uint32_t v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+            if (v <= o) lo += step;
+        }
+        return lo;
     }
 
     /// The predicate itself for the subtree of h leaves that starts at window offset o, for window t of the
@@ -187,15 +269,29 @@ namespace ipkgpu
         return true;
     }
 
+    /// first index of the descending list p[0..n) whose score is NOT > thr  (= number of elements above thr)
+    __device__ __forceinline__ int cut_above(const unsigned long long* p, int n, float thr)
+    {
+        int lo = 0, hi = n;
+        while (lo < hi)
+        {
+            const int mid = (lo + hi) >> 1;
+            if (el_score(p[mid]) > thr) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+    }
+
     template<bool DEBUG>
     __global__ void __launch_bounds__(ENUM_THREADS)
     k2_join(const __grid_constant__ enum_args A, const __grid_constant__ enum_program P, const __grid_constant__ join_program J)
     {
         extern __shared__ __align__(128) unsigned char smem_raw[];
         __shared__ __align__(8) unsigned long long mbar;
+        __shared__ unsigned long long s_base;
         __shared__ uint32_t s_pos[MAX_K];
         __shared__ uint32_t s_merge[MAX_K];
-        __shared__ uint32_t s_pool_used, s_defer;
+        __shared__ uint32_t s_pool_used, s_defer, s_qn[2];
+        __shared__ uint32_t s_wsum[2][ENUM_WARPS];
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma), bits = int(A.bits);
@@ -206,28 +302,28 @@ namespace ipkgpu
         const int nwin_tile = int(min(uint32_t(ENUM_THREADS), A.nwin - s0));
         const int ncols = nwin_tile + k - 1;
         const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
-        const join_layout L = make_join_layout(k, sigma, J.n_fam, A.pool_cap, DEBUG);
+        const join_layout L = make_join_layout(k, sigma, J.n_fam, A.pool_cap);
 
+        unsigned long long* pool = reinterpret_cast<unsigned long long*>(smem_raw + L.pool);
         float* sval = reinterpret_cast<float*>(smem_raw + L.sval);
         float* bs = reinterpret_cast<float*>(smem_raw + L.bs);
         float* eps = reinterpret_cast<float*>(smem_raw + L.eps);
+        float* gthr = reinterpret_cast<float*>(smem_raw + L.gthr);
+        uint32_t* wbase = reinterpret_cast<uint32_t*>(smem_raw + L.wbase);
+        uint32_t* rbase = reinterpret_cast<uint32_t*>(smem_raw + L.rbase);
         uint16_t* fcnt = reinterpret_cast<uint16_t*>(smem_raw + L.fcnt);
         uint16_t* foff = reinterpret_cast<uint16_t*>(smem_raw + L.foff);
-        float* gthr = reinterpret_cast<float*>(smem_raw + L.gthr);
-        float* pool_s = reinterpret_cast<float*>(smem_raw + L.pool_score);
-        uint32_t* pool_k = reinterpret_cast<uint32_t*>(smem_raw + L.pool_key);
-        unsigned long long* st_keys = reinterpret_cast<unsigned long long*>(smem_raw + L.st_keys) + warp * STAGE_CAP;
-        float* st_scores = reinterpret_cast<float*>(smem_raw + L.st_scores) + warp * STAGE_CAP;
-        uint32_t* st_win = DEBUG ? reinterpret_cast<uint32_t*>(smem_raw + L.st_win) + warp * STAGE_CAP : nullptr;
+        uint16_t* wnr = reinterpret_cast<uint16_t*>(smem_raw + L.wnr);
+        uint16_t* queue = reinterpret_cast<uint16_t*>(smem_raw + L.queue);
         uint8_t* sidx = smem_raw + L.sidx;
-        float* raw = pool_s;                               // the staged tile is consumed before the first list is written
+        float* raw = reinterpret_cast<float*>(pool);         // the staged tile is consumed before the first list is written
 
         if (tid < MAX_K)
         {
             s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
             s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
         }
-        if (tid == 0) { s_pool_used = 0; s_defer = 0; }
+        if (tid == 0) { s_pool_used = 0; s_defer = 0; s_qn[0] = 0; s_qn[1] = 0; }
         stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar);
 
         // ---- eps of every tree node for this thread's window (pk_compute.cpp:54-55; window.cpp:69-72) ---------------
@@ -249,7 +345,6 @@ namespace ipkgpu
         }
         __syncthreads();                                   // raw consumed, sval / eps complete
 
-
         // ---- G_h(c) for every family, shortest first -----------------------------------------------------------------
         const unsigned full = 0xffffffffu;
         for (int f = 0; f < J.n_fam; ++f)
@@ -259,7 +354,9 @@ namespace ipkgpu
             const int nlist = ncols - h + 1;
             uint16_t* cnt_f = fcnt + f * NCP;
             uint16_t* off_f = foff + f * NCP;
-            // pass 1: g_h(c) and the length of G_h(c)
+            if (tid == 0) s_qn[(f + 1) & 1] = 0;              // the other family's queue counter: last read before the previous barrier
+            // phase A, one thread per column: threshold, exact length (two-pointer walk over the staircase), and -- for
+            // short lists -- allocation, fill and sort.  Long lists are queued for phase B.
             for (int c = tid; c < nlist; c += ENUM_THREADS)
             {
                 float g = __int_as_float(0x7f800000);      // +inf: no window of this tile has a length-h node at column c
@@ -269,80 +366,116 @@ namespace ipkgpu
                     if (t >= 0 && t < nwin_tile) g = fminf(g, eps[int(J.fam[f].use_node[u]) * ENUM_THREADS + t]);
                 }
                 gthr[c] = g;
-                uint32_t n = 0;
+                uint32_t n = 0, off = 0;
                 if (h == 1)
                 {
                     while (n < uint32_t(sigma) && sval[n * NCP + c] > g) ++n;            // as_column (pk_compute.cpp:14-26): strict >
+                    if (n)
+                    {
+                        off = atomicAdd(&s_pool_used, n);
+                        if (off + n > A.pool_cap) s_defer = 1;
+                        else for (uint32_t r = 0; r < n; ++r) pool[off + r] = el_pack(sval[r * NCP + c], sidx[r * NCP + c]);
+                    }
                 }
                 else
                 {
                     const int na = cnt_f[(fa - f) * NCP + c], nb = cnt_f[(fb - f) * NCP + c + hl];
-                    const float* as = pool_s + off_f[(fa - f) * NCP + c];
-                    const float* bsc = pool_s + off_f[(fb - f) * NCP + c + hl];
-                    for (int i = 0; i < na && n <= A.pool_cap; ++i)
+                    const unsigned long long* la = pool + off_f[(fa - f) * NCP + c];
+                    const unsigned long long* lb = pool + off_f[(fb - f) * NCP + c + hl];
+                    int l = nb;
+                    for (int i = 0; i < na && l > 0; ++i)                                // both lists descend: rows only get shorter
                     {
-                        const float sa = as[i];
-                        int l = 0;
-                        while (l < nb && __fadd_rn(sa, bsc[l]) > g) ++l;                 // both lists descend: first failure ends the row
-                        if (l == 0) break;                                               // ... and the first empty row ends the join
-                        n += l;
+                        const float sa = el_score(la[i]);
+                        while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > g)) --l;
+                        n += uint32_t(l);
+                    }
+                    if (n > A.pool_cap) { s_defer = 1; n = 0; }
+                    else if (n > uint32_t(JOIN_SMALL_LIST)) queue[atomicAdd(&s_qn[f & 1], 1u)] = uint16_t(c);
+                    else if (n)
+                    {
+                        off = atomicAdd(&s_pool_used, n);
+                        if (off + n > A.pool_cap) s_defer = 1;
+                        else
+                        {
+                            unsigned long long* os = pool + off;
+                            int w = 0;
+                            l = nb;
+                            for (int i = 0; i < na && l > 0; ++i)
+                            {
+                                const unsigned long long ea = la[i];
+                                const float sa = el_score(ea);
+                                const uint32_t ka = el_key(ea) << (hr * bits);           // prefix = most significant digits (pk_compute.cpp:96-104)
+                                while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > g)) --l;
+                                for (int j = 0; j < l; ++j)
+                                {
+                                    const unsigned long long eb = lb[j];
+                                    os[w++] = el_pack(__fadd_rn(sa, el_score(eb)), ka | el_key(eb));
+                                }
+                            }
+                            sort_list_desc(os, int(n));
+                        }
                     }
                 }
-                cnt_f[c] = uint16_t(min(n, 0xffffu));
+                cnt_f[c] = uint16_t(n);
+                off_f[c] = uint16_t(off);
             }
             __syncthreads();
-            // exclusive scan of the lengths -> pool offsets (warp 0; nlist <= NCP <= 160)
-            if (warp == 0)
+            // phase B, one warp per long list: row lengths by binary search, staircase expanded 32 elements at a time,
+            // bitonic sort in place
+            const int qn = int(s_qn[f & 1]);
+            for (int q = warp; q < qn; q += ENUM_WARPS)
             {
-                const int per = (nlist + 31) / 32;
-                uint32_t sum = 0;
-                for (int i = 0; i < per; ++i) { const int c = lane * per + i; if (c < nlist) sum += cnt_f[c]; }
-                uint32_t inc = sum;
-                for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(full, inc, o); if (lane >= o) inc += v; }
-                uint32_t run = s_pool_used + inc - sum;
-                const uint32_t total = __shfl_sync(full, inc, 31);
-                const bool fits = s_pool_used + total <= A.pool_cap;
-                if (fits)
-                    for (int i = 0; i < per; ++i) { const int c = lane * per + i; if (c < nlist) { off_f[c] = uint16_t(run); run += cnt_f[c]; } }
+                if (__shfl_sync(full, *reinterpret_cast<volatile uint32_t*>(&s_defer), 0)) break;
+                const int c = queue[q];
+                const int n = cnt_f[c];
+                const int na = cnt_f[(fa - f) * NCP + c], nb = cnt_f[(fb - f) * NCP + c + hl];
+                const unsigned long long* la = pool + off_f[(fa - f) * NCP + c];
+                const unsigned long long* lb = pool + off_f[(fb - f) * NCP + c + hl];
+                const float g = gthr[c];
+                uint32_t off = 0;
+                if (lane == 0) off = atomicAdd(&s_pool_used, uint32_t(n));
+                off = __shfl_sync(full, off, 0);
+                if (off + uint32_t(n) > A.pool_cap) { if (lane == 0) s_defer = 1; break; }
+                unsigned long long* os = pool + off;
+                uint32_t carry = 0;
+                for (int i0 = 0; i0 < na; i0 += 32)
+                {
+                    const int i = i0 + lane;
+                    float sa = 0.0f;
+                    uint32_t ka = 0, len = 0;
+                    if (i < na)
+                    {
+                        const unsigned long long ea = la[i];
+                        sa = el_score(ea);
+                        ka = el_key(ea) << (hr * bits);
+                        len = uint32_t(row_length(lb, nb, sa, g));
+                    }
+                    const uint32_t incl = warp_incl_scan_u32(len, lane);
+                    const uint32_t total = __shfl_sync(full, incl, 31);
+                    if (total == 0) break;
+                    const uint32_t excl = incl - len;
+                    for (uint32_t o0 = 0; o0 < total; o0 += 32)
+                    {
+                        const uint32_t o = o0 + lane;
+                        const bool act = o < total;
+                        const int r = owner_lane(incl, act ? o : 0u);
+                        const float sa_r = __shfl_sync(full, sa, r);
+                        const uint32_t ka_r = __shfl_sync(full, ka, r);
+                        const uint32_t ex_r = __shfl_sync(full, excl, r);
+                        if (act)
+                        {
+                            const unsigned long long eb = lb[o - ex_r];
+                            os[carry + o] = el_pack(__fadd_rn(sa_r, el_score(eb)), ka_r | el_key(eb));
+                        }
+                    }
+                    carry += total;
+                }
                 __syncwarp();
-                if (lane == 0) { if (fits) s_pool_used += total; else s_defer = 1; }
+                warp_sort_desc(os, n, lane);
+                if (lane == 0) off_f[c] = uint16_t(off);
             }
             __syncthreads();
             if (s_defer) break;
-            // pass 2: fill and sort
-            for (int c = tid; c < nlist; c += ENUM_THREADS)
-            {
-                const int n = cnt_f[c];
-                if (n == 0) continue;
-                float* os = pool_s + off_f[c];
-                uint32_t* ok = pool_k + off_f[c];
-                if (h == 1)
-                {
-                    for (int r = 0; r < n; ++r) { os[r] = sval[r * NCP + c]; ok[r] = sidx[r * NCP + c]; }
-                }
-                else
-                {
-                    const float g = gthr[c];
-                    const int na = cnt_f[(fa - f) * NCP + c], nb = cnt_f[(fb - f) * NCP + c + hl];
-                    const uint32_t oa = off_f[(fa - f) * NCP + c], ob = off_f[(fb - f) * NCP + c + hl];
-                    int w = 0;
-                    for (int i = 0; i < na; ++i)
-                    {
-                        const float sa = pool_s[oa + i];
-                        const uint32_t ka = pool_k[oa + i] << (hr * bits);               // prefix = most significant digits (pk_compute.cpp:96-104)
-                        int l = 0;
-                        for (; l < nb; ++l)
-                        {
-                            const float S = __fadd_rn(sa, pool_s[ob + l]);
-                            if (!(S > g)) break;
-                            os[w] = S; ok[w] = ka | pool_k[ob + l]; ++w;
-                        }
-                        if (l == 0) break;
-                    }
-                    sort_list_desc(os, ok, n);
-                }
-            }
-            __syncthreads();
         }
         if (s_defer)
         {
@@ -351,34 +484,41 @@ namespace ipkgpu
             return;
         }
 
-
-        // ---- per window: cut L_left(s), L_right(s) out of the two top lists -------------------------------------------
+        // ---- per window: cut L_left(s), L_right(s) out of the two top lists, count the root join ----------------------
         const int hl0 = J.root_hl, hr0 = k - hl0;
-        int nl = 0, nr = 0;
-        uint32_t oa = 0, ob = 0;
+        const int fa0 = J.root_left, fb0 = J.root_right;
+        const float eps0 = A.log_threshold;
+        uint32_t my_out = 0, my_rows = 0;
         bool irregular = false;
         if (has_window)
         {
-            const int fa = J.root_left, fb = J.root_right;
-            const int na = fcnt[fa * NCP + tid], nb = fcnt[fb * NCP + tid + hl0];
-            oa = foff[fa * NCP + tid]; ob = foff[fb * NCP + tid + hl0];
+            const int na = fcnt[fa0 * NCP + tid], nb = fcnt[fb0 * NCP + tid + hl0];
+            const unsigned long long* la = pool + foff[fa0 * NCP + tid];
+            const unsigned long long* lb = pool + foff[fb0 * NCP + tid + hl0];
             const float eps_l = eps[1 * ENUM_THREADS + tid], eps_r = eps[2 * ENUM_THREADS + tid];   // nodes 1, 2 = the root's children
-            while (nl < na)
+            // S(a) > eps_left(s) is exact; the deeper checks of `a` are implied unless S(a) lies within delta of the
+            // threshold -- those few elements (the tail of the cut) are put through the predicate itself
+            const int nl = cut_above(la, na, eps_l);
+            if (hl0 > 1)
+                for (int q = nl - 1; q >= 0 && !(el_score(la[q]) > eps_l + delta); --q)
+                    if (!verify_subtree(el_key(la[q]), 0, hl0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
+            int nr = cut_above(lb, nb, eps_r);
+            if (hr0 > 1 && !irregular)
+                for (int q = nr - 1; q >= 0 && !(el_score(lb[q]) > eps_r + delta); --q)
+                    if (!verify_subtree(el_key(lb[q]), hl0, hr0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
+            // root join (pk_compute.cpp:75-105): row i = the b with fl(S(a_i) + S(b)) > eps, a prefix that only shrinks with i
+            int l = nr;
+            for (int i = 0; i < nl; ++i)
             {
-                const float sa = pool_s[oa + nl];
-                if (!(sa > eps_l)) break;
-                if (hl0 > 1 && !(sa > eps_l + delta) &&
-                    !verify_subtree(pool_k[oa + nl], 0, hl0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
-                ++nl;
+                const float sa = el_score(la[i]);
+                while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > eps0)) --l;
+                if (l == 0) break;
+                if (i == 0) nr = l;                        // no row is longer than the first
+                my_out += uint32_t(l);
+                my_rows = uint32_t(i + 1);
             }
-            while (nr < nb && !irregular)
-            {
-                const float sb = pool_s[ob + nr];
-                if (!(sb > eps_r)) break;
-                if (hr0 > 1 && !(sb > eps_r + delta) &&
-                    !verify_subtree(pool_k[ob + nr], hl0, hr0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
-                ++nr;
-            }
+            if (my_out > (1u << 24)) irregular = true;     // keeps the tile total inside 32 bits; the depth-first kernel has no such limit
+            wnr[tid] = uint16_t(nr);
         }
         // an element inside the DELTA band failed a deeper check: L(s) is not a prefix of the sorted list.  Rare enough to
         // give the whole tile to the depth-first kernel (nothing was emitted yet).
@@ -388,94 +528,79 @@ namespace ipkgpu
             return;
         }
 
-        // ---- root join (pk_compute.cpp:75-105) + warp-aggregated emission --------------------------------------------
-        const float eps0 = A.log_threshold;
-        const uint64_t group = DEBUG ? 0 : uint64_t(A.node_group[node] - A.group_sub);
-        const int shift0 = hr0 * bits;
-        bool active = has_window && nl > 0 && nr > 0;
-        int i = 0, l = 0;
-        float sa = active ? pool_s[oa] : 0.0f;
-        uint64_t ka = active ? uint64_t(pool_k[oa]) << shift0 : 0;
-        int wcount = 0;
-        unsigned long long emitted = 0;
-        while (__any_sync(full, active))
+        // ---- exclusive scans over the tile's windows: output offsets and row offsets ----------------------------------
         {
-            bool emit = false;
-            uint64_t ekey = 0;
-            float escore = 0.0f;
-            if (active)
+            const uint32_t io = warp_incl_scan_u32(my_out, lane), ir = warp_incl_scan_u32(my_rows, lane);
+            if (lane == 31) { s_wsum[0][warp] = io; s_wsum[1][warp] = ir; }
+            __syncthreads();
+            uint32_t bo = 0, br = 0;
+            for (int w = 0; w < warp; ++w) { bo += s_wsum[0][w]; br += s_wsum[1][w]; }
+            wbase[tid] = bo + io - my_out;
+            rbase[tid] = br + ir - my_rows;
+            if (tid == ENUM_THREADS - 1)
             {
-                bool ok = l < nr;
-                if (ok)
-                {
-                    escore = __fadd_rn(sa, pool_s[ob + l]);                               // pk_compute.cpp:90
-                    ok = escore > eps0;                                                   // :91 `score <= eps` => break
-                }
-                if (ok)
-                {
-                    emit = true;
-                    ekey = ka | uint64_t(pool_k[ob + l]);
-                    ++l;
-                }
-                else if (l == 0) active = false;                                          // rows only get shorter (both lists descend)
-                else
-                {
-                    ++i; l = 0;
-                    if (i < nl) { sa = pool_s[oa + i]; ka = uint64_t(pool_k[oa + i]) << shift0; }
-                    else active = false;
-                }
+                const uint32_t total = bo + io;
+                wbase[ENUM_THREADS] = total;
+                rbase[ENUM_THREADS] = br + ir;
+                // ONE global atomic per tile reserves the tile's exact output range
+                s_base = total ? atomicAdd(A.counter, (unsigned long long)total) : 0ull;
+                if (A.node_counts && total) atomicAdd(A.node_counts + lslot, (unsigned long long)total);
             }
-            const unsigned em = __ballot_sync(full, emit);
-            if (em)
+            __syncthreads();
+        }
+
+        // ---- emission: every warp expands the rows of its 32 windows, 32 records per step, straight to global memory ---
+        {
+            const int ws = warp * 32, we = min(ws + 32, nwin_tile);
+            if (ws >= we) return;
+            const uint32_t rbeg = rbase[ws], rend = rbase[we];
+            unsigned long long pos = s_base + wbase[ws];
+            const uint64_t group = DEBUG ? 0 : uint64_t(A.node_group[node] - A.group_sub);
+            const int shift0 = hr0 * bits;
+            for (uint32_t r0 = rbeg; r0 < rend; r0 += 32)
             {
-                const int n = __popc(em);
-                if (wcount + n > STAGE_CAP)
+                const uint32_t rho = r0 + lane;
+                float sa = 0.0f;
+                uint32_t ka = 0, len = 0, lbo = 0, win = 0;
+                if (rho < rend)
                 {
-                    unsigned long long base = 0;
-                    if (lane == 0) base = atomicAdd(A.counter, (unsigned long long)wcount);
-                    base = __shfl_sync(full, base, 0);
-                    __syncwarp();
-                    for (int q = lane; q < wcount; q += 32)
+                    int s = ws;                            // last window of [ws, we) whose first row is <= rho
+#pragma unroll
+                    for (int step = 16; step >= 1; step >>= 1)
+                        if (s + step < we && rbase[s + step] <= rho) s += step;
+                    const unsigned long long ea = pool[uint32_t(foff[fa0 * NCP + s]) + (rho - rbase[s])];
+                    sa = el_score(ea);
+                    ka = el_key(ea);
+                    lbo = foff[fb0 * NCP + s + hl0];
+                    len = uint32_t(row_length(pool + lbo, wnr[s], sa, eps0));
+                    win = uint32_t(s);
+                }
+                const uint32_t incl = warp_incl_scan_u32(len, lane);
+                const uint32_t total = __shfl_sync(full, incl, 31);
+                const uint32_t excl = incl - len;
+                for (uint32_t o0 = 0; o0 < total; o0 += 32)
+                {
+                    const uint32_t o = o0 + lane;
+                    const bool act = o < total;
+                    const int r = owner_lane(incl, act ? o : 0u);
+                    const float sa_r = __shfl_sync(full, sa, r);
+                    const uint32_t ka_r = __shfl_sync(full, ka, r);
+                    const uint32_t ex_r = __shfl_sync(full, excl, r);
+                    const uint32_t lbo_r = __shfl_sync(full, lbo, r);
+                    const uint32_t win_r = DEBUG ? __shfl_sync(full, win, r) : 0u;
+                    const unsigned long long gpos = pos + o;
+                    if (act && gpos < A.cap)
                     {
-                        const unsigned long long o = base + q;
-                        if (o < A.cap)
-                        {
-                            A.out_keys[o] = st_keys[q];
-                            A.out_scores[o] = st_scores[q];
-                            if (DEBUG) { A.out_node[o] = node; A.out_win[o] = st_win[q]; }
-                        }
+                        const unsigned long long eb = pool[lbo_r + (o - ex_r)];
+                        const float score = __fadd_rn(sa_r, el_score(eb));                          // pk_compute.cpp:90
+                        const uint64_t key = (uint64_t(ka_r) << shift0) | uint64_t(el_key(eb));     // :96-104
+                        A.out_keys[gpos] = DEBUG ? key : ((key << A.group_bits) | group);
+                        A.out_scores[gpos] = score;
+                        if (DEBUG) { A.out_node[gpos] = node; A.out_win[gpos] = s0 + win_r; }
                     }
-                    __syncwarp();
-                    wcount = 0;
                 }
-                if (emit)
-                {
-                    const int slot = wcount + __popc(em & ((1u << lane) - 1));
-                    st_keys[slot] = DEBUG ? ekey : ((ekey << A.group_bits) | group);
-                    st_scores[slot] = escore;
-                    if (DEBUG) st_win[slot] = s0 + tid;
-                }
-                wcount += n;
-                emitted += n;
+                pos += total;
             }
         }
-        __syncwarp();
-        if (wcount)
-        {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(A.counter, (unsigned long long)wcount);
-            base = __shfl_sync(full, base, 0);
-            for (int q = lane; q < wcount; q += 32)
-            {
-                const unsigned long long o = base + q;
-                if (o < A.cap)
-                {
-                    A.out_keys[o] = st_keys[q];
-                    A.out_scores[o] = st_scores[q];
-                    if (DEBUG) { A.out_node[o] = node; A.out_win[o] = st_win[q]; }
-                }
-            }
-        }
-        if (A.node_counts && lane == 0 && emitted) atomicAdd(A.node_counts + lslot, emitted);
     }
 }
