@@ -70,6 +70,8 @@ struct ipkgpu_ctx
     ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
     ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
     ipkgpu::dbuf dbg_node, dbg_win, deferred;
+    ipkgpu::dbuf rs_status;            // radix sort: look-back status words [tile][digit]
+    uint32_t rs_epoch = 0;             // ... and the pass counter that tags them
     int enum_mode = 0;                 // 0: list-join kernel + depth-first kernel on deferred tiles; 1: depth-first only
     uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet
     uint64_t last_tiles = 0, last_deferred_tiles = 0;   // of the current call

@@ -668,7 +668,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     ipkgpu::dbuf* all[] = { &ctx->logp, &ctx->colmax, &ctx->bestpref, &ctx->node_group, &ctx->node_order, &ctx->group_branch, &ctx->counters,
                             &ctx->node_counts, &ctx->keys_a, &ctx->keys_b, &ctx->vals_a, &ctx->vals_b, &ctx->hist, &ctx->scan_tmp,
-                            &ctx->block_counts, &ctx->block_offs, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->u_keys, &ctx->u_scores,
+                            &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt };
@@ -843,10 +843,9 @@ int ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys,
         const digit_owner own{ ctx->s1_group_bits, n_parts };
         radix_pass(ctx, ctx->u_keys.as<uint64_t>(), ctx->u_scores.as<uint32_t>(), d_keys, reinterpret_cast<uint32_t*>(d_scores), n,
                    own, ctx->hist, ctx->scan_tmp);
-        // bucket sizes: the scanned digit-major table holds the start of digit d's first tile at [d * n_tiles]
-        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
+        // bucket sizes: radix_pass leaves the exclusive digit starts in the first 256 words of the table
         std::vector<uint32_t> starts(n_parts);
-        IPK_CUDA(cudaMemcpy2DAsync(starts.data(), 4, ctx->hist.p, size_t(n_tiles) * 4, 4, n_parts, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(starts.data(), ctx->hist.p, size_t(n_parts) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));
         for (uint32_t p = 0; p < n_parts; ++p) counts[p] = (p + 1 < n_parts ? starts[p + 1] : n) - starts[p];
     });

@@ -131,7 +131,10 @@ namespace ipkgpu
     }
 
     // ------------------------------------------------------------------------------------------------------------
-    // radix sort
+    // radix sort ("one sweep" per pass): the digit histograms of ALL passes come from one read of the keys; every
+    // pass is then a single kernel that ranks a tile in shared memory, obtains the tile's global digit offsets by a
+    // decoupled look-back over the preceding tiles' status words, and scatters.  Traffic per pass: 12 B read + 12 B
+    // written per pair (+ one 8-byte status word per tile and digit).
     // ------------------------------------------------------------------------------------------------------------
 
     /// digit of a key in one LSD pass: bits [shift, shift+8) under mask
@@ -157,57 +160,120 @@ namespace ipkgpu
         __device__ __forceinline__ uint32_t operator()(uint64_t ckey) const { return uint32_t(mix64(ckey >> group_bits) % n_parts); }
     };
 
-    /// table[d * n_tiles + tile] = number of keys of this tile whose digit is d
+    constexpr int RS_MAX_PASSES = 8;
+    constexpr int RS_HIST_THREADS = 256;
+    constexpr int RS_HIST_ITEMS = 16;
+
+    /// hist[p * 256 + d] += number of keys whose p-th digit (bits [bit_begin + 8p, +8) under the pass's mask) is d.
+    /// One read of the keys serves every pass.  Per-warp replicated shared histograms keep same-address atomics apart.
+    __global__ void __launch_bounds__(RS_HIST_THREADS) rs_hist_bits(const uint64_t* __restrict__ keys, uint64_t n, uint32_t bit_begin,
+                                                                    uint32_t n_bits, uint32_t n_passes, uint32_t* __restrict__ hist)
+    {
+        extern __shared__ uint32_t sh[];                 // [2 copies][n_passes][256]
+        const uint32_t per_copy = n_passes * RS_RADIX;
+        for (uint32_t i = threadIdx.x; i < 2 * per_copy; i += RS_HIST_THREADS) sh[i] = 0;
+        __syncthreads();
+        uint32_t* mine = sh + ((threadIdx.x >> 5) & 1) * per_copy;
+        const uint64_t chunk = uint64_t(RS_HIST_THREADS) * RS_HIST_ITEMS;
+        for (uint64_t base = blockIdx.x * chunk; base < n; base += uint64_t(gridDim.x) * chunk)
+        {
+            uint64_t k[RS_HIST_ITEMS];
+#pragma unroll
+            for (int i = 0; i < RS_HIST_ITEMS; ++i)
+            {
+                const uint64_t idx = base + uint64_t(i) * RS_HIST_THREADS + threadIdx.x;
+                k[i] = idx < n ? keys[idx] : 0;
+            }
+#pragma unroll
+            for (int i = 0; i < RS_HIST_ITEMS; ++i)
+            {
+                const uint64_t idx = base + uint64_t(i) * RS_HIST_THREADS + threadIdx.x;
+                if (idx < n)
+                {
+                    const uint64_t kk = k[i] >> bit_begin;
+                    for (uint32_t p = 0; p < n_passes; ++p)
+                    {
+                        const uint32_t width = min(8u, n_bits - 8 * p);
+                        atomicAdd(&mine[p * RS_RADIX + (uint32_t(kk >> (8 * p)) & ((1u << width) - 1))], 1u);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < per_copy; i += RS_HIST_THREADS)
+        {
+            const uint32_t v = sh[i] + sh[per_copy + i];
+            if (v) atomicAdd(&hist[i], v);
+        }
+    }
+
+    /// single-pass histogram under an arbitrary digit function (the owner partition)
     template<class DigitFn>
-    __global__ void __launch_bounds__(RS_THREADS) rs_histogram(const uint64_t* __restrict__ keys, uint32_t* __restrict__ table,
-                                                               uint64_t n, uint32_t n_tiles, DigitFn digit)
+    __global__ void __launch_bounds__(RS_HIST_THREADS) rs_hist_fn(const uint64_t* __restrict__ keys, uint64_t n, DigitFn digit, uint32_t* __restrict__ hist)
     {
         __shared__ uint32_t sh[RS_RADIX];
         sh[threadIdx.x] = 0;
         __syncthreads();
-        const uint64_t base = uint64_t(blockIdx.x) * RS_TILE;
-#pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
-        {
-            const uint64_t idx = base + uint64_t(i) * RS_THREADS + threadIdx.x;
-            if (idx < n) atomicAdd(&sh[digit(keys[idx])], 1u);
-        }
+        for (uint64_t idx = blockIdx.x * uint64_t(RS_HIST_THREADS) + threadIdx.x; idx < n; idx += uint64_t(gridDim.x) * RS_HIST_THREADS)
+            atomicAdd(&sh[digit(keys[idx])], 1u);
         __syncthreads();
-        table[uint64_t(threadIdx.x) * n_tiles + blockIdx.x] = sh[threadIdx.x];
+        if (sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
     }
 
-    /// Stable scatter of one tile.  offs = exclusive scan of the digit-major table.
+    /// in place, one CTA per pass: hist[p][0..256) -> exclusive scan (the global start of every digit in that pass)
+    __global__ void __launch_bounds__(RS_RADIX) rs_scan_hist(uint32_t* __restrict__ hist)
+    {
+        __shared__ uint32_t s_warp[9];
+        uint32_t* h = hist + blockIdx.x * RS_RADIX;
+        const uint32_t v = h[threadIdx.x];
+        h[threadIdx.x] = block_excl_scan_256(v, s_warp, nullptr);
+    }
+
+    // status word of (tile, digit): epoch << 34 | flag << 32 | value.  The epoch changes with every pass, so words left by
+    // earlier passes read as "not ready" and the table is zeroed only when it is (re)allocated.
+    constexpr uint64_t RS_FLAG_LOCAL = 1, RS_FLAG_INCL = 2;
+    __device__ __forceinline__ uint64_t rs_status(uint32_t epoch, uint64_t flag, uint32_t value) { return uint64_t(epoch) << 34 | flag << 32 | value; }
+
+    /// One pass over one tile (tile ids are handed out by an atomic ticket, so every predecessor a tile waits for is
+    /// already running).  digit_base = exclusive scan of this pass's global digit histogram.
     template<class DigitFn>
-    __global__ void __launch_bounds__(RS_THREADS) rs_scatter(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                                                             uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                             const uint32_t* __restrict__ offs, uint64_t n, uint32_t n_tiles,
-                                                             DigitFn digit)
+    __global__ void __launch_bounds__(RS_THREADS) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                              uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                              const uint32_t* __restrict__ digit_base, uint64_t n,
+                                                              uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit)
     {
         __shared__ uint32_t wh[RS_WARPS][RS_RADIX];     // per-warp digit counts, then exclusive offsets over warps
         __shared__ uint32_t dbase[RS_RADIX];            // tile-local position of the first key with digit d
-        __shared__ uint32_t goff[RS_RADIX];             // global position of the first key of this tile with digit d
+        __shared__ uint32_t goff[RS_RADIX];             // global position of the first key of this tile with digit d, minus dbase
         __shared__ uint32_t s_warp[9];
+        __shared__ uint32_t s_tile;
         __shared__ uint64_t sk[RS_TILE];
-        __shared__ uint32_t sv[RS_TILE];
+        uint32_t* sv = reinterpret_cast<uint32_t*>(sk);  // the values reuse the key buffer once the keys are written out
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const unsigned full = 0xffffffffu;
+        if (tid == 0) s_tile = atomicAdd(ticket, 1u);
         for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&wh[0][0])[i] = 0;
         __syncthreads();
-
-        const uint64_t tile_base = uint64_t(blockIdx.x) * RS_TILE;
+        const uint32_t tile = s_tile;
+        const uint64_t tile_base = uint64_t(tile) * RS_TILE;
         const uint32_t tile_n = uint32_t(min(uint64_t(RS_TILE), n - tile_base));
+
         uint64_t key[RS_ITEMS];
-        uint32_t val[RS_ITEMS];
         uint16_t rank[RS_ITEMS];
-        // warp w owns items [w*512, (w+1)*512) of the tile, 32 consecutive items per round: order = (warp, round, lane)
+        // warp w owns items [w*32*ITEMS, (w+1)*32*ITEMS) of the tile, 32 consecutive items per round: order = (warp, round, lane)
 #pragma unroll
         for (int i = 0; i < RS_ITEMS; ++i)
         {
             const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
-            const bool valid = li < tile_n;
-            key[i] = valid ? keys_in[tile_base + li] : ~0ull;
-            val[i] = valid ? vals_in[tile_base + li] : 0u;
+            key[i] = li < tile_n ? keys_in[tile_base + li] : ~0ull;
+        }
+        uint32_t val[RS_ITEMS];
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i)
+        {
+            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            val[i] = li < tile_n ? vals_in[tile_base + li] : 0u;
         }
 #pragma unroll
         for (int i = 0; i < RS_ITEMS; ++i)
@@ -228,7 +294,7 @@ namespace ipkgpu
             __syncwarp();
         }
         __syncthreads();
-        // digit d = tid: exclusive prefix over warps, tile total, then exclusive scan over digits
+        // digit d = tid: exclusive prefix over warps and the tile's count
         uint32_t cnt = 0;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; ++w)
@@ -237,45 +303,122 @@ namespace ipkgpu
             wh[w][tid] = cnt;
             cnt += t;
         }
-        const uint32_t ex = block_excl_scan_256(cnt, s_warp, nullptr);
-        dbase[tid] = ex;
-        goff[tid] = offs[uint64_t(tid) * n_tiles + blockIdx.x];
+        // publish the tile's own count, then look back for the sum over all preceding tiles
+        uint64_t* my_status = status + uint64_t(tile) * RS_RADIX + tid;
+        if (tile == 0) *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, cnt);
+        else *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_LOCAL, cnt);
+        const uint32_t ex_local = block_excl_scan_256(cnt, s_warp, nullptr);
+        uint32_t before = 0;
+        if (tile > 0)
+        {
+            const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
+            while (true)
+            {
+                const uint64_t w = *p;
+                if (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0) continue;      // not published yet in this pass
+                before += uint32_t(w);
+                if (((w >> 32) & 3) == RS_FLAG_INCL) break;
+                p -= RS_RADIX;
+            }
+            *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
+        }
+        dbase[tid] = ex_local;
+        goff[tid] = digit_base[tid] + before - ex_local;
+        __syncthreads();
+        // keys: tile-local order -> shared memory -> runs of equal digits to global memory
+        uint32_t pos[RS_ITEMS];
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i)
+        {
+            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            pos[i] = 0;
+            if (li < tile_n)
+            {
+                const uint32_t d = digit(key[i]);
+                pos[i] = dbase[d] + wh[warp][d] + rank[i];
+                sk[pos[i]] = key[i];
+            }
+        }
+        __syncthreads();
+        uint32_t gpos[RS_ITEMS];
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i)
+        {
+            const uint32_t q = uint32_t(i) * RS_THREADS + tid;
+            gpos[i] = 0;
+            if (q < tile_n)
+            {
+                const uint64_t kk = sk[q];
+                gpos[i] = goff[digit(kk)] + q;
+                keys_out[gpos[i]] = kk;
+            }
+        }
+        // values: same route through the (reused) shared buffer
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < RS_ITEMS; ++i)
         {
             const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
-            if (li < tile_n)
-            {
-                const uint32_t d = digit(key[i]);
-                const uint32_t pos = dbase[d] + wh[warp][d] + rank[i];
-                sk[pos] = key[i];
-                sv[pos] = val[i];
-            }
+            if (li < tile_n) sv[pos[i]] = val[i];
         }
         __syncthreads();
-        for (uint32_t i = tid; i < tile_n; i += RS_THREADS)
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i)
         {
-            const uint64_t kk = sk[i];
-            const uint32_t d = digit(kk);
-            const uint32_t g = goff[d] + (i - dbase[d]);
-            keys_out[g] = kk;
-            vals_out[g] = sv[i];
+            const uint32_t q = uint32_t(i) * RS_THREADS + tid;
+            if (q < tile_n) vals_out[gpos[i]] = sv[q];
         }
     }
 
-    /// One stable bucketing pass (histogram -> scan -> scatter) under an arbitrary digit function.
+    /// scratch of the sort inside `table`: [0, 8*256) u32 digit histograms / bases of up to 8 passes, then 16 u32 tickets.
+    /// The status words live in ctx->rs_status (zeroed when it grows; epochs keep passes apart afterwards).
+    struct rs_scratch
+    {
+        uint32_t* hist;
+        uint32_t* tickets;
+        uint64_t* status;
+    };
+
+    inline rs_scratch rs_prepare(ipkgpu_ctx* ctx, uint64_t n, dbuf& table)
+    {
+        const uint64_t n_tiles = div_up<uint64_t>(n, RS_TILE);
+        ctx->reserve(table, (RS_MAX_PASSES * RS_RADIX + 16) * 4);
+        const size_t want = n_tiles * RS_RADIX * 8;
+        if (want > ctx->rs_status.cap)
+        {
+            ctx->reserve(ctx->rs_status, want);
+            IPK_CUDA(cudaMemsetAsync(ctx->rs_status.p, 0, ctx->rs_status.cap, ctx->stream));
+            ctx->rs_epoch = 0;
+        }
+        IPK_CUDA(cudaMemsetAsync(table.p, 0, (RS_MAX_PASSES * RS_RADIX + 16) * 4, ctx->stream));
+        return { table.as<uint32_t>(), table.as<uint32_t>() + RS_MAX_PASSES * RS_RADIX, ctx->rs_status.as<uint64_t>() };
+    }
+
+    inline uint32_t rs_next_epoch(ipkgpu_ctx* ctx)
+    {
+        if (++ctx->rs_epoch >= (1u << 30))
+        {
+            IPK_CUDA(cudaMemsetAsync(ctx->rs_status.p, 0, ctx->rs_status.cap, ctx->stream));
+            ctx->rs_epoch = 1;
+        }
+        return ctx->rs_epoch;
+    }
+
+    /// One stable bucketing pass (histogram -> scan -> one sweep) under an arbitrary digit function.  Leaves the
+    /// exclusive digit starts in table[0..256) (device) for the caller.
     template<class DigitFn>
     inline void radix_pass(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t n,
                            DigitFn digit, dbuf& table, dbuf& scan_tmp)
     {
+        (void)scan_tmp;
+        if (n == 0) return;
+        const rs_scratch S = rs_prepare(ctx, n, table);
         const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
-        const uint64_t table_n = uint64_t(n_tiles) * RS_RADIX;
-        ctx->reserve(table, table_n * 4);
-        uint32_t* tab = table.as<uint32_t>();
-        IPK_LAUNCH(ctx, "rs_histogram", n * 8 + table_n * 4, rs_histogram<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, tab, n, n_tiles, digit));
-        exclusive_scan_u32(ctx, tab, tab, table_n, scan_tmp);
-        IPK_LAUNCH(ctx, "rs_scatter", n * 24 + table_n * 4, rs_scatter<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, tab, n, n_tiles, digit));
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * 8), uint64_t(ctx->num_sms) * 8));
+        IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_fn<DigitFn><<<hgrid, RS_HIST_THREADS, 0, ctx->stream>>>(kin, n, digit, S.hist));
+        IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(S.hist));
+        IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
+                   rs_onesweep<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, S.hist, n, S.status, S.tickets, rs_next_epoch(ctx), digit));
     }
 
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);
@@ -284,10 +427,18 @@ namespace ipkgpu
                                  uint32_t n_bits, dbuf& table, dbuf& scan_tmp, uint32_t* passes_out = nullptr,
                                  uint32_t bit_begin = 0)
     {
+        (void)scan_tmp;
         if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "radix sort of %llu records exceeds 2^32-1", (unsigned long long)n);
         const uint32_t passes = n_bits ? div_up<uint32_t>(n_bits, 8) : 0;
+        if (passes > uint32_t(RS_MAX_PASSES)) fail(IPKGPU_EINVAL, "radix sort on %u bits needs more than %d passes", n_bits, RS_MAX_PASSES);
         if (passes_out) *passes_out = passes;
         if (n == 0 || passes == 0) return false;
+        const rs_scratch S = rs_prepare(ctx, n, table);
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * RS_HIST_ITEMS), uint64_t(ctx->num_sms) * 8));
+        IPK_LAUNCH(ctx, "rs_hist", n * 8,
+                   rs_hist_bits<<<hgrid, RS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(ka, n, bit_begin, n_bits, passes, S.hist));
+        IPK_LAUNCH(ctx, "rs_scan_hist", uint64_t(passes) * 2048, rs_scan_hist<<<passes, RS_RADIX, 0, ctx->stream>>>(S.hist));
         bool in_b = false;
         for (uint32_t p = 0; p < passes; ++p)
         {
@@ -298,7 +449,9 @@ namespace ipkgpu
             const uint32_t* vin = in_b ? vb : va;
             uint64_t* kout = in_b ? ka : kb;
             uint32_t* vout = in_b ? va : vb;
-            radix_pass(ctx, kin, vin, kout, vout, n, digit_bits{ bit_begin + shift, mask }, table, scan_tmp);
+            IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
+                       rs_onesweep<digit_bits><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, S.hist + p * RS_RADIX, n, S.status, S.tickets + p,
+                                                                                        rs_next_epoch(ctx), digit_bits{ bit_begin + shift, mask }));
             in_b = !in_b;
         }
         return in_b;

@@ -165,6 +165,57 @@ def test_build_batched_equals_single(ctx):
         c2.close()
 
 
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 200), (20, 5, 4, 8, 90)])
+def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W):
+    """The multi-GPU path, its ranks emulated one after the other on ONE device (B200_PROFILING.md: never several
+    waiting ranks on one GPU): stage 1 per rank -> partition by k-mer owner -> the all-to-all done with device copies
+    -> stage 2 per rank -> G-way merge.  Entry-for-entry equal to the single-GPU build."""
+    import torch
+    from types import SimpleNamespace
+    from ipk_b200 import capi as libipkgpu, dist as ipkdist
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    dev = torch.device("cuda", 0)
+    with libipkgpu.Context(0) as c1:
+        want = c1.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+    parts = ipkdist.split_branches(2 * n_taxa - 2, world)
+    group_branch = ipkdist.local_groups(nb)
+    group_bits = max(int(np.ceil(np.log2(len(group_branch)))), 0)
+    ctxs = [libipkgpu.Context(0) for _ in range(world)]
+    try:
+        send = []
+        for r, (b0, b1) in enumerate(parts):
+            sl = slice(2 * b0, 2 * b1)
+            inp, keep = libipkgpu.make_input(np.ascontiguousarray(logp[sl]), nb[sl], W, sigma, bits, k, lthr, thr, T, 0)
+            n_unique, st1 = ctxs[r].stage1(inp, b0, group_bits)
+            keys = torch.empty(max(n_unique, 1), dtype=torch.int64, device=dev)
+            scores = torch.empty(max(n_unique, 1), dtype=torch.float32, device=dev)
+            counts = ctxs[r].stage1_partition(world, keys, scores).astype(np.int64)
+            assert counts.sum() == n_unique
+            send.append((keys, scores, np.concatenate(([0], np.cumsum(counts)))))
+        shards = []
+        for r in range(world):
+            rk = torch.cat([send[s][0][send[s][2][r]:send[s][2][r + 1]] for s in range(world)])      # source-rank order
+            rs = torch.cat([send[s][1][send[s][2][r]:send[s][2][r + 1]] for s in range(world)])
+            n = int(rk.numel())
+            if n == 0:
+                rk = torch.empty(1, dtype=torch.int64, device=dev); rs = torch.empty(1, dtype=torch.float32, device=dev)
+            torch.cuda.synchronize()
+            res = ctxs[r].stage2(rk, rs, n, group_bits, group_branch, k * bits, thr, T, 0, True, False)
+            shards.append(libipkgpu.Context.to_db(res))
+        assert sum(s.n_entries for s in shards) == want.n_entries
+        merged = ipkdist.merge_shards(shards)
+        got = SimpleNamespace(keys=merged[0], fv=merged[1], offsets=merged[2], branch=merged[3], score=merged[4],
+                              n_kmers=len(merged[0]), n_entries=len(merged[3]))
+        assert_db_equal(got, want, exact_fv=True)
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_invalid_arguments(ctx):
     from ipk_b200.capi import IpkGpuError
     logp, nb = _synth(4, 50, 4)

@@ -53,6 +53,7 @@ def main():
     ap.add_argument("--so", default=os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "ipk_b200", "libipkgpu.so"))
     ap.add_argument("--top", type=int, default=40)
     ap.add_argument("--launch", type=int, default=0, help="which matching launch of the report (0 = first)")
+    ap.add_argument("--by", default="samples", choices=["samples", "inst", "thread"])
     ap.add_argument("--sass", action="store_true", help="also list the hottest SASS instructions")
     a = ap.parse_args()
     raw = subprocess.run(["ncu", "-i", a.report, "--page", "source", "--csv", "--kernel-name", f"regex:{a.kernel}"],
@@ -98,9 +99,9 @@ def main():
         hot.append((v[1], v[0], lines[i][3], key))
     print(f"kernel: {b['name'][:100]}")
     print(f"total warp instructions {tot[0]:.0f}, stall samples {tot[1]:.0f}, avg active threads {tot[2] / max(tot[0], 1):.1f}, shared conflicts {tot[3]:.0f}")
-    print(f"{'file:line':28s} {'inst%':>7s} {'samp%':>7s} {'thr/inst':>8s} {'conflicts':>10s}  sass")
-    for key, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[: a.top]:
-        print(f"{key[0] + ':' + str(key[1]):28s} {100 * v[0] / max(tot[0], 1):7.2f} {100 * v[1] / max(tot[1], 1):7.2f} {v[2] / max(v[0], 1):8.1f} {v[3]:10.0f}  {v[4]}")
+    print(f"{'file:line':28s} {'inst%':>7s} {'samp%':>7s} {'thr/inst':>8s} {'thrinst%':>8s} {'conflicts':>10s}  sass")
+    for key, v in sorted(agg.items(), key=lambda kv: -kv[1][{'samples': 1, 'inst': 0, 'thread': 2}[a.by]])[: a.top]:
+        print(f"{key[0] + ':' + str(key[1]):28s} {100 * v[0] / max(tot[0], 1):7.2f} {100 * v[1] / max(tot[1], 1):7.2f} {v[2] / max(v[0], 1):8.1f} {100 * v[2] / max(tot[2], 1):8.2f} {v[3]:10.0f}  {v[4]}")
     if a.sass:
         print("\nhottest SASS instructions (stall samples):")
         for s, e, txt, key in sorted(hot, key=lambda t: -t[0])[: a.top]:
