@@ -219,6 +219,8 @@ def run_b200(args):
     d_logp = h_logp.to(dev, non_blocking=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
     ctx = capi.Context(local_rank, stream.cuda_stream)
+    if os.environ.get("IPK_POOL_CAP") or os.environ.get("IPK_ENUM_MODE"):          # tuning knobs (defaults are the product)
+        ctx.set_enumeration(int(os.environ.get("IPK_ENUM_MODE", "0")), int(os.environ.get("IPK_POOL_CAP", "0")))
     inp_dev, keep1 = capi.make_input(d_logp, node_branch, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt)
     inp_host, keep2 = capi.make_input(h_logp.numpy(), node_branch, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt)
     table = ipkdist.exchange_group_table(node_branch, dev) if world > 1 else None
@@ -347,6 +349,7 @@ def run_b200(args):
             "path_roofline": {"algo_bytes_per_step": int(path_bytes), "t_hbm_ms": round(t_hbm * 1e3, 3), "t_nvlink_ms": round(t_nvl * 1e3, 3),
                               "frac": round(t_bound / (ms_dev / args.steps * 1e-3), 4), "nvlink_peak_gbs": 770.0},
             "counts": {"windows": wl.n_windows, "emitted": n_emitted, "entries": n_entries, "kmers": n_kmers, "sort_passes": passes,
+                       "tiles_rank0": int(st.get("n_tiles", 0)), "deferred_tiles_rank0": int(st.get("n_deferred_tiles", 0)),
                        "emitted_per_s": n_emitted * args.steps / (ms_dev * 1e-3)},
             "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order")},
             "kernels": kernels}

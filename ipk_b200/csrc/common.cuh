@@ -69,8 +69,12 @@ struct ipkgpu_ctx
     // device scratch
     ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
     ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
-    ipkgpu::dbuf dbg_node, dbg_win, deferred;
+    ipkgpu::dbuf dbg_node, dbg_win, deferred, deferred2;
+    ipkgpu::dbuf mif_chunks;           // MIF0: first k-mer of every chunk of entries
     ipkgpu::dbuf rs_status;            // radix sort: look-back status words [tile][digit]
+    ipkgpu::dbuf mg_status;            // merge: look-back status words [tile][2]
+    uint32_t mg_epoch = 0;
+    int rs_shape = 2;                  // tile shape of the sweep kernel (index into RS_SHAPES; env IPKGPU_RS_SHAPE)
     uint32_t rs_epoch = 0;             // ... and the pass counter that tags them
     int enum_mode = 0;                 // 0: list-join kernel + depth-first kernel on deferred tiles; 1: depth-first only
     uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet

@@ -25,47 +25,142 @@ namespace ipkgpu
         return __hiloint2double(hi, lo);
     }
 
-    /// G lanes per k-mer (G = 1, 4, 8 or 32, chosen by the host from the mean entries per k-mer).  The transcendental
-    /// work (exp10, log2, the divisions) is spread over the lanes, G entries at a time; the two fp64 running sums are then
-    /// advanced in the reference's order -- entries are visited in stored (group processing) order, as
-    /// filter.cpp:78-82,101-108 does -- by broadcasting the lanes' terms one after the other.
-    template<int G>
-    __global__ void __launch_bounds__(256) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores, uint64_t n_kmers,
-                                                   uint32_t total_num_groups, float threshold, float* __restrict__ fv)
+    // ----------------------------------------------------------------------------------------------------------
+    // K4 MIF0.  A CTA owns the k-mers whose first entry lies in its chunk of MIF_CHUNK entries, i.e. a contiguous run of
+    // entries.  The transcendental work (exp10, the division, log2) is done one ENTRY per thread into shared memory;
+    // the two fp64 running sums are then advanced one K-MER per thread, sequentially over that k-mer's entries in stored
+    // (group processing) order -- exactly the order of filter.cpp:78-82,101-108 -- so the accumulation is the
+    // reference's while no lane ever waits for another k-mer's chain.
+    // ----------------------------------------------------------------------------------------------------------
+    constexpr int MIF_THREADS = 256;
+    constexpr int MIF_CHUNK = 2048;          // entries per CTA chunk (k-mers are assigned by their first entry)
+    constexpr int MIF_CAP = 4096;            // entries a CTA can stage; longer runs take the streaming path
+    constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CHUNK) * 8 + size_t(MIF_CHUNK + 2) * 4 + size_t(MIF_CAP) * 2;
+
+    /// chunk_first[b] = first k-mer whose entries start at or after b * MIF_CHUNK  (b = 0 .. n_chunks; last = n_kmers)
+    __global__ void k4_chunk_first(const uint64_t* __restrict__ offs, uint64_t n_kmers, uint64_t n_chunks, uint32_t* __restrict__ chunk_first)
     {
-        const uint64_t q = (blockIdx.x * uint64_t(blockDim.x) + threadIdx.x) / G;
-        if (q >= n_kmers) return;                                    // whole groups leave together
-        const int gl = int(threadIdx.x) & (G - 1), lane = int(threadIdx.x) & 31;
-        const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
-        const uint64_t a = offs[q], b = offs[q + 1];
-        double score_sum = 0;
-        for (uint64_t base = a; base < b; base += G)
+        const uint64_t b = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        if (b > n_chunks) return;
+        if (b == n_chunks) { chunk_first[b] = uint32_t(n_kmers); return; }
+        const uint64_t target = b * MIF_CHUNK;
+        uint64_t lo = 0, hi = n_kmers;           // first q in [0, n_kmers] with offs[q] >= target
+        while (lo < hi)
         {
-            const uint64_t i = base + gl;
-            const float x = i < b ? logscore_to_score(scores[i]) : 0.0f;
-            const int cnt = int(min(uint64_t(G), b - base));
-            if (G == 1) score_sum = __dadd_rn(score_sum, double(x));
-            else for (int j = 0; j < cnt; ++j) score_sum = __dadd_rn(score_sum, double(__shfl_sync(gmask, x, j, G)));
+            const uint64_t mid = (lo + hi) >> 1;
+            if (offs[mid] >= target) hi = mid; else lo = mid + 1;
         }
-        score_sum = __dadd_rn(score_sum, __dmul_rn(double(uint64_t(total_num_groups) - (b - a)), double(threshold)));   // :86
-        const double weighted_threshold = double(threshold) / score_sum;
-        const double target_threshold = shannon(weighted_threshold);
-        double HcBw1 = __dmul_rn(double(total_num_groups), target_threshold);                                            // :93
-        for (uint64_t base = a; base < b; base += G)
+        chunk_first[b] = uint32_t(lo);
+    }
+
+    struct mif0_consts
+    {
+        double threshold, Hc, T;
+    };
+
+    /// filter.cpp:86-115 for one k-mer, given the sequential sum of its scores and a callable that yields the
+    /// shannon terms of its entries in stored order
+    __device__ __forceinline__ double mif0_tail_begin(double& score_sum, uint64_t n_entries_kmer, const mif0_consts& C, double& target_threshold)
+    {
+        score_sum = __dadd_rn(score_sum, __dmul_rn(C.T - double(n_entries_kmer), C.threshold));            // :86
+        const double weighted_threshold = C.threshold / score_sum;
+        target_threshold = shannon(weighted_threshold);
+        return __dmul_rn(C.T, target_threshold);                                                            // :93
+    }
+
+    __global__ void __launch_bounds__(MIF_THREADS) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores,
+                                                           const uint32_t* __restrict__ chunk_first, uint32_t total_num_groups,
+                                                           float threshold, float* __restrict__ fv)
+    {
+        extern __shared__ __align__(16) unsigned char mif_smem[];
+        double* slot = reinterpret_cast<double*>(mif_smem);                     // [MIF_CAP] x (float, low word) while summing; then the entry's shannon term
+        double* ssum = slot + MIF_CAP;                                          // [MIF_CHUNK] per k-mer: score_sum
+        uint32_t* koff = reinterpret_cast<uint32_t*>(ssum + MIF_CHUNK);         // [MIF_CHUNK + 2] per k-mer: first entry, relative to the run
+        uint16_t* seg = reinterpret_cast<uint16_t*>(koff + MIF_CHUNK + 2);      // [MIF_CAP] per entry: its k-mer, relative to the CTA's first
+        const uint32_t q0 = chunk_first[blockIdx.x], q1 = chunk_first[blockIdx.x + 1];
+        if (q0 == q1) return;
+        const int tid = threadIdx.x;
+        const uint32_t nk = q1 - q0;
+        const uint64_t e0 = offs[q0], e1 = offs[q1];
+        const uint64_t span = e1 - e0;
+        const mif0_consts C{ double(threshold), log2(double(total_num_groups)), double(total_num_groups) };
+        float* xs = reinterpret_cast<float*>(slot);    // xs[2*i] = x of entry i
+        if (span <= uint64_t(MIF_CAP))
         {
-            const uint64_t i = base + gl;
-            double target_value = 0;
-            if (i < b)
+            for (uint32_t j = tid; j <= nk; j += MIF_THREADS) koff[j] = uint32_t(offs[q0 + j] - e0);
+            for (uint32_t i = tid; i < uint32_t(span); i += MIF_THREADS) xs[2 * i] = logscore_to_score(scores[e0 + i]);
+            __syncthreads();
+            for (uint32_t j = tid; j < nk; j += MIF_THREADS)
             {
-                const double weighted_score = double(logscore_to_score(scores[i])) / score_sum;
-                target_value = shannon(weighted_score);
+                const uint32_t a = koff[j], b = koff[j + 1];
+                double s = 0;
+                for (uint32_t i = a; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }     // filter.cpp:78-82
+                ssum[j] = s;
             }
-            const int cnt = int(min(uint64_t(G), b - base));
-            if (G == 1) HcBw1 = __dadd_rn(__dsub_rn(HcBw1, target_threshold), target_value);                             // :107
-            else for (int j = 0; j < cnt; ++j) HcBw1 = __dadd_rn(__dsub_rn(HcBw1, target_threshold), shfl_f64(gmask, target_value, j, G));
+            __syncthreads();
+            // every k-mer's score_sum gets its threshold share (:86) -- recomputed by whoever needs it, it is one fp64 fma
+            for (uint32_t i = tid; i < uint32_t(span); i += MIF_THREADS)
+            {
+                const uint32_t j = seg[i];
+                const double ss = __dadd_rn(ssum[j], __dmul_rn(C.T - double(koff[j + 1] - koff[j]), C.threshold));
+                const double weighted_score = double(xs[2 * i]) / ss;
+                slot[i] = shannon(weighted_score);                                                                    // :103-105
+            }
+            __syncthreads();
+            for (uint32_t j = tid; j < nk; j += MIF_THREADS)
+            {
+                const uint32_t a = koff[j], b = koff[j + 1];
+                double ss = ssum[j], tt;
+                double H = mif0_tail_begin(ss, b - a, C, tt);
+                for (uint32_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);                            // :107
+                fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));                                                // :115
+            }
+            return;
         }
-        const double Hc = log2(double(total_num_groups));
-        if (gl == 0) fv[q] = float(__dmul_rn(score_sum, __dsub_rn(HcBw1, Hc)));                                          // :115
+        // streaming path: a run longer than the staging buffer (a k-mer present on thousands of branches).  One k-mer at a
+        // time, MIF_THREADS entries per step: all threads do the transcendental work, thread 0 advances the sums in order.
+        __shared__ double s_bcast[2];
+        for (uint32_t j = 0; j < nk; ++j)
+        {
+            const uint64_t a = offs[q0 + j], b = offs[q0 + j + 1];
+            double s = 0;
+            for (uint64_t base = a; base < b; base += MIF_THREADS)
+            {
+                const uint64_t i = base + tid;
+                if (i < b) xs[2 * tid] = logscore_to_score(scores[i]);
+                __syncthreads();
+                if (tid == 0)
+                {
+                    const int cnt = int(min(uint64_t(MIF_THREADS), b - base));
+                    for (int t = 0; t < cnt; ++t) s = __dadd_rn(s, double(xs[2 * t]));
+                }
+                __syncthreads();
+            }
+            if (tid == 0)
+            {
+                double tt;
+                const double H0 = mif0_tail_begin(s, b - a, C, tt);
+                s_bcast[0] = s; s_bcast[1] = tt;
+                ssum[0] = H0;
+            }
+            __syncthreads();
+            const double ss = s_bcast[0], tt = s_bcast[1];
+            double H = ssum[0];
+            for (uint64_t base = a; base < b; base += MIF_THREADS)
+            {
+                const uint64_t i = base + tid;
+                if (i < b) slot[tid] = shannon(double(logscore_to_score(scores[i])) / ss);
+                __syncthreads();
+                if (tid == 0)
+                {
+                    const int cnt = int(min(uint64_t(MIF_THREADS), b - base));
+                    for (int t = 0; t < cnt; ++t) H = __dadd_rn(__dsub_rn(H, tt), slot[t]);
+                }
+                __syncthreads();
+            }
+            if (tid == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));
+            __syncthreads();
+        }
     }
 
     __device__ __forceinline__ uint64_t mulmod31(uint64_t a, uint64_t b) { return (a * b) % 2147483647ull; }

@@ -155,8 +155,16 @@ namespace
     /// larger alphabets get most of the SM's shared memory
     uint32_t default_pool_cap(const ipkgpu_input* in)
     {
-        const uint32_t want = in->sigma <= 4 ? 6144u : 20000u;
+        const uint32_t want = in->sigma <= 4 ? 3072u : 20000u;
         return std::max(want, join_min_pool(int(in->k), int(in->sigma)));
+    }
+
+    /// largest list pool one CTA of the join kernel can have (the whole shared memory of an SM)
+    uint32_t max_pool_cap(const ipkgpu_input* in, int n_fam)
+    {
+        const size_t fixed = make_join_layout(int(in->k), int(in->sigma), n_fam, 0).total;
+        const size_t avail = size_t(226) * 1024 > fixed ? size_t(226) * 1024 - fixed : 0;
+        return uint32_t(std::min<size_t>(avail / 8, 65000));
     }
 
     /// K2 over a range of launch slots: the list-join kernel, then the depth-first kernel on the tiles it deferred
@@ -199,32 +207,55 @@ namespace
         const bool use_join = in->k >= 2 && ctx->enum_mode != 1;
         if (use_join)
         {
+            // Level 1: every tile with the default pool (several CTAs per SM).  Level 2: the tiles whose lists did not fit,
+            // again with the largest pool one SM can hold.  What is left after that goes to the depth-first kernel.
             const join_program J = make_join_program(int(in->k));
-            A.pool_cap = std::min<uint32_t>(65000u, std::max(ctx->pool_cap ? ctx->pool_cap : default_pool_cap(in), join_min_pool(int(in->k), int(in->sigma))));
+            const uint32_t min_pool = join_min_pool(int(in->k), int(in->sigma));
+            const uint32_t pool1 = std::min<uint32_t>(65000u, std::max(ctx->pool_cap ? ctx->pool_cap : default_pool_cap(in), min_pool));
+            const uint32_t pool_max = std::max(max_pool_cap(in, J.n_fam), min_pool);
             ctx->reserve(ctx->deferred, grid * 4);
-            A.deferred_tiles = ctx->deferred.as<uint32_t>();
-            IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
-            const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
-            if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
-            if (L.debug)
+            ctx->reserve(ctx->deferred2, grid * 4);
+            uint32_t* lists[2] = { ctx->deferred.as<uint32_t>(), ctx->deferred2.as<uint32_t>() };
+            uint64_t n_tiles_level = grid, emitted_before = 0;
+            // pool sizes of the levels: the default, four times that (still two or more CTAs per SM), everything
+            uint32_t pools[3] = { pool1, 0, 0 };
+            int n_levels = 1;
+            if (!ctx->pool_cap)
             {
-                IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                IPK_LAUNCH(ctx, "k2_join", in_bytes, k2_join<true><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                if (uint64_t(pool1) * 4 + pool1 < pool_max) pools[n_levels++] = pool1 * 4;
+                if (pool_max > pools[n_levels - 1] + pools[n_levels - 1] / 4) pools[n_levels++] = pool_max;
             }
-            else
+            for (int level = 0; level < n_levels && n_tiles_level > 0; ++level)
             {
-                IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                IPK_LAUNCH(ctx, "k2_join", in_bytes, k2_join<false><<<uint32_t(grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                A.pool_cap = pools[level];
+                A.tile_list = level == 0 ? nullptr : lists[(level - 1) & 1];
+                A.deferred_tiles = lists[level & 1];
+                IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
+                const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
+                if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
+                const uint64_t lvl_in_bytes = level == 0 ? in_bytes : n_tiles_level * uint64_t(ENUM_THREADS + in->k) * (in->sigma + 1) * 4;
+                if (L.debug)
+                {
+                    IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(n_tiles_level), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                }
+                else
+                {
+                    IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(n_tiles_level), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                }
+                uint64_t h[2] = { 0, 0 };
+                IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+                IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+                ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], L.cap) - std::min<uint64_t>(emitted_before, L.cap)));
+                emitted_before = h[0];
+                n_tiles_level = h[1];
+                A.tile_list = lists[level & 1];
             }
-            uint64_t h[2] = { 0, 0 };
-            IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
-            ctx->kprof_add_bytes("k2_join", 12 * std::min<uint64_t>(h[0], L.cap));
-            n_deferred = h[1];
-            ctx->enum_join_emitted = h[0];
+            n_deferred = n_tiles_level;
+            ctx->enum_join_emitted = emitted_before;
             ctx->last_deferred_tiles += n_deferred;
             ctx->last_tiles += grid;
-            A.tile_list = ctx->deferred.as<uint32_t>();
         }
         if (!use_join) { ctx->last_deferred_tiles += grid; ctx->last_tiles += grid; }
         if (n_deferred == 0) return;
@@ -258,43 +289,61 @@ namespace
     /// K3 on n sorted records (keys, scores): segmented max over equal composite keys, compaction, and -- when
     /// `csr` -- the CSR by k-mer (K3').  Unique records go to (u_keys, u_scores) + u_off when `unique`.
     merge_out run_merge(ipkgpu_ctx* ctx, const uint64_t* keys, const float* scores, uint64_t n, uint32_t group_bits,
-                        uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr)
+                        uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr, uint32_t key_bits)
     {
         merge_out r;
         if (n == 0) return r;
         const uint32_t tiles = uint32_t(div_up<uint64_t>(n, MG_TILE));
-        ctx->reserve(ctx->block_counts, size_t(tiles) * 8);
+        // single pass: the outputs are sized by their upper bounds (records <= n, k-mers <= min(n, 2^key_bits))
+        const uint64_t kmer_bound = key_bits < 40 ? std::min<uint64_t>(n, 1ull << key_bits) : n;
+        if (unique)
+        {
+            ctx->reserve_keep(ctx->u_keys, (u_off + n) * 8, u_off * 8);
+            ctx->reserve_keep(ctx->u_scores, (u_off + n) * 4, u_off * 4);
+        }
+        if (csr)
+        {
+            ctx->reserve(ctx->kmer_keys, kmer_bound * 8 + 8);
+            ctx->reserve(ctx->kmer_offs, (kmer_bound + 1) * 8);
+            ctx->reserve(ctx->ent_branch, n * 4 + 4);
+            ctx->reserve(ctx->ent_score, n * 4 + 4);
+        }
         ctx->reserve(ctx->counters, 64);
-        uint32_t* rc = ctx->block_counts.as<uint32_t>();
-        uint32_t* kc = rc + tiles;
-        IPK_LAUNCH(ctx, "mg_count", n * 8, mg_count<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, n, group_bits, rc, kc));
-        unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;
-        exclusive_scan_u32(ctx, rc, rc, tiles, ctx->scan_tmp, totals);
-        exclusive_scan_u32(ctx, kc, kc, tiles, ctx->scan_tmp, totals + 1);
+        const size_t status_bytes = size_t(tiles) * 16;
+        if (status_bytes > ctx->mg_status.cap)
+        {
+            ctx->reserve(ctx->mg_status, status_bytes);
+            IPK_CUDA(cudaMemsetAsync(ctx->mg_status.p, 0, ctx->mg_status.cap, ctx->stream));
+            ctx->mg_epoch = 0;
+        }
+        if (++ctx->mg_epoch >= (1u << 30))
+        {
+            IPK_CUDA(cudaMemsetAsync(ctx->mg_status.p, 0, ctx->mg_status.cap, ctx->stream));
+            ctx->mg_epoch = 1;
+        }
+        unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;      // [2], [3]: totals; [4]: ticket
+        IPK_CUDA(cudaMemsetAsync(totals, 0, 24, ctx->stream));
+        merge_args M;
+        M.ckeys = keys; M.scores = scores; M.n = n;
+        M.group_bits = group_bits; M.out_group_bits = out_group_bits; M.group_add = group_add;
+        M.u_keys = unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr;
+        M.u_scores = unique ? ctx->u_scores.as<float>() + u_off : nullptr;
+        M.group_branch = ctx->group_branch.as<uint32_t>();
+        M.kmer_keys = csr ? ctx->kmer_keys.as<uint64_t>() : nullptr;
+        M.kmer_offs = ctx->kmer_offs.as<uint64_t>();
+        M.ent_branch = ctx->ent_branch.as<uint32_t>();
+        M.ent_score = ctx->ent_score.as<float>();
+        M.status = ctx->mg_status.as<uint64_t>();
+        M.ticket = reinterpret_cast<uint32_t*>(totals + 2);
+        M.totals = totals;
+        M.epoch = ctx->mg_epoch;
+        IPK_LAUNCH(ctx, "mg_merge", n * 12, mg_merge<<<tiles, MG_THREADS, 0, ctx->stream>>>(M));
         uint64_t h[2];
         IPK_CUDA(cudaMemcpyAsync(h, totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));
         r.n_records = h[0];
         r.n_kmers = h[1];
-        if (unique)
-        {
-            ctx->reserve_keep(ctx->u_keys, (u_off + r.n_records) * 8, u_off * 8);
-            ctx->reserve_keep(ctx->u_scores, (u_off + r.n_records) * 4, u_off * 4);
-        }
-        if (csr)
-        {
-            ctx->reserve(ctx->kmer_keys, r.n_kmers * 8 + 8);
-            ctx->reserve(ctx->kmer_offs, (r.n_kmers + 1) * 8);
-            ctx->reserve(ctx->ent_branch, r.n_records * 4 + 4);
-            ctx->reserve(ctx->ent_score, r.n_records * 4 + 4);
-        }
-        IPK_LAUNCH(ctx, "mg_write", n * 12 + (unique ? r.n_records * 12 : 0) + (csr ? r.n_records * 8 + r.n_kmers * 16 : 0),
-                   mg_write<<<tiles, MG_THREADS, 0, ctx->stream>>>(keys, scores, n, group_bits, out_group_bits, group_add, rc, kc,
-                                                                   unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr,
-                                                                   unique ? ctx->u_scores.as<float>() + u_off : nullptr,
-                                                                   ctx->group_branch.as<uint32_t>(),
-                                                                   csr ? ctx->kmer_keys.as<uint64_t>() : nullptr, ctx->kmer_offs.as<uint64_t>(),
-                                                                   ctx->ent_branch.as<uint32_t>(), ctx->ent_score.as<float>()));
+        ctx->kprof_add_bytes("mg_merge", (unique ? r.n_records * 12 : 0) + (csr ? r.n_records * 8 + r.n_kmers * 16 : 0));
         if (csr)
             IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + r.n_kmers, &r.n_records, 8, cudaMemcpyHostToDevice, ctx->stream));
         return r;
@@ -424,7 +473,7 @@ namespace
             const uint64_t* sk = in_b ? ctx->keys_b.as<uint64_t>() : ctx->keys_a.as<uint64_t>();
             const float* sv = in_b ? ctx->vals_b.as<float>() : ctx->vals_a.as<float>();
             const bool csr = single && want_csr;
-            const merge_out m = run_merge(ctx, sk, sv, b.n, bbits, group_bits, group_base + b.g0, !csr, u_off, csr);
+            const merge_out m = run_merge(ctx, sk, sv, b.n, bbits, group_bits, group_base + b.g0, !csr, u_off, csr, key_bits);
             if (csr) { o.csr_done = true; o.n_kmers = m.n_kmers; }
             u_off += m.n_records;
             const size_t ed = tm.mark();
@@ -476,14 +525,16 @@ namespace
             const uint32_t grid = uint32_t(div_up<uint64_t>(n_kmers, 256));
             if (sp.filter == IPKGPU_FILTER_MIF0)
             {
-                // lanes per k-mer, from the mean number of entries per k-mer
-                const int G = lanes_per_kmer(n_kmers, n_entries);
-                const uint32_t ggrid = uint32_t(div_up<uint64_t>(n_kmers * uint64_t(G), 256));
-#define IPK_MIF0(G_) IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,                                                          \
-                                k4_mif0<G_><<<ggrid, 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(), n_kmers, \
-                                                                            sp.total_num_groups, sp.threshold, ctx->fv.as<float>()))
-                if (G == 1) IPK_MIF0(1); else if (G == 4) IPK_MIF0(4); else if (G == 8) IPK_MIF0(8); else IPK_MIF0(32);
-#undef IPK_MIF0
+                // CTA b owns the k-mers whose entries start in [b, b+1) * MIF_CHUNK
+                const uint64_t n_chunks = div_up<uint64_t>(std::max<uint64_t>(n_entries, 1), MIF_CHUNK);
+                ctx->reserve(ctx->mif_chunks, (n_chunks + 1) * 4);
+                IPK_LAUNCH(ctx, "k4_chunk_first", (n_chunks + 1) * 4,
+                           k4_chunk_first<<<uint32_t(div_up<uint64_t>(n_chunks + 1, 256)), 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), n_kmers, n_chunks,
+                                                                                                                  ctx->mif_chunks.as<uint32_t>()));
+                IPK_CUDA(cudaFuncSetAttribute(k4_mif0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(MIF_SMEM)));
+                IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,
+                           k4_mif0<<<uint32_t(n_chunks), MIF_THREADS, MIF_SMEM, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(),
+                                                                                        ctx->mif_chunks.as<uint32_t>(), sp.total_num_groups, sp.threshold, ctx->fv.as<float>()));
             }
             else
             {
@@ -575,7 +626,7 @@ namespace
             if (in_b) { sk = ctx->keys_b.as<uint64_t>(); sv = ctx->vals_b.as<float>(); }
         }
         const size_t e1 = tm.mark();
-        const merge_out m = run_merge(ctx, sk, sv, n, sp.group_bits, sp.group_bits, 0, false, 0, true);
+        const merge_out m = run_merge(ctx, sk, sv, n, sp.group_bits, sp.group_bits, 0, false, 0, true, sp.key_bits);
         if (n == 0)
         {
             ctx->reserve(ctx->kmer_offs, 8);
@@ -645,6 +696,7 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     if (!ctx) { g_create_error = "host allocation failed"; return IPKGPU_ENOMEM; }
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
+    if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);      // tuning knob; the default is the product
     cudaSetDevice(device);
     if (stream) ctx->stream = static_cast<cudaStream_t>(stream);
     else
@@ -668,7 +720,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     ipkgpu::dbuf* all[] = { &ctx->logp, &ctx->colmax, &ctx->bestpref, &ctx->node_group, &ctx->node_order, &ctx->group_branch, &ctx->counters,
                             &ctx->node_counts, &ctx->keys_a, &ctx->keys_b, &ctx->vals_a, &ctx->vals_b, &ctx->hist, &ctx->scan_tmp,
-                            &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->u_keys, &ctx->u_scores,
+                            &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->mg_status, &ctx->mif_chunks, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->deferred2, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt };

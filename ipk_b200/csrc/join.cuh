@@ -36,6 +36,8 @@ namespace ipkgpu
             uint8_t h, hl;                         // node length, left-child length (h/2); h == 1: leaf
             uint8_t left, right;                   // child families (h > 1)
             uint8_t n_uses;
+            uint8_t top;                           // list storage: 1 = taken from the top end of the pool, 0 = from the bottom
+            uint8_t reset;                         // 1 = every list at the bottom end is dead when this family is built: start over at 0
             uint8_t use_node[JOIN_MAX_USES];       // tree-node ids (index into eps[]) of the nodes of this length
             uint8_t use_off[JOIN_MAX_USES];        // ... and their offsets in the window
         } fam[JOIN_MAX_FAM];
@@ -93,6 +95,16 @@ namespace ipkgpu
         J.root_hl = k / 2;
         J.root_left = find(k / 2);
         J.root_right = find(k - k / 2);
+        // Two-ended pool.  Only the root's children (the one or two longest families) are needed by the root join, and
+        // while THEY are built only their own children must still exist.  So: children of the root's children live at the
+        // top end; every other family is built at the bottom end first and is dead by the time the first root child is
+        // built, which therefore starts the bottom end over.  (A root child that is also a child of the other one -- k = 3,
+        // 5 -- stays at the top.)
+        auto is_root_child = [&](int f) { return f == J.root_left || f == J.root_right; };
+        for (int f = 0; f < J.n_fam; ++f)
+            if (is_root_child(f) && J.fam[f].h > 1) { J.fam[J.fam[f].left].top = 1; J.fam[J.fam[f].right].top = 1; }
+        for (int f = 0; f < J.n_fam; ++f)
+            if (is_root_child(f) && !J.fam[f].top) { J.fam[f].reset = 1; break; }
         return J;
     }
 
@@ -269,6 +281,21 @@ namespace ipkgpu
         return true;
     }
 
+    /// n elements from the bottom (grows up) or the top (grows down) end of the pool; false when the two ends would meet.
+    /// All allocations of one family go to the same end, so the other cursor is stable while they race.
+    __device__ __forceinline__ bool pool_alloc(int* lo, int* hi, bool top, int n, uint32_t& off)
+    {
+        if (top)
+        {
+            const int o = atomicSub(hi, n) - n;
+            off = uint32_t(o);
+            return o >= *reinterpret_cast<volatile int*>(lo);
+        }
+        const int o = atomicAdd(lo, n);
+        off = uint32_t(o);
+        return o + n <= *reinterpret_cast<volatile int*>(hi);
+    }
+
     /// first index of the descending list p[0..n) whose score is NOT > thr  (= number of elements above thr)
     __device__ __forceinline__ int cut_above(const unsigned long long* p, int n, float thr)
     {
@@ -290,12 +317,13 @@ namespace ipkgpu
         __shared__ unsigned long long s_base;
         __shared__ uint32_t s_pos[MAX_K];
         __shared__ uint32_t s_merge[MAX_K];
-        __shared__ uint32_t s_pool_used, s_defer, s_qn[2];
+        __shared__ uint32_t s_defer, s_qn[2];
+        __shared__ int s_lo, s_hi;                           // pool cursors: bottom end grows up, top end grows down
         __shared__ uint32_t s_wsum[2][ENUM_WARPS];
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma), bits = int(A.bits);
-        const uint32_t tile = blockIdx.x;
+        const uint32_t tile = A.tile_list ? A.tile_list[blockIdx.x] : blockIdx.x;
         const uint32_t lslot = A.slot_base + tile / A.tiles_per_node;
         const uint32_t node = A.node_order[lslot];
         const uint32_t s0 = (tile % A.tiles_per_node) * ENUM_THREADS;
@@ -323,7 +351,7 @@ namespace ipkgpu
             s_pos[tid] = tid < k ? (uint32_t(P.leaf_eps[tid]) | uint32_t(P.merge_begin[tid]) << 16 | uint32_t(P.merge_begin[tid + 1]) << 24) : 0u;
             s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
         }
-        if (tid == 0) { s_pool_used = 0; s_defer = 0; s_qn[0] = 0; s_qn[1] = 0; }
+        if (tid == 0) { s_lo = 0; s_hi = int(A.pool_cap); s_defer = 0; s_qn[0] = 0; s_qn[1] = 0; }
         stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar);
 
         // ---- eps of every tree node for this thread's window (pk_compute.cpp:54-55; window.cpp:69-72) ---------------
@@ -354,6 +382,12 @@ namespace ipkgpu
             const int nlist = ncols - h + 1;
             uint16_t* cnt_f = fcnt + f * NCP;
             uint16_t* off_f = foff + f * NCP;
+            const bool top = J.fam[f].top != 0;
+            if (J.fam[f].reset)
+            {
+                if (tid == 0) s_lo = 0;                        // every list at the bottom end is dead by now (make_join_program)
+                __syncthreads();
+            }
             if (tid == 0) s_qn[(f + 1) & 1] = 0;              // the other family's queue counter: last read before the previous barrier
             // phase A, one thread per column: threshold, exact length (two-pointer walk over the staircase), and -- for
             // short lists -- allocation, fill and sort.  Long lists are queued for phase B.
@@ -372,8 +406,7 @@ namespace ipkgpu
                     while (n < uint32_t(sigma) && sval[n * NCP + c] > g) ++n;            // as_column (pk_compute.cpp:14-26): strict >
                     if (n)
                     {
-                        off = atomicAdd(&s_pool_used, n);
-                        if (off + n > A.pool_cap) s_defer = 1;
+                        if (!pool_alloc(&s_lo, &s_hi, top, int(n), off)) s_defer = 1;
                         else for (uint32_t r = 0; r < n; ++r) pool[off + r] = el_pack(sval[r * NCP + c], sidx[r * NCP + c]);
                     }
                 }
@@ -393,8 +426,7 @@ namespace ipkgpu
                     else if (n > uint32_t(JOIN_SMALL_LIST)) queue[atomicAdd(&s_qn[f & 1], 1u)] = uint16_t(c);
                     else if (n)
                     {
-                        off = atomicAdd(&s_pool_used, n);
-                        if (off + n > A.pool_cap) s_defer = 1;
+                        if (!pool_alloc(&s_lo, &s_hi, top, int(n), off)) s_defer = 1;
                         else
                         {
                             unsigned long long* os = pool + off;
@@ -433,9 +465,11 @@ namespace ipkgpu
                 const unsigned long long* lb = pool + off_f[(fb - f) * NCP + c + hl];
                 const float g = gthr[c];
                 uint32_t off = 0;
-                if (lane == 0) off = atomicAdd(&s_pool_used, uint32_t(n));
+                int ok = 0;
+                if (lane == 0) ok = pool_alloc(&s_lo, &s_hi, top, n, off) ? 1 : 0;
                 off = __shfl_sync(full, off, 0);
-                if (off + uint32_t(n) > A.pool_cap) { if (lane == 0) s_defer = 1; break; }
+                ok = __shfl_sync(full, ok, 0);
+                if (!ok) { if (lane == 0) s_defer = 1; break; }
                 unsigned long long* os = pool + off;
                 uint32_t carry = 0;
                 for (int i0 = 0; i0 < na; i0 += 32)

@@ -5,6 +5,9 @@
 //     node): keep the maximum score                      -- ipk::put, ipk/src/branch_group.cpp:88-101
 //   * equal kmer  = one database row: its (branch, score) entries in group processing order
 //                                                        -- unsafe_insert loop, ipk/src/db_builder.cpp:685-693
+//
+// One pass: a tile finds its record heads and k-mer heads, gets the number of heads in all preceding tiles by a
+// decoupled look-back (one warp per counter, 32 predecessors per step) and writes its compacted output.
 #pragma once
 #include "common.cuh"
 #include "radix_sort.cuh"
@@ -12,107 +15,151 @@
 namespace ipkgpu
 {
     constexpr int MG_THREADS = 256;
-    constexpr int MG_ITEMS = 8;
+    constexpr int MG_ITEMS = 12;
     constexpr int MG_TILE = MG_THREADS * MG_ITEMS;
+    constexpr int MG_WARPS = MG_THREADS / 32;
 
-    /// per tile: number of record heads (ckey differs from predecessor) and of k-mer heads
-    __global__ void __launch_bounds__(MG_THREADS) mg_count(const uint64_t* __restrict__ ckeys, uint64_t n, uint32_t group_bits,
-                                                           uint32_t* __restrict__ rec_counts, uint32_t* __restrict__ kmer_counts)
+    /// Look-back of one warp over status words  epoch << 34 | flag << 32 | value  at status[tile * stride]: returns the
+    /// sum of the values of all tiles before `tile` (every lane gets it).  Tiles take their ids from an atomic ticket, so
+    /// every predecessor is running or done.
+    __device__ __forceinline__ uint32_t warp_look_back(const uint64_t* status, uint32_t tile, uint32_t stride, uint32_t epoch, int lane)
     {
-        __shared__ uint32_t s_warp[9];
-        const uint64_t base = uint64_t(blockIdx.x) * MG_TILE + uint64_t(threadIdx.x) * MG_ITEMS;
-        uint32_t c1 = 0, c2 = 0;
-        if (base < n)
+        uint32_t sum = 0;
+        int64_t base = int64_t(tile) - 1;
+        while (base >= 0)
         {
-            uint64_t prev = base ? ckeys[base - 1] : ~ckeys[0];
-#pragma unroll
-            for (int i = 0; i < MG_ITEMS; ++i)
+            const int64_t t = base - lane;
+            uint64_t w = rs_status(epoch, RS_FLAG_INCL, 0);            // lanes that fall off the front see an inclusive zero
+            if (t >= 0)
             {
-                if (base + i < n)
-                {
-                    const uint64_t cur = ckeys[base + i];
-                    c1 += cur != prev;
-                    c2 += (cur >> group_bits) != (prev >> group_bits) || (base + i == 0);
-                    prev = cur;
-                }
+                const volatile uint64_t* p = status + uint64_t(t) * stride;
+                do { w = *p; } while (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0);
             }
+            const unsigned incl = __ballot_sync(0xffffffffu, ((w >> 32) & 3) == RS_FLAG_INCL);
+            const int first = incl ? __ffs(incl) - 1 : 32;             // nearest predecessor with an inclusive value
+            uint32_t v = lane <= first ? uint32_t(w) : 0u;
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            sum += v;
+            if (incl) break;
+            base -= 32;
         }
-        uint32_t t1, t2;
-        block_excl_scan_256(c1, s_warp, &t1);
-        block_excl_scan_256(c2, s_warp, &t2);
-        if (threadIdx.x == 0) { rec_counts[blockIdx.x] = t1; kmer_counts[blockIdx.x] = t2; }
+        return sum;
     }
 
-    /// Writes the compacted records (and, when kmer_keys != null, the CSR by k-mer).
-    /// rec_offs / kmer_offs_tile: exclusive scans of mg_count's outputs.
-    /// The group field of the input keys is batch-local (group_bits wide, offset group_add); compacted records are
-    /// re-encoded as (kmer << out_group_bits) | (group + group_add), the global form stage 2 and the exchange use.
-    __global__ void __launch_bounds__(MG_THREADS) mg_write(const uint64_t* __restrict__ ckeys, const float* __restrict__ scores, uint64_t n,
-                                                           uint32_t group_bits, uint32_t out_group_bits, uint32_t group_add,
-                                                           const uint32_t* __restrict__ rec_offs,
-                                                           const uint32_t* __restrict__ kmer_offs_tile,
-                                                           uint64_t* __restrict__ u_keys, float* __restrict__ u_scores,      // may be null
-                                                           const uint32_t* __restrict__ group_branch,                        // CSR outputs below may be null
-                                                           uint64_t* __restrict__ kmer_keys, uint64_t* __restrict__ kmer_offs,
-                                                           uint32_t* __restrict__ ent_branch, float* __restrict__ ent_score)
+    struct merge_args
     {
-        __shared__ uint32_t s_warp[9];
-        const uint64_t base = uint64_t(blockIdx.x) * MG_TILE + uint64_t(threadIdx.x) * MG_ITEMS;
-        uint64_t k[MG_ITEMS];
-        uint32_t c1 = 0, c2 = 0;
-        uint64_t prev0 = 0;
-        if (base < n)
-        {
-            prev0 = base ? ckeys[base - 1] : ~ckeys[0];
-            uint64_t prev = prev0;
+        const uint64_t* ckeys;             // sorted composite keys
+        const float* scores;
+        uint64_t n;
+        uint32_t group_bits;               // width of the (batch-local) group field of ckeys
+        uint32_t out_group_bits;           // width of the group field of the compacted records
+        uint32_t group_add;                // batch-local group + group_add = global group
+        uint64_t* u_keys; float* u_scores; // compacted records (kmer << out_group_bits | global group), or null
+        const uint32_t* group_branch;      // global group -> branch id
+        uint64_t* kmer_keys; uint64_t* kmer_offs; uint32_t* ent_branch; float* ent_score;     // CSR by k-mer, or kmer_keys == null
+        uint64_t* status;                  // [tiles][2]
+        uint32_t* ticket;
+        unsigned long long* totals;        // [0] records, [1] k-mers
+        uint32_t epoch;
+    };
+
+    __global__ void __launch_bounds__(MG_THREADS) mg_merge(const __grid_constant__ merge_args A)
+    {
+        __shared__ uint64_t sk[MG_TILE + 1];            // sk[0] = the key before the tile
+        __shared__ float ss[MG_TILE];
+        __shared__ uint32_t s_cnt[2][MG_ITEMS][MG_WARPS];
+        __shared__ uint32_t s_tile, s_before[2];
+
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const unsigned full = 0xffffffffu;
+        if (tid == 0) s_tile = atomicAdd(A.ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        const uint64_t base = uint64_t(tile) * MG_TILE;
+        const uint32_t tile_n = uint32_t(min(uint64_t(MG_TILE), A.n - base));
 #pragma unroll
-            for (int i = 0; i < MG_ITEMS; ++i)
+        for (int j = 0; j < MG_ITEMS; ++j)
+        {
+            const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+            if (q < tile_n) { sk[q + 1] = A.ckeys[base + q]; ss[q] = A.scores[base + q]; }
+        }
+        if (tid == 0) sk[0] = base ? A.ckeys[base - 1] : ~A.ckeys[0];
+        __syncthreads();
+        // heads: a record whose composite key differs from its predecessor's; a k-mer head: whose k-mer differs
+        unsigned hb[MG_ITEMS], kb[MG_ITEMS];
+#pragma unroll
+        for (int j = 0; j < MG_ITEMS; ++j)
+        {
+            const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+            bool head = false, khead = false;
+            if (q < tile_n)
             {
-                if (base + i < n)
-                {
-                    k[i] = ckeys[base + i];
-                    c1 += k[i] != prev;
-                    c2 += (k[i] >> group_bits) != (prev >> group_bits) || (base + i == 0);
-                    prev = k[i];
-                }
+                const uint64_t cur = sk[q + 1], prev = sk[q];
+                head = cur != prev;
+                khead = (cur >> A.group_bits) != (prev >> A.group_bits) || (base + q == 0);
+            }
+            hb[j] = __ballot_sync(full, head);
+            kb[j] = __ballot_sync(full, khead);
+            if (lane == 0) { s_cnt[0][j][warp] = __popc(hb[j]); s_cnt[1][j][warp] = __popc(kb[j]); }
+        }
+        __syncthreads();
+        // exclusive scan of the MG_ITEMS * MG_WARPS partial counts (tile order = row, warp), one warp per counter
+        if (warp < 2)
+        {
+            uint32_t* c = &s_cnt[warp][0][0];
+            constexpr int N = MG_ITEMS * MG_WARPS, PER = (N + 31) / 32;
+            uint32_t v[PER], sum = 0;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; v[i] = e < N ? c[e] : 0; sum += v[i]; }
+            const uint32_t inc = warp_incl_scan(sum, lane);
+            const uint32_t total = __shfl_sync(full, inc, 31);
+            uint32_t run = inc - sum;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; if (e < N) c[e] = run; run += v[i]; }
+            // publish, look back, publish the inclusive value
+            uint64_t* mine = A.status + uint64_t(tile) * 2 + warp;
+            if (lane == 0) *reinterpret_cast<volatile uint64_t*>(mine) = rs_status(A.epoch, tile == 0 ? RS_FLAG_INCL : RS_FLAG_LOCAL, total);
+            uint32_t before = 0;
+            if (tile > 0)
+            {
+                before = warp_look_back(A.status + warp, tile, 2, A.epoch, lane);
+                if (lane == 0) *reinterpret_cast<volatile uint64_t*>(mine) = rs_status(A.epoch, RS_FLAG_INCL, before + total);
+            }
+            if (lane == 0)
+            {
+                s_before[warp] = before;
+                if (base + tile_n == A.n) A.totals[warp] = (unsigned long long)(before) + total;      // the last tile knows the grand totals
             }
         }
-        uint64_t r1 = uint64_t(rec_offs[blockIdx.x]) + block_excl_scan_256(c1, s_warp, nullptr);
-        uint64_t r2 = uint64_t(kmer_offs_tile[blockIdx.x]) + block_excl_scan_256(c2, s_warp, nullptr);
-        if (base >= n) return;
-        const uint64_t group_mask = (1ull << group_bits) - 1;
-        uint64_t prev = prev0;
+        __syncthreads();
+        const uint64_t group_mask = (1ull << A.group_bits) - 1;
+        const uint32_t lt = (1u << lane) - 1;
 #pragma unroll
-        for (int i = 0; i < MG_ITEMS; ++i)
+        for (int j = 0; j < MG_ITEMS; ++j)
         {
-            if (base + i < n)
+            if (!((hb[j] >> lane) & 1)) continue;
+            const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+            const uint64_t cur = sk[q + 1];
+            // head of a run of equal (kmer, group): maximum score of the run (runs may leave the tile)
+            float m = ss[q];
+            uint32_t r = q + 1;
+            for (; r < tile_n && sk[r + 1] == cur; ++r) { const float v = ss[r]; if (m < v) m = v; }   // branch_group.cpp:92 `it->second < kmer.score`
+            if (r == tile_n)
+                for (uint64_t g = base + tile_n; g < A.n && A.ckeys[g] == cur; ++g) { const float v = A.scores[g]; if (m < v) m = v; }
+            const uint64_t r1 = uint64_t(s_before[0]) + s_cnt[0][j][warp] + __popc(hb[j] & lt);
+            const uint32_t group = uint32_t(cur & group_mask) + A.group_add;
+            if (A.u_keys) { A.u_keys[r1] = ((cur >> A.group_bits) << A.out_group_bits) | group; A.u_scores[r1] = m; }
+            if (A.kmer_keys)
             {
-                const uint64_t cur = k[i];
-                if (cur != prev)
+                A.ent_branch[r1] = A.group_branch[group];
+                A.ent_score[r1] = m;
+                if ((kb[j] >> lane) & 1)
                 {
-                    // head of a run of equal (kmer, group): maximum score of the run (runs may cross tiles)
-                    float m = scores[base + i];
-                    for (uint64_t j = base + i + 1; j < n && ckeys[j] == cur; ++j)
-                    {
-                        const float v = scores[j];
-                        if (m < v) m = v;                           // branch_group.cpp:92 `it->second < kmer.score`
-                    }
-                    const uint32_t group = uint32_t(cur & group_mask) + group_add;
-                    if (u_keys) { u_keys[r1] = ((cur >> group_bits) << out_group_bits) | group; u_scores[r1] = m; }
-                    if (kmer_keys)
-                    {
-                        ent_branch[r1] = group_branch[group];
-                        ent_score[r1] = m;
-                        if ((cur >> group_bits) != (prev >> group_bits) || (base + i == 0))
-                        {
-                            kmer_keys[r2] = cur >> group_bits;
-                            kmer_offs[r2] = r1;
-                            ++r2;
-                        }
-                    }
-                    ++r1;
+                    const uint64_t r2 = uint64_t(s_before[1]) + s_cnt[1][j][warp] + __popc(kb[j] & lt);
+                    A.kmer_keys[r2] = cur >> A.group_bits;
+                    A.kmer_offs[r2] = r1;
                 }
-                prev = cur;
             }
         }
     }

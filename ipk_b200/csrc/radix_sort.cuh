@@ -12,10 +12,6 @@
 
 namespace ipkgpu
 {
-    constexpr int RS_THREADS = 256;
-    constexpr int RS_ITEMS = 12;
-    constexpr int RS_TILE = RS_THREADS * RS_ITEMS;      // 3072 pairs per CTA: 46 KB of static shared memory, 4 CTAs / SM
-    constexpr int RS_WARPS = RS_THREADS / 32;
     constexpr int RS_RADIX = 256;
 
     // ------------------------------------------------------------------------------------------------------------
@@ -234,51 +230,56 @@ namespace ipkgpu
     constexpr uint64_t RS_FLAG_LOCAL = 1, RS_FLAG_INCL = 2;
     __device__ __forceinline__ uint64_t rs_status(uint32_t epoch, uint64_t flag, uint32_t value) { return uint64_t(epoch) << 34 | flag << 32 | value; }
 
-    /// One pass over one tile (tile ids are handed out by an atomic ticket, so every predecessor a tile waits for is
-    /// already running).  digit_base = exclusive scan of this pass's global digit histogram.
-    template<class DigitFn>
-    __global__ void __launch_bounds__(RS_THREADS) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                                                              uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-                                                              const uint32_t* __restrict__ digit_base, uint64_t n,
-                                                              uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit)
+    /// shared memory of rs_onesweep<THREADS, ITEMS>: wh u32[WARPS][256], dbase u32[256], goff u32[256], misc u32[16], sk u64[TILE]
+    template<int THREADS, int ITEMS> constexpr size_t rs_smem_bytes() { return size_t(THREADS / 32) * RS_RADIX * 4 + 2 * RS_RADIX * 4 + 64 + size_t(THREADS) * ITEMS * 8; }
+
+    /// One pass over one tile of THREADS * ITEMS pairs (tile ids are handed out by an atomic ticket, so every predecessor a
+    /// tile waits for is already running).  digit_base = exclusive scan of this pass's global digit histogram.
+    template<int THREADS, int ITEMS, class DigitFn>
+    __global__ void __launch_bounds__(THREADS) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                           uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                           const uint32_t* __restrict__ digit_base, uint64_t n,
+                                                           uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit)
     {
-        __shared__ uint32_t wh[RS_WARPS][RS_RADIX];     // per-warp digit counts, then exclusive offsets over warps
-        __shared__ uint32_t dbase[RS_RADIX];            // tile-local position of the first key with digit d
-        __shared__ uint32_t goff[RS_RADIX];             // global position of the first key of this tile with digit d, minus dbase
-        __shared__ uint32_t s_warp[9];
-        __shared__ uint32_t s_tile;
-        __shared__ uint64_t sk[RS_TILE];
-        uint32_t* sv = reinterpret_cast<uint32_t*>(sk);  // the values reuse the key buffer once the keys are written out
+        constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
+        static_assert(THREADS >= RS_RADIX && THREADS % 32 == 0, "one thread per digit is needed");
+        extern __shared__ __align__(16) unsigned char rs_smem[];
+        uint64_t* sk = reinterpret_cast<uint64_t*>(rs_smem);                        // [TILE]; the values reuse it once the keys are out
+        uint32_t* sv = reinterpret_cast<uint32_t*>(sk);
+        uint32_t (*wh)[RS_RADIX] = reinterpret_cast<uint32_t (*)[RS_RADIX]>(sk + TILE);   // per-warp digit counts, then exclusive offsets over warps
+        uint32_t* dbase = &wh[0][0] + WARPS * RS_RADIX;                             // tile-local position of the first key with digit d
+        uint32_t* goff = dbase + RS_RADIX;                                          // global position of the tile's first key with digit d, minus dbase
+        uint32_t* s_misc = goff + RS_RADIX;                                         // [0..8] warp sums of the digit scan, [15] tile id
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const unsigned full = 0xffffffffu;
-        if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-        for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&wh[0][0])[i] = 0;
+        if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
+        for (int i = tid; i < WARPS * RS_RADIX; i += THREADS) (&wh[0][0])[i] = 0;
         __syncthreads();
-        const uint32_t tile = s_tile;
-        const uint64_t tile_base = uint64_t(tile) * RS_TILE;
-        const uint32_t tile_n = uint32_t(min(uint64_t(RS_TILE), n - tile_base));
+        const uint32_t tile = s_misc[15];
+        const uint64_t tile_base = uint64_t(tile) * TILE;
+        const uint32_t tile_n = uint32_t(min(uint64_t(TILE), n - tile_base));
 
-        uint64_t key[RS_ITEMS];
-        uint16_t rank[RS_ITEMS];
+        uint64_t key[ITEMS];
+        uint32_t val[ITEMS];
+        uint16_t rank[ITEMS];
         // warp w owns items [w*32*ITEMS, (w+1)*32*ITEMS) of the tile, 32 consecutive items per round: order = (warp, round, lane)
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
             key[i] = li < tile_n ? keys_in[tile_base + li] : ~0ull;
         }
-        uint32_t val[RS_ITEMS];
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
             val[i] = li < tile_n ? vals_in[tile_base + li] : 0u;
         }
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
             const bool valid = li < tile_n;
             const uint32_t d = valid ? digit(key[i]) : RS_RADIX;   // invalid lanes form their own group
             const unsigned peers = __match_any_sync(full, d);
@@ -294,43 +295,60 @@ namespace ipkgpu
             __syncwarp();
         }
         __syncthreads();
-        // digit d = tid: exclusive prefix over warps and the tile's count
+        // digit d = tid (< 256): exclusive prefix over warps, the tile's count, its status word and the look-back
+        const bool is_digit = tid < RS_RADIX;
         uint32_t cnt = 0;
+        if (is_digit)
+        {
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; ++w)
-        {
-            const uint32_t t = wh[w][tid];
-            wh[w][tid] = cnt;
-            cnt += t;
-        }
-        // publish the tile's own count, then look back for the sum over all preceding tiles
-        uint64_t* my_status = status + uint64_t(tile) * RS_RADIX + tid;
-        if (tile == 0) *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, cnt);
-        else *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_LOCAL, cnt);
-        const uint32_t ex_local = block_excl_scan_256(cnt, s_warp, nullptr);
-        uint32_t before = 0;
-        if (tile > 0)
-        {
-            const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
-            while (true)
+            for (int w = 0; w < WARPS; ++w)
             {
-                const uint64_t w = *p;
-                if (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0) continue;      // not published yet in this pass
-                before += uint32_t(w);
-                if (((w >> 32) & 3) == RS_FLAG_INCL) break;
-                p -= RS_RADIX;
+                const uint32_t t = wh[w][tid];
+                wh[w][tid] = cnt;
+                cnt += t;
             }
-            *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
         }
-        dbase[tid] = ex_local;
-        goff[tid] = digit_base[tid] + before - ex_local;
+        uint64_t* my_status = status + uint64_t(tile) * RS_RADIX + (is_digit ? tid : 0);
+        if (is_digit)
+            *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, tile == 0 ? RS_FLAG_INCL : RS_FLAG_LOCAL, cnt);
+        // exclusive scan of cnt over the 256 digits (threads >= 256 only take part in the barriers)
+        const uint32_t inc = warp_incl_scan(cnt, lane);
+        if (is_digit && lane == 31) s_misc[warp] = inc;
+        __syncthreads();
+        if (warp == 0)
+        {
+            const uint32_t w = lane < 8 ? s_misc[lane] : 0;
+            const uint32_t winc = warp_incl_scan(w, lane);
+            if (lane < 8) s_misc[lane] = winc - w;
+        }
+        __syncthreads();
+        if (is_digit)
+        {
+            const uint32_t ex_local = s_misc[warp] + inc - cnt;
+            uint32_t before = 0;
+            if (tile > 0)
+            {
+                const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
+                while (true)
+                {
+                    const uint64_t w = *p;
+                    if (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0) continue;      // not published yet in this pass
+                    before += uint32_t(w);
+                    if (((w >> 32) & 3) == RS_FLAG_INCL) break;
+                    p -= RS_RADIX;
+                }
+                *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
+            }
+            dbase[tid] = ex_local;
+            goff[tid] = digit_base[tid] + before - ex_local;
+        }
         __syncthreads();
         // keys: tile-local order -> shared memory -> runs of equal digits to global memory
-        uint32_t pos[RS_ITEMS];
+        uint32_t pos[ITEMS];
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
             pos[i] = 0;
             if (li < tile_n)
             {
@@ -340,11 +358,11 @@ namespace ipkgpu
             }
         }
         __syncthreads();
-        uint32_t gpos[RS_ITEMS];
+        uint32_t gpos[ITEMS];
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t q = uint32_t(i) * RS_THREADS + tid;
+            const uint32_t q = uint32_t(i) * THREADS + tid;
             gpos[i] = 0;
             if (q < tile_n)
             {
@@ -356,19 +374,26 @@ namespace ipkgpu
         // values: same route through the (reused) shared buffer
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t li = warp * (32 * RS_ITEMS) + i * 32 + lane;
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
             if (li < tile_n) sv[pos[i]] = val[i];
         }
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < RS_ITEMS; ++i)
+        for (int i = 0; i < ITEMS; ++i)
         {
-            const uint32_t q = uint32_t(i) * RS_THREADS + tid;
+            const uint32_t q = uint32_t(i) * THREADS + tid;
             if (q < tile_n) vals_out[gpos[i]] = sv[q];
         }
     }
+
+    /// tile shapes the sweep kernel is instantiated for; ctx->rs_shape picks one (tuning knob, 0 = default)
+    struct rs_shape { int threads, items; };
+    constexpr rs_shape RS_SHAPES[] = { { 256, 12 }, { 256, 16 }, { 384, 16 }, { 512, 12 }, { 512, 16 }, { 384, 20 } };
+    constexpr int RS_N_SHAPES = int(sizeof(RS_SHAPES) / sizeof(RS_SHAPES[0]));
+    inline rs_shape rs_current_shape(const ipkgpu_ctx* ctx) { return RS_SHAPES[ctx->rs_shape >= 0 && ctx->rs_shape < RS_N_SHAPES ? ctx->rs_shape : 0]; }
+    inline uint32_t rs_tile(const ipkgpu_ctx* ctx) { const rs_shape s = rs_current_shape(ctx); return uint32_t(s.threads * s.items); }
 
     /// scratch of the sort inside `table`: [0, 8*256) u32 digit histograms / bases of up to 8 passes, then 16 u32 tickets.
     /// The status words live in ctx->rs_status (zeroed when it grows; epochs keep passes apart afterwards).
@@ -381,7 +406,7 @@ namespace ipkgpu
 
     inline rs_scratch rs_prepare(ipkgpu_ctx* ctx, uint64_t n, dbuf& table)
     {
-        const uint64_t n_tiles = div_up<uint64_t>(n, RS_TILE);
+        const uint64_t n_tiles = div_up<uint64_t>(n, rs_tile(ctx));
         ctx->reserve(table, (RS_MAX_PASSES * RS_RADIX + 16) * 4);
         const size_t want = n_tiles * RS_RADIX * 8;
         if (want > ctx->rs_status.cap)
@@ -404,6 +429,33 @@ namespace ipkgpu
         return ctx->rs_epoch;
     }
 
+    template<int THREADS, int ITEMS, class DigitFn>
+    inline void rs_launch_shape(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout,
+                                const uint32_t* digit_base, uint64_t n, uint64_t* status, uint32_t* ticket, DigitFn digit)
+    {
+        constexpr size_t smem = rs_smem_bytes<THREADS, ITEMS>();
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, uint64_t(THREADS) * ITEMS));
+        IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
+                   rs_onesweep<THREADS, ITEMS, DigitFn><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, digit_base, n, status, ticket,
+                                                                                                 rs_next_epoch(ctx), digit));
+    }
+
+    template<class DigitFn>
+    inline void rs_launch_onesweep(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout,
+                                   const uint32_t* digit_base, uint64_t n, uint64_t* status, uint32_t* ticket, DigitFn digit)
+    {
+        switch (ctx->rs_shape)
+        {
+        case 1: rs_launch_shape<256, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        case 2: rs_launch_shape<384, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        case 3: rs_launch_shape<512, 12>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        case 4: rs_launch_shape<512, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        case 5: rs_launch_shape<384, 20>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        default: rs_launch_shape<256, 12>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        }
+    }
+
     /// One stable bucketing pass (histogram -> scan -> one sweep) under an arbitrary digit function.  Leaves the
     /// exclusive digit starts in table[0..256) (device) for the caller.
     template<class DigitFn>
@@ -413,12 +465,10 @@ namespace ipkgpu
         (void)scan_tmp;
         if (n == 0) return;
         const rs_scratch S = rs_prepare(ctx, n, table);
-        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
         const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * 8), uint64_t(ctx->num_sms) * 8));
         IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_fn<DigitFn><<<hgrid, RS_HIST_THREADS, 0, ctx->stream>>>(kin, n, digit, S.hist));
         IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(S.hist));
-        IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
-                   rs_onesweep<DigitFn><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, S.hist, n, S.status, S.tickets, rs_next_epoch(ctx), digit));
+        rs_launch_onesweep(ctx, kin, vin, kout, vout, S.hist, n, S.status, S.tickets, digit);
     }
 
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);
@@ -434,7 +484,6 @@ namespace ipkgpu
         if (passes_out) *passes_out = passes;
         if (n == 0 || passes == 0) return false;
         const rs_scratch S = rs_prepare(ctx, n, table);
-        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, RS_TILE));
         const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * RS_HIST_ITEMS), uint64_t(ctx->num_sms) * 8));
         IPK_LAUNCH(ctx, "rs_hist", n * 8,
                    rs_hist_bits<<<hgrid, RS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(ka, n, bit_begin, n_bits, passes, S.hist));
@@ -445,13 +494,8 @@ namespace ipkgpu
             const uint32_t shift = p * 8;
             const uint32_t width = std::min<uint32_t>(8, n_bits - shift);
             const uint32_t mask = (1u << width) - 1;
-            const uint64_t* kin = in_b ? kb : ka;
-            const uint32_t* vin = in_b ? vb : va;
-            uint64_t* kout = in_b ? ka : kb;
-            uint32_t* vout = in_b ? va : vb;
-            IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
-                       rs_onesweep<digit_bits><<<n_tiles, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, S.hist + p * RS_RADIX, n, S.status, S.tickets + p,
-                                                                                        rs_next_epoch(ctx), digit_bits{ bit_begin + shift, mask }));
+            rs_launch_onesweep(ctx, in_b ? kb : ka, in_b ? vb : va, in_b ? ka : kb, in_b ? va : vb, S.hist + p * RS_RADIX, n, S.status, S.tickets + p,
+                               digit_bits{ bit_begin + shift, mask });
             in_b = !in_b;
         }
         return in_b;

@@ -53,6 +53,7 @@ def main():
     ap.add_argument("--so", default=os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "ipk_b200", "libipkgpu.so"))
     ap.add_argument("--top", type=int, default=40)
     ap.add_argument("--launch", type=int, default=0, help="which matching launch of the report (0 = first)")
+    ap.add_argument("--mangled", default=None, help="regex on the mangled name in the cubin (default: the kernel regex)")
     ap.add_argument("--by", default="samples", choices=["samples", "inst", "thread"])
     ap.add_argument("--sass", action="store_true", help="also list the hottest SASS instructions")
     a = ap.parse_args()
@@ -75,7 +76,7 @@ def main():
     b = blocks[min(a.launch, len(blocks) - 1)]
     hdr = b["hdr"]
     col = {n: i for i, n in enumerate(hdr)}
-    lines = sass_lines(a.so, a.kernel)
+    lines = sass_lines(a.so, a.mangled or a.kernel)
     if len(lines) != len(b["rows"]):
         print(f"warning: {len(lines)} SASS instructions in the cubin vs {len(b['rows'])} in the report (rebuilt since?)", file=sys.stderr)
     n = min(len(lines), len(b["rows"]))
