@@ -145,10 +145,36 @@ namespace ipkgpu
         uint32_t n_nodes, W, sigma, bits, group_bits, tiles_per_node, nwin;
         float log_threshold;
         int use_tma;
-        const uint32_t* tile_list;    // depth-first kernel: blockIdx.x -> tile index (null: identity)
-        uint32_t* deferred_tiles;     // join kernel: tiles it hands to the depth-first kernel; their number is counter[1]
+        // Work items.  An item is a run of item_windows consecutive windows (a power of two <= ENUM_THREADS) inside one
+        // (node, ENUM_THREADS-window) tile: item id = tile * items_per_tile + sub.  blockIdx.x is the item id itself, or -- when
+        // tile_list is set -- child blockIdx.x % parent_ratio of the coarser item tile_list[blockIdx.x / parent_ratio].
+        const uint32_t* tile_list;
+        uint32_t item_windows, items_per_tile, parent_ratio;
+        uint32_t* deferred_tiles;     // join kernel: items it could not finish (lists too long for the pool ...); their number is counter[1]
         uint32_t pool_cap;            // join kernel: list-pool capacity in elements (<= 65535)
+        uint32_t small_list;          // join kernel: lists up to this length are filled and sorted by their owner thread
     };
+
+    struct tile_geom
+    {
+        uint32_t item, lslot, node, s0;
+        int nwin;
+    };
+
+    /// false: the item lies past the node's last window (nothing to do)
+    __device__ __forceinline__ bool tile_geometry(const enum_args& A, tile_geom& g)
+    {
+        uint32_t item = blockIdx.x;
+        if (A.tile_list) item = A.tile_list[blockIdx.x / A.parent_ratio] * A.parent_ratio + blockIdx.x % A.parent_ratio;
+        const uint32_t tile = item / A.items_per_tile, sub = item % A.items_per_tile;
+        g.item = item;
+        g.lslot = A.slot_base + tile / A.tiles_per_node;
+        g.node = A.node_order[g.lslot];
+        g.s0 = (tile % A.tiles_per_node) * ENUM_THREADS + sub * A.item_windows;
+        if (g.s0 >= A.nwin) { g.nwin = 0; return false; }
+        g.nwin = int(min(A.item_windows, A.nwin - g.s0));
+        return true;
+    }
 
     __device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
 
@@ -268,11 +294,10 @@ namespace ipkgpu
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma);
-        const uint32_t tile = A.tile_list ? A.tile_list[blockIdx.x] : blockIdx.x;
-        const uint32_t lslot = A.slot_base + tile / A.tiles_per_node;
-        const uint32_t node = A.node_order[lslot];
-        const uint32_t s0 = (tile % A.tiles_per_node) * ENUM_THREADS;
-        const int nwin_tile = int(min(uint32_t(ENUM_THREADS), A.nwin - s0));
+        tile_geom G;
+        if (!tile_geometry(A, G)) return;
+        const uint32_t lslot = G.lslot, node = G.node, s0 = G.s0;
+        const int nwin_tile = G.nwin;
         const int ncols = nwin_tile + k - 1;
         const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
 

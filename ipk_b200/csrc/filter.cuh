@@ -33,8 +33,8 @@ namespace ipkgpu
     // reference's while no lane ever waits for another k-mer's chain.
     // ----------------------------------------------------------------------------------------------------------
     constexpr int MIF_THREADS = 256;
-    constexpr int MIF_CHUNK = 2048;          // entries per CTA chunk (k-mers are assigned by their first entry)
-    constexpr int MIF_CAP = 4096;            // entries a CTA can stage; longer runs take the streaming path
+    constexpr int MIF_CHUNK = 1024;          // entries per CTA chunk (k-mers are assigned by their first entry)
+    constexpr int MIF_CAP = 2048;            // entries a CTA can stage; longer runs take the streaming path
     constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CHUNK) * 8 + size_t(MIF_CHUNK + 2) * 4 + size_t(MIF_CAP) * 2;
 
     /// chunk_first[b] = first k-mer whose entries start at or after b * MIF_CHUNK  (b = 0 .. n_chunks; last = n_kmers)
@@ -94,7 +94,14 @@ namespace ipkgpu
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
                 double s = 0;
-                for (uint32_t i = a; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }     // filter.cpp:78-82
+                uint32_t i = a;
+                for (; i + 4 <= b; i += 4)                 // loads first, then the ordered adds (filter.cpp:78-82)
+                {
+                    const float x0 = xs[2 * i], x1 = xs[2 * i + 2], x2 = xs[2 * i + 4], x3 = xs[2 * i + 6];
+                    seg[i] = uint16_t(j); seg[i + 1] = uint16_t(j); seg[i + 2] = uint16_t(j); seg[i + 3] = uint16_t(j);
+                    s = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(s, double(x0)), double(x1)), double(x2)), double(x3));
+                }
+                for (; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
                 ssum[j] = s;
             }
             __syncthreads();
@@ -112,7 +119,14 @@ namespace ipkgpu
                 const uint32_t a = koff[j], b = koff[j + 1];
                 double ss = ssum[j], tt;
                 double H = mif0_tail_begin(ss, b - a, C, tt);
-                for (uint32_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);                            // :107
+                uint32_t i = a;
+                for (; i + 4 <= b; i += 4)
+                {
+                    const double t0 = slot[i], t1 = slot[i + 1], t2 = slot[i + 2], t3 = slot[i + 3];
+                    H = __dadd_rn(__dsub_rn(H, tt), t0); H = __dadd_rn(__dsub_rn(H, tt), t1);                         // :107
+                    H = __dadd_rn(__dsub_rn(H, tt), t2); H = __dadd_rn(__dsub_rn(H, tt), t3);
+                }
+                for (; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);
                 fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));                                                // :115
             }
             return;

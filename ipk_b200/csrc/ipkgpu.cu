@@ -151,20 +151,29 @@ namespace
 
     uint64_t read_u64(ipkgpu_ctx* ctx, const void* d);
 
-    /// default list-pool capacity of the join kernel (elements of 8 bytes): DNA-sized alphabets keep three CTAs per SM,
-    /// larger alphabets get most of the SM's shared memory
-    uint32_t default_pool_cap(const ipkgpu_input* in)
-    {
-        const uint32_t want = in->sigma <= 4 ? 3072u : 20000u;
-        return std::max(want, join_min_pool(int(in->k), int(in->sigma)));
-    }
-
     /// largest list pool one CTA of the join kernel can have (the whole shared memory of an SM)
     uint32_t max_pool_cap(const ipkgpu_input* in, int n_fam)
     {
         const size_t fixed = make_join_layout(int(in->k), int(in->sigma), n_fam, 0).total;
         const size_t avail = size_t(226) * 1024 > fixed ? size_t(226) * 1024 - fixed : 0;
         return uint32_t(std::min<size_t>(avail / 8, 65000));
+    }
+
+    struct enum_level { uint32_t pool, width; };       // pool 0 = the largest one CTA can hold
+
+    /// levels of the join kernel: IPKGPU_LEVELS="pool:width,pool:width,..." (tuning knob), an explicit pool from
+    /// ipkgpu_set_enumeration (a single level), or the defaults per alphabet
+    std::vector<enum_level> enumeration_levels(const ipkgpu_ctx* ctx, const ipkgpu_input* in)
+    {
+        if (ctx->pool_cap) return { { ctx->pool_cap, uint32_t(ENUM_THREADS) } };
+        if (!ctx->levels.empty())
+        {
+            std::vector<enum_level> v;
+            for (auto& p : ctx->levels) v.push_back({ p.first, p.second });
+            return v;
+        }
+        if (in->sigma <= 4) return { { 3072, 128 }, { 12288, 128 }, { 0, 128 }, { 0, 16 }, { 0, 1 } };
+        return { { 20000, 128 }, { 0, 128 }, { 0, 16 }, { 0, 1 } };
     }
 
     /// K2 over a range of launch slots: the list-join kernel, then the depth-first kernel on the tiles it deferred
@@ -205,54 +214,59 @@ namespace
         uint64_t n_deferred = grid;
         ctx->enum_join_emitted = 0;
         const bool use_join = in->k >= 2 && ctx->enum_mode != 1;
+        A.item_windows = ENUM_THREADS; A.items_per_tile = 1; A.parent_ratio = 1;
+        A.small_list = ctx->small_list;
         if (use_join)
         {
-            // Level 1: every tile with the default pool (several CTAs per SM).  Level 2: the tiles whose lists did not fit,
-            // again with the largest pool one SM can hold.  What is left after that goes to the depth-first kernel.
+            // Levels: every tile with a small pool (several CTAs per SM); what did not fit is retried with larger pools, then
+            // in narrower runs of windows (shorter lists); what is left after the last level goes to the depth-first kernel.
             const join_program J = make_join_program(int(in->k));
             const uint32_t min_pool = join_min_pool(int(in->k), int(in->sigma));
-            const uint32_t pool1 = std::min<uint32_t>(65000u, std::max(ctx->pool_cap ? ctx->pool_cap : default_pool_cap(in), min_pool));
             const uint32_t pool_max = std::max(max_pool_cap(in, J.n_fam), min_pool);
+            std::vector<enum_level> levels = enumeration_levels(ctx, in);
             ctx->reserve(ctx->deferred, grid * 4);
-            ctx->reserve(ctx->deferred2, grid * 4);
-            uint32_t* lists[2] = { ctx->deferred.as<uint32_t>(), ctx->deferred2.as<uint32_t>() };
-            uint64_t n_tiles_level = grid, emitted_before = 0;
-            // pool sizes of the levels: the default, four times that (still two or more CTAs per SM), everything
-            uint32_t pools[3] = { pool1, 0, 0 };
-            int n_levels = 1;
-            if (!ctx->pool_cap)
+            uint32_t* lists[2] = { nullptr, nullptr };
+            uint64_t n_items = grid, emitted_before = 0;            // items of the level about to run
+            uint32_t prev_width = ENUM_THREADS;
+            for (size_t level = 0; level < levels.size() && n_items > 0; ++level)
             {
-                if (uint64_t(pool1) * 4 + pool1 < pool_max) pools[n_levels++] = pool1 * 4;
-                if (pool_max > pools[n_levels - 1] + pools[n_levels - 1] / 4) pools[n_levels++] = pool_max;
-            }
-            for (int level = 0; level < n_levels && n_tiles_level > 0; ++level)
-            {
-                A.pool_cap = pools[level];
+                const uint32_t width = std::min<uint32_t>(levels[level].width, prev_width);
+                const uint32_t ratio = prev_width / width;
+                const uint64_t lvl_grid = n_items * ratio;
+                if (lvl_grid > 0x7fffffffull) break;
+                A.pool_cap = std::min(pool_max, std::max(levels[level].pool ? levels[level].pool : pool_max, min_pool));
+                A.item_windows = width; A.items_per_tile = ENUM_THREADS / width; A.parent_ratio = ratio;
                 A.tile_list = level == 0 ? nullptr : lists[(level - 1) & 1];
+                dbuf& out_list = (level & 1) ? ctx->deferred2 : ctx->deferred;
+                ctx->reserve(out_list, lvl_grid * 4);
+                lists[level & 1] = out_list.as<uint32_t>();
                 A.deferred_tiles = lists[level & 1];
                 IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
                 const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
                 if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
-                const uint64_t lvl_in_bytes = level == 0 ? in_bytes : n_tiles_level * uint64_t(ENUM_THREADS + in->k) * (in->sigma + 1) * 4;
+                const uint64_t lvl_in_bytes = level == 0 ? in_bytes : lvl_grid * uint64_t(width + in->k) * (in->sigma + 1) * 4;
                 if (L.debug)
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(n_tiles_level), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(lvl_grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 else
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(n_tiles_level), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 uint64_t h[2] = { 0, 0 };
                 IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
                 IPK_CUDA(cudaStreamSynchronize(ctx->stream));
                 ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], L.cap) - std::min<uint64_t>(emitted_before, L.cap)));
                 emitted_before = h[0];
-                n_tiles_level = h[1];
+                n_items = h[1];
+                prev_width = width;
                 A.tile_list = lists[level & 1];
             }
-            n_deferred = n_tiles_level;
+            // the depth-first kernel takes the remaining items as they are
+            A.parent_ratio = 1;
+            n_deferred = n_items;
             ctx->enum_join_emitted = emitted_before;
             ctx->last_deferred_tiles += n_deferred;
             ctx->last_tiles += grid;
@@ -696,7 +710,23 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     if (!ctx) { g_create_error = "host allocation failed"; return IPKGPU_ENOMEM; }
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
-    if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);      // tuning knob; the default is the product
+    if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
+    if (const char* e = getenv("IPKGPU_SMALL_LIST")) ctx->small_list = uint32_t(std::max(1, atoi(e)));
+    if (const char* e = getenv("IPKGPU_LEVELS"))
+    {
+        // "pool:width,pool:width,..."; width a power of two <= 128
+        const char* p = e;
+        while (*p)
+        {
+            char* q = nullptr;
+            const unsigned long pool = strtoul(p, &q, 10);
+            unsigned long width = ENUM_THREADS;
+            if (*q == ':') width = strtoul(q + 1, &q, 10);
+            if (width >= 1 && width <= uint32_t(ENUM_THREADS) && (width & (width - 1)) == 0) ctx->levels.push_back({ uint32_t(pool), uint32_t(width) });
+            p = *q == ',' ? q + 1 : q;
+            if (q == p && *p) break;
+        }
+    }      // tuning knob; the default is the product
     cudaSetDevice(device);
     if (stream) ctx->stream = static_cast<cudaStream_t>(stream);
     else

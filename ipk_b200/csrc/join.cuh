@@ -176,16 +176,16 @@ namespace ipkgpu
     /// comparison moves the larger element to the lower index), so the virtual -inf padding above n never moves.
     __device__ __forceinline__ void warp_sort_desc(unsigned long long* p, int n, int lane)
     {
-        int pw = 1;
-        while (pw < n) pw <<= 1;
-        const int half = pw >> 1;
-        for (int size = 2; size <= pw; size <<= 1)
+        int lg = 0;
+        while ((1 << lg) < n) ++lg;                       // pw = 1 << lg >= n
+        const int half = (1 << lg) >> 1;
+        for (int ls = 1; ls <= lg; ++ls)                   // merge blocks of size 1 << ls
         {
-            const int hs = size >> 1;
+            const int size = 1 << ls, lh = ls - 1;
             for (int t = lane; t < half; t += 32)
             {
-                const int blk = t / hs, j = t - blk * hs;
-                const int lo = blk * size + j, hi = blk * size + size - 1 - j;
+                const int blk = t >> lh, j = t & ((1 << lh) - 1);
+                const int lo = (blk << ls) + j, hi = (blk << ls) + size - 1 - j;
                 if (hi < n)
                 {
                     const unsigned long long a = p[lo], b = p[hi];
@@ -193,11 +193,11 @@ namespace ipkgpu
                 }
             }
             __syncwarp();
-            for (int d = hs >> 1; d >= 1; d >>= 1)
+            for (int ld = lh - 1; ld >= 0; --ld)           // half-cleaners at distance 1 << ld
             {
                 for (int t = lane; t < half; t += 32)
                 {
-                    const int lo = (t / d) * 2 * d + (t % d), hi = lo + d;
+                    const int lo = ((t >> ld) << (ld + 1)) + (t & ((1 << ld) - 1)), hi = lo + (1 << ld);
                     if (hi < n)
                     {
                         const unsigned long long a = p[lo], b = p[hi];
@@ -323,11 +323,10 @@ namespace ipkgpu
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma), bits = int(A.bits);
-        const uint32_t tile = A.tile_list ? A.tile_list[blockIdx.x] : blockIdx.x;
-        const uint32_t lslot = A.slot_base + tile / A.tiles_per_node;
-        const uint32_t node = A.node_order[lslot];
-        const uint32_t s0 = (tile % A.tiles_per_node) * ENUM_THREADS;
-        const int nwin_tile = int(min(uint32_t(ENUM_THREADS), A.nwin - s0));
+        tile_geom G;
+        if (!tile_geometry(A, G)) return;
+        const uint32_t lslot = G.lslot, node = G.node, s0 = G.s0, tile = G.item;
+        const int nwin_tile = G.nwin;
         const int ncols = nwin_tile + k - 1;
         const int NC = ENUM_THREADS + k - 1, NCP = (NC + 3) & ~3;
         const join_layout L = make_join_layout(k, sigma, J.n_fam, A.pool_cap);
@@ -423,7 +422,7 @@ namespace ipkgpu
                         n += uint32_t(l);
                     }
                     if (n > A.pool_cap) { s_defer = 1; n = 0; }
-                    else if (n > uint32_t(JOIN_SMALL_LIST)) queue[atomicAdd(&s_qn[f & 1], 1u)] = uint16_t(c);
+                    else if (n > A.small_list) queue[atomicAdd(&s_qn[f & 1], 1u)] = uint16_t(c);
                     else if (n)
                     {
                         if (!pool_alloc(&s_lo, &s_hi, top, int(n), off)) s_defer = 1;

@@ -104,7 +104,10 @@ namespace ipkgpu
             if (lane == 0) { s_cnt[0][j][warp] = __popc(hb[j]); s_cnt[1][j][warp] = __popc(kb[j]); }
         }
         __syncthreads();
-        // exclusive scan of the MG_ITEMS * MG_WARPS partial counts (tile order = row, warp), one warp per counter
+        // exclusive scan of the MG_ITEMS * MG_WARPS partial counts (tile order = row, warp), one warp per counter; the
+        // tile's totals are published at once so that the successors' look-backs find them early
+        uint32_t total = 0;
+        uint64_t* mine = A.status + uint64_t(tile) * 2 + (warp < 2 ? warp : 0);
         if (warp < 2)
         {
             uint32_t* c = &s_cnt[warp][0][0];
@@ -113,13 +116,30 @@ namespace ipkgpu
 #pragma unroll
             for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; v[i] = e < N ? c[e] : 0; sum += v[i]; }
             const uint32_t inc = warp_incl_scan(sum, lane);
-            const uint32_t total = __shfl_sync(full, inc, 31);
+            total = __shfl_sync(full, inc, 31);
             uint32_t run = inc - sum;
 #pragma unroll
             for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; if (e < N) c[e] = run; run += v[i]; }
-            // publish, look back, publish the inclusive value
-            uint64_t* mine = A.status + uint64_t(tile) * 2 + warp;
             if (lane == 0) *reinterpret_cast<volatile uint64_t*>(mine) = rs_status(A.epoch, tile == 0 ? RS_FLAG_INCL : RS_FLAG_LOCAL, total);
+        }
+        // maximum score of every run that starts in this tile (runs may leave the tile): needs no global offsets
+        float best[MG_ITEMS];
+#pragma unroll
+        for (int j = 0; j < MG_ITEMS; ++j)
+        {
+            best[j] = 0.0f;
+            if (!((hb[j] >> lane) & 1)) continue;
+            const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+            const uint64_t cur = sk[q + 1];
+            float m = ss[q];
+            uint32_t r = q + 1;
+            for (; r < tile_n && sk[r + 1] == cur; ++r) { const float v = ss[r]; if (m < v) m = v; }   // branch_group.cpp:92 `it->second < kmer.score`
+            if (r == tile_n)
+                for (uint64_t g = base + tile_n; g < A.n && A.ckeys[g] == cur; ++g) { const float v = A.scores[g]; if (m < v) m = v; }
+            best[j] = m;
+        }
+        if (warp < 2)
+        {
             uint32_t before = 0;
             if (tile > 0)
             {
@@ -141,12 +161,7 @@ namespace ipkgpu
             if (!((hb[j] >> lane) & 1)) continue;
             const uint32_t q = uint32_t(j) * MG_THREADS + tid;
             const uint64_t cur = sk[q + 1];
-            // head of a run of equal (kmer, group): maximum score of the run (runs may leave the tile)
-            float m = ss[q];
-            uint32_t r = q + 1;
-            for (; r < tile_n && sk[r + 1] == cur; ++r) { const float v = ss[r]; if (m < v) m = v; }   // branch_group.cpp:92 `it->second < kmer.score`
-            if (r == tile_n)
-                for (uint64_t g = base + tile_n; g < A.n && A.ckeys[g] == cur; ++g) { const float v = A.scores[g]; if (m < v) m = v; }
+            const float m = best[j];
             const uint64_t r1 = uint64_t(s_before[0]) + s_cnt[0][j][warp] + __popc(hb[j] & lt);
             const uint32_t group = uint32_t(cur & group_mask) + A.group_add;
             if (A.u_keys) { A.u_keys[r1] = ((cur >> A.group_bits) << A.out_group_bits) | group; A.u_scores[r1] = m; }
