@@ -130,11 +130,17 @@ int  ipkgpu_enumerate(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint64_t cap,
  * *n_out = their number.  stats may be NULL. */
 int  ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out,
                    ipkgpu_stats* stats);
+/* Same, without the local sort and per-branch max: the records are left as emitted (duplicates of a (k-mer, group)
+ * included, any order), so that they are sorted ONCE, by their owner rank after the exchange -- stage 2 with
+ * chunks_group_ordered = 0 takes the maximum over equal composite keys.  If the emitted volume does not fit the
+ * workspace the call falls back to batches of whole groups merged locally (records then unique, as ipkgpu_stage1). */
+int  ipkgpu_stage1_raw(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out,
+                       ipkgpu_stats* stats);
 /* Buckets the stage-1 records by owner = mix64(kmer) % n_parts, stably, into caller-provided DEVICE buffers of n_out
  * records (the send buffers of the all-to-all); counts[n_parts] (host) receives the bucket sizes. */
 int  ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys, float* d_scores, uint64_t* counts);
 /* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
- * values -> order.  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
+ * values -> order (equal composite keys are merged by maximum score).  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
  * chunks_group_ordered != 0 promises that the records are a concatenation of chunks in ascending group ranges, each
  * sorted by (kmer, group) -- what the all-to-all of stably partitioned stage-1 records delivers -- so that a stable
  * sort on the k-mer bits alone suffices; 0 sorts on all key_bits + group_bits.

@@ -126,6 +126,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_enumerate.restype = C.c_int
     lib.ipkgpu_stage1.argtypes = [C.c_void_p, P(Input), C.c_uint32, C.c_uint32, P(C.c_uint64), P(Stats)]
     lib.ipkgpu_stage1.restype = C.c_int
+    lib.ipkgpu_stage1_raw.argtypes = [C.c_void_p, P(Input), C.c_uint32, C.c_uint32, P(C.c_uint64), P(Stats)]
+    lib.ipkgpu_stage1_raw.restype = C.c_int
     lib.ipkgpu_stage1_partition.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, P(C.c_uint64)]
     lib.ipkgpu_stage1_partition.restype = C.c_int
     lib.ipkgpu_stage2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
@@ -308,10 +310,12 @@ class Context:
         m = min(int(n.value), cap)
         return int(n.value), node[:m], win[:m], key[:m], score[:m]
 
-    def stage1(self, inp: Input, group_base: int, group_bits: int) -> tuple[int, dict]:
+    def stage1(self, inp: Input, group_base: int, group_bits: int, raw: bool = False) -> tuple[int, dict]:
+        """raw: leave the records as emitted (no local sort / per-branch max): they are sorted once, after the exchange"""
         n = C.c_uint64(0)
         st = Stats()
-        self._check(self._lib.ipkgpu_stage1(self._h, C.byref(inp), group_base, group_bits, C.byref(n), C.byref(st)))
+        fn = self._lib.ipkgpu_stage1_raw if raw else self._lib.ipkgpu_stage1
+        self._check(fn(self._h, C.byref(inp), group_base, group_bits, C.byref(n), C.byref(st)))
         return int(n.value), st.as_dict()
 
     def stage1_partition(self, n_parts: int, d_keys, d_scores) -> np.ndarray:

@@ -90,6 +90,8 @@ struct ipkgpu_ctx
     // stage-1 state kept for ipkgpu_stage1_partition
     uint64_t s1_n = 0;
     uint32_t s1_group_bits = 0;
+    uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
+    uint32_t* s1_scores = nullptr;
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
     // pinned host staging
     ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score;

@@ -385,7 +385,7 @@ namespace
     /// With want_csr and a single batch the CSR by k-mer comes out of the same K3 pass; otherwise the unique
     /// records are left in ctx->u_keys/u_scores as (kmer << group_bits) | global group, batch after batch.
     stage1_out run_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& T, uint32_t group_base, uint32_t group_bits,
-                          bool want_csr, ipkgpu_stats* st, stage_timer& tm)
+                          bool want_csr, ipkgpu_stats* st, stage_timer& tm, bool raw = false)
     {
         stage1_out o;
         o.n_groups = uint32_t(T.group_branch.size());
@@ -422,7 +422,8 @@ namespace
 
         ctx->reserve(ctx->keys_a, cap0 * 8);
         ctx->reserve(ctx->vals_a, cap0 * 4);
-        enum_launch L{ 0, in->n_nodes, group_base, all_bits, cap0, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
+        // raw: the records leave this rank unsorted and unmerged, so they carry the GLOBAL group field from the start
+        enum_launch L{ 0, in->n_nodes, raw ? 0u : group_base, raw ? group_bits : all_bits, cap0, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
         launch_enumerate(ctx, d_logp, in, P, L, true);
         o.enum_launches = 1;
         o.n_emitted = read_u64(ctx, ctx->counters.p);
@@ -451,6 +452,21 @@ namespace
             batches.push_back({ g0, o.n_groups, acc });
         }
         size_t e_prev = tm.mark();
+        ctx->s1_keys = nullptr; ctx->s1_scores = nullptr;
+        if (raw && first_valid)
+        {
+            IPK_CUDA(cudaEventSynchronize(ctx->event(e_prev)));
+            o.ms_h2d = tm.ms(eh, e0);
+            o.ms_prefix = tm.ms(e0, e1);
+            o.ms_enumerate = tm.ms(e1, e_prev);
+            o.n_unique = o.n_emitted;
+            o.n_batches = 1;
+            ctx->s1_n = o.n_emitted;
+            ctx->s1_group_bits = group_bits;
+            ctx->s1_keys = ctx->keys_a.as<uint64_t>();
+            ctx->s1_scores = ctx->vals_a.as<uint32_t>();
+            return o;
+        }
         o.ms_h2d = tm.ms(eh, e0);
         o.ms_prefix = tm.ms(e0, e1);
         float ms_enum = 0, ms_sort = 0, ms_merge = 0;
@@ -499,6 +515,8 @@ namespace
         o.ms_enumerate = ms_enum; o.ms_sort = ms_sort; o.ms_merge = ms_merge;
         ctx->s1_n = o.csr_done ? 0 : u_off;
         ctx->s1_group_bits = group_bits;
+        ctx->s1_keys = ctx->u_keys.as<uint64_t>();
+        ctx->s1_scores = ctx->u_scores.as<uint32_t>();
         return o;
     }
 }
@@ -885,7 +903,7 @@ int ipkgpu_enumerate(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint64_t cap,
     });
 }
 
-int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out, ipkgpu_stats* stats)
+static int stage1_entry(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out, ipkgpu_stats* stats, bool raw)
 {
     return guarded(ctx, [&] {
         validate(in);
@@ -897,7 +915,7 @@ int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, 
         const group_tables T = make_groups(in->node_branch, in->n_nodes, group_base);
         if (group_base + T.group_branch.size() > (1ull << group_bits) && !(group_bits >= 32))
             fail(IPKGPU_EINVAL, "group_base %u + %zu groups do not fit %u group bits", group_base, T.group_branch.size(), group_bits);
-        const stage1_out s1 = run_stage1(ctx, in, T, group_base, group_bits, false, &st, tm);
+        const stage1_out s1 = run_stage1(ctx, in, T, group_base, group_bits, false, &st, tm, raw);
         const size_t t1 = tm.mark();
         IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
         *n_out = s1.n_unique;
@@ -912,6 +930,16 @@ int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, 
     });
 }
 
+int ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out, ipkgpu_stats* stats)
+{
+    return stage1_entry(ctx, in, group_base, group_bits, n_out, stats, false);
+}
+
+int ipkgpu_stage1_raw(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out, ipkgpu_stats* stats)
+{
+    return stage1_entry(ctx, in, group_base, group_bits, n_out, stats, true);
+}
+
 int ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys, float* d_scores, uint64_t* counts)
 {
     return guarded(ctx, [&] {
@@ -923,7 +951,7 @@ int ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys,
         if (!d_keys || !d_scores) fail(IPKGPU_EINVAL, "send buffer is null");
         if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed one shard's 2^32-1 limit", (unsigned long long)n);
         const digit_owner own{ ctx->s1_group_bits, n_parts };
-        radix_pass(ctx, ctx->u_keys.as<uint64_t>(), ctx->u_scores.as<uint32_t>(), d_keys, reinterpret_cast<uint32_t*>(d_scores), n,
+        radix_pass(ctx, ctx->s1_keys, ctx->s1_scores, d_keys, reinterpret_cast<uint32_t*>(d_scores), n,
                    own, ctx->hist, ctx->scan_tmp);
         // bucket sizes: radix_pass leaves the exclusive digit starts in the first 256 words of the table
         std::vector<uint32_t> starts(n_parts);

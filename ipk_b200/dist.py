@@ -5,10 +5,13 @@ its on-disk mode already has: k-mer space split into batches by key (branch_grou
 and a final N-way merge by filter value (merge_stage2, db_builder.cpp:392-458).
 
 Per rank r of G:
-  stage 1   enumerate + per-branch max over the rank's own branch groups        (ipkgpu_stage1; no communication)
-  partition bucket the unique records by owner = mix64(kmer) % G, stably          (ipkgpu_stage1_partition)
+  stage 1   enumerate the rank's own branch groups, records left as emitted      (ipkgpu_stage1_raw; no communication)
+  partition bucket the records by owner = mix64(kmer) % G, stably                 (ipkgpu_stage1_partition)
   exchange  counts all-gather, then one all-to-all-v of (u64 key, f32 score)     (NCCL over NVLink)
-  stage 2   regroup by k-mer, filter values, order by filter value               (ipkgpu_stage2)
+  stage 2   ONE sort on (kmer, group), per-branch max, CSR by k-mer, filter values, order   (ipkgpu_stage2)
+Sorting after the exchange instead of before and after it costs 10 % more exchanged bytes (duplicates of a (k-mer,
+branch) travel) and saves 3 of 9 radix passes and one merge pass per rank (r01e: N=2 ran 8 + 1 passes per rank).
+`raw=False` keeps the earlier shape (local sort + max, exchange of unique records, stable regroup on the k-mer bits).
 The final database is the G-way merge of the shards by (filter value, key): `merge_shards`.
 
 All device work goes through a context object exposing stage1 / stage1_partition / stage2 (ipk_b200.capi.Context);
@@ -91,13 +94,13 @@ def exchange_records(send_keys: torch.Tensor, send_scores: torch.Tensor, counts:
 
 
 def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: float, total_num_groups: int, filter: int,
-                  device, result_on_device: bool = False, group=None, table: GroupTable | None = None):
+                  device, result_on_device: bool = False, group=None, table: GroupTable | None = None, raw: bool = True):
     """The whole multi-GPU path for this rank.  ctx: ipk_b200.capi.Context (or anything with its stage methods);
     inp: the rank's ipkgpu_input (its own ghost nodes only).  Returns (stage-2 result, info dict)."""
     world = dist.get_world_size(group)
     if table is None:
         table = exchange_group_table(node_branch, device, group)
-    n_unique, st1 = ctx.stage1(inp, table.group_base, table.group_bits)
+    n_unique, st1 = ctx.stage1(inp, table.group_base, table.group_bits, raw)
     send_keys = torch.empty(max(n_unique, 1), dtype=torch.int64, device=device)
     send_scores = torch.empty(max(n_unique, 1), dtype=torch.float32, device=device)
     counts = ctx.stage1_partition(world, send_keys, send_scores)
@@ -105,7 +108,7 @@ def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: f
     del send_keys, send_scores
     n_recv = int(recv_counts.sum())
     res = ctx.stage2(recv_keys, recv_scores, n_recv, table.group_bits, table.group_branch, key_bits, threshold,
-                     total_num_groups, filter, True, result_on_device)
+                     total_num_groups, filter, not raw, result_on_device)
     info = dict(stage1=st1, n_unique_local=int(n_unique), n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
                 n_received=n_recv, keep=(recv_keys, recv_scores))
     return res, info

@@ -42,7 +42,7 @@ class OracleStages:
     def __init__(self):
         self.records = None
 
-    def stage1(self, inp, group_base, group_bits):
+    def stage1(self, inp, group_base, group_bits, raw=False):
         import oraclelib as O
         from ipk_b200.dist import local_groups
         db = O.build(inp.logp, inp.node_branch, inp.W, inp.sigma, inp.bits, inp.k, inp.lthr, inp.thr, inp.total, 1, 1)
@@ -53,7 +53,15 @@ class OracleStages:
         grp = np.array([gidx[int(b)] for b in db.branch], dtype=np.uint64)
         o = np.lexsort((grp, kmer))
         ckey = (kmer[o] << np.uint64(group_bits)) | grp[o]
-        self.records = (ckey, db.score[o].copy(), group_bits)
+        score = db.score[o].copy()
+        if raw:       # as emitted: any order, with duplicates of a (k-mer, group) that stage 2 must merge by maximum
+            rng = np.random.default_rng(5 + group_base)
+            dup = rng.integers(0, len(ckey), size=len(ckey) // 7) if len(ckey) else np.zeros(0, np.int64)
+            ckey = np.concatenate([ckey, ckey[dup]])
+            score = np.concatenate([score, score[dup] - np.float32(0.25)])
+            o2 = rng.permutation(len(ckey))
+            ckey, score = ckey[o2], score[o2]
+        self.records = (ckey, score, group_bits)
         return len(ckey), dict(n_emitted=db.n_emitted)
 
     def stage1_partition(self, n_parts, d_keys, d_scores):
@@ -76,8 +84,12 @@ class OracleStages:
             o = np.argsort(kmer, kind="stable")        # chunks arrive in ascending group ranges: stable on the k-mer alone
             assert np.all(np.diff(grp[o])[np.diff(kmer[o].astype(np.int64)) == 0] > 0), "chunks were not group ordered"
         else:
-            o = np.lexsort((grp, kmer))
+            o = np.lexsort((-score.astype(np.float64), grp, kmer))
         kmer, grp, score = kmer[o], grp[o], score[o]
+        if not chunks_group_ordered and len(kmer):      # per-branch max: the first of every (k-mer, group) run
+            head = np.ones(len(kmer), bool)
+            head[1:] = (kmer[1:] != kmer[:-1]) | (grp[1:] != grp[:-1])
+            kmer, grp, score = kmer[head], grp[head], score[head]
         keys, first = np.unique(kmer, return_index=True)
         offsets = np.append(first, len(kmer)).astype(np.uint64)
         fv = np.array([O.mif0(score[int(offsets[i]):int(offsets[i + 1])], total_num_groups, threshold) for i in range(len(keys))],
@@ -102,7 +114,7 @@ def _thresholds():
     return float(thr), float(np.log10(thr, dtype=np.float32))
 
 
-def _worker(rank, world, port, out_dir):
+def _worker(rank, world, port, out_dir, raw):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -115,8 +127,8 @@ def _worker(rank, world, port, out_dir):
         inp = SimpleNamespace(logp=logp[sl], node_branch=nb[sl], W=W, sigma=SIGMA, bits=BITS, k=K, lthr=lthr, thr=thr, total=2 * N_TAXA - 1)
         table = ipkdist.exchange_group_table(nb[sl], torch.device("cpu"))
         assert table.group_base == b0 and len(table.group_branch) == n_branches
-        res, info = ipkdist.sharded_build(OracleStages(), inp, nb[sl], K * BITS, thr, 2 * N_TAXA - 1, 0, torch.device("cpu"), table=table)
-        assert info["n_received"] == res.n_entries
+        res, info = ipkdist.sharded_build(OracleStages(), inp, nb[sl], K * BITS, thr, 2 * N_TAXA - 1, 0, torch.device("cpu"), table=table, raw=raw)
+        assert info["n_received"] > res.n_entries if raw else info["n_received"] == res.n_entries
         shards = [None] * world
         dist.all_gather_object(shards, dict(keys=res.keys, fv=res.fv, offsets=res.offsets, branch=res.branch, score=res.score))
         if rank == 0:
@@ -133,11 +145,12 @@ def _free_port():
         return s.getsockname()[1]
 
 
+@pytest.mark.parametrize("raw", [True, False])
 @pytest.mark.parametrize("world", [2, 3])
-def test_sharded_build_equals_single(world, tmp_path):
+def test_sharded_build_equals_single(world, raw, tmp_path):
     import oraclelib as O
     from parity import assert_db_equal
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), raw), nprocs=world, join=True)
     z = np.load(os.path.join(str(tmp_path), "merged.npz"))
     got = SimpleNamespace(keys=z["keys"], fv=z["fv"], offsets=z["offsets"], branch=z["branch"], score=z["score"],
                           n_kmers=len(z["keys"]), n_entries=len(z["branch"]))

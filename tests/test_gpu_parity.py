@@ -165,9 +165,10 @@ def test_build_batched_equals_single(ctx):
         c2.close()
 
 
+@pytest.mark.parametrize("raw", [True, False])
 @pytest.mark.parametrize("world", [2, 3])
 @pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 200), (20, 5, 4, 8, 90)])
-def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W):
+def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W, raw):
     """The multi-GPU path, its ranks emulated one after the other on ONE device (B200_PROFILING.md: never several
     waiting ranks on one GPU): stage 1 per rank -> partition by k-mer owner -> the all-to-all done with device copies
     -> stage 2 per rank -> G-way merge.  Entry-for-entry equal to the single-GPU build."""
@@ -190,7 +191,8 @@ def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W):
         for r, (b0, b1) in enumerate(parts):
             sl = slice(2 * b0, 2 * b1)
             inp, keep = libipkgpu.make_input(np.ascontiguousarray(logp[sl]), nb[sl], W, sigma, bits, k, lthr, thr, T, 0)
-            n_unique, st1 = ctxs[r].stage1(inp, b0, group_bits)
+            n_unique, st1 = ctxs[r].stage1(inp, b0, group_bits, raw)
+            assert n_unique == st1["n_emitted"] if raw else n_unique <= st1["n_emitted"]
             keys = torch.empty(max(n_unique, 1), dtype=torch.int64, device=dev)
             scores = torch.empty(max(n_unique, 1), dtype=torch.float32, device=dev)
             counts = ctxs[r].stage1_partition(world, keys, scores).astype(np.int64)
@@ -204,7 +206,7 @@ def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W):
             if n == 0:
                 rk = torch.empty(1, dtype=torch.int64, device=dev); rs = torch.empty(1, dtype=torch.float32, device=dev)
             torch.cuda.synchronize()
-            res = ctxs[r].stage2(rk, rs, n, group_bits, group_branch, k * bits, thr, T, 0, True, False)
+            res = ctxs[r].stage2(rk, rs, n, group_bits, group_branch, k * bits, thr, T, 0, not raw, False)
             shards.append(libipkgpu.Context.to_db(res))
         assert sum(s.n_entries for s in shards) == want.n_entries
         merged = ipkdist.merge_shards(shards)
