@@ -152,7 +152,9 @@ def cpu_baseline(wl, seed, target_s=15.0, forced=0):
 def workload_config(wl, n_gpus):
     return {"workload": wl.name, "n_taxa": wl.n_taxa, "alignment_columns": wl.width, "k": wl.k, "omega": wl.omega,
             "states": wl.sigma, "filter": wl.filter, "branch_groups": wl.n_branches, "ghost_matrices": wl.n_ghost_nodes,
-            "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", all-to-all by k-mer hash" if n_gpus > 1 else "")}
+            "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", records bucketed by k-mer hash and stored into the owners' buffers over NVLink peer memory, sorted once by the owner"
+                                                                   if n_gpus > 1 and os.environ.get("IPK_EXCHANGE", "peer") == "peer" else
+                                                                   ", NCCL all-to-all by k-mer hash" if n_gpus > 1 else "")}
 
 
 def run_reference(args):
@@ -233,12 +235,14 @@ def run_b200(args):
             res = ctx.build_raw(inp, result_on_device=not host)
             st = res.stats.as_dict()
             return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), int(st["kernel_launches"]), 0
-        res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table)
+        res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table,
+                                          exchange=os.environ.get("IPK_EXCHANGE", "peer"))
         st = res.stats.as_dict()
         st1 = info["stage1"]
         for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):
             st[k_] = st1[k_]
         st["ms_sort"] += st1["ms_sort"]; st["ms_merge"] += st1["ms_merge"]; st["sort_passes"] += st1["sort_passes"]
+        st["ms_partition"] = info.get("ms_partition", 0.0); st["ms_exchange"] = info.get("ms_exchange", 0.0)
         launches = int(st["kernel_launches"]) + int(st1["kernel_launches"]) + 1
         return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), launches, info["n_sent_remote"]
 
@@ -351,7 +355,7 @@ def run_b200(args):
             "counts": {"windows": wl.n_windows, "emitted": n_emitted, "entries": n_entries, "kmers": n_kmers, "sort_passes": passes,
                        "tiles_rank0": int(st.get("n_tiles", 0)), "deferred_tiles_rank0": int(st.get("n_deferred_tiles", 0)),
                        "emitted_per_s": n_emitted * args.steps / (ms_dev * 1e-3)},
-            "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order")},
+            "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order", "ms_partition", "ms_exchange") if k_ in st},
             "kernels": kernels}
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(wl, args.seed, 15.0, args.cpu_sample_branches)

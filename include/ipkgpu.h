@@ -136,9 +136,25 @@ int  ipkgpu_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base,
  * workspace the call falls back to batches of whole groups merged locally (records then unique, as ipkgpu_stage1). */
 int  ipkgpu_stage1_raw(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint32_t group_base, uint32_t group_bits, uint64_t* n_out,
                        ipkgpu_stats* stats);
-/* Buckets the stage-1 records by owner = mix64(kmer) % n_parts, stably, into caller-provided DEVICE buffers of n_out
+/* Buckets the stage-1 records by owner = (mix64(kmer) >> 32) * n_parts >> 32, stably, into caller-provided DEVICE buffers of n_out
  * records (the send buffers of the all-to-all); counts[n_parts] (host) receives the bucket sizes. */
 int  ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys, float* d_scores, uint64_t* counts);
+/* ---- fused partition + exchange over NVLink peer memory (one process per GPU; no NCCL on the data path) ------------
+ * 1. every rank:  ipkgpu_stage1_owner_counts -> counts[dst];   the caller all-gathers the G x G matrix
+ * 2. every rank:  ipkgpu_recv_buffers(sum over src of matrix[src][me]) -> its receive buffers + their CUDA IPC handles;
+ *                 the caller all-gathers the handles (only when they changed) and maps them with ipkgpu_open_peer
+ * 3. every rank:  ipkgpu_stage1_scatter: ONE pass over its stage-1 records; bucket d is stored straight into rank d's
+ *                 receive buffers at element offset base_offsets[d] = sum over src < me of matrix[src][d]  (chunks land
+ *                 in source-rank order = ascending group ranges).  Returns when the stores have completed.
+ * 4. a barrier among the ranks, then ipkgpu_stage2 on the receive buffers. */
+#define IPKGPU_IPC_HANDLE_BYTES 64
+int  ipkgpu_stage1_owner_counts(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* counts);
+int  ipkgpu_recv_buffers(ipkgpu_ctx* ctx, uint64_t n_records, uint64_t** d_keys, float** d_scores,
+                         unsigned char* handle_keys /*[64] or NULL*/, unsigned char* handle_scores /*[64] or NULL*/);
+int  ipkgpu_open_peer(ipkgpu_ctx* ctx, const unsigned char* handle /*[64]*/, void** d_ptr);
+int  ipkgpu_stage1_scatter(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* peer_keys, float* const* peer_scores,
+                           const uint64_t* base_offsets);
+
 /* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
  * values -> order (equal composite keys are merged by maximum score).  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
  * chunks_group_ordered != 0 promises that the records are a concatenation of chunks in ascending group ranges, each

@@ -130,6 +130,14 @@ def load() -> C.CDLL:
     lib.ipkgpu_stage1_raw.restype = C.c_int
     lib.ipkgpu_stage1_partition.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, P(C.c_uint64)]
     lib.ipkgpu_stage1_partition.restype = C.c_int
+    lib.ipkgpu_stage1_owner_counts.argtypes = [C.c_void_p, C.c_uint32, P(C.c_uint64)]
+    lib.ipkgpu_stage1_owner_counts.restype = C.c_int
+    lib.ipkgpu_recv_buffers.argtypes = [C.c_void_p, C.c_uint64, P(C.c_void_p), P(C.c_void_p), C.c_void_p, C.c_void_p]
+    lib.ipkgpu_recv_buffers.restype = C.c_int
+    lib.ipkgpu_open_peer.argtypes = [C.c_void_p, C.c_void_p, P(C.c_void_p)]
+    lib.ipkgpu_open_peer.restype = C.c_int
+    lib.ipkgpu_stage1_scatter.argtypes = [C.c_void_p, C.c_uint32, P(C.c_void_p), P(C.c_void_p), P(C.c_uint64)]
+    lib.ipkgpu_stage1_scatter.restype = C.c_int
     lib.ipkgpu_stage2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
                                   C.c_uint32, C.c_float, C.c_uint32, C.c_int32, C.c_int32, C.c_int, P(Result)]
     lib.ipkgpu_stage2.restype = C.c_int
@@ -323,6 +331,31 @@ class Context:
         self._check(self._lib.ipkgpu_stage1_partition(self._h, n_parts, _ptr(d_keys), _ptr(d_scores),
                                                       counts.ctypes.data_as(C.POINTER(C.c_uint64))))
         return counts
+
+    # ---- fused partition + exchange over peer memory (include/ipkgpu.h) ----
+    def stage1_owner_counts(self, n_parts: int) -> np.ndarray:
+        counts = np.zeros(n_parts, np.uint64)
+        self._check(self._lib.ipkgpu_stage1_owner_counts(self._h, n_parts, counts.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return counts
+
+    def recv_buffers(self, n_records: int) -> tuple[int, int, bytes, bytes]:
+        """-> (device address of the key buffer, of the score buffer, their CUDA IPC handles)"""
+        k, s = C.c_void_p(0), C.c_void_p(0)
+        hk, hs = C.create_string_buffer(64), C.create_string_buffer(64)
+        self._check(self._lib.ipkgpu_recv_buffers(self._h, n_records, C.byref(k), C.byref(s), hk, hs))
+        return int(k.value or 0), int(s.value or 0), hk.raw, hs.raw
+
+    def open_peer(self, handle: bytes) -> int:
+        p = C.c_void_p(0)
+        self._check(self._lib.ipkgpu_open_peer(self._h, C.create_string_buffer(handle, 64), C.byref(p)))
+        return int(p.value or 0)
+
+    def stage1_scatter(self, peer_keys: list[int], peer_scores: list[int], base_offsets) -> None:
+        n = len(peer_keys)
+        pk = (C.c_void_p * n)(*peer_keys)
+        ps = (C.c_void_p * n)(*peer_scores)
+        base = (C.c_uint64 * n)(*[int(b) for b in base_offsets])
+        self._check(self._lib.ipkgpu_stage1_scatter(self._h, n, pk, ps, base))
 
     def stage2(self, d_keys, d_scores, n: int, group_bits: int, group_branch: np.ndarray, key_bits: int, threshold: float,
                total_num_groups: int, filter: int = FILTER_MIF0, chunks_group_ordered: bool = True,

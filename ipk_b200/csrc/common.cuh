@@ -90,6 +90,9 @@ struct ipkgpu_ctx
     // stage-1 state kept for ipkgpu_stage1_partition
     uint64_t s1_n = 0;
     uint32_t s1_group_bits = 0;
+    ipkgpu::dbuf recv_keys, recv_scores, peer_base;   // receive side of the fused partition + exchange (exported through CUDA IPC)
+    struct ipc_mapping { unsigned char handle[64]; void* ptr; };
+    std::vector<ipc_mapping> ipc_open;  // peers' receive buffers mapped into this process
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt

@@ -771,7 +771,9 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->mg_status, &ctx->mif_chunks, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->deferred2, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
-                            &ctx->out_score, &ctx->out_cnt };
+                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base };
+    for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
+    ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);
     ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score };
     for (auto* b : hall) if (b->p) cudaFreeHost(b->p);
@@ -958,6 +960,94 @@ int ipkgpu_stage1_partition(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* d_keys,
         IPK_CUDA(cudaMemcpyAsync(starts.data(), ctx->hist.p, size_t(n_parts) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));
         for (uint32_t p = 0; p < n_parts; ++p) counts[p] = (p + 1 < n_parts ? starts[p + 1] : n) - starts[p];
+    });
+}
+
+int ipkgpu_stage1_owner_counts(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* counts)
+{
+    return guarded(ctx, [&] {
+        if (n_parts < 1 || n_parts > uint32_t(RS_MAX_PEERS)) fail(IPKGPU_EINVAL, "n_parts = %u outside [1, %d]", n_parts, RS_MAX_PEERS);
+        if (!counts) fail(IPKGPU_EINVAL, "counts is null");
+        for (uint32_t p = 0; p < n_parts; ++p) counts[p] = 0;
+        const uint64_t n = ctx->s1_n;
+        if (n == 0) return;
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed one shard's 2^32-1 limit", (unsigned long long)n);
+        owner_histogram(ctx, ctx->s1_keys, n, digit_owner{ ctx->s1_group_bits, n_parts }, ctx->hist);
+        std::vector<uint32_t> h(n_parts);
+        IPK_CUDA(cudaMemcpyAsync(h.data(), ctx->hist.p, size_t(n_parts) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t p = 0; p < n_parts; ++p) counts[p] = h[p];
+    });
+}
+
+int ipkgpu_recv_buffers(ipkgpu_ctx* ctx, uint64_t n_records, uint64_t** d_keys, float** d_scores, unsigned char* handle_keys,
+                        unsigned char* handle_scores)
+{
+    return guarded(ctx, [&] {
+        if (!d_keys || !d_scores) fail(IPKGPU_EINVAL, "output pointer is null");
+        static_assert(sizeof(cudaIpcMemHandle_t) == IPKGPU_IPC_HANDLE_BYTES, "IPC handle size");
+        // peers hold mappings of these allocations: grow rarely (25 % head room) so that handles stay valid across builds
+        if (n_records * 8 + 8 > ctx->recv_keys.cap) ctx->reserve(ctx->recv_keys, (n_records + n_records / 4) * 8 + 8);
+        if (n_records * 4 + 4 > ctx->recv_scores.cap) ctx->reserve(ctx->recv_scores, (n_records + n_records / 4) * 4 + 4);
+        *d_keys = ctx->recv_keys.as<uint64_t>();
+        *d_scores = ctx->recv_scores.as<float>();
+        if (handle_keys)
+        {
+            cudaIpcMemHandle_t h;
+            IPK_CUDA(cudaIpcGetMemHandle(&h, ctx->recv_keys.p));
+            memcpy(handle_keys, &h, sizeof h);
+        }
+        if (handle_scores)
+        {
+            cudaIpcMemHandle_t h;
+            IPK_CUDA(cudaIpcGetMemHandle(&h, ctx->recv_scores.p));
+            memcpy(handle_scores, &h, sizeof h);
+        }
+    });
+}
+
+int ipkgpu_open_peer(ipkgpu_ctx* ctx, const unsigned char* handle, void** d_ptr)
+{
+    return guarded(ctx, [&] {
+        if (!handle || !d_ptr) fail(IPKGPU_EINVAL, "null argument");
+        for (auto& m : ctx->ipc_open)
+            if (!memcmp(m.handle, handle, sizeof m.handle)) { *d_ptr = m.ptr; return; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handle, sizeof h);
+        void* p = nullptr;
+        IPK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        ipkgpu_ctx::ipc_mapping m;
+        memcpy(m.handle, handle, sizeof m.handle);
+        m.ptr = p;
+        ctx->ipc_open.push_back(m);
+        *d_ptr = p;
+    });
+}
+
+int ipkgpu_stage1_scatter(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* peer_keys, float* const* peer_scores, const uint64_t* base_offsets)
+{
+    return guarded(ctx, [&] {
+        if (n_parts < 1 || n_parts > uint32_t(RS_MAX_PEERS)) fail(IPKGPU_EINVAL, "n_parts = %u outside [1, %d]", n_parts, RS_MAX_PEERS);
+        if (!peer_keys || !peer_scores || !base_offsets) fail(IPKGPU_EINVAL, "null argument");
+        const uint64_t n = ctx->s1_n;
+        if (n == 0) return;
+        rs_peer_table PT;
+        memset(&PT, 0, sizeof PT);
+        uint32_t base[RS_RADIX];
+        memset(base, 0, sizeof base);
+        for (uint32_t p = 0; p < n_parts; ++p)
+        {
+            if (!peer_keys[p] || !peer_scores[p]) fail(IPKGPU_EINVAL, "receive buffer of rank %u is null", p);
+            if (base_offsets[p] > 0xffffffffull) fail(IPKGPU_EINVAL, "offset into rank %u's receive buffer exceeds 2^32-1", p);
+            PT.keys[p] = peer_keys[p];
+            PT.vals[p] = reinterpret_cast<uint32_t*>(peer_scores[p]);
+            base[p] = uint32_t(base_offsets[p]);
+        }
+        ctx->reserve(ctx->peer_base, sizeof base);
+        IPK_CUDA(cudaMemcpyAsync(ctx->peer_base.p, base, sizeof base, cudaMemcpyHostToDevice, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));          // `base` is a stack array
+        scatter_to_peers(ctx, ctx->s1_keys, ctx->s1_scores, n, digit_owner{ ctx->s1_group_bits, n_parts }, ctx->peer_base.as<uint32_t>(), PT, ctx->hist);
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));          // the caller's barrier may only follow completed stores
     });
 }
 

@@ -148,12 +148,27 @@ namespace ipkgpu
         return x ^ (x >> 31);
     }
 
-    /// "digit" = owner rank of a k-mer in the multi-GPU exchange: mix64(kmer) % n_parts (n_parts <= 256).
-    /// The same kernels then bucket the records by owner, stably.
+    /// owner rank of a k-mer in the multi-GPU exchange: the high word of mix64(kmer) scaled to [0, n_parts) by a
+    /// multiply-shift (a 64-bit `%` by a run-time divisor cost the r01g partition pass 3x its memory time)
+    __host__ __device__ __forceinline__ uint32_t kmer_owner(uint64_t kmer, uint32_t n_parts)
+    {
+        return uint32_t(((mix64(kmer) >> 32) * uint64_t(n_parts)) >> 32);
+    }
+
+    /// "digit" = owner rank (n_parts <= 256).  The same kernels then bucket the records by owner, stably.
     struct digit_owner
     {
         uint32_t group_bits, n_parts;
-        __device__ __forceinline__ uint32_t operator()(uint64_t ckey) const { return uint32_t(mix64(ckey >> group_bits) % n_parts); }
+        __device__ __forceinline__ uint32_t operator()(uint64_t ckey) const { return kmer_owner(ckey >> group_bits, n_parts); }
+    };
+
+    /// destinations of the fused partition + exchange: bucket d is written straight into rank d's receive buffers
+    /// (peer device memory mapped through CUDA IPC, or this rank's own) starting at the element offset digit_base[d]
+    constexpr int RS_MAX_PEERS = 16;
+    struct rs_peer_table
+    {
+        uint64_t* keys[RS_MAX_PEERS];
+        uint32_t* vals[RS_MAX_PEERS];
     };
 
     constexpr int RS_MAX_PASSES = 8;
@@ -235,12 +250,16 @@ namespace ipkgpu
 
     /// One pass over one tile of THREADS * ITEMS pairs (tile ids are handed out by an atomic ticket, so every predecessor a
     /// tile waits for is already running).  digit_base = exclusive scan of this pass's global digit histogram.
-    template<int THREADS, int ITEMS, class DigitFn>
+    template<int THREADS, int ITEMS, class DigitFn, bool PEERS>
     __global__ void __launch_bounds__(THREADS) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                            const uint32_t* __restrict__ digit_base, uint64_t n,
-                                                           uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit)
+                                                           uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit,
+                                                           const __grid_constant__ rs_peer_table PT)
     {
+        __shared__ uint64_t* s_pk[PEERS ? RS_MAX_PEERS : 1];
+        __shared__ uint32_t* s_pv[PEERS ? RS_MAX_PEERS : 1];
+        if (PEERS && threadIdx.x < RS_MAX_PEERS) { s_pk[threadIdx.x] = PT.keys[threadIdx.x]; s_pv[threadIdx.x] = PT.vals[threadIdx.x]; }
         constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
         static_assert(THREADS >= RS_RADIX && THREADS % 32 == 0, "one thread per digit is needed");
         extern __shared__ __align__(16) unsigned char rs_smem[];
@@ -360,16 +379,20 @@ namespace ipkgpu
         }
         __syncthreads();
         uint32_t gpos[ITEMS];
+        uint8_t gdst[PEERS ? ITEMS : 1];
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
         {
             const uint32_t q = uint32_t(i) * THREADS + tid;
             gpos[i] = 0;
+            if (PEERS) gdst[i] = 0;
             if (q < tile_n)
             {
                 const uint64_t kk = sk[q];
-                gpos[i] = goff[digit(kk)] + q;
-                keys_out[gpos[i]] = kk;
+                const uint32_t d = digit(kk);
+                gpos[i] = goff[d] + q;
+                if (PEERS) { gdst[i] = uint8_t(d); s_pk[d][gpos[i]] = kk; }          // a store over NVLink when d is a peer
+                else keys_out[gpos[i]] = kk;
             }
         }
         // values: same route through the (reused) shared buffer
@@ -385,7 +408,11 @@ namespace ipkgpu
         for (int i = 0; i < ITEMS; ++i)
         {
             const uint32_t q = uint32_t(i) * THREADS + tid;
-            if (q < tile_n) vals_out[gpos[i]] = sv[q];
+            if (q < tile_n)
+            {
+                if (PEERS) s_pv[gdst[i]][gpos[i]] = sv[q];
+                else vals_out[gpos[i]] = sv[q];
+            }
         }
     }
 
@@ -407,7 +434,7 @@ namespace ipkgpu
 
     inline rs_scratch rs_prepare(ipkgpu_ctx* ctx, uint64_t n, dbuf& table)
     {
-        const uint64_t n_tiles = div_up<uint64_t>(n, rs_tile(ctx));
+        const uint64_t n_tiles = div_up<uint64_t>(n, std::min<uint32_t>(rs_tile(ctx), 3072u));      // enough for every tile shape
         ctx->reserve(table, (RS_MAX_PASSES * RS_RADIX + 16) * 4);
         const size_t want = n_tiles * RS_RADIX * 8;
         if (want > ctx->rs_status.cap)
@@ -432,14 +459,25 @@ namespace ipkgpu
 
     template<int THREADS, int ITEMS, class DigitFn>
     inline void rs_launch_shape(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout,
-                                const uint32_t* digit_base, uint64_t n, uint64_t* status, uint32_t* ticket, DigitFn digit)
+                                const uint32_t* digit_base, uint64_t n, uint64_t* status, uint32_t* ticket, DigitFn digit,
+                                const rs_peer_table* peers = nullptr)
     {
         constexpr size_t smem = rs_smem_bytes<THREADS, ITEMS>();
         const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, uint64_t(THREADS) * ITEMS));
-        IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        rs_peer_table none;
+        memset(&none, 0, sizeof none);
+        if (peers)
+        {
+            IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            IPK_LAUNCH(ctx, "rs_scatter_peers", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
+                       rs_onesweep<THREADS, ITEMS, DigitFn, true><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, nullptr, nullptr, digit_base, n, status,
+                                                                                                           ticket, rs_next_epoch(ctx), digit, *peers));
+            return;
+        }
+        IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
-                   rs_onesweep<THREADS, ITEMS, DigitFn><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, digit_base, n, status, ticket,
-                                                                                                 rs_next_epoch(ctx), digit));
+                   rs_onesweep<THREADS, ITEMS, DigitFn, false><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, digit_base, n, status, ticket,
+                                                                                                        rs_next_epoch(ctx), digit, none));
     }
 
     template<class DigitFn>
@@ -470,6 +508,26 @@ namespace ipkgpu
         IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_fn<DigitFn><<<hgrid, RS_HIST_THREADS, 0, ctx->stream>>>(kin, n, digit, S.hist));
         IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(S.hist));
         rs_launch_onesweep(ctx, kin, vin, kout, vout, S.hist, n, S.status, S.tickets, digit);
+    }
+
+    /// Owner histogram of n records: table[0..n_parts) (device) = number of records per owner rank.
+    inline void owner_histogram(ipkgpu_ctx* ctx, const uint64_t* kin, uint64_t n, digit_owner own, dbuf& table)
+    {
+        const rs_scratch S = rs_prepare(ctx, std::max<uint64_t>(n, 1), table);
+        if (n == 0) return;
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * 8), uint64_t(ctx->num_sms) * 8));
+        IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_fn<digit_owner><<<hgrid, RS_HIST_THREADS, 0, ctx->stream>>>(kin, n, own, S.hist));
+    }
+
+    /// The fused partition + exchange pass: bucket d of the n records goes to peers.keys[d] / peers.vals[d] starting at
+    /// element d_base[d] (device table, 256 words; the caller computed it from the all-gathered owner histograms), in
+    /// stable order.  Remote buckets are plain stores into peer memory over NVLink -- no staging buffer, no collective.
+    inline void scatter_to_peers(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t n, digit_owner own,
+                                 const uint32_t* d_base, const rs_peer_table& peers, dbuf& table)
+    {
+        if (n == 0) return;
+        const rs_scratch S = rs_prepare(ctx, n, table);
+        rs_launch_shape<384, 16>(ctx, kin, vin, nullptr, nullptr, d_base, n, S.status, S.tickets, own, &peers);
     }
 
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);

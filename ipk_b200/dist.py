@@ -6,7 +6,7 @@ and a final N-way merge by filter value (merge_stage2, db_builder.cpp:392-458).
 
 Per rank r of G:
   stage 1   enumerate the rank's own branch groups, records left as emitted      (ipkgpu_stage1_raw; no communication)
-  partition bucket the records by owner = mix64(kmer) % G, stably                 (ipkgpu_stage1_partition)
+  partition bucket the records by owner = (mix64(kmer) >> 32) * G >> 32                 (ipkgpu_stage1_partition)
   exchange  counts all-gather, then one all-to-all-v of (u64 key, f32 score)     (NCCL over NVLink)
   stage 2   ONE sort on (kmer, group), per-branch max, CSR by k-mer, filter values, order   (ipkgpu_stage2)
 Sorting after the exchange instead of before and after it costs 10 % more exchanged bytes (duplicates of a (k-mer,
@@ -93,24 +93,77 @@ def exchange_records(send_keys: torch.Tensor, send_scores: torch.Tensor, counts:
     return recv_keys, recv_scores, recv_counts
 
 
+def peer_exchange(ctx, device, group=None):
+    """The fused partition + exchange (include/ipkgpu.h): owner counts all-gathered, every rank's receive buffers mapped
+    into every other rank through CUDA IPC, then ONE scatter pass per rank that stores each bucket straight into its
+    owner's buffers over NVLink, and a barrier.  No NCCL call touches the records.
+    Returns (address of received keys, of received scores, n_received, counts this rank sent per destination)."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    counts = ctx.stage1_owner_counts(world)
+    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device=device)
+    rows = [torch.zeros(world, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)            # also orders this build after every rank's previous stage 2
+    matrix = torch.stack(rows).cpu().numpy()            # matrix[src][dst]
+    n_recv = int(matrix[:, rank].sum())
+    rk, rs, hk, hs = ctx.recv_buffers(max(n_recv, 1))
+    h_mine = torch.frombuffer(bytearray(hk + hs), dtype=torch.uint8).to(device)
+    h_all = [torch.zeros(128, dtype=torch.uint8, device=device) for _ in range(world)]
+    dist.all_gather(h_all, h_mine, group=group)
+    peer_keys, peer_scores = [], []
+    for r in range(world):
+        if r == rank:
+            peer_keys.append(rk); peer_scores.append(rs)
+        else:
+            hb = bytes(h_all[r].cpu().numpy().tobytes())
+            peer_keys.append(ctx.open_peer(hb[:64])); peer_scores.append(ctx.open_peer(hb[64:]))
+    base = [int(matrix[:rank, d].sum()) for d in range(world)]
+    ctx.stage1_scatter(peer_keys, peer_scores, base)    # returns once this rank's stores have completed
+    done = torch.ones(1, dtype=torch.int32, device=device)
+    dist.all_reduce(done, group=group)
+    assert int(done.item()) == world                    # host-side wait: every rank's stores have landed
+    return rk, rs, n_recv, counts
+
+
 def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: float, total_num_groups: int, filter: int,
-                  device, result_on_device: bool = False, group=None, table: GroupTable | None = None, raw: bool = True):
+                  device, result_on_device: bool = False, group=None, table: GroupTable | None = None, raw: bool = True,
+                  exchange: str = "peer"):
     """The whole multi-GPU path for this rank.  ctx: ipk_b200.capi.Context (or anything with its stage methods);
     inp: the rank's ipkgpu_input (its own ghost nodes only).  Returns (stage-2 result, info dict)."""
     world = dist.get_world_size(group)
     if table is None:
         table = exchange_group_table(node_branch, device, group)
+    cuda = torch.device(device).type == "cuda"
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if cuda else None
     n_unique, st1 = ctx.stage1(inp, table.group_base, table.group_bits, raw)
+    if exchange == "peer" and cuda and hasattr(ctx, "stage1_scatter"):
+        ev[0].record()
+        rk, rs, n_recv, counts = peer_exchange(ctx, device, group)
+        ev[2].record()
+        res = ctx.stage2(rk, rs, n_recv, table.group_bits, table.group_branch, key_bits, threshold, total_num_groups, filter,
+                         not raw, result_on_device)
+        info = dict(stage1=st1, n_unique_local=int(n_unique), n_received=n_recv, keep=None, ms_partition=0.0,
+                    n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
+                    ms_exchange=ev[0].elapsed_time(ev[2]), exchange="peer-memory scatter")
+        return res, info
     send_keys = torch.empty(max(n_unique, 1), dtype=torch.int64, device=device)
     send_scores = torch.empty(max(n_unique, 1), dtype=torch.float32, device=device)
+    if cuda:
+        ev[0].record()
     counts = ctx.stage1_partition(world, send_keys, send_scores)
+    if cuda:
+        ev[1].record()
     recv_keys, recv_scores, recv_counts = exchange_records(send_keys, send_scores, counts, group)
+    if cuda:
+        ev[2].record()
     del send_keys, send_scores
     n_recv = int(recv_counts.sum())
     res = ctx.stage2(recv_keys, recv_scores, n_recv, table.group_bits, table.group_branch, key_bits, threshold,
                      total_num_groups, filter, not raw, result_on_device)
     info = dict(stage1=st1, n_unique_local=int(n_unique), n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
                 n_received=n_recv, keep=(recv_keys, recv_scores))
+    if cuda:           # stage 2 has synchronised the stream by now
+        info["ms_partition"] = ev[0].elapsed_time(ev[1])
+        info["ms_exchange"] = ev[1].elapsed_time(ev[2])
     return res, info
 
 

@@ -27,7 +27,7 @@ N_TAXA, W, SIGMA, BITS, K, OMEGA = 12, 120, 4, 2, 8, 1.5
 
 
 def mix64(x: np.ndarray) -> np.ndarray:
-    """same mixer as ipk_b200/csrc/radix_sort.cuh: mix64 (owner rank of a k-mer = mix64(kmer) % G)"""
+    """same mixer as ipk_b200/csrc/radix_sort.cuh: mix64 (owner rank of a k-mer = (mix64(kmer) >> 32) * G >> 32)"""
     x = x.astype(np.uint64)
     with np.errstate(over="ignore"):
         x = x + np.uint64(0x9E3779B97F4A7C15)
@@ -66,7 +66,7 @@ class OracleStages:
 
     def stage1_partition(self, n_parts, d_keys, d_scores):
         ckey, score, gb = self.records
-        owner = (mix64(ckey >> np.uint64(gb)) % np.uint64(n_parts)).astype(np.int64)
+        owner = (((mix64(ckey >> np.uint64(gb)) >> np.uint64(32)) * np.uint64(n_parts)) >> np.uint64(32)).astype(np.int64)
         o = np.argsort(owner, kind="stable")
         n = len(ckey)
         d_keys[:n] = torch.from_numpy(ckey[o].view(np.int64).copy())

@@ -218,6 +218,52 @@ def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W, raw):
             c.close()
 
 
+@pytest.mark.parametrize("raw", [True, False])
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 200), (20, 5, 4, 8, 90)])
+def test_peer_scatter_equals_single(world, sigma, bits, k, n_taxa, W, raw):
+    """The fused partition + exchange (ipkgpu_stage1_owner_counts / recv_buffers / stage1_scatter), ranks emulated as
+    contexts of ONE process on one device, so the "peer" buffers are plain device pointers (the IPC mapping itself is
+    exercised by bench.py --gpus 2).  Entry-for-entry equal to the single-GPU build."""
+    from types import SimpleNamespace
+    from ipk_b200 import capi as libipkgpu, dist as ipkdist
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    with libipkgpu.Context(0) as c1:
+        want = c1.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+    parts = ipkdist.split_branches(2 * n_taxa - 2, world)
+    group_branch = ipkdist.local_groups(nb)
+    group_bits = max(int(np.ceil(np.log2(len(group_branch)))), 0)
+    ctxs = [libipkgpu.Context(0) for _ in range(world)]
+    try:
+        matrix = np.zeros((world, world), np.int64)
+        for r, (b0, b1) in enumerate(parts):
+            sl = slice(2 * b0, 2 * b1)
+            inp, keep = libipkgpu.make_input(np.ascontiguousarray(logp[sl]), nb[sl], W, sigma, bits, k, lthr, thr, T, 0)
+            n1, _ = ctxs[r].stage1(inp, b0, group_bits, raw)
+            matrix[r] = ctxs[r].stage1_owner_counts(world).astype(np.int64)
+            assert matrix[r].sum() == n1
+        bufs = [ctxs[r].recv_buffers(max(int(matrix[:, r].sum()), 1)) for r in range(world)]
+        assert all(len(b[2]) == 64 and len(b[3]) == 64 and b[2] != b[3] for b in bufs)
+        for r in range(world):
+            ctxs[r].stage1_scatter([b[0] for b in bufs], [b[1] for b in bufs], [int(matrix[:r, d].sum()) for d in range(world)])
+        shards = []
+        for r in range(world):
+            res = ctxs[r].stage2(bufs[r][0], bufs[r][1], int(matrix[:, r].sum()), group_bits, group_branch, k * bits, thr, T, 0, not raw, False)
+            shards.append(libipkgpu.Context.to_db(res))
+        assert sum(s.n_entries for s in shards) == want.n_entries
+        assert all(s.n_entries > 0 for s in shards)
+        merged = ipkdist.merge_shards(shards)
+        got = SimpleNamespace(keys=merged[0], fv=merged[1], offsets=merged[2], branch=merged[3], score=merged[4],
+                              n_kmers=len(merged[0]), n_entries=len(merged[3]))
+        assert_db_equal(got, want, exact_fv=True)
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_invalid_arguments(ctx):
     from ipk_b200.capi import IpkGpuError
     logp, nb = _synth(4, 50, 4)
