@@ -12,7 +12,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libipkgpu.so")
+LIB_PATH = os.environ.get("IPKGPU_LIB") or os.path.join(_HERE, "libipkgpu.so")      # IPKGPU_LIB: A/B builds while tuning
 
 FILTER_MIF0 = 0
 FILTER_RANDOM = 1

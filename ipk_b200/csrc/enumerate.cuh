@@ -152,6 +152,8 @@ namespace ipkgpu
         uint32_t item_windows, items_per_tile, parent_ratio;
         uint32_t* deferred_tiles;     // join kernel: items it could not finish (lists too long for the pool ...); their number is counter[1]
         uint32_t pool_cap;            // join kernel: list-pool capacity in elements (<= 65535)
+        unsigned long long* phase_clocks;   // debug (IPKGPU_PHASE_CLOCKS): cycles of thread 0 per phase of the join kernel, summed over tiles
+        uint32_t group_min;           // join kernel: lists of at least this many elements are built by a lane group
         uint32_t small_list;          // join kernel: lists up to this length are filled and sorted by their owner thread
     };
 
@@ -207,7 +209,7 @@ namespace ipkgpu
     /// column's states are ordered by descending score into sval / sidx (ties by state index).
     /// Ends WITHOUT a barrier: callers __syncthreads() before reusing `raw` or reading sval.
     __device__ __forceinline__ void stage_tile(const enum_args& A, uint32_t node, uint32_t s0, int ncols, int NCP, float* raw, float* bs,
-                                               float* sval, uint8_t* sidx, unsigned long long* mbar_p)
+                                               float* sval, uint8_t* sidx, unsigned long long* mbar_p, const int nthreads = ENUM_THREADS)
     {
         const int tid = threadIdx.x;
         const int sigma = int(A.sigma);
@@ -233,11 +235,11 @@ namespace ipkgpu
         }
         else
         {
-            for (int i = tid; i < ncols * sigma; i += ENUM_THREADS) raw[i] = gsrc[i];
+            for (int i = tid; i < ncols * sigma; i += nthreads) raw[i] = gsrc[i];
         }
         {
             const float* brow = A.B + uint64_t(node) * (A.W + 1) + s0;
-            for (int i = tid; i <= ncols; i += ENUM_THREADS) bs[i] = brow[i];
+            for (int i = tid; i <= ncols; i += nthreads) bs[i] = brow[i];
         }
         if (A.use_tma)
         {
@@ -251,7 +253,7 @@ namespace ipkgpu
         __syncthreads();
 
         // ---- per column: order the states by descending score (ties by state index; tied states behave identically)
-        for (int c = tid; c < ncols; c += ENUM_THREADS)
+        for (int c = tid; c < ncols; c += nthreads)
         {
             const float* col = raw + c * sigma;
             if (sigma == 4)

@@ -215,7 +215,15 @@ namespace
         ctx->enum_join_emitted = 0;
         const bool use_join = in->k >= 2 && ctx->enum_mode != 1;
         A.item_windows = ENUM_THREADS; A.items_per_tile = 1; A.parent_ratio = 1;
-        A.small_list = ctx->small_list;
+        A.group_min = std::min<uint32_t>(std::max<uint32_t>(ctx->group_min, 1), 31);
+        A.small_list = std::min<uint32_t>(ctx->small_list, 8 * JOIN_GROUP);      // build_list_group holds 8 elements per lane
+        static const bool phase_dbg = getenv("IPKGPU_PHASE_CLOCKS") != nullptr;
+        if (phase_dbg && use_join)
+        {
+            ctx->reserve(ctx->peer_base, 1024);
+            IPK_CUDA(cudaMemsetAsync(ctx->peer_base.p, 0, 256, ctx->stream));
+            A.phase_clocks = ctx->peer_base.as<unsigned long long>();
+        }
         if (use_join)
         {
             // Levels: every tile with a small pool (several CTAs per SM); what did not fit is retried with larger pools, then
@@ -248,12 +256,12 @@ namespace
                 if (L.debug)
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(lvl_grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 else
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), ENUM_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 uint64_t h[2] = { 0, 0 };
                 IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
@@ -263,6 +271,15 @@ namespace
                 n_items = h[1];
                 prev_width = width;
                 A.tile_list = lists[level & 1];
+            }
+            if (A.phase_clocks)
+            {
+                unsigned long long pc[32];
+                IPK_CUDA(cudaMemcpyAsync(pc, A.phase_clocks, sizeof pc, cudaMemcpyDeviceToHost, ctx->stream));
+                IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+                fprintf(stderr, "[ipkgpu] join phases, mean cycles of thread 0 per tile (%llu tiles):", pc[31]);
+                for (int i = 0; i < 16; ++i) fprintf(stderr, " %d:%.0f", i, pc[31] ? double(pc[i]) / double(pc[31]) : 0.0);
+                fprintf(stderr, "\n");
             }
             // the depth-first kernel takes the remaining items as they are
             A.parent_ratio = 1;
@@ -729,6 +746,7 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
     if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
+    if (const char* e = getenv("IPKGPU_GROUP_MIN")) ctx->group_min = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_SMALL_LIST")) ctx->small_list = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_LEVELS"))
     {

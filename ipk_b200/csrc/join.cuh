@@ -122,11 +122,12 @@ namespace ipkgpu
     //   foff  u16 [n_fam][NCP]          its start in the pool
     //   wnr   u16 [ENUM_THREADS]        |L_right(s)|
     //   queue u16 [NCP]                 columns whose list is built by a whole warp (long lists)
+    //   perm  u16 [NCP]                 columns with a short list, by descending length (phase A2)
     //   sidx  u8  [sigma][NCP]
     // ----------------------------------------------------------------------------------------------------------
     struct join_layout
     {
-        size_t pool, sval, bs, eps, gthr, wbase, rbase, fcnt, foff, wnr, queue, sidx, total;
+        size_t pool, sval, bs, eps, gthr, wbase, rbase, fcnt, foff, wnr, queue, perm, sidx, total;
     };
 
     __host__ __device__ inline join_layout make_join_layout(int k, int sigma, int n_fam, uint32_t pool_cap)
@@ -145,6 +146,7 @@ namespace ipkgpu
         L.foff = b; b += size_t(n_fam) * NCP * 2;
         L.wnr = b; b += size_t(ENUM_THREADS) * 2;
         L.queue = b; b += size_t(NCP) * 2;
+        L.perm = b; b += size_t(NCP) * 2;
         L.sidx = b; b += size_t(sigma) * NCP;
         L.total = ((b + 15) & ~size_t(15)) + 16;
         return L;
@@ -153,6 +155,16 @@ namespace ipkgpu
     /// smallest pool the raw tile fits in (it is staged over the pool's start before any list exists)
     inline uint32_t join_min_pool(int k, int sigma) { return uint32_t((size_t(ENUM_THREADS + k - 1) * sigma * 4 + 7) / 8 + 16); }
 
+    // threads of a k2_join CTA: one per window of the tile (ENUM_THREADS) plus one warp, so that the tile's
+    // ENUM_THREADS + k - 1 columns (k <= 33) are covered by ONE pass of every per-column loop (phase clocks r01m: the second
+    // pass over the last k - 1 columns cost as much latency as the first)
+    constexpr int JOIN_THREADS = ENUM_THREADS + 32;
+    constexpr int JOIN_WARPS = JOIN_THREADS / 32;
+#ifndef IPK_JOIN_GROUP
+#define IPK_JOIN_GROUP 4
+#endif
+    constexpr int JOIN_GROUP = IPK_JOIN_GROUP;   // lanes that share one of the longer lists in phase A2
+    constexpr int JOIN_GROUP_MIN = 10;       // ... lists of at least this many elements (and at most 8 * JOIN_GROUP, see small_list)
     constexpr int JOIN_SMALL_LIST = 24;      // lists up to this length are filled and insertion-sorted by their owner thread
 
     __device__ __forceinline__ unsigned long long el_pack(float s, uint32_t key) { return (unsigned long long)__float_as_uint(s) << 32 | key; }
@@ -308,8 +320,74 @@ namespace ipkgpu
         return lo;
     }
 
+    /// G lanes (a power of two, aligned in the warp) build and sort ONE list of n <= 8*G elements: rows by binary search,
+    /// row offsets by a scan inside the group, then a rank sort -- every lane counts, for each of its elements, how many
+    /// elements precede it (descending score, ties by fill position), all from independent loads, and the elements move to
+    /// their ranks in place.  Replaces the owner thread's serial fill + insertion sort for the longer lists: the critical
+    /// path of a 24-element list drops from ~150 dependent moves to ~6 rank loops of 24 independent compares.
+    template<int G>
+    __device__ __forceinline__ void build_list_group(const unsigned long long* la, int na, const unsigned long long* lb, int nb, float g,
+                                                     unsigned long long* os, int n, int shift, int gl, unsigned gmask)
+    {
+        int carry = 0;
+        for (int i0 = 0; i0 < na; i0 += G)
+        {
+            const int i = i0 + gl;
+            float sa = 0.0f;
+            uint32_t ka = 0;
+            int len = 0;
+            if (i < na)
+            {
+                const unsigned long long ea = la[i];
+                sa = el_score(ea);
+                ka = el_key(ea) << shift;
+                len = row_length(lb, nb, sa, g);
+            }
+            int inc = len;
+#pragma unroll
+            for (int o = 1; o < G; o <<= 1)
+            {
+                const int t = __shfl_up_sync(gmask, inc, o, G);
+                if (gl >= o) inc += t;
+            }
+            const int tot = __shfl_sync(gmask, inc, G - 1, G);
+            unsigned long long* w = os + carry + inc - len;
+            for (int j = 0; j < len; ++j)
+            {
+                const unsigned long long eb = lb[j];
+                w[j] = el_pack(__fadd_rn(sa, el_score(eb)), ka | el_key(eb));
+            }
+            carry += tot;
+            if (tot == 0) break;                           // rows only get shorter
+        }
+        __syncwarp(gmask);
+        // rank sort: every element of the list is loaded once and compared against the lane's (up to 8) own elements
+        unsigned long long ev[8];
+        float v[8];
+        int rk[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+        {
+            const int e = gl + q * G;
+            ev[q] = e < n ? os[e] : 0ull;
+            v[q] = e < n ? el_score(ev[q]) : __int_as_float(0x7f800000);
+            rk[q] = 0;
+        }
+#pragma unroll 4
+        for (int j = 0; j < n; ++j)
+        {
+            const float sj = el_score(os[j]);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) rk[q] += int((sj > v[q]) | ((sj == v[q]) & (j < gl + q * G)));
+        }
+        __syncwarp(gmask);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            if (gl + q * G < n) os[rk[q]] = ev[q];
+    }
+
     template<bool DEBUG>
-    __global__ void __launch_bounds__(ENUM_THREADS)
+    __global__ void __launch_bounds__(JOIN_THREADS)
     k2_join(const __grid_constant__ enum_args A, const __grid_constant__ enum_program P, const __grid_constant__ join_program J)
     {
         extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -317,12 +395,15 @@ namespace ipkgpu
         __shared__ unsigned long long s_base;
         __shared__ uint32_t s_pos[MAX_K];
         __shared__ uint32_t s_merge[MAX_K];
-        __shared__ uint32_t s_defer, s_qn[2];
+        __shared__ uint32_t s_defer, s_qn[2], s_bh[32], s_nwork, s_nheavy;
         __shared__ int s_lo, s_hi;                           // pool cursors: bottom end grows up, top end grows down
-        __shared__ uint32_t s_wsum[2][ENUM_WARPS];
+        __shared__ uint32_t s_wsum[2][JOIN_WARPS];
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma), bits = int(A.bits);
+        long long t_phase = A.phase_clocks ? clock64() : 0;
+#define IPK_PHASE(i_) do { if (A.phase_clocks && tid == 0) { const long long t_ = clock64(); atomicAdd(A.phase_clocks + (i_), (unsigned long long)(t_ - t_phase)); \
+                                                            if ((i_) == 0) atomicAdd(A.phase_clocks + 31, 1ull); t_phase = t_; } } while (0)
         tile_geom G;
         if (!tile_geometry(A, G)) return;
         const uint32_t lslot = G.lslot, node = G.node, s0 = G.s0, tile = G.item;
@@ -342,6 +423,7 @@ namespace ipkgpu
         uint16_t* foff = reinterpret_cast<uint16_t*>(smem_raw + L.foff);
         uint16_t* wnr = reinterpret_cast<uint16_t*>(smem_raw + L.wnr);
         uint16_t* queue = reinterpret_cast<uint16_t*>(smem_raw + L.queue);
+        uint16_t* perm = reinterpret_cast<uint16_t*>(smem_raw + L.perm);
         uint8_t* sidx = smem_raw + L.sidx;
         float* raw = reinterpret_cast<float*>(pool);         // the staged tile is consumed before the first list is written
 
@@ -351,7 +433,7 @@ namespace ipkgpu
             s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
         }
         if (tid == 0) { s_lo = 0; s_hi = int(A.pool_cap); s_defer = 0; s_qn[0] = 0; s_qn[1] = 0; }
-        stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar);
+        stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar, JOIN_THREADS);
 
         // ---- eps of every tree node for this thread's window (pk_compute.cpp:54-55; window.cpp:69-72) ---------------
         const bool has_window = tid < nwin_tile;
@@ -371,6 +453,7 @@ namespace ipkgpu
             delta = 2.0f * float(k) * 1.2e-7f * bmax + 1e-4f;
         }
         __syncthreads();                                   // raw consumed, sval / eps complete
+        IPK_PHASE(0);
 
         // ---- G_h(c) for every family, shortest first -----------------------------------------------------------------
         const unsigned full = 0xffffffffu;
@@ -388,9 +471,11 @@ namespace ipkgpu
                 __syncthreads();
             }
             if (tid == 0) s_qn[(f + 1) & 1] = 0;              // the other family's queue counter: last read before the previous barrier
-            // phase A, one thread per column: threshold, exact length (two-pointer walk over the staircase), and -- for
-            // short lists -- allocation, fill and sort.  Long lists are queued for phase B.
-            for (int c = tid; c < nlist; c += ENUM_THREADS)
+            // phase A1, one thread per column: threshold and exact length (two-pointer walk over the staircase).  Leaf lists
+            // are filled on the spot; long lists are queued for phase B; the others are ranked by length for phase A2.
+            if (tid < 32) s_bh[tid] = 0;
+            __syncthreads();
+            for (int c = tid; c < nlist; c += JOIN_THREADS)
             {
                 float g = __int_as_float(0x7f800000);      // +inf: no window of this tile has a length-h node at column c
                 for (int u = 0; u < J.fam[f].n_uses; ++u)
@@ -423,38 +508,88 @@ namespace ipkgpu
                     }
                     if (n > A.pool_cap) { s_defer = 1; n = 0; }
                     else if (n > A.small_list) queue[atomicAdd(&s_qn[f & 1], 1u)] = uint16_t(c);
-                    else if (n)
-                    {
-                        if (!pool_alloc(&s_lo, &s_hi, top, int(n), off)) s_defer = 1;
-                        else
-                        {
-                            unsigned long long* os = pool + off;
-                            int w = 0;
-                            l = nb;
-                            for (int i = 0; i < na && l > 0; ++i)
-                            {
-                                const unsigned long long ea = la[i];
-                                const float sa = el_score(ea);
-                                const uint32_t ka = el_key(ea) << (hr * bits);           // prefix = most significant digits (pk_compute.cpp:96-104)
-                                while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > g)) --l;
-                                for (int j = 0; j < l; ++j)
-                                {
-                                    const unsigned long long eb = lb[j];
-                                    os[w++] = el_pack(__fadd_rn(sa, el_score(eb)), ka | el_key(eb));
-                                }
-                            }
-                            sort_list_desc(os, int(n));
-                        }
-                    }
+                    else if (n) atomicAdd(&s_bh[31 - min(n, 31u)], 1u);                   // longest lists first
                 }
                 cnt_f[c] = uint16_t(n);
                 off_f[c] = uint16_t(off);
             }
             __syncthreads();
+            IPK_PHASE(1 + 3 * min(f, 3));
+            if (h > 1)
+            {
+                // phase A2: the short lists are filled and sorted by one thread each, IN ORDER OF DESCENDING LENGTH, so that the
+                // lanes of a warp run loops of similar trip counts (r01e ncu: 3.5-10 of 32 lanes active in these loops when
+                // thread c simply took column c) and the light warps retire early.
+                if (warp == 0)
+                {
+                    const uint32_t v = s_bh[lane];
+                    const uint32_t inc = warp_incl_scan_u32(v, lane);
+                    s_bh[lane] = inc - v;
+                    if (lane == 31) s_nwork = inc;
+                    if (lane == 31 - (int(A.group_min) - 1)) s_nheavy = inc - v;        // lists of >= JOIN_GROUP_MIN elements come first
+                }
+                __syncthreads();
+                for (int c = tid; c < nlist; c += JOIN_THREADS)
+                {
+                    const uint32_t n = cnt_f[c];
+                    if (n && n <= A.small_list) perm[atomicAdd(&s_bh[31 - min(n, 31u)], 1u)] = uint16_t(c);
+                }
+                __syncthreads();
+                const int nwork = int(s_nwork), nheavy = int(s_nheavy);
+                // the longer lists: JOIN_GROUP lanes each
+                for (int w0 = warp * (32 / JOIN_GROUP); w0 < nheavy; w0 += JOIN_THREADS / JOIN_GROUP)
+                {
+                    const int w = w0 + lane / JOIN_GROUP, gl = lane & (JOIN_GROUP - 1);
+                    const unsigned gmask = ((1u << JOIN_GROUP) - 1) << (lane & ~(JOIN_GROUP - 1));
+                    if (w >= nheavy) continue;                                    // uniform within a group
+                    const int c = perm[w];
+                    const int n = cnt_f[c];
+                    uint32_t off = 0;
+                    int ok = 0;
+                    if (gl == 0) ok = pool_alloc(&s_lo, &s_hi, top, n, off) ? 1 : 0;
+                    off = __shfl_sync(gmask, off, 0, JOIN_GROUP);
+                    ok = __shfl_sync(gmask, ok, 0, JOIN_GROUP);
+                    if (!ok) { if (gl == 0) s_defer = 1; continue; }
+                    build_list_group<JOIN_GROUP>(pool + off_f[(fa - f) * NCP + c], cnt_f[(fa - f) * NCP + c],
+                                                 pool + off_f[(fb - f) * NCP + c + hl], cnt_f[(fb - f) * NCP + c + hl], gthr[c],
+                                                 pool + off, n, hr * bits, gl, gmask);
+                    if (gl == 0) off_f[c] = uint16_t(off);
+                }
+                // the short ones: one thread each
+                for (int w = nheavy + tid; w < nwork; w += JOIN_THREADS)
+                {
+                    const int c = perm[w];
+                    const uint32_t n = cnt_f[c];
+                    const float g = gthr[c];
+                    const int na = cnt_f[(fa - f) * NCP + c], nb = cnt_f[(fb - f) * NCP + c + hl];
+                    const unsigned long long* la = pool + off_f[(fa - f) * NCP + c];
+                    const unsigned long long* lb = pool + off_f[(fb - f) * NCP + c + hl];
+                    uint32_t off = 0;
+                    if (!pool_alloc(&s_lo, &s_hi, top, int(n), off)) { s_defer = 1; continue; }
+                    unsigned long long* os = pool + off;
+                    int wr = 0, l = nb;
+                    for (int i = 0; i < na && l > 0; ++i)
+                    {
+                        const unsigned long long ea = la[i];
+                        const float sa = el_score(ea);
+                        const uint32_t ka = el_key(ea) << (hr * bits);           // prefix = most significant digits (pk_compute.cpp:96-104)
+                        while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > g)) --l;
+                        for (int j = 0; j < l; ++j)
+                        {
+                            const unsigned long long eb = lb[j];
+                            os[wr++] = el_pack(__fadd_rn(sa, el_score(eb)), ka | el_key(eb));
+                        }
+                    }
+                    sort_list_desc(os, int(n));
+                    off_f[c] = uint16_t(off);
+                }
+                __syncthreads();
+            }
+            IPK_PHASE(2 + 3 * min(f, 3));
             // phase B, one warp per long list: row lengths by binary search, staircase expanded 32 elements at a time,
             // bitonic sort in place
             const int qn = int(s_qn[f & 1]);
-            for (int q = warp; q < qn; q += ENUM_WARPS)
+            for (int q = warp; q < qn; q += JOIN_WARPS)
             {
                 if (__shfl_sync(full, *reinterpret_cast<volatile uint32_t*>(&s_defer), 0)) break;
                 const int c = queue[q];
@@ -508,6 +643,7 @@ namespace ipkgpu
                 if (lane == 0) off_f[c] = uint16_t(off);
             }
             __syncthreads();
+            IPK_PHASE(3 + 3 * min(f, 3));
             if (s_defer) break;
         }
         if (s_defer)
@@ -561,6 +697,7 @@ namespace ipkgpu
             return;
         }
 
+        IPK_PHASE(13);
         // ---- exclusive scans over the tile's windows: output offsets and row offsets ----------------------------------
         {
             const uint32_t io = warp_incl_scan_u32(my_out, lane), ir = warp_incl_scan_u32(my_rows, lane);
@@ -568,8 +705,11 @@ namespace ipkgpu
             __syncthreads();
             uint32_t bo = 0, br = 0;
             for (int w = 0; w < warp; ++w) { bo += s_wsum[0][w]; br += s_wsum[1][w]; }
-            wbase[tid] = bo + io - my_out;
-            rbase[tid] = br + ir - my_rows;
+            if (tid < ENUM_THREADS)
+            {
+                wbase[tid] = bo + io - my_out;
+                rbase[tid] = br + ir - my_rows;
+            }
             if (tid == ENUM_THREADS - 1)
             {
                 const uint32_t total = bo + io;
@@ -580,6 +720,7 @@ namespace ipkgpu
                 if (A.node_counts && total) atomicAdd(A.node_counts + lslot, (unsigned long long)total);
             }
             __syncthreads();
+            IPK_PHASE(14);
         }
 
         // ---- emission: every warp expands the rows of its 32 windows, 32 records per step, straight to global memory ---
@@ -615,7 +756,11 @@ namespace ipkgpu
                 {
                     const uint32_t o = o0 + lane;
                     const bool act = o < total;
-                    const int r = owner_lane(incl, act ? o : 0u);
+                    // every row of the batch is non-empty (rbase counts rows with a non-empty join only), so the row of output o is
+                    // (rows that start at or before o0) - 1 + (row starts in (o0, o]): one ballot and one warp OR-reduction
+                    const int first = __popc(__ballot_sync(full, len > 0 && excl <= o0)) - 1;
+                    const uint32_t starts = __reduce_or_sync(full, (len > 0 && excl > o0 && excl < o0 + 32) ? 1u << (excl - o0) : 0u);
+                    const int r = first + __popc(starts & (0xffffffffu >> (31 - lane)));
                     const float sa_r = __shfl_sync(full, sa, r);
                     const uint32_t ka_r = __shfl_sync(full, ka, r);
                     const uint32_t ex_r = __shfl_sync(full, excl, r);
@@ -634,6 +779,8 @@ namespace ipkgpu
                 }
                 pos += total;
             }
+            IPK_PHASE(15);
         }
+#undef IPK_PHASE
     }
 }
