@@ -114,8 +114,10 @@ namespace ipkgpu
     //   pool  u64 [pool_cap]            list elements: fp32 score bits << 32 | key   (the raw TMA-staged tile aliases its start)
     //   sval  f32 [sigma][NCP]          column states' scores, descending
     //   bs    f32 [NCP+4]               B[n][s0 .. s0+NC]
-    //   eps   f32 [2k][ENUM_THREADS]    eps of every tree node for every window of the tile (index-major)
-    //   gthr  f32 [NCP]                 g_h(c) of the family being built
+    //   (eps  f32 [2k][ENUM_THREADS]    eps of every tree node for every window of the tile, index-major: lives in the POOL,
+    //                                   behind the raw tile, only until gall / epsl / epsr have been derived from it)
+    //   gall  f32 [n_fam][NCP]          g_h(c) of every family
+    //   epsl  f32 [ENUM_THREADS]        eps of the root's left child per window;  epsr: of its right child
     //   wbase u32 [ENUM_THREADS+1]      exclusive scan of the windows' output counts
     //   rbase u32 [ENUM_THREADS+1]      exclusive scan of the windows' row counts (rows = left elements with a non-empty row)
     //   fcnt  u16 [n_fam][NCP]          length of G_h(c)
@@ -127,7 +129,7 @@ namespace ipkgpu
     // ----------------------------------------------------------------------------------------------------------
     struct join_layout
     {
-        size_t pool, sval, bs, eps, gthr, wbase, rbase, fcnt, foff, wnr, queue, perm, sidx, total;
+        size_t pool, sval, bs, eps, gall, epsl, epsr, wbase, rbase, fcnt, foff, wnr, queue, perm, sidx, total;
     };
 
     __host__ __device__ inline join_layout make_join_layout(int k, int sigma, int n_fam, uint32_t pool_cap)
@@ -138,8 +140,10 @@ namespace ipkgpu
         L.pool = b; b += size_t(pool_cap) * 8;
         L.sval = b; b += size_t(sigma) * NCP * 4;
         L.bs = b; b += size_t(NCP + 4) * 4;
-        L.eps = b; b += size_t(2 * k) * ENUM_THREADS * 4;
-        L.gthr = b; b += size_t(NCP) * 4;
+        L.eps = L.pool + ((size_t(NC) * sigma * 4 + 15) & ~size_t(15));      // inside the pool, behind the raw tile
+        L.gall = b; b += size_t(n_fam) * NCP * 4;
+        L.epsl = b; b += size_t(ENUM_THREADS) * 4;
+        L.epsr = b; b += size_t(ENUM_THREADS) * 4;
         L.wbase = b; b += size_t(ENUM_THREADS + 1) * 4;
         L.rbase = b; b += size_t(ENUM_THREADS + 1) * 4;
         L.fcnt = b; b += size_t(n_fam) * NCP * 2;
@@ -152,8 +156,11 @@ namespace ipkgpu
         return L;
     }
 
-    /// smallest pool the raw tile fits in (it is staged over the pool's start before any list exists)
-    inline uint32_t join_min_pool(int k, int sigma) { return uint32_t((size_t(ENUM_THREADS + k - 1) * sigma * 4 + 7) / 8 + 16); }
+    /// smallest pool: the raw tile and the transient eps table are staged in it before any list exists
+    inline uint32_t join_min_pool(int k, int sigma)
+    {
+        return uint32_t((((size_t(ENUM_THREADS + k - 1) * sigma * 4 + 15) & ~size_t(15)) + size_t(2 * k) * ENUM_THREADS * 4 + 7) / 8 + 16);
+    }
 
     // threads of a k2_join CTA: one per window of the tile (ENUM_THREADS) plus one warp, so that the tile's
     // ENUM_THREADS + k - 1 columns (k <= 33) are covered by ONE pass of every per-column loop (phase clocks r01m: the second
@@ -263,10 +270,16 @@ namespace ipkgpu
     /// tile: every leaf and every internal node of the subtree is checked against its own eps.  Used only for list
     /// elements whose score lies within DELTA of their node's threshold.
     __device__ __noinline__ bool verify_subtree(uint32_t key, int o, int h, int t, int bits, int sigma, int NCP,
-                                                const float* sval, const uint8_t* sidx, const float* eps,
-                                                const uint32_t* s_pos, const uint32_t* s_merge)
+                                                const float* sval, const uint8_t* sidx, const float* bs, float log_threshold,
+                                                const enum_program& P, const uint32_t* s_pos, const uint32_t* s_merge)
     {
-        float val[2 * MAX_K];
+        float val[2 * MAX_K], eps[2 * MAX_K];
+        eps[0] = log_threshold;                        // the window's threshold chain again (pk_compute.cpp:54-55); this path is rare
+        for (int i = 0; i < P.n_eps_ops; ++i)
+        {
+            const auto op = P.eps_ops[i];
+            eps[op.dst] = __fsub_rn(eps[op.src], __fsub_rn(bs[t + op.hi], bs[t + op.lo]));
+        }
         int merges_left = h - 1;                       // internal nodes of the subtree; they complete before any ancestor's merge
         const uint32_t mask = (1u << bits) - 1;
         for (int q = 0; q < h; ++q)
@@ -279,14 +292,14 @@ namespace ipkgpu
                 if (sidx[r * NCP + col] == state) { v = sval[r * NCP + col]; found = true; break; }
             if (!found) return false;
             const uint32_t pi = s_pos[p];
-            if (!(v > eps[(pi & 0xff) * ENUM_THREADS + t])) return false;
+            if (!(v > eps[pi & 0xff])) return false;
             val[pi & 0xff] = v;
             for (uint32_t m = (pi >> 16) & 0xff; m < (pi >> 24) && merges_left > 0; ++m, --merges_left)
             {
                 const uint32_t mg = s_merge[m];
                 const uint32_t left = mg >> 8, id = mg & 0xff;
                 const float S = __fadd_rn(val[left], val[left + 1]);
-                if (!(S > eps[id * ENUM_THREADS + t])) return false;
+                if (!(S > eps[id])) return false;
                 val[id] = S;
             }
         }
@@ -416,7 +429,9 @@ namespace ipkgpu
         float* sval = reinterpret_cast<float*>(smem_raw + L.sval);
         float* bs = reinterpret_cast<float*>(smem_raw + L.bs);
         float* eps = reinterpret_cast<float*>(smem_raw + L.eps);
-        float* gthr = reinterpret_cast<float*>(smem_raw + L.gthr);
+        float* gall = reinterpret_cast<float*>(smem_raw + L.gall);
+        float* epsl = reinterpret_cast<float*>(smem_raw + L.epsl);
+        float* epsr = reinterpret_cast<float*>(smem_raw + L.epsr);
         uint32_t* wbase = reinterpret_cast<uint32_t*>(smem_raw + L.wbase);
         uint32_t* rbase = reinterpret_cast<uint32_t*>(smem_raw + L.rbase);
         uint16_t* fcnt = reinterpret_cast<uint16_t*>(smem_raw + L.fcnt);
@@ -453,6 +468,20 @@ namespace ipkgpu
             delta = 2.0f * float(k) * 1.2e-7f * bmax + 1e-4f;
         }
         __syncthreads();                                   // raw consumed, sval / eps complete
+        // everything the rest of the kernel needs from the eps table: g_h(c) of every family and the root children's eps
+        for (int c = tid; c < ncols; c += JOIN_THREADS)
+            for (int f = 0; f < J.n_fam; ++f)
+            {
+                float g = __int_as_float(0x7f800000);      // +inf: no window of this tile has a length-h node at column c
+                for (int u = 0; u < J.fam[f].n_uses; ++u)
+                {
+                    const int t = c - int(J.fam[f].use_off[u]);
+                    if (t >= 0 && t < nwin_tile) g = fminf(g, eps[int(J.fam[f].use_node[u]) * ENUM_THREADS + t]);
+                }
+                gall[f * NCP + c] = g;
+            }
+        if (has_window) { epsl[tid] = eps[1 * ENUM_THREADS + tid]; epsr[tid] = eps[2 * ENUM_THREADS + tid]; }   // nodes 1, 2 = the root's children
+        __syncthreads();                                   // the pool may now be overwritten
         IPK_PHASE(0);
 
         // ---- G_h(c) for every family, shortest first -----------------------------------------------------------------
@@ -465,6 +494,7 @@ namespace ipkgpu
             uint16_t* cnt_f = fcnt + f * NCP;
             uint16_t* off_f = foff + f * NCP;
             const bool top = J.fam[f].top != 0;
+            const float* gthr = gall + f * NCP;
             if (J.fam[f].reset)
             {
                 if (tid == 0) s_lo = 0;                        // every list at the bottom end is dead by now (make_join_program)
@@ -477,13 +507,7 @@ namespace ipkgpu
             __syncthreads();
             for (int c = tid; c < nlist; c += JOIN_THREADS)
             {
-                float g = __int_as_float(0x7f800000);      // +inf: no window of this tile has a length-h node at column c
-                for (int u = 0; u < J.fam[f].n_uses; ++u)
-                {
-                    const int t = c - int(J.fam[f].use_off[u]);
-                    if (t >= 0 && t < nwin_tile) g = fminf(g, eps[int(J.fam[f].use_node[u]) * ENUM_THREADS + t]);
-                }
-                gthr[c] = g;
+                const float g = gthr[c];
                 uint32_t n = 0, off = 0;
                 if (h == 1)
                 {
@@ -664,17 +688,17 @@ namespace ipkgpu
             const int na = fcnt[fa0 * NCP + tid], nb = fcnt[fb0 * NCP + tid + hl0];
             const unsigned long long* la = pool + foff[fa0 * NCP + tid];
             const unsigned long long* lb = pool + foff[fb0 * NCP + tid + hl0];
-            const float eps_l = eps[1 * ENUM_THREADS + tid], eps_r = eps[2 * ENUM_THREADS + tid];   // nodes 1, 2 = the root's children
+            const float eps_l = epsl[tid], eps_r = epsr[tid];
             // S(a) > eps_left(s) is exact; the deeper checks of `a` are implied unless S(a) lies within delta of the
             // threshold -- those few elements (the tail of the cut) are put through the predicate itself
             const int nl = cut_above(la, na, eps_l);
             if (hl0 > 1)
                 for (int q = nl - 1; q >= 0 && !(el_score(la[q]) > eps_l + delta); --q)
-                    if (!verify_subtree(el_key(la[q]), 0, hl0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
+                    if (!verify_subtree(el_key(la[q]), 0, hl0, tid, bits, sigma, NCP, sval, sidx, bs, A.log_threshold, P, s_pos, s_merge)) { irregular = true; break; }
             int nr = cut_above(lb, nb, eps_r);
             if (hr0 > 1 && !irregular)
                 for (int q = nr - 1; q >= 0 && !(el_score(lb[q]) > eps_r + delta); --q)
-                    if (!verify_subtree(el_key(lb[q]), hl0, hr0, tid, bits, sigma, NCP, sval, sidx, eps, s_pos, s_merge)) { irregular = true; break; }
+                    if (!verify_subtree(el_key(lb[q]), hl0, hr0, tid, bits, sigma, NCP, sval, sidx, bs, A.log_threshold, P, s_pos, s_merge)) { irregular = true; break; }
             // root join (pk_compute.cpp:75-105): row i = the b with fl(S(a_i) + S(b)) > eps, a prefix that only shrinks with i
             int l = nr;
             for (int i = 0; i < nl; ++i)
