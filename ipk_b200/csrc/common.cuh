@@ -72,6 +72,7 @@ struct ipkgpu_ctx
     ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
     ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
     ipkgpu::dbuf dbg_node, dbg_win, deferred, deferred2;
+    ipkgpu::dbuf mif_tab;              // MIF0: bucket table of mif_log2 (mif_math.cuh)
     ipkgpu::dbuf mif_chunks;           // MIF0: first k-mer of every chunk of entries
     ipkgpu::dbuf rs_status;            // radix sort: look-back status words [tile][digit]
     ipkgpu::dbuf mg_status;            // merge: look-back status words [tile][2]

@@ -5,18 +5,31 @@
 //            std::sort(kmer_order) + the db.at(kmer) walk of filter_in_ram   ipk/src/db_builder.cpp:284,323-332
 #pragma once
 #include "common.cuh"
+#include "mif_math.cuh"
 
 namespace ipkgpu
 {
     /// filter.cpp:20-23: std::min(std::pow(10, log_score), 1.0) evaluated in double, returned as score_type (float).
-    /// exp10 (<= 1 ulp in fp64) stands in for pow(10, x); after the rounding to float the two agree (FV_RTOL covers the rest).
+    /// mif_exp10 (mif_math.cuh; relative error < 1e-14) stands in for pow(10, x): after the rounding to float the two agree.
     __device__ __forceinline__ float logscore_to_score(float log_score)
     {
-        const double p = exp10(double(log_score));
+        const double p = (log_score > -300.0f && log_score <= 0.0f) ? mif_exp10(log_score) : exp10(double(log_score));
         return float(p < 1.0 ? p : 1.0);
     }
-    __device__ __forceinline__ double shannon(double x) { return -x * log2(x); }    // filter.cpp:55-58
+    __device__ __forceinline__ double shannon(double x) { return -x * log2(x); }    // filter.cpp:55-58 (once per k-mer)
+    /// the same for the per-entry terms: mif_log2 for normal positive arguments, libdevice for anything else
+    __device__ __forceinline__ double shannon_fast(double x, const mif_log2_entry* tab)
+    {
+        return (x >= 2.3e-308 && x < 1.0e300) ? -x * mif_log2(x, tab) : -x * log2(x);
+    }
 
+    __device__ __forceinline__ double shfl_xor_f64(unsigned mask, double v, int lane_mask)
+    {
+        int lo = __double2loint(v), hi = __double2hiint(v);
+        lo = __shfl_xor_sync(mask, lo, lane_mask);
+        hi = __shfl_xor_sync(mask, hi, lane_mask);
+        return __hiloint2double(hi, lo);
+    }
     __device__ __forceinline__ double shfl_f64(unsigned mask, double v, int src, int width)
     {
         int lo = __double2loint(v), hi = __double2hiint(v);
@@ -34,6 +47,7 @@ namespace ipkgpu
     // ----------------------------------------------------------------------------------------------------------
     constexpr int MIF_THREADS = 256;
     constexpr int MIF_CHUNK = 1024;          // entries per CTA chunk (k-mers are assigned by their first entry)
+    constexpr int MIF_LONG = 16;             // k-mers with at least this many entries are summed by a warp (fixed lane order)
     constexpr int MIF_CAP = 2048;            // entries a CTA can stage; longer runs take the streaming path
     constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CHUNK) * 8 + size_t(MIF_CHUNK + 2) * 4 + size_t(MIF_CAP) * 2;
 
@@ -70,8 +84,9 @@ namespace ipkgpu
 
     __global__ void __launch_bounds__(MIF_THREADS) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores,
                                                            const uint32_t* __restrict__ chunk_first, uint32_t total_num_groups,
-                                                           float threshold, float* __restrict__ fv)
+                                                           float threshold, float* __restrict__ fv, const mif_log2_entry* __restrict__ log2_tab)
     {
+        __shared__ mif_log2_entry s_tab[MIF_LOG2_BUCKETS];
         extern __shared__ __align__(16) unsigned char mif_smem[];
         double* slot = reinterpret_cast<double*>(mif_smem);                     // [MIF_CAP] x (float, low word) while summing; then the entry's shannon term
         double* ssum = slot + MIF_CAP;                                          // [MIF_CHUNK] per k-mer: score_sum
@@ -80,29 +95,40 @@ namespace ipkgpu
         const uint32_t q0 = chunk_first[blockIdx.x], q1 = chunk_first[blockIdx.x + 1];
         if (q0 == q1) return;
         const int tid = threadIdx.x;
+        if (tid < MIF_LOG2_BUCKETS) s_tab[tid] = log2_tab[tid];          // visible after the first barrier below
         const uint32_t nk = q1 - q0;
         const uint64_t e0 = offs[q0], e1 = offs[q1];
         const uint64_t span = e1 - e0;
         const mif0_consts C{ double(threshold), log2(double(total_num_groups)), double(total_num_groups) };
         float* xs = reinterpret_cast<float*>(slot);    // xs[2*i] = x of entry i
+        const int lane = tid & 31, warp = tid >> 5;
+        constexpr int MIF_WARPS = MIF_THREADS / 32;
+        const unsigned full = 0xffffffffu;
         if (span <= uint64_t(MIF_CAP))
         {
             for (uint32_t j = tid; j <= nk; j += MIF_THREADS) koff[j] = uint32_t(offs[q0 + j] - e0);
             for (uint32_t i = tid; i < uint32_t(span); i += MIF_THREADS) xs[2 * i] = logscore_to_score(scores[e0 + i]);
             __syncthreads();
+            // score sums.  Short k-mers: one thread, stored order (filter.cpp:78-82).  Long ones (>= MIF_LONG entries): one
+            // warp, lane l adds entries l, l+32, ... in order, then the xor butterfly -- a fixed association per k-mer,
+            // whichever path or chunk the k-mer falls into.
             for (uint32_t j = tid; j < nk; j += MIF_THREADS)
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
+                if (b - a >= uint32_t(MIF_LONG)) continue;
                 double s = 0;
-                uint32_t i = a;
-                for (; i + 4 <= b; i += 4)                 // loads first, then the ordered adds (filter.cpp:78-82)
-                {
-                    const float x0 = xs[2 * i], x1 = xs[2 * i + 2], x2 = xs[2 * i + 4], x3 = xs[2 * i + 6];
-                    seg[i] = uint16_t(j); seg[i + 1] = uint16_t(j); seg[i + 2] = uint16_t(j); seg[i + 3] = uint16_t(j);
-                    s = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(s, double(x0)), double(x1)), double(x2)), double(x3));
-                }
-                for (; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
+                for (uint32_t i = a; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
                 ssum[j] = s;
+            }
+            for (uint32_t j = warp; j < nk; j += MIF_WARPS)
+            {
+                const uint32_t a = koff[j], b = koff[j + 1];
+                if (b - a < uint32_t(MIF_LONG)) continue;
+                double s = 0;
+                for (uint32_t i = a + lane; i < b; i += 32) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) s = __dadd_rn(s, shfl_xor_f64(full, s, o));
+                if (lane == 0) ssum[j] = s;
             }
             __syncthreads();
             // every k-mer's score_sum gets its threshold share (:86) -- recomputed by whoever needs it, it is one fp64 fma
@@ -111,69 +137,64 @@ namespace ipkgpu
                 const uint32_t j = seg[i];
                 const double ss = __dadd_rn(ssum[j], __dmul_rn(C.T - double(koff[j + 1] - koff[j]), C.threshold));
                 const double weighted_score = double(xs[2 * i]) / ss;
-                slot[i] = shannon(weighted_score);                                                                    // :103-105
+                slot[i] = shannon_fast(weighted_score, s_tab);                                                                    // :103-105
             }
             __syncthreads();
             for (uint32_t j = tid; j < nk; j += MIF_THREADS)
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
+                if (b - a >= uint32_t(MIF_LONG)) continue;
                 double ss = ssum[j], tt;
                 double H = mif0_tail_begin(ss, b - a, C, tt);
-                uint32_t i = a;
-                for (; i + 4 <= b; i += 4)
-                {
-                    const double t0 = slot[i], t1 = slot[i + 1], t2 = slot[i + 2], t3 = slot[i + 3];
-                    H = __dadd_rn(__dsub_rn(H, tt), t0); H = __dadd_rn(__dsub_rn(H, tt), t1);                         // :107
-                    H = __dadd_rn(__dsub_rn(H, tt), t2); H = __dadd_rn(__dsub_rn(H, tt), t3);
-                }
-                for (; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);
-                fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));                                                // :115
+                for (uint32_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);                        // :107
+                fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));                                            // :115
+            }
+            for (uint32_t j = warp; j < nk; j += MIF_WARPS)
+            {
+                const uint32_t a = koff[j], b = koff[j + 1];
+                if (b - a < uint32_t(MIF_LONG)) continue;
+                double ss = ssum[j], tt;
+                const double H0 = mif0_tail_begin(ss, b - a, C, tt);
+                double d = 0;                                      // sum of (term - target_threshold), same lane order as above
+                for (uint32_t i = a + lane; i < b; i += 32) d = __dadd_rn(d, __dsub_rn(slot[i], tt));
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) d = __dadd_rn(d, shfl_xor_f64(full, d, o));
+                if (lane == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(__dadd_rn(H0, d), C.Hc)));
             }
             return;
         }
-        // streaming path: a run longer than the staging buffer (a k-mer present on thousands of branches).  One k-mer at a
-        // time, MIF_THREADS entries per step: all threads do the transcendental work, thread 0 advances the sums in order.
-        __shared__ double s_bcast[2];
-        for (uint32_t j = 0; j < nk; ++j)
+        // streaming path: a run longer than the staging buffer (a k-mer present on thousands of branches).  Straight from
+        // global memory, one warp per k-mer, in the same two orders.
+        __syncthreads();                                           // s_tab
+        for (uint32_t j = warp; j < nk; j += MIF_WARPS)
         {
             const uint64_t a = offs[q0 + j], b = offs[q0 + j + 1];
+            const bool is_long = b - a >= uint64_t(MIF_LONG);
             double s = 0;
-            for (uint64_t base = a; base < b; base += MIF_THREADS)
+            if (is_long)
             {
-                const uint64_t i = base + tid;
-                if (i < b) xs[2 * tid] = logscore_to_score(scores[i]);
-                __syncthreads();
-                if (tid == 0)
-                {
-                    const int cnt = int(min(uint64_t(MIF_THREADS), b - base));
-                    for (int t = 0; t < cnt; ++t) s = __dadd_rn(s, double(xs[2 * t]));
-                }
-                __syncthreads();
+                for (uint64_t i = a + lane; i < b; i += 32) s = __dadd_rn(s, double(logscore_to_score(scores[i])));
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) s = __dadd_rn(s, shfl_xor_f64(full, s, o));
             }
-            if (tid == 0)
+            else if (lane == 0)
+                for (uint64_t i = a; i < b; ++i) s = __dadd_rn(s, double(logscore_to_score(scores[i])));
+            s = shfl_f64(full, s, 0, 32);
+            double ss = s, tt;
+            const double H0 = mif0_tail_begin(ss, b - a, C, tt);
+            double H = H0;
+            if (is_long)
             {
-                double tt;
-                const double H0 = mif0_tail_begin(s, b - a, C, tt);
-                s_bcast[0] = s; s_bcast[1] = tt;
-                ssum[0] = H0;
+                double d = 0;
+                for (uint64_t i = a + lane; i < b; i += 32)
+                    d = __dadd_rn(d, __dsub_rn(shannon_fast(double(logscore_to_score(scores[i])) / ss, s_tab), tt));
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) d = __dadd_rn(d, shfl_xor_f64(full, d, o));
+                H = __dadd_rn(H0, d);
             }
-            __syncthreads();
-            const double ss = s_bcast[0], tt = s_bcast[1];
-            double H = ssum[0];
-            for (uint64_t base = a; base < b; base += MIF_THREADS)
-            {
-                const uint64_t i = base + tid;
-                if (i < b) slot[tid] = shannon(double(logscore_to_score(scores[i])) / ss);
-                __syncthreads();
-                if (tid == 0)
-                {
-                    const int cnt = int(min(uint64_t(MIF_THREADS), b - base));
-                    for (int t = 0; t < cnt; ++t) H = __dadd_rn(__dsub_rn(H, tt), slot[t]);
-                }
-                __syncthreads();
-            }
-            if (tid == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));
-            __syncthreads();
+            else if (lane == 0)
+                for (uint64_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), shannon_fast(double(logscore_to_score(scores[i])) / ss, s_tab));
+            if (lane == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));
         }
     }
 

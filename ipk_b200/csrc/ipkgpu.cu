@@ -580,10 +580,19 @@ namespace
                 IPK_LAUNCH(ctx, "k4_chunk_first", (n_chunks + 1) * 4,
                            k4_chunk_first<<<uint32_t(div_up<uint64_t>(n_chunks + 1, 256)), 256, 0, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), n_kmers, n_chunks,
                                                                                                                   ctx->mif_chunks.as<uint32_t>()));
+                if (!ctx->mif_tab.p)
+                {
+                    mif_log2_entry tab[MIF_LOG2_BUCKETS];
+                    mif_log2_table(tab);
+                    ctx->reserve(ctx->mif_tab, sizeof tab);
+                    IPK_CUDA(cudaMemcpyAsync(ctx->mif_tab.p, tab, sizeof tab, cudaMemcpyHostToDevice, ctx->stream));
+                    IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+                }
                 IPK_CUDA(cudaFuncSetAttribute(k4_mif0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(MIF_SMEM)));
                 IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,
                            k4_mif0<<<uint32_t(n_chunks), MIF_THREADS, MIF_SMEM, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(),
-                                                                                        ctx->mif_chunks.as<uint32_t>(), sp.total_num_groups, sp.threshold, ctx->fv.as<float>()));
+                                                                                        ctx->mif_chunks.as<uint32_t>(), sp.total_num_groups, sp.threshold, ctx->fv.as<float>(),
+                                                                                        ctx->mif_tab.as<mif_log2_entry>()));
             }
             else
             {
@@ -789,7 +798,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->mg_status, &ctx->mif_chunks, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->deferred2, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
-                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base };
+                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);
