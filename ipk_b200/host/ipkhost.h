@@ -1,0 +1,75 @@
+/* ipkhost.h -- host side of the B200 phylo-k-mer database build above the device C ABI (include/ipkgpu.h).
+ *
+ * Mirrors, for the hot path only, what ipk::build's callers hand it and what it hands the serializer:
+ *   posterior loader   ar::raxmlng_reader::build_index / read_node      ipk/src/ar.cpp:150-270
+ *                      (csv float parsing: strasser csv.h parse_float, csv.h:1024-1085; AA column order ar.cpp:232-234)
+ *   database writer    i2l::save_header + i2l::save_phylo_kmer walk     ipk/src/db_builder.cpp:297-306,323-332
+ *   database reader    what tools/src/diff.cpp:129-295 and dump.cpp:18-33 consume
+ * Plain C entry points so that tests bind them with ctypes; the ipk-b200 executable (main.cpp) is built on them.
+ */
+#ifndef IPKHOST_H
+#define IPKHOST_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IPKHOST_OK       0
+#define IPKHOST_EIO     -1    /* file cannot be opened / read / written */
+#define IPKHOST_EFORMAT -2    /* malformed row, wrong column count, not a number (csv.h error::no_digit) */
+#define IPKHOST_ENOENT  -3    /* node label not in the file ("Could not read the AR matrix for the node", ar.cpp:262) */
+#define IPKHOST_EINVAL  -4
+
+typedef struct ipkhost_ar ipkhost_ar;
+
+/* Index a raxml-ng `*.ancestralProbs` file (ar.cpp:150-188): header line skipped, one block of consecutive rows per
+ * node label.  sigma = 4 (DNA: p_A p_C p_G p_T) or 20 (AA, raxml-ng column order).  n_threads <= 0: all cores. */
+int  ipkhost_ar_open(const char* path, uint32_t sigma, int n_threads, ipkhost_ar** out);
+void ipkhost_ar_close(ipkhost_ar* ar);
+const char* ipkhost_last_error(void);
+uint32_t ipkhost_ar_num_nodes(const ipkhost_ar* ar);
+uint32_t ipkhost_ar_width(const ipkhost_ar* ar);                 /* sites of the first node; every node must agree */
+const char* ipkhost_ar_label(const ipkhost_ar* ar, uint32_t i);  /* labels in file order */
+/* read_node (ar.cpp:200-270) for n labels at once: out[n][width][sigma] log10 posteriors in IPK's state order
+ * (DNA A,C,G,T; AA R,H,K,D,E,S,T,N,Q,C,G,P,A,I,L,M,F,W,Y,V), float arithmetic as the reference's csv reader. */
+int  ipkhost_ar_read_nodes(ipkhost_ar* ar, const char* const* labels, uint32_t n, float* out);
+/* the csv reader's float parser alone (known-answer tests against the reference's own csv.h) */
+int  ipkhost_parse_float(const char* text, float* out);
+
+/* ---- .ipk database file ------------------------------------------------------------------------------------
+ * Layout (UNVERIFIED against i2l, whose source is absent here -- SURVEY.md 8f1; everything below is written and read
+ * through this one module so that a correction is local):
+ *   "serialization::archive" preamble of a Boost binary_oarchive: u64 length 22, the 22 bytes, u16 version 19,
+ *   then raw little-endian primitives:
+ *   header   string sequence_type ("DNA" | "Proteins"); u64 n_index, n_index x { u64 num_nodes; f64 subtree_branch_length };
+ *            string tree (newick); u64 kmer_size; f32 omega; u64 num_kmers; u64 num_entries
+ *   k-mers   num_kmers x { u64 key; f32 filter_value; u64 n; n x { u32 branch; f32 score } }   in the order given
+ *   (strings: u64 length + bytes). */
+typedef struct ipkhost_db
+{
+    const char* sequence_type;
+    const char* tree;
+    uint64_t n_index;
+    const uint64_t* index_num_nodes;           /* [n_index] */
+    const double* index_subtree_branch_length; /* [n_index] */
+    uint64_t kmer_size;
+    float omega;
+    uint64_t n_kmers, n_entries;
+    const uint64_t* keys;                      /* [n_kmers] */
+    const float* fv;                           /* [n_kmers] */
+    const uint64_t* offsets;                   /* [n_kmers + 1] */
+    const uint32_t* branch;                    /* [n_entries] */
+    const float* score;                        /* [n_entries] */
+} ipkhost_db;
+
+int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);
+/* reads a file written by ipkhost_write_ipk; arrays are owned by the returned handle */
+typedef struct ipkhost_db_file ipkhost_db_file;
+int  ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view);
+void ipkhost_free_ipk(ipkhost_db_file* f);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

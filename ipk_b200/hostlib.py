@@ -1,0 +1,120 @@
+"""ctypes bindings of libipkhost.so (ipk_b200/host: posterior loader + .ipk file) -- test / tooling harness of the
+C++ host side; the product path is the ipk-b200 executable built from the same sources."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libipkhost.so")
+EXE_PATH = os.path.join(_HERE, "host", "ipk-b200")
+
+
+class HostDb(C.Structure):
+    _fields_ = [("sequence_type", C.c_char_p), ("tree", C.c_char_p), ("n_index", C.c_uint64),
+                ("index_num_nodes", C.POINTER(C.c_uint64)), ("index_subtree_branch_length", C.POINTER(C.c_double)),
+                ("kmer_size", C.c_uint64), ("omega", C.c_float), ("n_kmers", C.c_uint64), ("n_entries", C.c_uint64),
+                ("keys", C.POINTER(C.c_uint64)), ("fv", C.POINTER(C.c_float)), ("offsets", C.POINTER(C.c_uint64)),
+                ("branch", C.POINTER(C.c_uint32)), ("score", C.POINTER(C.c_float))]
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run __graft_entry__.build()")
+        lib = C.CDLL(LIB_PATH)
+        P = C.POINTER
+        lib.ipkhost_ar_open.argtypes = [C.c_char_p, C.c_uint32, C.c_int, P(C.c_void_p)]
+        lib.ipkhost_ar_close.argtypes = [C.c_void_p]
+        lib.ipkhost_ar_close.restype = None
+        lib.ipkhost_last_error.restype = C.c_char_p
+        lib.ipkhost_ar_num_nodes.argtypes = [C.c_void_p]
+        lib.ipkhost_ar_num_nodes.restype = C.c_uint32
+        lib.ipkhost_ar_width.argtypes = [C.c_void_p]
+        lib.ipkhost_ar_width.restype = C.c_uint32
+        lib.ipkhost_ar_label.argtypes = [C.c_void_p, C.c_uint32]
+        lib.ipkhost_ar_label.restype = C.c_char_p
+        lib.ipkhost_ar_read_nodes.argtypes = [C.c_void_p, P(C.c_char_p), C.c_uint32, C.c_void_p]
+        lib.ipkhost_parse_float.argtypes = [C.c_char_p, P(C.c_float)]
+        lib.ipkhost_write_ipk.argtypes = [C.c_char_p, P(HostDb)]
+        lib.ipkhost_read_ipk.argtypes = [C.c_char_p, P(C.c_void_p), P(HostDb)]
+        lib.ipkhost_free_ipk.argtypes = [C.c_void_p]
+        lib.ipkhost_free_ipk.restype = None
+        _lib = lib
+    return _lib
+
+
+class HostError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"ipkhost error {code}: {message}")
+        self.code = code
+
+
+def parse_float(text: str) -> float:
+    v = C.c_float(0)
+    rc = load().ipkhost_parse_float(text.encode(), C.byref(v))
+    if rc != 0:
+        raise HostError(rc, load().ipkhost_last_error().decode())
+    return v.value
+
+
+def read_ar(path: str, sigma: int, labels: list[str] | None = None, threads: int = 0):
+    """-> (labels, logp [n, width, sigma] f32) for the given node labels (default: every node, file order)"""
+    lib = load()
+    h = C.c_void_p(0)
+    rc = lib.ipkhost_ar_open(path.encode(), sigma, threads, C.byref(h))
+    if rc != 0:
+        raise HostError(rc, lib.ipkhost_last_error().decode())
+    try:
+        if labels is None:
+            labels = [lib.ipkhost_ar_label(h, i).decode() for i in range(lib.ipkhost_ar_num_nodes(h))]
+        width = lib.ipkhost_ar_width(h)
+        out = np.empty((len(labels), width, sigma), np.float32)
+        arr = (C.c_char_p * len(labels))(*[s.encode() for s in labels])
+        rc = lib.ipkhost_ar_read_nodes(h, arr, len(labels), out.ctypes.data)
+        if rc != 0:
+            raise HostError(rc, lib.ipkhost_last_error().decode())
+        return labels, out
+    finally:
+        lib.ipkhost_ar_close(h)
+
+
+def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega: float, sequence_type: str = "DNA",
+              tree: str = "", index_num_nodes=None, index_len=None) -> None:
+    keys = np.ascontiguousarray(keys, np.uint64); fv = np.ascontiguousarray(fv, np.float32)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    branch = np.ascontiguousarray(branch, np.uint32); score = np.ascontiguousarray(score, np.float32)
+    inn = np.ascontiguousarray(index_num_nodes if index_num_nodes is not None else [], np.uint64)
+    il = np.ascontiguousarray(index_len if index_len is not None else [], np.float64)
+    db = HostDb(sequence_type.encode(), tree.encode(), len(inn), inn.ctypes.data_as(C.POINTER(C.c_uint64)),
+                il.ctypes.data_as(C.POINTER(C.c_double)), kmer_size, omega, len(keys), len(branch),
+                keys.ctypes.data_as(C.POINTER(C.c_uint64)), fv.ctypes.data_as(C.POINTER(C.c_float)),
+                offsets.ctypes.data_as(C.POINTER(C.c_uint64)), branch.ctypes.data_as(C.POINTER(C.c_uint32)),
+                score.ctypes.data_as(C.POINTER(C.c_float)))
+    rc = load().ipkhost_write_ipk(path.encode(), C.byref(db))
+    if rc != 0:
+        raise HostError(rc, "cannot write " + path)
+
+
+def read_ipk(path: str) -> dict:
+    lib = load()
+    h = C.c_void_p(0)
+    v = HostDb()
+    rc = lib.ipkhost_read_ipk(path.encode(), C.byref(h), C.byref(v))
+    if rc != 0:
+        raise HostError(rc, "cannot read " + path)
+    try:
+        nk, ne, ni = int(v.n_kmers), int(v.n_entries), int(v.n_index)
+        arr = lambda p, n: np.ctypeslib.as_array(p, (n,)).copy() if n else np.zeros(0, np.ctypeslib.as_array(p, (1,)).dtype if p else np.uint8)
+        return dict(sequence_type=v.sequence_type.decode(), tree=v.tree.decode(), kmer_size=int(v.kmer_size), omega=float(v.omega),
+                    index_num_nodes=arr(v.index_num_nodes, ni), index_len=arr(v.index_subtree_branch_length, ni),
+                    keys=arr(v.keys, nk), fv=arr(v.fv, nk), offsets=np.ctypeslib.as_array(v.offsets, (nk + 1,)).copy(),
+                    branch=arr(v.branch, ne), score=arr(v.score, ne))
+    finally:
+        lib.ipkhost_free_ipk(h)
