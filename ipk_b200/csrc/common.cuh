@@ -72,6 +72,10 @@ struct ipkgpu_ctx
     ipkgpu::dbuf logp, colmax, bestpref, node_group, node_order, group_branch, counters, node_counts;
     ipkgpu::dbuf keys_a, keys_b, vals_a, vals_b, hist, scan_tmp, block_counts, block_offs;
     ipkgpu::dbuf dbg_node, dbg_win, deferred, deferred2;
+    ipkgpu::dbuf tile_status;          // ordered emission: look-back status word per tile of the join kernel's first level
+    ipkgpu::dbuf side_keys_a, side_keys_b, side_vals_a, side_vals_b;   // ... and the side stream of the tiles it deferred
+    ipkgpu::dbuf mg_split;             // merge: B-elements before every tile boundary of the merged (main, side) sequence
+    int ordered = 0;                   // 1: ordered emission + k-mer-only sort (env IPKGPU_ORDERED=1); measured slower, see DESIGN.md
     ipkgpu::dbuf mif_tab;              // MIF0: bucket table of mif_log2 (mif_math.cuh)
     ipkgpu::dbuf mif_chunks;           // MIF0: first k-mer of every chunk of entries
     ipkgpu::dbuf rs_status;            // radix sort: look-back status words [tile][digit]
@@ -97,6 +101,7 @@ struct ipkgpu_ctx
     std::vector<ipc_mapping> ipc_open;  // peers' receive buffers mapped into this process
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;
+    uint64_t hint_side = 0;            // ... and of its side stream
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
     // pinned host staging
     ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score;

@@ -152,6 +152,9 @@ namespace ipkgpu
         uint32_t item_windows, items_per_tile, parent_ratio;
         uint32_t* deferred_tiles;     // join kernel: items it could not finish (lists too long for the pool ...); their number is counter[1]
         uint32_t pool_cap;            // join kernel: list-pool capacity in elements (<= 65535)
+        // ordered emission (level 0 of the join kernel): status word per tile, flag << 62 | records; a tile's output offset is the
+        // sum over all tiles BEFORE it (decoupled look-back), so the record stream is in tile order = branch-group order
+        unsigned long long* tile_status;
         unsigned long long* phase_clocks;   // debug (IPKGPU_PHASE_CLOCKS): cycles of thread 0 per phase of the join kernel, summed over tiles
         uint32_t group_min;           // join kernel: lists of at least this many elements are built by a lane group
         uint32_t small_list;          // join kernel: lists up to this length are filled and sorted by their owner thread

@@ -147,6 +147,9 @@ namespace
         uint64_t* out_keys; float* out_scores;
         uint32_t* out_node = nullptr; uint32_t* out_win = nullptr;     // debug
         bool debug = false;
+        // ordered emission: level 0 of the join kernel writes (out_keys, out_scores) in tile order; the tiles it defers are
+        // enumerated into this side stream (any order).  side_keys == nullptr: one stream, any order.
+        uint64_t* side_keys = nullptr; float* side_scores = nullptr; uint64_t side_cap = 0;
     };
 
     uint64_t read_u64(ipkgpu_ctx* ctx, const void* d);
@@ -224,6 +227,15 @@ namespace
             IPK_CUDA(cudaMemsetAsync(ctx->peer_base.p, 0, 256, ctx->stream));
             A.phase_clocks = ctx->peer_base.as<unsigned long long>();
         }
+        const bool ordered = use_join && !L.debug && L.side_keys != nullptr;
+        unsigned long long* const counters = ctx->counters.as<unsigned long long>();
+        if (ordered)
+        {
+            ctx->reserve(ctx->tile_status, grid * 8);
+            IPK_CUDA(cudaMemsetAsync(ctx->tile_status.p, 0, grid * 8, ctx->stream));
+            IPK_CUDA(cudaMemsetAsync(counters + 8, 0, 16, ctx->stream));
+            A.tile_status = ctx->tile_status.as<unsigned long long>();
+        }
         if (use_join)
         {
             // Levels: every tile with a small pool (several CTAs per SM); what did not fit is retried with larger pools, then
@@ -249,7 +261,7 @@ namespace
                 ctx->reserve(out_list, lvl_grid * 4);
                 lists[level & 1] = out_list.as<uint32_t>();
                 A.deferred_tiles = lists[level & 1];
-                IPK_CUDA(cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 1, 0, 8, ctx->stream));
+                IPK_CUDA(cudaMemsetAsync(A.counter + 1, 0, 8, ctx->stream));
                 const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
                 if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
                 const uint64_t lvl_in_bytes = level == 0 ? in_bytes : lvl_grid * uint64_t(width + in->k) * (in->sigma + 1) * 4;
@@ -264,13 +276,21 @@ namespace
                     IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 uint64_t h[2] = { 0, 0 };
-                IPK_CUDA(cudaMemcpyAsync(h, ctx->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+                IPK_CUDA(cudaMemcpyAsync(h, A.counter, 16, cudaMemcpyDeviceToHost, ctx->stream));
                 IPK_CUDA(cudaStreamSynchronize(ctx->stream));
-                ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], L.cap) - std::min<uint64_t>(emitted_before, L.cap)));
+                ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], A.cap) - std::min<uint64_t>(emitted_before, A.cap)));
                 emitted_before = h[0];
                 n_items = h[1];
                 prev_width = width;
                 A.tile_list = lists[level & 1];
+                if (ordered && level == 0)
+                {
+                    // everything after the ordered level goes to the side stream, with its own counters
+                    A.tile_status = nullptr;
+                    A.out_keys = L.side_keys; A.out_scores = L.side_scores; A.cap = L.side_cap;
+                    A.counter = counters + 8;
+                    emitted_before = 0;
+                }
             }
             if (A.phase_clocks)
             {
@@ -284,7 +304,7 @@ namespace
             // the depth-first kernel takes the remaining items as they are
             A.parent_ratio = 1;
             n_deferred = n_items;
-            ctx->enum_join_emitted = emitted_before;
+            ctx->enum_join_emitted = ordered ? 0 : emitted_before;      // (only used for the byte accounting of the depth-first kernel)
             ctx->last_deferred_tiles += n_deferred;
             ctx->last_tiles += grid;
         }
@@ -319,11 +339,14 @@ namespace
 
     /// K3 on n sorted records (keys, scores): segmented max over equal composite keys, compaction, and -- when
     /// `csr` -- the CSR by k-mer (K3').  Unique records go to (u_keys, u_scores) + u_off when `unique`.
-    merge_out run_merge(ipkgpu_ctx* ctx, const uint64_t* keys, const float* scores, uint64_t n, uint32_t group_bits,
-                        uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr, uint32_t key_bits)
+    merge_out run_merge(ipkgpu_ctx* ctx, const uint64_t* keys, const float* scores, uint64_t n_main, uint32_t group_bits,
+                        uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr, uint32_t key_bits,
+                        const uint64_t* side_keys = nullptr, const float* side_scores = nullptr, uint64_t n_side = 0)
     {
         merge_out r;
+        const uint64_t n = n_main + n_side;          // the kernel walks the merge of the two sorted streams
         if (n == 0) return r;
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed the 2^32-1 limit of one merge", (unsigned long long)n);
         const uint32_t tiles = uint32_t(div_up<uint64_t>(n, MG_TILE));
         // single pass: the outputs are sized by their upper bounds (records <= n, k-mers <= min(n, 2^key_bits))
         const uint64_t kmer_bound = key_bits < 40 ? std::min<uint64_t>(n, 1ull << key_bits) : n;
@@ -339,7 +362,7 @@ namespace
             ctx->reserve(ctx->ent_branch, n * 4 + 4);
             ctx->reserve(ctx->ent_score, n * 4 + 4);
         }
-        ctx->reserve(ctx->counters, 64);
+        ctx->reserve(ctx->counters, 128);
         const size_t status_bytes = size_t(tiles) * 16;
         if (status_bytes > ctx->mg_status.cap)
         {
@@ -356,6 +379,14 @@ namespace
         IPK_CUDA(cudaMemsetAsync(totals, 0, 24, ctx->stream));
         merge_args M;
         M.ckeys = keys; M.scores = scores; M.n = n;
+        M.skeys = side_keys; M.sscores = side_scores; M.ns = n_side; M.split = nullptr;
+        if (n_side)
+        {
+            ctx->reserve(ctx->mg_split, (size_t(tiles) + 1) * 4);
+            M.split = ctx->mg_split.as<uint32_t>();
+            IPK_LAUNCH(ctx, "mg_split", (uint64_t(tiles) + 1) * 20,
+                       mg_split<<<div_up<uint32_t>(tiles + 1, 256), 256, 0, ctx->stream>>>(keys, n_main, side_keys, n_side, tiles, ctx->mg_split.as<uint32_t>()));
+        }
         M.group_bits = group_bits; M.out_group_bits = out_group_bits; M.group_add = group_add;
         M.u_keys = unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr;
         M.u_scores = unique ? ctx->u_scores.as<float>() + u_off : nullptr;
@@ -413,9 +444,9 @@ namespace
         const size_t e0 = tm.mark();
         run_best_prefix(ctx, d_logp, in);
         const size_t e1 = tm.mark();
-        ctx->reserve(ctx->counters, 64);
+        ctx->reserve(ctx->counters, 128);
         ctx->reserve(ctx->node_counts, size_t(in->n_nodes) * 8 + 8);
-        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 128, ctx->stream));
         IPK_CUDA(cudaMemsetAsync(ctx->node_counts.p, 0, size_t(in->n_nodes) * 8 + 8, ctx->stream));
         ctx->s1_n = 0;
         if (in->n_nodes == 0 || in->width < in->k)
@@ -441,13 +472,31 @@ namespace
         ctx->reserve(ctx->vals_a, cap0 * 4);
         // raw: the records leave this rank unsorted and unmerged, so they carry the GLOBAL group field from the start
         enum_launch L{ 0, in->n_nodes, raw ? 0u : group_base, raw ? group_bits : all_bits, cap0, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>() };
+        // Ordered emission (single batch, local sort): the join kernel's first level writes its records in tile order = group
+        // order, so a STABLE sort on the k-mer bits alone brings equal (k-mer, group) together -- key_bits / 8 radix passes
+        // instead of (key_bits + group_bits) / 8.  The few tiles that level defers go to a side stream that is sorted on
+        // all bits and merged in by the max-merge kernel.
+        const bool ordered = ctx->ordered && !raw && in->k >= 2 && ctx->enum_mode != 1;
+        uint64_t side_cap = 0;
+        if (ordered)
+        {
+            side_cap = std::max<uint64_t>({ uint64_t(1) << 20, cap0 / 16, ctx->hint_side + ctx->hint_side / 2 });
+            ctx->reserve(ctx->side_keys_a, side_cap * 8);
+            ctx->reserve(ctx->side_vals_a, side_cap * 4);
+            L.side_keys = ctx->side_keys_a.as<uint64_t>(); L.side_scores = ctx->side_vals_a.as<float>(); L.side_cap = side_cap;
+        }
         launch_enumerate(ctx, d_logp, in, P, L, true);
         o.enum_launches = 1;
-        o.n_emitted = read_u64(ctx, ctx->counters.p);
-        ctx->kprof_add_bytes("k2_enumerate", 12 * (std::min(o.n_emitted, cap0) - std::min(ctx->enum_join_emitted, cap0)));
+        uint64_t n_main = read_u64(ctx, ctx->counters.p), n_side = 0;
+        if (ordered) n_side = read_u64(ctx, ctx->counters.as<unsigned long long>() + 8);
+        o.n_emitted = n_main + n_side;
+        ctx->kprof_add_bytes("k2_enumerate", 12 * (ordered ? std::min(n_side, side_cap) : std::min(o.n_emitted, cap0) - std::min(ctx->enum_join_emitted, cap0)));
         ctx->hint_emitted = o.n_emitted;
-        bool first_valid = o.n_emitted <= cap0;
-        if (first_valid) batches.push_back({ 0, o.n_groups, o.n_emitted });
+        ctx->hint_side = n_side;
+        // a side stream that overflowed its buffer sends the build down the batch path, which enumerates unordered
+        bool first_valid = n_main <= cap0 && n_side <= side_cap;
+        const bool use_side = ordered && first_valid;
+        if (first_valid) batches.push_back({ 0, o.n_groups, n_main });
         else
         {
             // the first attempt overflowed its buffer: it still counted every node exactly -> plan batches of whole groups
@@ -513,14 +562,28 @@ namespace
             ctx->reserve(ctx->keys_b, b.n * 8 + 8);
             ctx->reserve(ctx->vals_b, b.n * 4 + 4);
             uint32_t passes = 0;
+            // ordered main stream: stable sort on the k-mer bits only (bit_begin = width of the group field)
             const bool in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
-                                               ctx->vals_b.as<uint32_t>(), b.n, key_bits + bbits, ctx->hist, ctx->scan_tmp, &passes);
+                                               ctx->vals_b.as<uint32_t>(), b.n, use_side ? key_bits : key_bits + bbits, ctx->hist, ctx->scan_tmp,
+                                               &passes, use_side ? bbits : 0);
             o.sort_passes += passes;
+            const uint64_t* side_k = nullptr;
+            const float* side_v = nullptr;
+            if (use_side && n_side)
+            {
+                ctx->reserve(ctx->side_keys_b, n_side * 8 + 8);
+                ctx->reserve(ctx->side_vals_b, n_side * 4 + 4);
+                const bool side_in_b = radix_sort_pairs(ctx, ctx->side_keys_a.as<uint64_t>(), ctx->side_vals_a.as<uint32_t>(), ctx->side_keys_b.as<uint64_t>(),
+                                                        ctx->side_vals_b.as<uint32_t>(), n_side, key_bits + bbits, ctx->hist, ctx->scan_tmp);
+                side_k = side_in_b ? ctx->side_keys_b.as<uint64_t>() : ctx->side_keys_a.as<uint64_t>();
+                side_v = side_in_b ? ctx->side_vals_b.as<float>() : ctx->side_vals_a.as<float>();
+            }
             const size_t ec = tm.mark();
             const uint64_t* sk = in_b ? ctx->keys_b.as<uint64_t>() : ctx->keys_a.as<uint64_t>();
             const float* sv = in_b ? ctx->vals_b.as<float>() : ctx->vals_a.as<float>();
             const bool csr = single && want_csr;
-            const merge_out m = run_merge(ctx, sk, sv, b.n, bbits, group_bits, group_base + b.g0, !csr, u_off, csr, key_bits);
+            const merge_out m = run_merge(ctx, sk, sv, b.n, bbits, group_bits, group_base + b.g0, !csr, u_off, csr, key_bits,
+                                          side_k, side_v, side_k ? n_side : 0);
             if (csr) { o.csr_done = true; o.n_kmers = m.n_kmers; }
             u_off += m.n_records;
             const size_t ed = tm.mark();
@@ -755,6 +818,7 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
     if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
+    if (const char* e = getenv("IPKGPU_ORDERED")) ctx->ordered = atoi(e);
     if (const char* e = getenv("IPKGPU_GROUP_MIN")) ctx->group_min = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_SMALL_LIST")) ctx->small_list = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_LEVELS"))
@@ -798,7 +862,8 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->mg_status, &ctx->mif_chunks, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->deferred2, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
-                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab };
+                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
+                            &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);
@@ -911,8 +976,8 @@ int ipkgpu_enumerate(ipkgpu_ctx* ctx, const ipkgpu_input* in, uint64_t cap,
         const group_tables T = make_groups(in->node_branch, in->n_nodes, 0);
         const float* d_logp = stage_inputs(ctx, in, T, nullptr);
         run_best_prefix(ctx, d_logp, in);
-        ctx->reserve(ctx->counters, 64);
-        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+        ctx->reserve(ctx->counters, 128);
+        IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 128, ctx->stream));
         ctx->reserve(ctx->keys_a, cap * 8 + 8); ctx->reserve(ctx->vals_a, cap * 4 + 4);
         ctx->reserve(ctx->dbg_node, cap * 4 + 4); ctx->reserve(ctx->dbg_win, cap * 4 + 4);
         *n_out = 0;

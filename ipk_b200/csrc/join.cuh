@@ -399,6 +399,31 @@ namespace ipkgpu
             if (gl + q * G < n) os[rk[q]] = ev[q];
     }
 
+    constexpr unsigned long long JOIN_ST_LOCAL = 1ull << 62, JOIN_ST_INCL = 2ull << 62, JOIN_ST_MASK = (1ull << 62) - 1;
+
+    /// records emitted by all tiles before `tile` (one warp; 32 predecessors per step; every lane gets the sum).  Tiles are
+    /// block indices of one launch, dispatched in order, so every predecessor is running or done.
+    __device__ __forceinline__ unsigned long long join_look_back(const volatile unsigned long long* st, uint32_t tile, int lane)
+    {
+        unsigned long long sum = 0;
+        long long base = (long long)tile - 1;
+        while (base >= 0)
+        {
+            const long long t = base - lane;
+            unsigned long long w = JOIN_ST_INCL;                       // lanes that fall off the front see an inclusive zero
+            if (t >= 0) do { w = st[t]; } while ((w >> 62) == 0);
+            const unsigned incl = __ballot_sync(0xffffffffu, (w >> 62) == 2);
+            const int first = incl ? __ffs(incl) - 1 : 32;
+            unsigned long long v = lane <= first ? (w & JOIN_ST_MASK) : 0ull;
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            sum += v;
+            if (incl) break;
+            base -= 32;
+        }
+        return sum;
+    }
+
     template<bool DEBUG>
     __global__ void __launch_bounds__(JOIN_THREADS)
     k2_join(const __grid_constant__ enum_args A, const __grid_constant__ enum_program P, const __grid_constant__ join_program J)
@@ -672,8 +697,12 @@ namespace ipkgpu
         }
         if (s_defer)
         {
-            // the lists of this tile do not fit: hand the whole tile to the depth-first kernel (nothing was emitted yet)
-            if (tid == 0) A.deferred_tiles[atomicAdd(A.counter + 1, 1ull)] = tile;
+            // the lists of this tile do not fit: hand the whole tile to the next level (nothing was emitted yet)
+            if (tid == 0)
+            {
+                A.deferred_tiles[atomicAdd(A.counter + 1, 1ull)] = tile;
+                if (A.tile_status) *reinterpret_cast<volatile unsigned long long*>(A.tile_status + tile) = JOIN_ST_LOCAL;     // no records from here
+            }
             return;
         }
 
@@ -717,7 +746,11 @@ namespace ipkgpu
         // give the whole tile to the depth-first kernel (nothing was emitted yet).
         if (__syncthreads_or(irregular ? 1 : 0))
         {
-            if (tid == 0) A.deferred_tiles[atomicAdd(A.counter + 1, 1ull)] = tile;
+            if (tid == 0)
+            {
+                A.deferred_tiles[atomicAdd(A.counter + 1, 1ull)] = tile;
+                if (A.tile_status) *reinterpret_cast<volatile unsigned long long*>(A.tile_status + tile) = JOIN_ST_LOCAL;
+            }
             return;
         }
 
@@ -739,11 +772,31 @@ namespace ipkgpu
                 const uint32_t total = bo + io;
                 wbase[ENUM_THREADS] = total;
                 rbase[ENUM_THREADS] = br + ir;
-                // ONE global atomic per tile reserves the tile's exact output range
-                s_base = total ? atomicAdd(A.counter, (unsigned long long)total) : 0ull;
+                // ONE global atomic per tile reserves the tile's exact output range ...
+                if (!A.tile_status) s_base = total ? atomicAdd(A.counter, (unsigned long long)total) : 0ull;
+                else
+                {
+                    // ... or, in ordered mode, only counts; the range follows from the look-back below
+                    *reinterpret_cast<volatile unsigned long long*>(A.tile_status + tile) = (tile == 0 ? JOIN_ST_INCL : JOIN_ST_LOCAL) | total;
+                    if (total) atomicAdd(A.counter, (unsigned long long)total);
+                }
                 if (A.node_counts && total) atomicAdd(A.node_counts + lslot, (unsigned long long)total);
             }
             __syncthreads();
+            if (A.tile_status)
+            {
+                if (warp == 0)
+                {
+                    unsigned long long before = 0;
+                    if (tile > 0)
+                    {
+                        before = join_look_back(A.tile_status, tile, lane);
+                        if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(A.tile_status + tile) = JOIN_ST_INCL | (before + wbase[ENUM_THREADS]);
+                    }
+                    if (lane == 0) s_base = before;
+                }
+                __syncthreads();
+            }
             IPK_PHASE(14);
         }
 

@@ -49,9 +49,12 @@ namespace ipkgpu
 
     struct merge_args
     {
-        const uint64_t* ckeys;             // sorted composite keys
+        const uint64_t* ckeys;             // sorted composite keys (main stream)
         const float* scores;
-        uint64_t n;
+        uint64_t n;                        // records of BOTH streams
+        // side stream (the tiles the ordered enumeration level deferred), sorted too; the kernel walks the MERGE of the two
+        // (equal keys: main first).  split[t] = side records among the first t * MG_TILE merged records (mg_split).
+        const uint64_t* skeys; const float* sscores; uint64_t ns; const uint32_t* split;
         uint32_t group_bits;               // width of the (batch-local) group field of ckeys
         uint32_t out_group_bits;           // width of the group field of the compacted records
         uint32_t group_add;                // batch-local group + group_add = global group
@@ -64,12 +67,30 @@ namespace ipkgpu
         uint32_t epoch;
     };
 
+    /// split[t] = number of side records among the first min(t * MG_TILE, n) records of the merge (equal keys: main first),
+    /// t = 0 .. tiles: the smallest j with  main[m - j - 1] <= side[j]  (merge path).
+    __global__ void mg_split(const uint64_t* __restrict__ mkeys, uint64_t nm, const uint64_t* __restrict__ skeys, uint64_t ns,
+                             uint32_t tiles, uint32_t* __restrict__ split)
+    {
+        const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+        if (t > tiles) return;
+        const uint64_t m = min(uint64_t(t) * MG_TILE, nm + ns);
+        uint64_t lo = m > nm ? m - nm : 0, hi = min(m, ns);
+        while (lo < hi)
+        {
+            const uint64_t j = (lo + hi) >> 1;
+            // m - j main records precede: fine iff the last of them is not greater than the next side record
+            if (m - j > 0 && mkeys[m - j - 1] > skeys[j]) lo = j + 1; else hi = j;
+        }
+        split[t] = uint32_t(lo);
+    }
+
     __global__ void __launch_bounds__(MG_THREADS) mg_merge(const __grid_constant__ merge_args A)
     {
         __shared__ uint64_t sk[MG_TILE + 1];            // sk[0] = the key before the tile
         __shared__ float ss[MG_TILE];
         __shared__ uint32_t s_cnt[2][MG_ITEMS][MG_WARPS];
-        __shared__ uint32_t s_tile, s_before[2];
+        __shared__ uint32_t s_tile, s_before[2], s_first;
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const unsigned full = 0xffffffffu;
@@ -78,13 +99,47 @@ namespace ipkgpu
         const uint32_t tile = s_tile;
         const uint64_t base = uint64_t(tile) * MG_TILE;
         const uint32_t tile_n = uint32_t(min(uint64_t(MG_TILE), A.n - base));
-#pragma unroll
-        for (int j = 0; j < MG_ITEMS; ++j)
+        const uint32_t j0 = A.ns ? A.split[tile] : 0u, j1 = A.ns ? A.split[tile + 1] : 0u;
+        const uint64_t a0 = base - j0, na = A.n - A.ns;          // first main record of the tile; main records in all
+        const uint32_t nst = j1 - j0, nat = tile_n - nst;        // side / main records of this tile
+        if (nst == 0)
         {
-            const uint32_t q = uint32_t(j) * MG_THREADS + tid;
-            if (q < tile_n) { sk[q + 1] = A.ckeys[base + q]; ss[q] = A.scores[base + q]; }
+#pragma unroll
+            for (int j = 0; j < MG_ITEMS; ++j)
+            {
+                const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+                if (q < tile_n) { sk[q + 1] = A.ckeys[a0 + q]; ss[q] = A.scores[a0 + q]; }
+            }
         }
-        if (tid == 0) sk[0] = base ? A.ckeys[base - 1] : ~A.ckeys[0];
+        else
+        {
+            // a tile with records of both streams (rare): every record finds its merged position by a binary search in the
+            // other stream's part of the tile
+            for (uint32_t q = tid; q < nat; q += MG_THREADS)
+            {
+                const uint64_t key = A.ckeys[a0 + q];
+                uint32_t lo = 0, hi = nst;                       // side records of the tile with a key < this one
+                while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (A.skeys[j0 + mid] < key) lo = mid + 1; else hi = mid; }
+                sk[q + lo + 1] = key; ss[q + lo] = A.scores[a0 + q];
+            }
+            for (uint32_t q = tid; q < nst; q += MG_THREADS)
+            {
+                const uint64_t key = A.skeys[j0 + q];
+                uint32_t lo = 0, hi = nat;                       // main records of the tile with a key <= this one
+                while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (A.ckeys[a0 + mid] <= key) lo = mid + 1; else hi = mid; }
+                sk[q + lo + 1] = key; ss[q + lo] = A.sscores[j0 + q];
+            }
+        }
+        if (tid == 0)
+        {
+            // the merged record before the tile = the larger of the two streams' predecessors
+            uint64_t prev = 0;
+            bool any = false;
+            if (a0 > 0) { prev = A.ckeys[a0 - 1]; any = true; }
+            if (j0 > 0) { const uint64_t p = A.skeys[j0 - 1]; if (!any || p > prev) prev = p; any = true; }
+            sk[0] = prev;
+            s_first = any ? 0u : 1u;
+        }
         __syncthreads();
         // heads: a record whose composite key differs from its predecessor's; a k-mer head: whose k-mer differs
         unsigned hb[MG_ITEMS], kb[MG_ITEMS];
@@ -96,8 +151,9 @@ namespace ipkgpu
             if (q < tile_n)
             {
                 const uint64_t cur = sk[q + 1], prev = sk[q];
-                head = cur != prev;
-                khead = (cur >> A.group_bits) != (prev >> A.group_bits) || (base + q == 0);
+                const bool very_first = q == 0 && s_first;
+                head = cur != prev || very_first;
+                khead = (cur >> A.group_bits) != (prev >> A.group_bits) || very_first;
             }
             hb[j] = __ballot_sync(full, head);
             kb[j] = __ballot_sync(full, khead);
@@ -135,7 +191,10 @@ namespace ipkgpu
             uint32_t r = q + 1;
             for (; r < tile_n && sk[r + 1] == cur; ++r) { const float v = ss[r]; if (m < v) m = v; }   // branch_group.cpp:92 `it->second < kmer.score`
             if (r == tile_n)
-                for (uint64_t g = base + tile_n; g < A.n && A.ckeys[g] == cur; ++g) { const float v = A.scores[g]; if (m < v) m = v; }
+            {
+                for (uint64_t g = a0 + nat; g < na && A.ckeys[g] == cur; ++g) { const float v = A.scores[g]; if (m < v) m = v; }
+                for (uint64_t g = j1; g < A.ns && A.skeys[g] == cur; ++g) { const float v = A.sscores[g]; if (m < v) m = v; }
+            }
             best[j] = m;
         }
         if (warp < 2)

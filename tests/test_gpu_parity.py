@@ -264,6 +264,31 @@ def test_peer_scatter_equals_single(world, sigma, bits, k, n_taxa, W, raw):
             c.close()
 
 
+@pytest.mark.parametrize("pool_cap", [0, 700])
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 10, 12, 400), (20, 5, 4, 6, 150)])
+def test_ordered_emission_equals_default(sigma, bits, k, n_taxa, W, pool_cap, monkeypatch):
+    """IPKGPU_ORDERED=1: the join kernel's first level emits in tile (= branch-group) order through a decoupled look-back,
+    the main stream is sorted on the k-mer bits only, and the tiles that level deferred (forced here by a small list
+    pool) arrive through a side stream that the max-merge kernel merges in.  Same database, bit for bit."""
+    from ipk_b200 import capi as libipkgpu
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    with libipkgpu.Context(0) as c1:
+        want = c1.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+    monkeypatch.setenv("IPKGPU_ORDERED", "1")
+    with libipkgpu.Context(0) as c2:
+        if pool_cap:
+            c2.set_enumeration(0, pool_cap)
+        got = c2.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+        if pool_cap and sigma == 4:
+            assert got.stats["n_deferred_tiles"] > 0, "the small pool should have deferred some tiles to the side stream"
+        assert got.stats["sort_passes"] <= want.stats["sort_passes"]
+    assert want.n_entries > 1000
+    assert_db_equal(got, want, exact_fv=True)
+
+
 def test_invalid_arguments(ctx):
     from ipk_b200.capi import IpkGpuError
     logp, nb = _synth(4, 50, 4)
