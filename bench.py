@@ -232,11 +232,11 @@ def run_b200(args):
         """one build; returns (n_entries of this rank's shard, n_kmers, stats dict, d2h bytes, launches)"""
         inp = inp_host if host else inp_dev
         if world == 1:
-            res = ctx.build_raw(inp, result_on_device=not host)
+            res = ctx.build_raw(inp, result_on_device=not host, indexed=True)
             st = res.stats.as_dict()
             return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), int(st["kernel_launches"]), 0
         res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table,
-                                          exchange=os.environ.get("IPK_EXCHANGE", "peer"))
+                                          exchange=os.environ.get("IPK_EXCHANGE", "peer"), indexed=True)
         st = res.stats.as_dict()
         st1 = info["stage1"]
         for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):
@@ -346,7 +346,8 @@ def run_b200(args):
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {**workload_config(wl, world), "seed": args.seed, "l2": "flushed between steps (256 MiB write)",
-                       "timing": "CUDA events on the launching stream, per step, summed; max over ranks"},
+                       "timing": "CUDA events on the launching stream, per step, summed; max over ranks",
+                       "result": "indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries"},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "build_time_s": ms_e2e / args.steps * 1e-3},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,

@@ -79,7 +79,11 @@ typedef struct ipkgpu_result
     const uint64_t* offsets;       /* [n_kmers+1] CSR offsets into branch/score */
     const uint32_t* branch;        /* [n_entries] pkdb_value::branch (post-order id) */
     const float*    score;         /* [n_entries] pkdb_value::score (log10) */
-    int32_t on_device;             /* 1: the five arrays are device pointers; 0: pinned host memory */
+    int32_t on_device;             /* 1: the arrays are device pointers; 0: pinned host memory */
+    const uint32_t* counts;        /* NULL: contiguous CSR, k-mer q owns [offsets[q], offsets[q+1]).  Indexed results
+                                    * (IPKGPU_RESULT_*_INDEXED): [n_kmers], k-mer q owns [offsets[q], offsets[q] + counts[q])
+                                    * and branch/score hold the k-mers in ascending KEY order -- the db.at(kmer) walk of
+                                    * db_builder.cpp:323-332 as a look-up instead of a device-side gather */
     ipkgpu_stats stats;
 } ipkgpu_result;
 
@@ -108,6 +112,13 @@ int  ipkgpu_set_enumeration(ipkgpu_ctx* ctx, int mode, uint32_t pool_cap);
 int  ipkgpu_kernel_profile(ipkgpu_ctx* ctx, int enable);
 int  ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name, size_t name_cap, uint32_t* launches,
                                double* ms, uint64_t* bytes);
+
+/* values of result_on_device (ipkgpu_build, ipkgpu_stage2) */
+#define IPKGPU_RESULT_HOST           0   /* pinned host arrays, contiguous CSR in filter-value order */
+#define IPKGPU_RESULT_DEVICE         1   /* the same, left in device memory */
+#define IPKGPU_RESULT_HOST_INDEXED   2   /* pinned host arrays, indexed (see ipkgpu_result.counts): no gather kernel, and the
+                                          * entries cross PCIe under the filter / ordering kernels */
+#define IPKGPU_RESULT_DEVICE_INDEXED 3
 
 /* The whole path: H2D (if needed) -> best_prefix -> enumerate -> sort + per-branch max -> CSR by k-mer -> filter
  * values -> order by filter value -> gather (-> D2H unless result_on_device).  Blocking. */

@@ -235,14 +235,18 @@ namespace ipkgpu
     /// out position i takes k-mer perm[i]: its key, filter value and entry count
     __global__ void k6_gather_heads(const uint32_t* __restrict__ perm, const uint64_t* __restrict__ kmer_keys,
                                     const uint64_t* __restrict__ kmer_offs, const float* __restrict__ fv, uint64_t n,
-                                    uint64_t* __restrict__ out_keys, float* __restrict__ out_fv, uint32_t* __restrict__ out_cnt)
+                                    uint64_t* __restrict__ out_keys, float* __restrict__ out_fv, uint32_t* __restrict__ out_cnt,
+                                    uint64_t* __restrict__ out_offs /* indexed results: where the k-mer's entries start, or null */, uint64_t n_entries)
     {
         const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        if (out_offs && i == 0) out_offs[n] = n_entries;
         if (i >= n) return;
         const uint32_t src = perm[i];
         out_keys[i] = kmer_keys[src];
         out_fv[i] = fv[src];
-        out_cnt[i] = uint32_t(kmer_offs[src + 1] - kmer_offs[src]);
+        const uint64_t a = kmer_offs[src];
+        out_cnt[i] = uint32_t(kmer_offs[src + 1] - a);
+        if (out_offs) out_offs[i] = a;
     }
 
     /// entries of k-mer perm[i] move to [out_offs32[i], +cnt), G lanes per k-mer; also widens the offsets to u64 (+ the final sentinel)

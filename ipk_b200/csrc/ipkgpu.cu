@@ -623,14 +623,37 @@ namespace
     {
         if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard", (unsigned long long)n_entries);
         ipkgpu_stats& st = out->stats;
+        const bool on_device = (result_on_device & 1) != 0, indexed = (result_on_device & 2) != 0;
+        // Indexed results leave the entries where the max-merge wrote them (k-mers in ascending key order) and hand back,
+        // per k-mer in filter-value order, where its entries start and how many there are -- the db.at(kmer) walk of
+        // db_builder.cpp:323-332 without a gather.  For host results the 8 bytes per entry start crossing PCIe right now, on
+        // a second stream, under the filter and ordering kernels.
+        cudaEvent_t copy_done = nullptr;
+        if (indexed && !on_device && n_entries)
+        {
+            if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+            ctx->reserve_host(ctx->h_branch, n_entries * 4 + 4); ctx->reserve_host(ctx->h_score, n_entries * 4 + 4);
+            if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
+            cudaEvent_t merged = ctx->ev_merged, done = ctx->ev_copied;
+            IPK_CUDA(cudaEventRecord(merged, ctx->stream));
+            IPK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, merged, 0));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->ent_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_score.p, ctx->ent_score.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            IPK_CUDA(cudaEventRecord(done, ctx->copy_stream));
+            copy_done = done;
+            st.d2h_bytes += n_entries * 8;
+        }
         const size_t e0 = tm.mark();
         ctx->reserve(ctx->fv, n_kmers * 4 + 4);
         ctx->reserve(ctx->out_keys, n_kmers * 8 + 8);
         ctx->reserve(ctx->out_fv, n_kmers * 4 + 4);
         ctx->reserve(ctx->out_offs, (n_kmers + 1) * 8);
         ctx->reserve(ctx->out_cnt, n_kmers * 4 + 4);
-        ctx->reserve(ctx->out_branch, n_entries * 4 + 4);
-        ctx->reserve(ctx->out_score, n_entries * 4 + 4);
+        if (!indexed)
+        {
+            ctx->reserve(ctx->out_branch, n_entries * 4 + 4);
+            ctx->reserve(ctx->out_score, n_entries * 4 + 4);
+        }
         size_t e1 = e0, e2 = e0;
         if (n_kmers)
         {
@@ -673,9 +696,11 @@ namespace
             // K6
             IPK_LAUNCH(ctx, "k6_gather_heads", n_kmers * 44,
                        k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
-                                                                      n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>()));
-            exclusive_scan_u32(ctx, ctx->out_cnt.as<uint32_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, ctx->scan_tmp);
+                                                                      n_kmers, ctx->out_keys.as<uint64_t>(), ctx->out_fv.as<float>(), ctx->out_cnt.as<uint32_t>(),
+                                                                      indexed ? ctx->out_offs.as<uint64_t>() : nullptr, n_entries));
+            if (!indexed)
             {
+                exclusive_scan_u32(ctx, ctx->out_cnt.as<uint32_t>(), ctx->out_cnt.as<uint32_t>(), n_kmers, ctx->scan_tmp);
                 const int G = lanes_per_kmer(n_kmers, n_entries);
                 const uint32_t ggrid = uint32_t(div_up<uint64_t>(n_kmers * uint64_t(G), 256));
 #define IPK_GATHER(G_) IPK_LAUNCH(ctx, "k6_gather_entries", n_kmers * 32 + n_entries * 16,                                                  \
@@ -694,12 +719,15 @@ namespace
         }
         out->n_kmers = n_kmers;
         out->n_entries = n_entries;
-        out->on_device = result_on_device ? 1 : 0;
+        out->on_device = on_device ? 1 : 0;
+        out->counts = nullptr;
         size_t e3 = e2;
-        if (result_on_device)
+        if (on_device)
         {
             out->keys = ctx->out_keys.as<uint64_t>(); out->fv = ctx->out_fv.as<float>(); out->offsets = ctx->out_offs.as<uint64_t>();
-            out->branch = ctx->out_branch.as<uint32_t>(); out->score = ctx->out_score.as<float>();
+            out->branch = indexed ? ctx->ent_branch.as<uint32_t>() : ctx->out_branch.as<uint32_t>();
+            out->score = indexed ? ctx->ent_score.as<float>() : ctx->out_score.as<float>();
+            if (indexed) out->counts = ctx->out_cnt.as<uint32_t>();
         }
         else
         {
@@ -709,9 +737,21 @@ namespace
             IPK_CUDA(cudaMemcpyAsync(ctx->h_keys.p, ctx->out_keys.p, n_kmers * 8, cudaMemcpyDeviceToHost, ctx->stream));
             IPK_CUDA(cudaMemcpyAsync(ctx->h_fv.p, ctx->out_fv.p, n_kmers * 4, cudaMemcpyDeviceToHost, ctx->stream));
             IPK_CUDA(cudaMemcpyAsync(ctx->h_offs.p, ctx->out_offs.p, (n_kmers + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->out_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
-            IPK_CUDA(cudaMemcpyAsync(ctx->h_score.p, ctx->out_score.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
-            st.d2h_bytes += n_kmers * 12 + (n_kmers + 1) * 8 + n_entries * 8;
+            st.d2h_bytes += n_kmers * 12 + (n_kmers + 1) * 8;
+            if (indexed)
+            {
+                ctx->reserve_host(ctx->h_cnt, n_kmers * 4 + 4);
+                IPK_CUDA(cudaMemcpyAsync(ctx->h_cnt.p, ctx->out_cnt.p, n_kmers * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                st.d2h_bytes += n_kmers * 4;
+                out->counts = ctx->h_cnt.as<uint32_t>();
+                if (copy_done) IPK_CUDA(cudaStreamWaitEvent(ctx->stream, copy_done, 0));      // the entries: under way since the merge
+            }
+            else
+            {
+                IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->out_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                IPK_CUDA(cudaMemcpyAsync(ctx->h_score.p, ctx->out_score.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                st.d2h_bytes += n_entries * 8;
+            }
             e3 = tm.mark();
             out->keys = ctx->h_keys.as<uint64_t>(); out->fv = ctx->h_fv.as<float>(); out->offsets = ctx->h_offs.as<uint64_t>();
             out->branch = ctx->h_branch.as<uint32_t>(); out->score = ctx->h_score.as<float>();
@@ -867,7 +907,9 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);
-    ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score };
+    ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score, &ctx->h_cnt };
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->ev_merged) { cudaEventDestroy(ctx->ev_merged); cudaEventDestroy(ctx->ev_copied); }
     for (auto* b : hall) if (b->p) cudaFreeHost(b->p);
     for (auto e : ctx->events) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

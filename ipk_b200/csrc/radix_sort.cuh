@@ -250,8 +250,8 @@ namespace ipkgpu
 
     /// One pass over one tile of THREADS * ITEMS pairs (tile ids are handed out by an atomic ticket, so every predecessor a
     /// tile waits for is already running).  digit_base = exclusive scan of this pass's global digit histogram.
-    template<int THREADS, int ITEMS, class DigitFn, bool PEERS>
-    __global__ void __launch_bounds__(THREADS) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+    template<int THREADS, int ITEMS, class DigitFn, bool PEERS, int MINB = 1>
+    __global__ void __launch_bounds__(THREADS, MINB) rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                            const uint32_t* __restrict__ digit_base, uint64_t n,
                                                            uint64_t* status, uint32_t* ticket, uint32_t epoch, DigitFn digit,
@@ -416,7 +416,9 @@ namespace ipkgpu
         }
     }
 
-    /// tile shapes the sweep kernel is instantiated for; ctx->rs_shape picks one (tuning knob, 0 = default)
+    /// tile shapes the sweep kernel is instantiated for; ctx->rs_shape picks one (tuning knob; 2 = default).  r01r-t sweeps on
+    /// cfg3 (ms of sort per step): 256x12 77.9, 256x16 81.5, 384x16 63.0, 512x12 91.7, 512x16 86.2, 384x20 92.4; forcing 3 CTAs/SM
+    /// (384x12 at 56 registers) 66.0; the 384x16 shape must keep 2 CTAs/SM (80 registers): __launch_bounds__(384, 2)
     struct rs_shape { int threads, items; };
     constexpr rs_shape RS_SHAPES[] = { { 256, 12 }, { 256, 16 }, { 384, 16 }, { 512, 12 }, { 512, 16 }, { 384, 20 } };
     constexpr int RS_N_SHAPES = int(sizeof(RS_SHAPES) / sizeof(RS_SHAPES[0]));
@@ -457,7 +459,7 @@ namespace ipkgpu
         return ctx->rs_epoch;
     }
 
-    template<int THREADS, int ITEMS, class DigitFn>
+    template<int THREADS, int ITEMS, class DigitFn, int MINB = 1>
     inline void rs_launch_shape(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout,
                                 const uint32_t* digit_base, uint64_t n, uint64_t* status, uint32_t* ticket, DigitFn digit,
                                 const rs_peer_table* peers = nullptr)
@@ -468,15 +470,15 @@ namespace ipkgpu
         memset(&none, 0, sizeof none);
         if (peers)
         {
-            IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, true, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
             IPK_LAUNCH(ctx, "rs_scatter_peers", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
-                       rs_onesweep<THREADS, ITEMS, DigitFn, true><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, nullptr, nullptr, digit_base, n, status,
+                       rs_onesweep<THREADS, ITEMS, DigitFn, true, MINB><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, nullptr, nullptr, digit_base, n, status,
                                                                                                            ticket, rs_next_epoch(ctx), digit, *peers));
             return;
         }
-        IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        IPK_CUDA(cudaFuncSetAttribute(rs_onesweep<THREADS, ITEMS, DigitFn, false, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         IPK_LAUNCH(ctx, "rs_onesweep", n * 24 + uint64_t(n_tiles) * RS_RADIX * 8,
-                   rs_onesweep<THREADS, ITEMS, DigitFn, false><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, digit_base, n, status, ticket,
+                   rs_onesweep<THREADS, ITEMS, DigitFn, false, MINB><<<n_tiles, THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, digit_base, n, status, ticket,
                                                                                                         rs_next_epoch(ctx), digit, none));
     }
 
@@ -487,7 +489,7 @@ namespace ipkgpu
         switch (ctx->rs_shape)
         {
         case 1: rs_launch_shape<256, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
-        case 2: rs_launch_shape<384, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
+        case 2: rs_launch_shape<384, 16, DigitFn, 2>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
         case 3: rs_launch_shape<512, 12>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
         case 4: rs_launch_shape<512, 16>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
         case 5: rs_launch_shape<384, 20>(ctx, kin, vin, kout, vout, digit_base, n, status, ticket, digit); break;
@@ -527,7 +529,7 @@ namespace ipkgpu
     {
         if (n == 0) return;
         const rs_scratch S = rs_prepare(ctx, n, table);
-        rs_launch_shape<384, 16>(ctx, kin, vin, nullptr, nullptr, d_base, n, S.status, S.tickets, own, &peers);
+        rs_launch_shape<384, 16, digit_owner, 2>(ctx, kin, vin, nullptr, nullptr, d_base, n, S.status, S.tickets, own, &peers);
     }
 
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);

@@ -93,7 +93,7 @@ int ipkhost_write_ipk(const char* path, const ipkhost_db* db)
     // save_phylo_kmer(kmer, filter_value, entries) in the order handed over (db_builder.cpp:323-332)
     for (uint64_t q = 0; q < db->n_kmers; ++q)
     {
-        const uint64_t a = db->offsets[q], b = db->offsets[q + 1];
+        const uint64_t a = db->offsets[q], b = db->counts ? a + db->counts[q] : db->offsets[q + 1];
         w.put<uint64_t>(db->keys[q]);
         w.put<float>(db->fv[q]);
         w.put<uint64_t>(b - a);
@@ -152,6 +152,7 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
     view->n_kmers = n_kmers; view->n_entries = n_entries;
     view->keys = d->keys.data(); view->fv = d->fv.data(); view->offsets = d->offsets.data();
     view->branch = d->branch.data(); view->score = d->score.data();
+    view->counts = nullptr;
     *out = d;
     return IPKHOST_OK;
 }

@@ -59,6 +59,8 @@ typedef struct ipkhost_db
     const uint64_t* keys;                      /* [n_kmers] */
     const float* fv;                           /* [n_kmers] */
     const uint64_t* offsets;                   /* [n_kmers + 1] */
+    const uint32_t* counts;                    /* NULL (contiguous: k-mer q owns [offsets[q], offsets[q+1])) or [n_kmers]: k-mer q
+                                                * owns [offsets[q], offsets[q] + counts[q]) -- ipkgpu's indexed results */
     const uint32_t* branch;                    /* [n_entries] */
     const float* score;                        /* [n_entries] */
 } ipkhost_db;

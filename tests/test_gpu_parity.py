@@ -289,6 +289,40 @@ def test_ordered_emission_equals_default(sigma, bits, k, n_taxa, W, pool_cap, mo
     assert_db_equal(got, want, exact_fv=True)
 
 
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W,filt", [(4, 2, 8, 20, 300, 0), (20, 5, 3, 6, 120, 1)])
+def test_indexed_result_equals_contiguous(sigma, bits, k, n_taxa, W, filt):
+    """IPKGPU_RESULT_HOST_INDEXED / _DEVICE_INDEXED: no gather kernel, the entries stay in k-mer key order and every k-mer
+    (in filter-value order) points at its own -- walking it yields the contiguous result, bit for bit."""
+    import torch
+    from ipk_b200 import capi as libipkgpu
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    inp, keep = libipkgpu.make_input(logp, nb, W, sigma, bits, k, lthr, thr, T, filt)
+    with libipkgpu.Context(0) as c:
+        want = libipkgpu.Context.to_db(c.build_raw(inp, False))
+        res = c.build_raw(inp, False, indexed=True)
+        assert res.counts and not res.on_device
+        got = libipkgpu.Context.to_db(res)
+        launches = got.stats["kernel_launches"]
+        assert launches < want.stats["kernel_launches"]                    # the scan and the gather are gone
+        assert_db_equal(got, want, exact_fv=True)
+        # the device-resident flavour: same index arrays
+        res = c.build_raw(inp, True, indexed=True)
+        assert res.on_device and res.counts
+        nk = int(res.n_kmers)
+        torch.cuda.synchronize()
+        import ctypes as C
+        cnt = np.empty(nk, np.uint32); off = np.empty(nk + 1, np.uint64)
+        cudart = C.CDLL("libcudart.so")
+        assert cudart.cudaMemcpy(C.c_void_p(cnt.ctypes.data), C.c_void_p(res.counts), C.c_size_t(nk * 4), 2) == 0
+        assert cudart.cudaMemcpy(C.c_void_p(off.ctypes.data), C.c_void_p(res.offsets), C.c_size_t((nk + 1) * 8), 2) == 0
+        assert np.array_equal(cnt, np.diff(want.offsets).astype(np.uint32))
+        assert int(off[-1]) == want.n_entries and int(cnt.sum()) == want.n_entries
+    assert want.n_entries > 1000
+
+
 def test_invalid_arguments(ctx):
     from ipk_b200.capi import IpkGpuError
     logp, nb = _synth(4, 50, 4)
