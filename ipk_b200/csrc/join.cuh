@@ -710,7 +710,8 @@ namespace ipkgpu
         const int hl0 = J.root_hl, hr0 = k - hl0;
         const int fa0 = J.root_left, fb0 = J.root_right;
         const float eps0 = A.log_threshold;
-        uint32_t my_out = 0, my_rows = 0;
+        uint32_t my_out = 0, my_rows = 0, la_off = 0, lb_off = 0;
+        int l0 = 0;
         bool irregular = false;
         if (has_window)
         {
@@ -728,19 +729,52 @@ namespace ipkgpu
             if (hr0 > 1 && !irregular)
                 for (int q = nr - 1; q >= 0 && !(el_score(lb[q]) > eps_r + delta); --q)
                     if (!verify_subtree(el_key(lb[q]), hl0, hr0, tid, bits, sigma, NCP, sval, sidx, bs, A.log_threshold, P, s_pos, s_merge)) { irregular = true; break; }
-            // root join (pk_compute.cpp:75-105): row i = the b with fl(S(a_i) + S(b)) > eps, a prefix that only shrinks with i
-            int l = nr;
-            for (int i = 0; i < nl; ++i)
+            // root join (pk_compute.cpp:75-105): row i = the b with fl(S(a_i) + S(b)) > eps, a prefix that only shrinks with i.
+            // Here only the number of non-empty rows (the a_i whose sum with the best b passes) and the first row's length;
+            // the row lengths are summed below, flat over the warp's rows.
+            if (nl > 0 && nr > 0)
             {
-                const float sa = el_score(la[i]);
-                while (l > 0 && !(__fadd_rn(sa, el_score(lb[l - 1])) > eps0)) --l;
-                if (l == 0) break;
-                if (i == 0) nr = l;                        // no row is longer than the first
-                my_out += uint32_t(l);
-                my_rows = uint32_t(i + 1);
+                const float sb0 = el_score(lb[0]);
+                int lo = 0, hi = nl;                       // rows [0, lo) are non-empty
+                while (lo < hi)
+                {
+                    const int mid = (lo + hi) >> 1;
+                    if (__fadd_rn(el_score(la[mid]), sb0) > eps0) lo = mid + 1; else hi = mid;
+                }
+                my_rows = uint32_t(lo);
+                if (my_rows) nr = row_length(lb, nr, el_score(la[0]), eps0);      // no row is longer than the first
             }
-            if (my_out > (1u << 24)) irregular = true;     // keeps the tile total inside 32 bits; the depth-first kernel has no such limit
             wnr[tid] = uint16_t(nr);
+            la_off = uint32_t(la - pool);
+            lb_off = uint32_t(lb - pool);
+            l0 = my_rows ? nr : 0;
+        }
+        // sum of the row lengths per window: the warp's rows are spread over its lanes (a window with many rows no longer
+        // holds its warp up: phase clocks r01m, 16k of 142k cycles per tile)
+        if (warp < ENUM_WARPS)
+        {
+            wbase[tid] = 0;
+            const uint32_t incl = warp_incl_scan_u32(my_rows, lane);
+            const uint32_t total_rows = __shfl_sync(full, incl, 31);
+            const uint32_t excl = incl - my_rows;
+            __syncwarp();
+            for (uint32_t r0 = 0; r0 < total_rows; r0 += 32)
+            {
+                const uint32_t rho = r0 + lane;
+                const bool act = rho < total_rows;
+                const int s = owner_lane(incl, act ? rho : 0u);
+                const uint32_t la_s = __shfl_sync(full, la_off, s), lb_s = __shfl_sync(full, lb_off, s);
+                const int l0_s = __shfl_sync(full, l0, s);
+                const uint32_t ex_s = __shfl_sync(full, excl, s);
+                if (act)
+                {
+                    const float sa = el_score(pool[la_s + (rho - ex_s)]);
+                    atomicAdd(&wbase[(tid & ~31) + s], uint32_t(row_length(pool + lb_s, l0_s, sa, eps0)));
+                }
+            }
+            __syncwarp();
+            my_out = wbase[tid];
+            if (my_out > (1u << 24)) irregular = true;     // keeps the tile total inside 32 bits; the depth-first kernel has no such limit
         }
         // an element inside the DELTA band failed a deeper check: L(s) is not a prefix of the sorted list.  Rare enough to
         // give the whole tile to the depth-first kernel (nothing was emitted yet).
@@ -829,6 +863,7 @@ namespace ipkgpu
                 const uint32_t incl = warp_incl_scan_u32(len, lane);
                 const uint32_t total = __shfl_sync(full, incl, 31);
                 const uint32_t excl = incl - len;
+#pragma unroll 2
                 for (uint32_t o0 = 0; o0 < total; o0 += 32)
                 {
                     const uint32_t o = o0 + lane;
