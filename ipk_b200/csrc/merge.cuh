@@ -104,11 +104,28 @@ namespace ipkgpu
         const uint32_t nst = j1 - j0, nat = tile_n - nst;        // side / main records of this tile
         if (nst == 0)
         {
+            // all loads first (12 keys + 12 scores in flight per thread), then the shared-memory stores
+            const uint64_t* __restrict__ gk = A.ckeys + a0;
+            const float* __restrict__ gs = A.scores + a0;
+            uint64_t rk[MG_ITEMS];
+            float rs[MG_ITEMS];
 #pragma unroll
             for (int j = 0; j < MG_ITEMS; ++j)
             {
                 const uint32_t q = uint32_t(j) * MG_THREADS + tid;
-                if (q < tile_n) { sk[q + 1] = A.ckeys[a0 + q]; ss[q] = A.scores[a0 + q]; }
+                rk[j] = q < tile_n ? __ldg(gk + q) : 0ull;
+            }
+#pragma unroll
+            for (int j = 0; j < MG_ITEMS; ++j)
+            {
+                const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+                rs[j] = q < tile_n ? __ldg(gs + q) : 0.0f;
+            }
+#pragma unroll
+            for (int j = 0; j < MG_ITEMS; ++j)
+            {
+                const uint32_t q = uint32_t(j) * MG_THREADS + tid;
+                if (q < tile_n) { sk[q + 1] = rk[j]; ss[q] = rs[j]; }
             }
         }
         else
