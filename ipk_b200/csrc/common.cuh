@@ -85,8 +85,8 @@ struct ipkgpu_ctx
     uint32_t rs_epoch = 0;             // ... and the pass counter that tags them
     int enum_mode = 0;                 // 0: list-join kernel + depth-first kernel on deferred tiles; 1: depth-first only
     std::vector<std::pair<uint32_t, uint32_t>> levels;   // join levels (pool, windows per item) from IPKGPU_LEVELS; empty = defaults
-    uint32_t group_min = 10;           // join kernel: shortest list a lane group builds (env IPKGPU_GROUP_MIN)
-    uint32_t small_list = 32;          // join kernel: longest list its owner thread fills and sorts alone (env IPKGPU_SMALL_LIST)
+    uint32_t group_min = 20;           // join kernel: shortest list a lane group builds (env IPKGPU_GROUP_MIN)
+    uint32_t small_list = 64;          // join kernel: longest list its owner thread fills and sorts alone (env IPKGPU_SMALL_LIST)
     uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet
     uint64_t last_tiles = 0, last_deferred_tiles = 0;   // of the current call
     uint64_t enum_join_emitted = 0;    // records the join kernel of the last enumeration launch emitted

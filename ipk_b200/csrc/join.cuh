@@ -168,10 +168,12 @@ namespace ipkgpu
     constexpr int JOIN_THREADS = ENUM_THREADS + 32;
     constexpr int JOIN_WARPS = JOIN_THREADS / 32;
 #ifndef IPK_JOIN_GROUP
-#define IPK_JOIN_GROUP 4
+#define IPK_JOIN_GROUP 8
 #endif
     constexpr int JOIN_GROUP = IPK_JOIN_GROUP;   // lanes that share one of the longer lists in phase A2
-    constexpr int JOIN_GROUP_MIN = 10;       // ... lists of at least this many elements (and at most 8 * JOIN_GROUP, see small_list)
+    constexpr int JOIN_GROUP_MIN = 20;       // ... lists of at least this many elements (and at most 8 * JOIN_GROUP, see small_list)
+    // r01x/r01y sweeps on cfg3 (ms of enumeration): 4 lanes, lists 14..32: 48.7; 8 lanes, lists 20..64: 44.8; 8 lanes, 24..64: 45.6;
+    // 8 lanes, 31..64: 57.9 (a single thread insertion-sorting 30 elements); cfg4 (amino acids) 157 -> 125
     constexpr int JOIN_SMALL_LIST = 24;      // lists up to this length are filled and insertion-sorted by their owner thread
 
     __device__ __forceinline__ unsigned long long el_pack(float s, uint32_t key) { return (unsigned long long)__float_as_uint(s) << 32 | key; }
