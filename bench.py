@@ -232,11 +232,11 @@ def run_b200(args):
         """one build; returns (n_entries of this rank's shard, n_kmers, stats dict, d2h bytes, launches)"""
         inp = inp_host if host else inp_dev
         if world == 1:
-            res = ctx.build_raw(inp, result_on_device=not host, indexed=True)
+            res = ctx.build_raw(inp, result_on_device=not host, indexed=True, branch16=host)
             st = res.stats.as_dict()
             return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), int(st["kernel_launches"]), 0
         res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table,
-                                          exchange=os.environ.get("IPK_EXCHANGE", "peer"), indexed=True)
+                                          exchange=os.environ.get("IPK_EXCHANGE", "peer"), indexed=True, branch16=host)
         st = res.stats.as_dict()
         st1 = info["stage1"]
         for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):

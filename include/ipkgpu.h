@@ -84,6 +84,7 @@ typedef struct ipkgpu_result
                                     * (IPKGPU_RESULT_*_INDEXED): [n_kmers], k-mer q owns [offsets[q], offsets[q] + counts[q])
                                     * and branch/score hold the k-mers in ascending KEY order -- the db.at(kmer) walk of
                                     * db_builder.cpp:323-332 as a look-up instead of a device-side gather */
+    const uint16_t* branch16;      /* IPKGPU_RESULT_BRANCH16 honoured: the branch ids as 16-bit values and branch == NULL */
     ipkgpu_stats stats;
 } ipkgpu_result;
 
@@ -119,6 +120,9 @@ int  ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name
 #define IPKGPU_RESULT_HOST_INDEXED   2   /* pinned host arrays, indexed (see ipkgpu_result.counts): no gather kernel, and the
                                           * entries cross PCIe under the filter / ordering kernels */
 #define IPKGPU_RESULT_DEVICE_INDEXED 3
+#define IPKGPU_RESULT_BRANCH16       4   /* OR-ed to IPKGPU_RESULT_HOST_INDEXED: if every branch id is below 65,536 the branch
+                                          * ids come back as uint16_t (ipkgpu_result.branch16, branch == NULL) -- the result
+                                          * crossing PCIe is the end-to-end bottleneck, and this takes 2 of its 8 bytes per entry */
 
 /* The whole path: H2D (if needed) -> best_prefix -> enumerate -> sort + per-branch max -> CSR by k-mer -> filter
  * values -> order by filter value -> gather (-> D2H unless result_on_device).  Blocking. */

@@ -83,6 +83,7 @@ class Result(C.Structure):
         ("score", C.c_void_p),
         ("on_device", C.c_int32),
         ("counts", C.c_void_p),
+        ("branch16", C.c_void_p),
         ("stats", Stats),
     ]
 
@@ -275,10 +276,11 @@ class Context:
         return rows
 
     # ---- whole path ------------------------------------------------------------------------------------------------
-    def build_raw(self, inp: Input, result_on_device: bool | int = False, indexed: bool = False) -> Result:
-        """result_on_device: bool, or one of the RESULT_* codes; indexed: leave the entries in k-mer key order (no gather)"""
+    def build_raw(self, inp: Input, result_on_device: bool | int = False, indexed: bool = False, branch16: bool = False) -> Result:
+        """result_on_device: bool, or one of the RESULT_* codes; indexed: leave the entries in k-mer key order (no gather);
+        branch16: host indexed results carry 16-bit branch ids when they all fit"""
         res = Result()
-        mode = (int(result_on_device) & 3) | (2 if indexed else 0)
+        mode = (int(result_on_device) & 7) | (2 if indexed else 0) | (4 if branch16 else 0)
         self._check(self._lib.ipkgpu_build(self._h, C.byref(inp), mode, C.byref(res)))
         return res
 
@@ -287,6 +289,7 @@ class Context:
         if res.on_device:
             raise ValueError("result lives on the device")
         nk, ne = int(res.n_kmers), int(res.n_entries)
+        branch = _view(res.branch16, ne, np.uint16).astype(np.uint32) if res.branch16 else _view(res.branch, ne, np.uint32)
         if res.counts:
             # indexed result -> contiguous CSR in filter-value order (what the serializer's walk produces)
             start = _view(res.offsets, nk, np.uint64).astype(np.int64)
@@ -295,7 +298,7 @@ class Context:
             offsets[1:] = np.cumsum(cnt)
             idx = np.repeat(start - offsets[:-1].astype(np.int64), cnt) + np.arange(int(cnt.sum()), dtype=np.int64)
             return PhyloKmerDB(_view(res.keys, nk, np.uint64).copy(), _view(res.fv, nk, np.float32).copy(), offsets,
-                               _view(res.branch, ne, np.uint32)[idx], _view(res.score, ne, np.float32)[idx], res.stats.as_dict())
+                               branch[idx], _view(res.score, ne, np.float32)[idx], res.stats.as_dict())
         return PhyloKmerDB(_view(res.keys, nk, np.uint64).copy(), _view(res.fv, nk, np.float32).copy(),
                            _view(res.offsets, nk + 1, np.uint64).copy() if nk or res.offsets else np.zeros(1, np.uint64),
                            _view(res.branch, ne, np.uint32).copy(), _view(res.score, ne, np.float32).copy(),
@@ -371,10 +374,10 @@ class Context:
 
     def stage2(self, d_keys, d_scores, n: int, group_bits: int, group_branch: np.ndarray, key_bits: int, threshold: float,
                total_num_groups: int, filter: int = FILTER_MIF0, chunks_group_ordered: bool = True,
-               result_on_device: bool | int = False, indexed: bool = False) -> Result:
+               result_on_device: bool | int = False, indexed: bool = False, branch16: bool = False) -> Result:
         group_branch = np.ascontiguousarray(group_branch, dtype=np.uint32)
         res = Result()
         self._check(self._lib.ipkgpu_stage2(self._h, _ptr(d_keys), _ptr(d_scores), n, group_bits, group_branch.ctypes.data,
                                             int(group_branch.shape[0]), key_bits, threshold, total_num_groups, filter,
-                                            1 if chunks_group_ordered else 0, (int(result_on_device) & 3) | (2 if indexed else 0), C.byref(res)))
+                                            1 if chunks_group_ordered else 0, (int(result_on_device) & 7) | (2 if indexed else 0) | (4 if branch16 else 0), C.byref(res)))
         return res

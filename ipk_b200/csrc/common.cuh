@@ -105,6 +105,7 @@ struct ipkgpu_ctx
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
     // pinned host staging
     ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score, h_cnt;
+    uint32_t max_branch = 0;           // largest branch id of the current build (16-bit branch results)
     cudaEvent_t ev_merged = nullptr, ev_copied = nullptr;
     cudaStream_t copy_stream = nullptr;   // indexed host results: the entries leave under the filter / ordering kernels
 

@@ -249,6 +249,18 @@ namespace ipkgpu
         if (out_offs) out_offs[i] = a;
     }
 
+    /// u32 -> u16 branch ids (IPKGPU_RESULT_BRANCH16), four per thread and step
+    __global__ void __launch_bounds__(256) k6_narrow_branch(const uint32_t* __restrict__ in, uint64_t n, uint16_t* __restrict__ out)
+    {
+        const uint64_t n4 = n / 4;
+        for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n4; i += uint64_t(gridDim.x) * blockDim.x)
+        {
+            const uint4 v = reinterpret_cast<const uint4*>(in)[i];
+            reinterpret_cast<uint2*>(out)[i] = make_uint2(v.x | v.y << 16, v.z | v.w << 16);
+        }
+        if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[n4 * 4 + threadIdx.x] = uint16_t(in[n4 * 4 + threadIdx.x]);
+    }
+
     /// entries of k-mer perm[i] move to [out_offs32[i], +cnt), G lanes per k-mer; also widens the offsets to u64 (+ the final sentinel)
     template<int G>
     __global__ void __launch_bounds__(256) k6_gather_entries(const uint32_t* __restrict__ perm, const uint64_t* __restrict__ kmer_offs,

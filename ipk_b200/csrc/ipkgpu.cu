@@ -114,6 +114,8 @@ namespace
         IPK_CUDA(cudaMemcpyAsync(ctx->node_group.p, t.node_group.data(), nb, cudaMemcpyHostToDevice, ctx->stream));
         IPK_CUDA(cudaMemcpyAsync(ctx->node_order.p, t.node_order.data(), nb, cudaMemcpyHostToDevice, ctx->stream));
         IPK_CUDA(cudaMemcpyAsync(ctx->group_branch.p, t.group_branch.data(), t.group_branch.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->max_branch = 0;
+        for (uint32_t b : t.group_branch) ctx->max_branch = std::max(ctx->max_branch, b);
         if (st) st->h2d_bytes += 2 * nb + t.group_branch.size() * 4;
         // the host vectors above are pageable: the copies are staged synchronously by the runtime, safe to drop after
         return d_logp;
@@ -624,6 +626,8 @@ namespace
         if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard", (unsigned long long)n_entries);
         ipkgpu_stats& st = out->stats;
         const bool on_device = (result_on_device & 1) != 0, indexed = (result_on_device & 2) != 0;
+        // 16-bit branch ids for host results whose every branch id fits: 6 instead of 8 bytes per entry over PCIe
+        const bool branch16 = (result_on_device & 4) != 0 && indexed && !on_device && ctx->max_branch < 65536u;
         // Indexed results leave the entries where the max-merge wrote them (k-mers in ascending key order) and hand back,
         // per k-mer in filter-value order, where its entries start and how many there are -- the db.at(kmer) walk of
         // db_builder.cpp:323-332 without a gather.  For host results the 8 bytes per entry start crossing PCIe right now, on
@@ -637,11 +641,20 @@ namespace
             cudaEvent_t merged = ctx->ev_merged, done = ctx->ev_copied;
             IPK_CUDA(cudaEventRecord(merged, ctx->stream));
             IPK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, merged, 0));
-            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->ent_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            if (branch16)
+            {
+                // narrowed on the copy stream (it only reads ent_branch), into the buffer the contiguous mode gathers into
+                ctx->reserve(ctx->out_branch, n_entries * 2 + 4);
+                k6_narrow_branch<<<uint32_t(std::min<uint64_t>(div_up<uint64_t>(n_entries, 1024), 1u << 20)), 256, 0, ctx->copy_stream>>>(
+                    ctx->ent_branch.as<uint32_t>(), n_entries, ctx->out_branch.as<uint16_t>());
+                check_launch(ctx, "k6_narrow_branch", 0);
+                IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->out_branch.p, n_entries * 2, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            }
+            else IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->ent_branch.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
             IPK_CUDA(cudaMemcpyAsync(ctx->h_score.p, ctx->ent_score.p, n_entries * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
             IPK_CUDA(cudaEventRecord(done, ctx->copy_stream));
             copy_done = done;
-            st.d2h_bytes += n_entries * 8;
+            st.d2h_bytes += n_entries * (branch16 ? 6 : 8);
         }
         const size_t e0 = tm.mark();
         ctx->reserve(ctx->fv, n_kmers * 4 + 4);
@@ -721,6 +734,7 @@ namespace
         out->n_entries = n_entries;
         out->on_device = on_device ? 1 : 0;
         out->counts = nullptr;
+        out->branch16 = nullptr;
         size_t e3 = e2;
         if (on_device)
         {
@@ -755,6 +769,7 @@ namespace
             e3 = tm.mark();
             out->keys = ctx->h_keys.as<uint64_t>(); out->fv = ctx->h_fv.as<float>(); out->offsets = ctx->h_offs.as<uint64_t>();
             out->branch = ctx->h_branch.as<uint32_t>(); out->score = ctx->h_score.as<float>();
+            if (branch16 && n_entries) { out->branch16 = ctx->h_branch.as<uint16_t>(); out->branch = nullptr; }
         }
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));
         st.ms_filter = tm.ms(e0, e1);
@@ -1201,6 +1216,8 @@ int ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t n
         const size_t t0 = tm.mark();
         ctx->reserve(ctx->group_branch, size_t(n_groups_total) * 4 + 4);
         IPK_CUDA(cudaMemcpyAsync(ctx->group_branch.p, group_branch, size_t(n_groups_total) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->max_branch = 0;
+        for (uint32_t g = 0; g < n_groups_total; ++g) ctx->max_branch = std::max(ctx->max_branch, group_branch[g]);
         const stage2_params sp{ group_bits, key_bits, total_num_groups, threshold, filter };
         run_stage2(ctx, d_keys, d_scores, n, chunks_group_ordered != 0, sp, result_on_device, out, tm);
         const size_t t1 = tm.mark();

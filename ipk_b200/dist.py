@@ -126,7 +126,7 @@ def peer_exchange(ctx, device, group=None):
 
 def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: float, total_num_groups: int, filter: int,
                   device, result_on_device: bool = False, group=None, table: GroupTable | None = None, raw: bool = True,
-                  exchange: str = "peer", indexed: bool = False):
+                  exchange: str = "peer", indexed: bool = False, branch16: bool = False):
     """The whole multi-GPU path for this rank.  ctx: ipk_b200.capi.Context (or anything with its stage methods);
     inp: the rank's ipkgpu_input (its own ghost nodes only).  Returns (stage-2 result, info dict)."""
     world = dist.get_world_size(group)
@@ -140,7 +140,7 @@ def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: f
         rk, rs, n_recv, counts = peer_exchange(ctx, device, group)
         ev[2].record()
         res = ctx.stage2(rk, rs, n_recv, table.group_bits, table.group_branch, key_bits, threshold, total_num_groups, filter,
-                         not raw, result_on_device, **({"indexed": True} if indexed else {}))
+                         not raw, result_on_device, **({"indexed": True, "branch16": branch16} if indexed else {}))
         info = dict(stage1=st1, n_unique_local=int(n_unique), n_received=n_recv, keep=None, ms_partition=0.0,
                     n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
                     ms_exchange=ev[0].elapsed_time(ev[2]), exchange="peer-memory scatter")
@@ -158,7 +158,7 @@ def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: f
     del send_keys, send_scores
     n_recv = int(recv_counts.sum())
     res = ctx.stage2(recv_keys, recv_scores, n_recv, table.group_bits, table.group_branch, key_bits, threshold,
-                     total_num_groups, filter, not raw, result_on_device, **({"indexed": True} if indexed else {}))
+                     total_num_groups, filter, not raw, result_on_device, **({"indexed": True, "branch16": branch16} if indexed else {}))
     info = dict(stage1=st1, n_unique_local=int(n_unique), n_sent_remote=int(sum(int(c) for i, c in enumerate(counts) if i != dist.get_rank(group))),
                 n_received=n_recv, keep=(recv_keys, recv_scores))
     if cuda:           # stage 2 has synchronised the stream by now

@@ -70,7 +70,7 @@ int ipkhost_write_ipk(const char* path, const ipkhost_db* db)
 {
     if (!path || !db) return IPKHOST_EINVAL;
     if (db->n_kmers && (!db->keys || !db->fv || !db->offsets)) return IPKHOST_EINVAL;
-    if (db->n_entries && (!db->branch || !db->score)) return IPKHOST_EINVAL;
+    if (db->n_entries && ((!db->branch && !db->branch16) || !db->score)) return IPKHOST_EINVAL;
     FILE* f = fopen(path, "wb");
     if (!f) return IPKHOST_EIO;
     writer w(f);
@@ -97,7 +97,7 @@ int ipkhost_write_ipk(const char* path, const ipkhost_db* db)
         w.put<uint64_t>(db->keys[q]);
         w.put<float>(db->fv[q]);
         w.put<uint64_t>(b - a);
-        for (uint64_t e = a; e < b; ++e) { w.put<uint32_t>(db->branch[e]); w.put<float>(db->score[e]); }
+        for (uint64_t e = a; e < b; ++e) { w.put<uint32_t>(db->branch16 ? uint32_t(db->branch16[e]) : db->branch[e]); w.put<float>(db->score[e]); }
     }
     w.flush();
     const bool ok = w.ok && fclose(f) == 0;
@@ -153,6 +153,7 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
     view->keys = d->keys.data(); view->fv = d->fv.data(); view->offsets = d->offsets.data();
     view->branch = d->branch.data(); view->score = d->score.data();
     view->counts = nullptr;
+    view->branch16 = nullptr;
     *out = d;
     return IPKHOST_OK;
 }

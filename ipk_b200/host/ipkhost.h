@@ -61,8 +61,9 @@ typedef struct ipkhost_db
     const uint64_t* offsets;                   /* [n_kmers + 1] */
     const uint32_t* counts;                    /* NULL (contiguous: k-mer q owns [offsets[q], offsets[q+1])) or [n_kmers]: k-mer q
                                                 * owns [offsets[q], offsets[q] + counts[q]) -- ipkgpu's indexed results */
-    const uint32_t* branch;                    /* [n_entries] */
+    const uint32_t* branch;                    /* [n_entries], or NULL when branch16 is set */
     const float* score;                        /* [n_entries] */
+    const uint16_t* branch16;                  /* NULL, or the branch ids as 16-bit values (ipkgpu's IPKGPU_RESULT_BRANCH16) */
 } ipkhost_db;
 
 int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);

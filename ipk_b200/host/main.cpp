@@ -137,7 +137,7 @@ int main(int argc, char** argv)
         in.total_num_groups = node_count;
         in.filter = o.filter;
         ipkgpu_result res;
-        if (ipkgpu_build(ctx, &in, IPKGPU_RESULT_HOST_INDEXED, &res) != IPKGPU_OK)
+        if (ipkgpu_build(ctx, &in, IPKGPU_RESULT_HOST_INDEXED | IPKGPU_RESULT_BRANCH16, &res) != IPKGPU_OK)
         {
             const std::string msg = ipkgpu_last_error(ctx);
             ipkgpu_destroy(ctx);
@@ -166,13 +166,13 @@ int main(int argc, char** argv)
         db.kmer_size = o.k;
         db.omega = o.omega;
         db.n_kmers = res.n_kmers; db.n_entries = res.n_entries;
-        db.keys = res.keys; db.fv = res.fv; db.offsets = res.offsets; db.counts = res.counts; db.branch = res.branch; db.score = res.score;
+        db.keys = res.keys; db.fv = res.fv; db.offsets = res.offsets; db.counts = res.counts; db.branch = res.branch; db.branch16 = res.branch16; db.score = res.score;
         if (ipkhost_write_ipk(o.output.c_str(), &db) != IPKHOST_OK) throw std::runtime_error("cannot write " + o.output);
         fprintf(stderr, "Wrote %s in %.3f s\n", o.output.c_str(), seconds_since(t0));
         if (o.dump)
             for (uint64_t q = 0; q < res.n_kmers; ++q)
                 for (uint64_t e = res.offsets[q]; e < (res.counts ? res.offsets[q] + res.counts[q] : res.offsets[q + 1]); ++e)
-                    printf("%llu\t%.9g\t%u\t%.9g\n", (unsigned long long)res.keys[q], double(res.fv[q]), res.branch[e], double(res.score[e]));
+                    printf("%llu\t%.9g\t%u\t%.9g\n", (unsigned long long)res.keys[q], double(res.fv[q]), res.branch16 ? uint32_t(res.branch16[e]) : res.branch[e], double(res.score[e]));
         ipkgpu_free_result(ctx, &res);
         ipkgpu_destroy(ctx);
         return 0;

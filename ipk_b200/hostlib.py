@@ -17,7 +17,8 @@ class HostDb(C.Structure):
                 ("index_num_nodes", C.POINTER(C.c_uint64)), ("index_subtree_branch_length", C.POINTER(C.c_double)),
                 ("kmer_size", C.c_uint64), ("omega", C.c_float), ("n_kmers", C.c_uint64), ("n_entries", C.c_uint64),
                 ("keys", C.POINTER(C.c_uint64)), ("fv", C.POINTER(C.c_float)), ("offsets", C.POINTER(C.c_uint64)),
-                ("counts", C.POINTER(C.c_uint32)), ("branch", C.POINTER(C.c_uint32)), ("score", C.POINTER(C.c_float))]
+                ("counts", C.POINTER(C.c_uint32)), ("branch", C.POINTER(C.c_uint32)), ("score", C.POINTER(C.c_float)),
+                ("branch16", C.POINTER(C.c_uint16))]
 
 
 _lib = None
@@ -96,7 +97,7 @@ def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega
                 il.ctypes.data_as(C.POINTER(C.c_double)), kmer_size, omega, len(keys), len(branch),
                 keys.ctypes.data_as(C.POINTER(C.c_uint64)), fv.ctypes.data_as(C.POINTER(C.c_float)),
                 offsets.ctypes.data_as(C.POINTER(C.c_uint64)), None, branch.ctypes.data_as(C.POINTER(C.c_uint32)),
-                score.ctypes.data_as(C.POINTER(C.c_float)))
+                score.ctypes.data_as(C.POINTER(C.c_float)), None)
     rc = load().ipkhost_write_ipk(path.encode(), C.byref(db))
     if rc != 0:
         raise HostError(rc, "cannot write " + path)

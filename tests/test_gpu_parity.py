@@ -308,6 +308,11 @@ def test_indexed_result_equals_contiguous(sigma, bits, k, n_taxa, W, filt):
         launches = got.stats["kernel_launches"]
         assert launches < want.stats["kernel_launches"]                    # the scan and the gather are gone
         assert_db_equal(got, want, exact_fv=True)
+        # 16-bit branch ids (2 of the 8 bytes per entry that cross PCIe)
+        res = c.build_raw(inp, False, indexed=True, branch16=True)
+        assert res.branch16 and not res.branch
+        assert res.stats.d2h_bytes < got.stats["d2h_bytes"]
+        assert_db_equal(libipkgpu.Context.to_db(res), want, exact_fv=True)
         # the device-resident flavour: same index arrays
         res = c.build_raw(inp, True, indexed=True)
         assert res.on_device and res.counts
