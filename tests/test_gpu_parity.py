@@ -328,6 +328,22 @@ def test_indexed_result_equals_contiguous(sigma, bits, k, n_taxa, W, filt):
     assert want.n_entries > 1000
 
 
+def test_branch16_falls_back_when_ids_do_not_fit():
+    """IPKGPU_RESULT_BRANCH16 is a request: with a branch id >= 65,536 the result keeps 32-bit ids"""
+    from ipk_b200 import capi as libipkgpu
+    logp, nb = _synth(6, 80, 4)
+    nb = (nb.astype(np.uint64) + 70000).astype(np.uint32)
+    thr, lthr = _thr(1.5, 4, 8)
+    inp, keep = libipkgpu.make_input(logp, nb, 80, 4, 2, 8, lthr, thr, 11, 0)
+    with libipkgpu.Context(0) as c:
+        want = libipkgpu.Context.to_db(c.build_raw(inp, False))
+        res = c.build_raw(inp, False, indexed=True, branch16=True)
+        assert not res.branch16 and res.branch and res.counts
+        got = libipkgpu.Context.to_db(res)
+    assert int(got.branch.min()) >= 70000
+    assert_db_equal(got, want, exact_fv=True)
+
+
 def test_invalid_arguments(ctx):
     from ipk_b200.capi import IpkGpuError
     logp, nb = _synth(4, 50, 4)
