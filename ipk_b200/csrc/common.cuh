@@ -107,6 +107,11 @@ struct ipkgpu_ctx
     ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score, h_cnt;
     uint32_t max_branch = 0;           // largest branch id of the current build (16-bit branch results)
     cudaEvent_t ev_merged = nullptr, ev_copied = nullptr;
+    // host-bound indexed results: sort + merge in n_parts k-mer ranges once there are part_min records (env IPKGPU_PARTS,
+    // IPKGPU_PART_MIN), each range's entries queued on the copy stream as soon as it is merged
+    uint32_t n_parts = 8;
+    uint64_t part_min = 1ull << 25;
+    bool entries_streamed = false, streamed_branch16 = false;
     cudaStream_t copy_stream = nullptr;   // indexed host results: the entries leave under the filter / ordering kernels
 
     std::vector<cudaEvent_t> events;

@@ -249,16 +249,21 @@ namespace ipkgpu
         if (out_offs) out_offs[i] = a;
     }
 
-    /// u32 -> u16 branch ids (IPKGPU_RESULT_BRANCH16), four per thread and step
-    __global__ void __launch_bounds__(256) k6_narrow_branch(const uint32_t* __restrict__ in, uint64_t n, uint16_t* __restrict__ out)
+    /// u32 -> u16 branch ids (IPKGPU_RESULT_BRANCH16) of the entries [lo, hi), four per thread and step between the
+    /// multiples of four (both arrays are indexed from their 16-byte aligned starts, so one alignment serves both)
+    __global__ void __launch_bounds__(256) k6_narrow_branch(const uint32_t* __restrict__ in, uint64_t lo, uint64_t hi, uint16_t* __restrict__ out)
     {
-        const uint64_t n4 = n / 4;
-        for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n4; i += uint64_t(gridDim.x) * blockDim.x)
+        const uint64_t v0 = min(hi, (lo + 3) & ~uint64_t(3)), v1 = max(v0, hi & ~uint64_t(3));
+        for (uint64_t i = v0 / 4 + blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < v1 / 4; i += uint64_t(gridDim.x) * blockDim.x)
         {
             const uint4 v = reinterpret_cast<const uint4*>(in)[i];
             reinterpret_cast<uint2*>(out)[i] = make_uint2(v.x | v.y << 16, v.z | v.w << 16);
         }
-        if (blockIdx.x == 0 && threadIdx.x < (n & 3)) out[n4 * 4 + threadIdx.x] = uint16_t(in[n4 * 4 + threadIdx.x]);
+        if (blockIdx.x == 0)
+        {
+            if (lo + threadIdx.x < v0) out[lo + threadIdx.x] = uint16_t(in[lo + threadIdx.x]);
+            if (v1 + threadIdx.x < hi) out[v1 + threadIdx.x] = uint16_t(in[v1 + threadIdx.x]);
+        }
     }
 
     /// entries of k-mer perm[i] move to [out_offs32[i], +cnt), G lanes per k-mer; also widens the offsets to u64 (+ the final sentinel)

@@ -343,15 +343,19 @@ namespace
     /// `csr` -- the CSR by k-mer (K3').  Unique records go to (u_keys, u_scores) + u_off when `unique`.
     merge_out run_merge(ipkgpu_ctx* ctx, const uint64_t* keys, const float* scores, uint64_t n_main, uint32_t group_bits,
                         uint32_t out_group_bits, uint32_t group_add, bool unique, uint64_t u_off, bool csr, uint32_t key_bits,
-                        const uint64_t* side_keys = nullptr, const float* side_scores = nullptr, uint64_t n_side = 0)
+                        const uint64_t* side_keys = nullptr, const float* side_scores = nullptr, uint64_t n_side = 0,
+                        uint64_t ent_base = 0, uint64_t kmer_base = 0, uint64_t n_total = 0)
     {
+        // (ent_base, kmer_base, n_total): this call appends one k-mer range to a CSR of at most n_total entries that earlier
+        // calls began -- the outputs start at those bases and the buffers are sized once, for the whole
         merge_out r;
         const uint64_t n = n_main + n_side;          // the kernel walks the merge of the two sorted streams
         if (n == 0) return r;
         if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed the 2^32-1 limit of one merge", (unsigned long long)n);
         const uint32_t tiles = uint32_t(div_up<uint64_t>(n, MG_TILE));
         // single pass: the outputs are sized by their upper bounds (records <= n, k-mers <= min(n, 2^key_bits))
-        const uint64_t kmer_bound = key_bits < 40 ? std::min<uint64_t>(n, 1ull << key_bits) : n;
+        const uint64_t n_cap = std::max(n_total, ent_base + n);
+        const uint64_t kmer_bound = key_bits < 40 ? std::min<uint64_t>(n_cap, 1ull << key_bits) : n_cap;
         if (unique)
         {
             ctx->reserve_keep(ctx->u_keys, (u_off + n) * 8, u_off * 8);
@@ -361,8 +365,8 @@ namespace
         {
             ctx->reserve(ctx->kmer_keys, kmer_bound * 8 + 8);
             ctx->reserve(ctx->kmer_offs, (kmer_bound + 1) * 8);
-            ctx->reserve(ctx->ent_branch, n * 4 + 4);
-            ctx->reserve(ctx->ent_score, n * 4 + 4);
+            ctx->reserve(ctx->ent_branch, n_cap * 4 + 4);
+            ctx->reserve(ctx->ent_score, n_cap * 4 + 4);
         }
         ctx->reserve(ctx->counters, 128);
         const size_t status_bytes = size_t(tiles) * 16;
@@ -393,10 +397,11 @@ namespace
         M.u_keys = unique ? ctx->u_keys.as<uint64_t>() + u_off : nullptr;
         M.u_scores = unique ? ctx->u_scores.as<float>() + u_off : nullptr;
         M.group_branch = ctx->group_branch.as<uint32_t>();
-        M.kmer_keys = csr ? ctx->kmer_keys.as<uint64_t>() : nullptr;
-        M.kmer_offs = ctx->kmer_offs.as<uint64_t>();
-        M.ent_branch = ctx->ent_branch.as<uint32_t>();
-        M.ent_score = ctx->ent_score.as<float>();
+        M.kmer_keys = csr ? ctx->kmer_keys.as<uint64_t>() + kmer_base : nullptr;
+        M.kmer_offs = ctx->kmer_offs.as<uint64_t>() + kmer_base;
+        M.ent_branch = ctx->ent_branch.as<uint32_t>() + ent_base;
+        M.ent_score = ctx->ent_score.as<float>() + ent_base;
+        M.offs_add = ent_base;
         M.status = ctx->mg_status.as<uint64_t>();
         M.ticket = reinterpret_cast<uint32_t*>(totals + 2);
         M.totals = totals;
@@ -409,8 +414,116 @@ namespace
         r.n_kmers = h[1];
         ctx->kprof_add_bytes("mg_merge", (unique ? r.n_records * 12 : 0) + (csr ? r.n_records * 8 + r.n_kmers * 16 : 0));
         if (csr)
-            IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + r.n_kmers, &r.n_records, 8, cudaMemcpyHostToDevice, ctx->stream));
+        {
+            const uint64_t end = ent_base + r.n_records;
+            IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + kmer_base + r.n_kmers, &end, 8, cudaMemcpyHostToDevice, ctx->stream));
+        }
         return r;
+    }
+}
+
+namespace
+{
+    struct parts_out
+    {
+        merge_out m;
+        uint32_t passes = 0;
+        float ms_sort = 0, ms_merge = 0;
+    };
+
+    /// Host-bound indexed results of at least ctx->part_min records are sorted and merged in k-mer ranges.
+    bool parts_eligible(const ipkgpu_ctx* ctx, uint64_t n, uint32_t key_bits, uint32_t n_bits, int result_mode)
+    {
+        return (result_mode & 3) == IPKGPU_RESULT_HOST_INDEXED && ctx->n_parts > 1 && n >= ctx->part_min && key_bits >= 8 && n_bits > 8 && n <= 0xffffffffull;
+    }
+
+    /// Sort + max-merge + CSR of n records in k-mer RANGES, so that the entries start crossing PCIe while later ranges are
+    /// still being sorted: one most-significant-digit pass splits (ka, va) into 256 ranges of the composite key in (kb, vb);
+    /// the ranges are then sorted on the bits below (in aligned units, see inside), and runs of about n / n_parts records
+    /// ("parts") are max-merged onto the end of the CSR the earlier parts began and handed to the copy stream.  The pass
+    /// count equals the plain sort's (1 + ceil((n_bits - 8) / 8)); the extra cost is a second read of the keys for the
+    /// per-unit digit histograms and the shorter launches.  Needs key_bits >= 8, so that no k-mer spans two ranges.
+    /// On return every entry copy is queued behind ctx->ev_copied and ctx->entries_streamed tells finish_from_csr so.
+    parts_out sort_merge_parts(ipkgpu_ctx* ctx, uint64_t* ka, uint32_t* va, uint64_t* kb, uint32_t* vb, uint64_t n, uint32_t key_bits,
+                               uint32_t gbits, uint32_t out_group_bits, uint32_t group_add, int result_mode, stage_timer& tm)
+    {
+        parts_out R;
+        const uint32_t low_bits = key_bits + gbits - 8;
+        const bool b16 = (result_mode & 4) != 0 && ctx->max_branch < 65536u;
+        // everything the copies touch is sized now, by the record count (an upper bound of the entry count)
+        if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
+        ctx->reserve_host(ctx->h_branch, n * 4 + 4);
+        ctx->reserve_host(ctx->h_score, n * 4 + 4);
+        if (b16) ctx->reserve(ctx->out_branch, n * 2 + 4);
+
+        uint32_t start[257];
+        const size_t e0 = tm.mark();
+        radix_partition_top(ctx, ka, va, kb, vb, n, low_bits, ctx->hist, start);
+        start[256] = uint32_t(n);
+        const size_t e1 = tm.mark();
+        R.passes = 1;
+        struct mark3 { size_t a, b, c; };
+        std::vector<mark3> marks;
+        // The passes below the top digit cover 8 * lsd_passes >= low_bits bits; the `slack` bits they have to spare are spent
+        // on the lowest bits of the top digit, so a sort UNIT is an aligned run of 2^slack digit ranges, sorted on exactly
+        // 8 * lsd_passes bits.  A part = a run of whole units of about n / n_parts records: one merge, one copy.
+        const uint32_t lsd_passes = div_up<uint32_t>(low_bits, 8), unit_bits = 8 * lsd_passes;
+        const uint32_t unit = 1u << (unit_bits - low_bits);                 // digit ranges per unit (1 .. 128)
+        const uint64_t target = div_up<uint64_t>(n, ctx->n_parts);
+        uint64_t ent_base = 0, kmer_base = 0;
+        for (uint32_t d0 = 0; d0 < 256;)
+        {
+            uint32_t d1 = d0 + unit;
+            while (d1 < 256 && uint64_t(start[d1]) - start[d0] < target) d1 += unit;
+            const uint64_t o = start[d0], c = uint64_t(start[d1]) - start[d0];
+            const uint32_t first = d0;
+            d0 = d1;
+            if (c == 0) continue;
+            const size_t ea = tm.mark();
+            for (uint32_t u = first; u < d1; u += unit)
+            {
+                const uint64_t uo = start[u], uc = uint64_t(start[u + unit]) - start[u];
+                radix_sort_pairs(ctx, kb + uo, vb + uo, ka + uo, va + uo, uc, unit_bits, ctx->hist, ctx->scan_tmp);
+            }
+            const bool in_a = (lsd_passes & 1) != 0;                           // every unit ping-pongs the same number of times
+            const size_t eb = tm.mark();
+            const uint64_t* sk = in_a ? ka + o : kb + o;
+            const float* sv = reinterpret_cast<const float*>(in_a ? va + o : vb + o);
+            const merge_out m = run_merge(ctx, sk, sv, c, gbits, out_group_bits, group_add, false, 0, true, key_bits, nullptr, nullptr, 0,
+                                          ent_base, kmer_base, n);
+            marks.push_back({ ea, eb, tm.mark() });
+            if (m.n_records)
+            {
+                IPK_CUDA(cudaEventRecord(ctx->ev_merged, ctx->stream));
+                IPK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_merged, 0));
+                if (b16)
+                {
+                    k6_narrow_branch<<<uint32_t(std::min<uint64_t>(div_up<uint64_t>(m.n_records, 1024), 1u << 20)), 256, 0, ctx->copy_stream>>>(
+                        ctx->ent_branch.as<uint32_t>(), ent_base, ent_base + m.n_records, ctx->out_branch.as<uint16_t>());
+                    check_launch(ctx, "k6_narrow_branch", 0);
+                    IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.as<uint16_t>() + ent_base, ctx->out_branch.as<uint16_t>() + ent_base, m.n_records * 2,
+                                             cudaMemcpyDeviceToHost, ctx->copy_stream));
+                }
+                else
+                    IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.as<uint32_t>() + ent_base, ctx->ent_branch.as<uint32_t>() + ent_base, m.n_records * 4,
+                                             cudaMemcpyDeviceToHost, ctx->copy_stream));
+                IPK_CUDA(cudaMemcpyAsync(ctx->h_score.as<float>() + ent_base, ctx->ent_score.as<float>() + ent_base, m.n_records * 4,
+                                         cudaMemcpyDeviceToHost, ctx->copy_stream));
+            }
+            ent_base += m.n_records;
+            kmer_base += m.n_kmers;
+        }
+        IPK_CUDA(cudaEventRecord(ctx->ev_copied, ctx->copy_stream));
+        ctx->entries_streamed = true;
+        ctx->streamed_branch16 = b16;
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        R.passes += lsd_passes;
+        R.m.n_records = ent_base;
+        R.m.n_kmers = kmer_base;
+        R.ms_sort = tm.ms(e0, e1);
+        for (const mark3& k : marks) { R.ms_sort += tm.ms(k.a, k.b); R.ms_merge += tm.ms(k.b, k.c); }
+        return R;
     }
 }
 
@@ -435,7 +548,7 @@ namespace
     /// With want_csr and a single batch the CSR by k-mer comes out of the same K3 pass; otherwise the unique
     /// records are left in ctx->u_keys/u_scores as (kmer << group_bits) | global group, batch after batch.
     stage1_out run_stage1(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& T, uint32_t group_base, uint32_t group_bits,
-                          bool want_csr, ipkgpu_stats* st, stage_timer& tm, bool raw = false)
+                          bool want_csr, ipkgpu_stats* st, stage_timer& tm, bool raw = false, int result_mode = 0)
     {
         stage1_out o;
         o.n_groups = uint32_t(T.group_branch.size());
@@ -563,6 +676,17 @@ namespace
             const size_t eb = tm.mark();
             ctx->reserve(ctx->keys_b, b.n * 8 + 8);
             ctx->reserve(ctx->vals_b, b.n * 4 + 4);
+            if (single && want_csr && !use_side && parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode))
+            {
+                const parts_out po = sort_merge_parts(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
+                                                      ctx->vals_b.as<uint32_t>(), b.n, key_bits, bbits, group_bits, group_base + b.g0, result_mode, tm);
+                o.sort_passes += po.passes;
+                o.csr_done = true; o.n_kmers = po.m.n_kmers;
+                u_off += po.m.n_records;
+                ms_enum += tm.ms(ea, eb); ms_sort += po.ms_sort; ms_merge += po.ms_merge;
+                e_prev = tm.mark();
+                continue;
+            }
             uint32_t passes = 0;
             // ordered main stream: stable sort on the k-mer bits only (bit_begin = width of the group field)
             const bool in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
@@ -627,13 +751,21 @@ namespace
         ipkgpu_stats& st = out->stats;
         const bool on_device = (result_on_device & 1) != 0, indexed = (result_on_device & 2) != 0;
         // 16-bit branch ids for host results whose every branch id fits: 6 instead of 8 bytes per entry over PCIe
-        const bool branch16 = (result_on_device & 4) != 0 && indexed && !on_device && ctx->max_branch < 65536u;
+        // entries that sort_merge_parts already queued on the copy stream, k-mer range by k-mer range
+        const bool streamed = ctx->entries_streamed && indexed && !on_device;
+        ctx->entries_streamed = false;
+        const bool branch16 = streamed ? ctx->streamed_branch16 : (result_on_device & 4) != 0 && indexed && !on_device && ctx->max_branch < 65536u;
         // Indexed results leave the entries where the max-merge wrote them (k-mers in ascending key order) and hand back,
         // per k-mer in filter-value order, where its entries start and how many there are -- the db.at(kmer) walk of
         // db_builder.cpp:323-332 without a gather.  For host results the 8 bytes per entry start crossing PCIe right now, on
         // a second stream, under the filter and ordering kernels.
         cudaEvent_t copy_done = nullptr;
-        if (indexed && !on_device && n_entries)
+        if (streamed)
+        {
+            copy_done = ctx->ev_copied;
+            st.d2h_bytes += n_entries * (branch16 ? 6 : 8);
+        }
+        else if (indexed && !on_device && n_entries)
         {
             if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
             ctx->reserve_host(ctx->h_branch, n_entries * 4 + 4); ctx->reserve_host(ctx->h_score, n_entries * 4 + 4);
@@ -646,7 +778,7 @@ namespace
                 // narrowed on the copy stream (it only reads ent_branch), into the buffer the contiguous mode gathers into
                 ctx->reserve(ctx->out_branch, n_entries * 2 + 4);
                 k6_narrow_branch<<<uint32_t(std::min<uint64_t>(div_up<uint64_t>(n_entries, 1024), 1u << 20)), 256, 0, ctx->copy_stream>>>(
-                    ctx->ent_branch.as<uint32_t>(), n_entries, ctx->out_branch.as<uint16_t>());
+                    ctx->ent_branch.as<uint32_t>(), 0, n_entries, ctx->out_branch.as<uint16_t>());
                 check_launch(ctx, "k6_narrow_branch", 0);
                 IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.p, ctx->out_branch.p, n_entries * 2, cudaMemcpyDeviceToHost, ctx->copy_stream));
             }
@@ -747,7 +879,7 @@ namespace
         {
             ctx->reserve_host(ctx->h_keys, n_kmers * 8 + 8); ctx->reserve_host(ctx->h_fv, n_kmers * 4 + 4);
             ctx->reserve_host(ctx->h_offs, (n_kmers + 1) * 8);
-            ctx->reserve_host(ctx->h_branch, n_entries * 4 + 4); ctx->reserve_host(ctx->h_score, n_entries * 4 + 4);
+            if (!streamed) { ctx->reserve_host(ctx->h_branch, n_entries * 4 + 4); ctx->reserve_host(ctx->h_score, n_entries * 4 + 4); }
             IPK_CUDA(cudaMemcpyAsync(ctx->h_keys.p, ctx->out_keys.p, n_kmers * 8, cudaMemcpyDeviceToHost, ctx->stream));
             IPK_CUDA(cudaMemcpyAsync(ctx->h_fv.p, ctx->out_fv.p, n_kmers * 4, cudaMemcpyDeviceToHost, ctx->stream));
             IPK_CUDA(cudaMemcpyAsync(ctx->h_offs.p, ctx->out_offs.p, (n_kmers + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -791,6 +923,16 @@ namespace
         {
             ctx->reserve(ctx->keys_b, n * 8 + 8);
             ctx->reserve(ctx->vals_b, n * 4 + 4);
+            if (!group_ordered && parts_eligible(ctx, n, sp.key_bits, sp.key_bits + sp.group_bits, result_on_device))
+            {
+                const parts_out po = sort_merge_parts(ctx, keys, reinterpret_cast<uint32_t*>(scores), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(),
+                                                      n, sp.key_bits, sp.group_bits, sp.group_bits, 0, result_on_device, tm);
+                out->stats.sort_passes += po.passes;
+                finish_from_csr(ctx, po.m.n_kmers, po.m.n_records, sp, result_on_device, out, tm);
+                out->stats.ms_sort += po.ms_sort;
+                out->stats.ms_merge += po.ms_merge;
+                return;
+            }
             uint32_t passes = 0;
             // chunks that arrive in group order, each sorted by (kmer, group): a STABLE sort on the k-mer bits alone regroups them
             const bool in_b = group_ordered
@@ -821,6 +963,7 @@ namespace
             if (!ctx) return IPKGPU_EINVAL;
             IPK_CUDA(cudaSetDevice(ctx->device));
             ctx->launches = 0;
+            ctx->entries_streamed = false;
             ctx->last_tiles = ctx->last_deferred_tiles = 0;
             ctx->kprof_marks.clear();
             f();
@@ -873,6 +1016,8 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
     if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
+    if (const char* e = getenv("IPKGPU_PARTS")) ctx->n_parts = uint32_t(std::max(1, atoi(e)));
+    if (const char* e = getenv("IPKGPU_PART_MIN")) ctx->part_min = uint64_t(std::max(1ll, atoll(e)));
     if (const char* e = getenv("IPKGPU_ORDERED")) ctx->ordered = atoi(e);
     if (const char* e = getenv("IPKGPU_GROUP_MIN")) ctx->group_min = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_SMALL_LIST")) ctx->small_list = uint32_t(std::max(1, atoi(e)));
@@ -984,7 +1129,7 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         ipkgpu_stats& st = out->stats;
         st.n_windows = in->width >= in->k ? uint64_t(in->n_nodes) * (in->width - in->k + 1) : 0;
         st.n_groups = n_groups;
-        const stage1_out s1 = run_stage1(ctx, in, T, 0, group_bits, true, &st, tm);
+        const stage1_out s1 = run_stage1(ctx, in, T, 0, group_bits, true, &st, tm, false, result_on_device);
         st.n_emitted = s1.n_emitted;
         st.sort_passes = s1.sort_passes;
         st.enum_launches = s1.enum_launches;

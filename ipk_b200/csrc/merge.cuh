@@ -64,6 +64,7 @@ namespace ipkgpu
         uint64_t* status;                  // [tiles][2]
         uint32_t* ticket;
         unsigned long long* totals;        // [0] records, [1] k-mers
+        uint64_t offs_add = 0;             // added to the entry offsets written to kmer_offs (a k-mer range of a larger CSR)
         uint32_t epoch;
     };
 
@@ -249,7 +250,7 @@ namespace ipkgpu
                 {
                     const uint64_t r2 = uint64_t(s_before[1]) + s_cnt[1][j][warp] + __popc(kb[j] & lt);
                     A.kmer_keys[r2] = cur >> A.group_bits;
-                    A.kmer_offs[r2] = r1;
+                    A.kmer_offs[r2] = r1 + A.offs_add;
                 }
             }
         }

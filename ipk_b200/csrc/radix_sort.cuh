@@ -532,6 +532,21 @@ namespace ipkgpu
         rs_launch_shape<384, 16, digit_owner, 2>(ctx, kin, vin, nullptr, nullptr, d_base, n, S.status, S.tickets, own, &peers);
     }
 
+    /// One most-significant-digit pass: (ka, va) -> (kb, vb) by the 8 key bits from bit_begin, stably.  start[0..256) (host) =
+    /// where each digit's range begins in the output; the caller sorts the ranges on the bits below independently.
+    inline void radix_partition_top(ipkgpu_ctx* ctx, const uint64_t* ka, const uint32_t* va, uint64_t* kb, uint32_t* vb, uint64_t n,
+                                    uint32_t bit_begin, dbuf& table, uint32_t* start)
+    {
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "radix partition of %llu records exceeds 2^32-1", (unsigned long long)n);
+        const rs_scratch S = rs_prepare(ctx, n, table);
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * RS_HIST_ITEMS), uint64_t(ctx->num_sms) * 8));
+        IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_bits<<<hgrid, RS_HIST_THREADS, 2 * RS_RADIX * 4, ctx->stream>>>(ka, n, bit_begin, 8, 1, S.hist));
+        IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(S.hist));
+        IPK_CUDA(cudaMemcpyAsync(start, S.hist, RS_RADIX * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        rs_launch_onesweep(ctx, ka, va, kb, vb, S.hist, n, S.status, S.tickets, digit_bits{ bit_begin, 0xffu });
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+
     /// Sorts n pairs on key bits [bit_begin, bit_begin + n_bits), stably.  Ping-pongs between (ka,va) and (kb,vb);
     /// returns true if the sorted result is in (kb,vb).  n < 2^32.
     inline bool radix_sort_pairs(ipkgpu_ctx* ctx, uint64_t* ka, uint32_t* va, uint64_t* kb, uint32_t* vb, uint64_t n,

@@ -221,12 +221,19 @@ def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W, raw):
 @pytest.mark.parametrize("raw", [True, False])
 @pytest.mark.parametrize("world", [2, 3])
 @pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 200), (20, 5, 4, 8, 90)])
-def test_peer_scatter_equals_single(world, sigma, bits, k, n_taxa, W, raw):
+@pytest.mark.parametrize("streamed", [False, True])
+def test_peer_scatter_equals_single(world, sigma, bits, k, n_taxa, W, raw, streamed, monkeypatch):
     """The fused partition + exchange (ipkgpu_stage1_owner_counts / recv_buffers / stage1_scatter), ranks emulated as
     contexts of ONE process on one device, so the "peer" buffers are plain device pointers (the IPC mapping itself is
-    exercised by bench.py --gpus 2).  Entry-for-entry equal to the single-GPU build."""
+    exercised by bench.py --gpus 2).  Entry-for-entry equal to the single-GPU build.  streamed: the owner's stage 2 hands
+    back an indexed host shard with 16-bit branch ids, sorted / merged / copied in k-mer ranges (forced at this size)."""
     from types import SimpleNamespace
     from ipk_b200 import capi as libipkgpu, dist as ipkdist
+    if streamed and not raw:
+        pytest.skip("k-mer ranges apply to the single sort of raw records")
+    if streamed:
+        monkeypatch.setenv("IPKGPU_PART_MIN", "1")
+        monkeypatch.setenv("IPKGPU_PARTS", "3")
     omega = 1.5 if sigma == 4 else 10.0
     logp, nb = _synth(n_taxa, W, sigma)
     thr, lthr = _thr(omega, sigma, k)
@@ -251,7 +258,9 @@ def test_peer_scatter_equals_single(world, sigma, bits, k, n_taxa, W, raw):
             ctxs[r].stage1_scatter([b[0] for b in bufs], [b[1] for b in bufs], [int(matrix[:r, d].sum()) for d in range(world)])
         shards = []
         for r in range(world):
-            res = ctxs[r].stage2(bufs[r][0], bufs[r][1], int(matrix[:, r].sum()), group_bits, group_branch, k * bits, thr, T, 0, not raw, False)
+            res = ctxs[r].stage2(bufs[r][0], bufs[r][1], int(matrix[:, r].sum()), group_bits, group_branch, k * bits, thr, T, 0, not raw, False,
+                                 indexed=streamed, branch16=streamed)
+            assert bool(res.branch16) == streamed
             shards.append(libipkgpu.Context.to_db(res))
         assert sum(s.n_entries for s in shards) == want.n_entries
         assert all(s.n_entries > 0 for s in shards)
@@ -287,6 +296,38 @@ def test_ordered_emission_equals_default(sigma, bits, k, n_taxa, W, pool_cap, mo
         assert got.stats["sort_passes"] <= want.stats["sort_passes"]
     assert want.n_entries > 1000
     assert_db_equal(got, want, exact_fv=True)
+
+
+@pytest.mark.parametrize("parts", [2, 5, 300])
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W,filt", [(4, 2, 10, 12, 400, 0), (4, 2, 4, 9, 60, 0), (4, 2, 6, 40, 90, 0), (20, 5, 4, 6, 150, 1)])
+def test_streamed_parts_equal_single_sort(sigma, bits, k, n_taxa, W, filt, parts, monkeypatch):
+    """Host-bound indexed results above IPKGPU_PART_MIN records are sorted and max-merged in k-mer ranges (one MSD radix pass,
+    then per range the remaining LSD passes + merge appended to the CSR), each range's entries copied to the host while the
+    next is sorted.  Forced here at test sizes; same database as the single sort, bit for bit, with and without 16-bit
+    branch ids, with more requested parts than there are digit ranges, and with keys of 13 .. 25 bits (sort units of 1 .. 8
+    digit ranges)."""
+    from ipk_b200 import capi as libipkgpu
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    inp, keep = libipkgpu.make_input(logp, nb, W, sigma, bits, k, lthr, thr, T, filt)
+    with libipkgpu.Context(0) as c:
+        want = libipkgpu.Context.to_db(c.build_raw(inp, False, indexed=True))
+    monkeypatch.setenv("IPKGPU_PART_MIN", "1")
+    monkeypatch.setenv("IPKGPU_PARTS", str(parts))
+    with libipkgpu.Context(0) as c:
+        for b16 in (False, True, False):                 # the third build reuses every buffer of the first two
+            res = c.build_raw(inp, False, indexed=True, branch16=b16)
+            assert bool(res.branch16) == b16
+            got = libipkgpu.Context.to_db(res)
+            assert got.stats["kernel_launches"] > want.stats["kernel_launches"]        # it did go through the parts
+            assert got.stats["sort_passes"] == want.stats["sort_passes"]
+            assert_db_equal(got, want, exact_fv=True)
+        # contiguous and device-resident results keep the single sort
+        res = c.build_raw(inp, True, indexed=True)
+        assert res.stats.kernel_launches == want.stats["kernel_launches"]
+    assert want.n_entries > 500
 
 
 @pytest.mark.parametrize("sigma,bits,k,n_taxa,W,filt", [(4, 2, 8, 20, 300, 0), (20, 5, 3, 6, 120, 1)])
