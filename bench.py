@@ -356,6 +356,7 @@ def run_b200(args):
             "counts": {"windows": wl.n_windows, "emitted": n_emitted, "entries": n_entries, "kmers": n_kmers, "sort_passes": passes,
                        "tiles_rank0": int(st.get("n_tiles", 0)), "deferred_tiles_rank0": int(st.get("n_deferred_tiles", 0)),
                        "emitted_per_s": n_emitted * args.steps / (ms_dev * 1e-3)},
+            "stages_e2e_ms_rank0": {k_: round(float(last_e2e[2][k_]), 3) for k_ in ("ms_h2d", "ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order", "ms_d2h", "ms_total", "ms_partition", "ms_exchange") if k_ in last_e2e[2]},
             "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order", "ms_partition", "ms_exchange") if k_ in st},
             "kernels": kernels}
     if not args.no_cpu_baseline and world == 1:

@@ -109,6 +109,10 @@ struct ipkgpu_ctx
     cudaEvent_t ev_merged = nullptr, ev_copied = nullptr;
     // host-bound indexed results: sort + merge in n_parts k-mer ranges once there are part_min records (env IPKGPU_PARTS,
     // IPKGPU_PART_MIN), each range's entries queued on the copy stream as soon as it is merged
+    // host posteriors of at least h2d_chunk_min bytes go up in h2d_chunks node ranges (env IPKGPU_H2D_CHUNKS, IPKGPU_H2D_CHUNK_MIN)
+    uint32_t h2d_chunks = 4;
+    uint64_t h2d_chunk_min = 64ull << 20;
+    std::vector<cudaEvent_t> ev_h2d;
     uint32_t n_parts = 8;
     uint64_t part_min = 1ull << 25;
     bool entries_streamed = false, streamed_branch16 = false;

@@ -96,17 +96,18 @@ namespace
     }
 
     /// device pointer to the posteriors (copying them in when they are on the host) + group tables on the device
-    const float* stage_inputs(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& t, ipkgpu_stats* st)
+    __global__ void k0_nop() {}
+
+    /// node_bounds (optional): filled with c + 1 node indices when the host posteriors are uploaded in c > 1 chunks on the
+    /// copy stream (ctx->ev_h2d[i] fires when chunk i has landed), so that K1 / K2 of a chunk run under the next upload.
+    /// That needs launch slots == node indices (nodes arrive grouped by branch, the reference's own order).
+    const float* stage_inputs(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& t, ipkgpu_stats* st,
+                              std::vector<uint32_t>* node_bounds = nullptr)
     {
-        const size_t logp_bytes = size_t(in->n_nodes) * in->width * in->sigma * sizeof(float);
+        const size_t node_bytes = size_t(in->width) * in->sigma * sizeof(float);
+        const size_t logp_bytes = size_t(in->n_nodes) * node_bytes;
         const float* d_logp = in->logp;
-        if (!in->logp_on_device)
-        {
-            ctx->reserve(ctx->logp, logp_bytes);
-            IPK_CUDA(cudaMemcpyAsync(ctx->logp.p, in->logp, logp_bytes, cudaMemcpyHostToDevice, ctx->stream));
-            d_logp = ctx->logp.as<float>();
-            if (st) st->h2d_bytes += logp_bytes;
-        }
+        // the small tables first: same-direction copies share one DMA queue, and these must not wait behind the posteriors
         const size_t nb = size_t(in->n_nodes) * 4;
         ctx->reserve(ctx->node_group, nb);
         ctx->reserve(ctx->node_order, nb);
@@ -117,25 +118,70 @@ namespace
         ctx->max_branch = 0;
         for (uint32_t b : t.group_branch) ctx->max_branch = std::max(ctx->max_branch, b);
         if (st) st->h2d_bytes += 2 * nb + t.group_branch.size() * 4;
+        if (!in->logp_on_device)
+        {
+            ctx->reserve(ctx->logp, logp_bytes);
+            d_logp = ctx->logp.as<float>();
+            bool in_order = node_bounds != nullptr && ctx->h2d_chunks > 1 && logp_bytes >= ctx->h2d_chunk_min && in->n_nodes >= ctx->h2d_chunks;
+            for (uint32_t i = 0; in_order && i < in->n_nodes; ++i) in_order = t.node_order[i] == i;
+            if (in_order)
+            {
+                if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+                while (ctx->ev_h2d.size() < ctx->h2d_chunks)
+                {
+                    cudaEvent_t e;
+                    IPK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    ctx->ev_h2d.push_back(e);
+                }
+                // (whatever read ctx->logp before has finished: every entry point ends with a stream synchronize)
+                // The uploads are held back until the small tables above are through: the copy engine serves one channel's
+                // queue at a time in no promised order, and the first kernels wait for those tables.
+                while (ctx->ev_h2d.size() < ctx->h2d_chunks + 1)
+                {
+                    cudaEvent_t e;
+                    IPK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    ctx->ev_h2d.push_back(e);
+                }
+                // (an empty kernel, so that the stream's next event records are not the copy engine's to process either)
+                k0_nop<<<1, 32, 0, ctx->stream>>>();
+                IPK_CUDA(cudaEventRecord(ctx->ev_h2d[ctx->h2d_chunks], ctx->stream));
+                IPK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_h2d[ctx->h2d_chunks], 0));
+                node_bounds->assign(1, 0u);
+                for (uint32_t c = 0; c < ctx->h2d_chunks; ++c)
+                {
+                    const uint32_t n0 = node_bounds->back(), n1 = uint32_t(uint64_t(in->n_nodes) * (c + 1) / ctx->h2d_chunks);
+                    IPK_CUDA(cudaMemcpyAsync(ctx->logp.as<char>() + size_t(n0) * node_bytes, reinterpret_cast<const char*>(in->logp) + size_t(n0) * node_bytes,
+                                             size_t(n1 - n0) * node_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+                    IPK_CUDA(cudaEventRecord(ctx->ev_h2d[c], ctx->copy_stream));
+                    node_bounds->push_back(n1);
+                }
+            }
+            else IPK_CUDA(cudaMemcpyAsync(ctx->logp.p, in->logp, logp_bytes, cudaMemcpyHostToDevice, ctx->stream));
+            if (st) st->h2d_bytes += logp_bytes;
+        }
         // the host vectors above are pageable: the copies are staged synchronously by the runtime, safe to drop after
         return d_logp;
     }
 
     /// K1: matrix::preprocess for every node (window.cpp:16-27)
-    void run_best_prefix(ipkgpu_ctx* ctx, const float* d_logp, const ipkgpu_input* in)
+    /// nodes [node0, node1) (default: all); a range keeps its transposed column maxima in its own slice of ctx->colmax
+    void run_best_prefix(ipkgpu_ctx* ctx, const float* d_logp, const ipkgpu_input* in, uint32_t node0 = 0, uint32_t node1 = ~0u)
     {
-        const uint64_t cols = uint64_t(in->n_nodes) * in->width;
-        ctx->reserve(ctx->colmax, cols * 4 + 4);
+        node1 = std::min(node1, in->n_nodes);
+        ctx->reserve(ctx->colmax, uint64_t(in->n_nodes) * in->width * 4 + 4);
         ctx->reserve(ctx->bestpref, uint64_t(in->n_nodes) * (in->width + 1) * 4 + 4);
-        if (in->n_nodes == 0) return;
+        if (node1 <= node0) return;
+        const uint32_t nn = node1 - node0;
+        const uint64_t cols = uint64_t(nn) * in->width;
+        float* colmax = ctx->colmax.as<float>() + uint64_t(node0) * in->width;
         if (cols)
         {
             const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(cols, 256), uint64_t(ctx->num_sms) * 16));
             IPK_LAUNCH(ctx, "k1a_colmax", cols * (in->sigma + 1) * 4,
-                       k1a_colmax<<<grid, 256, 0, ctx->stream>>>(d_logp, ctx->colmax.as<float>(), in->n_nodes, in->width, in->sigma));
+                       k1a_colmax<<<grid, 256, 0, ctx->stream>>>(d_logp + uint64_t(node0) * in->width * in->sigma, colmax, nn, in->width, in->sigma));
         }
-        IPK_LAUNCH(ctx, "k1b_prefix", cols * 8 + uint64_t(in->n_nodes) * 4,
-                   k1b_prefix<<<div_up<uint32_t>(in->n_nodes, 64), 64, 0, ctx->stream>>>(ctx->colmax.as<float>(), ctx->bestpref.as<float>(), in->n_nodes, in->width));
+        IPK_LAUNCH(ctx, "k1b_prefix", cols * 8 + uint64_t(nn) * 4,
+                   k1b_prefix<<<div_up<uint32_t>(nn, 64), 64, 0, ctx->stream>>>(colmax, ctx->bestpref.as<float>() + uint64_t(node0) * (in->width + 1), nn, in->width));
     }
 }
 
@@ -152,6 +198,7 @@ namespace
         // ordered emission: level 0 of the join kernel writes (out_keys, out_scores) in tile order; the tiles it defers are
         // enumerated into this side stream (any order).  side_keys == nullptr: one stream, any order.
         uint64_t* side_keys = nullptr; float* side_scores = nullptr; uint64_t side_cap = 0;
+        uint64_t emitted_before = 0;       // records already in (out_keys, out_scores): a later node chunk of the same enumeration
     };
 
     uint64_t read_u64(ipkgpu_ctx* ctx, const void* d);
@@ -248,7 +295,7 @@ namespace
             std::vector<enum_level> levels = enumeration_levels(ctx, in);
             ctx->reserve(ctx->deferred, grid * 4);
             uint32_t* lists[2] = { nullptr, nullptr };
-            uint64_t n_items = grid, emitted_before = 0;            // items of the level about to run
+            uint64_t n_items = grid, emitted_before = L.emitted_before;            // items of the level about to run
             uint32_t prev_width = ENUM_THREADS;
             for (size_t level = 0; level < levels.size() && n_items > 0; ++level)
             {
@@ -554,15 +601,18 @@ namespace
         o.n_groups = uint32_t(T.group_branch.size());
         const uint32_t key_bits = in->k * in->bits;
         if (key_bits + group_bits > 64) fail(IPKGPU_EINVAL, "k*bits + group bits = %u exceeds 64", key_bits + group_bits);
-        const size_t eh = tm.mark();
-        const float* d_logp = stage_inputs(ctx, in, T, st);
-        const size_t e0 = tm.mark();
-        run_best_prefix(ctx, d_logp, in);
-        const size_t e1 = tm.mark();
         ctx->reserve(ctx->counters, 128);
         ctx->reserve(ctx->node_counts, size_t(in->n_nodes) * 8 + 8);
         IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 128, ctx->stream));
         IPK_CUDA(cudaMemsetAsync(ctx->node_counts.p, 0, size_t(in->n_nodes) * 8 + 8, ctx->stream));
+        const size_t eh = tm.mark();
+        // host posteriors of some size go up in node chunks on the copy stream, K1 + K2 of a chunk under the next upload
+        std::vector<uint32_t> chunk_bounds;
+        const float* d_logp = stage_inputs(ctx, in, T, st, ctx->ordered || in->width < in->k ? nullptr : &chunk_bounds);
+        const bool chunked = chunk_bounds.size() > 2;
+        const size_t e0 = tm.mark();
+        if (!chunked) run_best_prefix(ctx, d_logp, in);
+        const size_t e1 = tm.mark();
         ctx->s1_n = 0;
         if (in->n_nodes == 0 || in->width < in->k)
         {
@@ -600,7 +650,19 @@ namespace
             ctx->reserve(ctx->side_vals_a, side_cap * 4);
             L.side_keys = ctx->side_keys_a.as<uint64_t>(); L.side_scores = ctx->side_vals_a.as<float>(); L.side_cap = side_cap;
         }
-        launch_enumerate(ctx, d_logp, in, P, L, true);
+        if (chunked)
+        {
+            for (size_t c = 0; c + 1 < chunk_bounds.size(); ++c)
+            {
+                IPK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[c], 0));
+                run_best_prefix(ctx, d_logp, in, chunk_bounds[c], chunk_bounds[c + 1]);
+                enum_launch Lc = L;
+                Lc.slot_begin = chunk_bounds[c]; Lc.slot_end = chunk_bounds[c + 1];
+                Lc.emitted_before = c ? read_u64(ctx, ctx->counters.p) : 0;
+                launch_enumerate(ctx, d_logp, in, P, Lc, true);
+            }
+        }
+        else launch_enumerate(ctx, d_logp, in, P, L, true);
         o.enum_launches = 1;
         uint64_t n_main = read_u64(ctx, ctx->counters.p), n_side = 0;
         if (ordered) n_side = read_u64(ctx, ctx->counters.as<unsigned long long>() + 8);
@@ -1016,6 +1078,8 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     ctx->device = device;
     ctx->num_sms = prop.multiProcessorCount;
     if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
+    if (const char* e = getenv("IPKGPU_H2D_CHUNKS")) ctx->h2d_chunks = uint32_t(std::min(64, std::max(1, atoi(e))));
+    if (const char* e = getenv("IPKGPU_H2D_CHUNK_MIN")) ctx->h2d_chunk_min = uint64_t(std::max(1ll, atoll(e)));
     if (const char* e = getenv("IPKGPU_PARTS")) ctx->n_parts = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_PART_MIN")) ctx->part_min = uint64_t(std::max(1ll, atoll(e)));
     if (const char* e = getenv("IPKGPU_ORDERED")) ctx->ordered = atoi(e);
@@ -1072,6 +1136,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     if (ctx->ev_merged) { cudaEventDestroy(ctx->ev_merged); cudaEventDestroy(ctx->ev_copied); }
     for (auto* b : hall) if (b->p) cudaFreeHost(b->p);
     for (auto e : ctx->events) cudaEventDestroy(e);
+    for (auto e : ctx->ev_h2d) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -298,6 +298,36 @@ def test_ordered_emission_equals_default(sigma, bits, k, n_taxa, W, pool_cap, mo
     assert_db_equal(got, want, exact_fv=True)
 
 
+@pytest.mark.parametrize("shuffled", [False, True])
+@pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 300), (20, 5, 3, 6, 120)])
+def test_chunked_upload_equals_single_copy(sigma, bits, k, n_taxa, W, shuffled, monkeypatch):
+    """Host posteriors above IPKGPU_H2D_CHUNK_MIN bytes go up in node chunks on the copy stream, with the best-prefix and
+    enumeration kernels of a chunk running under the next upload (forced here at test size).  Same database; nodes that do
+    not arrive grouped by branch keep the single copy."""
+    from ipk_b200 import capi as libipkgpu
+    omega = 1.5 if sigma == 4 else 10.0
+    logp, nb = _synth(n_taxa, W, sigma)
+    if shuffled:
+        perm = np.random.default_rng(5).permutation(len(nb))
+        logp, nb = np.ascontiguousarray(logp[perm]), np.ascontiguousarray(nb[perm])
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    with libipkgpu.Context(0) as c:
+        want = c.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+    monkeypatch.setenv("IPKGPU_H2D_CHUNK_MIN", "1")
+    monkeypatch.setenv("IPKGPU_H2D_CHUNKS", "3")
+    with libipkgpu.Context(0) as c:
+        for _ in range(2):
+            got = c.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+            if shuffled:
+                assert got.stats["kernel_launches"] == want.stats["kernel_launches"]
+            else:
+                assert got.stats["kernel_launches"] > want.stats["kernel_launches"]
+            assert got.stats["n_emitted"] == want.stats["n_emitted"]
+            assert_db_equal(got, want, exact_fv=True)
+    assert want.n_entries > 500
+
+
 @pytest.mark.parametrize("parts", [2, 5, 300])
 @pytest.mark.parametrize("sigma,bits,k,n_taxa,W,filt", [(4, 2, 10, 12, 400, 0), (4, 2, 4, 9, 60, 0), (4, 2, 6, 40, 90, 0), (20, 5, 4, 6, 150, 1)])
 def test_streamed_parts_equal_single_sort(sigma, bits, k, n_taxa, W, filt, parts, monkeypatch):
