@@ -522,7 +522,8 @@ namespace
         for (uint32_t d0 = 0; d0 < 256;)
         {
             uint32_t d1 = d0 + unit;
-            while (d1 < 256 && uint64_t(start[d1]) - start[d0] < target) d1 += unit;
+            // (a smaller first part would start the copy chain earlier; on cfg3 the copy engine then idles until the second part is merged and the build ends later -- r02e)
+            while (d1 < 256 && uint64_t(start[d1]) - start[d0] < (ent_base == 0 && d0 == 0 ? target / ctx->first_part_div : target)) d1 += unit;
             const uint64_t o = start[d0], c = uint64_t(start[d1]) - start[d0];
             const uint32_t first = d0;
             d0 = d1;
@@ -1080,6 +1081,7 @@ int ipkgpu_create(ipkgpu_ctx** out, int device, void* stream)
     if (const char* e = getenv("IPKGPU_RS_SHAPE")) ctx->rs_shape = atoi(e);
     if (const char* e = getenv("IPKGPU_H2D_CHUNKS")) ctx->h2d_chunks = uint32_t(std::min(64, std::max(1, atoi(e))));
     if (const char* e = getenv("IPKGPU_H2D_CHUNK_MIN")) ctx->h2d_chunk_min = uint64_t(std::max(1ll, atoll(e)));
+    if (const char* e = getenv("IPKGPU_FIRST_PART_DIV")) ctx->first_part_div = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_PARTS")) ctx->n_parts = uint32_t(std::max(1, atoi(e)));
     if (const char* e = getenv("IPKGPU_PART_MIN")) ctx->part_min = uint64_t(std::max(1ll, atoll(e)));
     if (const char* e = getenv("IPKGPU_ORDERED")) ctx->ordered = atoi(e);
