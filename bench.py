@@ -205,6 +205,7 @@ def run_b200(args):
         raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torchrun --nproc-per-node {args.gpus}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_bound = world > 1 and os.environ.get("IPK_BIND", "1") != "0" and ipkdist.bind_near_gpu(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     wl = synth.WORKLOADS[args.workload]
@@ -347,7 +348,8 @@ def run_b200(args):
             "dtype": "f32", "data": "synthetic",
             "config": {**workload_config(wl, world), "seed": args.seed, "l2": "flushed between steps (256 MiB write)",
                        "timing": "CUDA events on the launching stream, per step, summed; max over ranks",
-                       "result": "indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries"},
+                       "result": "indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries",
+                       "host": "rank processes bound to the CPUs next to their GPU (NVML affinity)" if numa_bound else "unbound"},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "build_time_s": ms_e2e / args.steps * 1e-3},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,

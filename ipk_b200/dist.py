@@ -27,6 +27,23 @@ import torch
 import torch.distributed as dist
 
 
+def bind_near_gpu(device_index: int) -> bool:
+    """Pins the calling process to the CPUs next to its GPU (NVML's ideal affinity), so that the pinned host buffers it
+    allocates afterwards -- posteriors, and the library's result staging -- land on that GPU's NUMA node.  With one process
+    per GPU and all eight copying results back at once, unbound processes put every buffer wherever they happen to run and
+    the copies share one socket's memory controllers.  Returns False (and changes nothing) when NVML cannot say."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        props = torch.cuda.get_device_properties(device_index)
+        bus = "%08x:%02x:%02x.0" % (getattr(props, "pci_domain_id", 0), props.pci_bus_id, props.pci_device_id)
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        return True
+    except Exception:
+        return False
+
+
 def split_branches(n_branches: int, world: int) -> list[tuple[int, int]]:
     """contiguous blocks of the branch-group processing order, sizes differing by at most one"""
     base, extra = divmod(n_branches, world)
