@@ -101,6 +101,12 @@ const char* ipkgpu_last_error(const ipkgpu_ctx* ctx);      /* ctx may be NULL: m
 void* ipkgpu_stream(const ipkgpu_ctx* ctx);                /* the cudaStream_t all work of ctx is ordered on */
 int  ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes);   /* cap on device scratch; 0 = 85% of free memory */
 
+/* Page-locked host memory for the posteriors a caller is about to load (matrix rows of window.h:67 in node order): only
+ * pinned input lets ipkgpu_build upload in node chunks under the enumeration kernels; pageable input works, unpipelined.
+ * No context needed (the loader runs before the device path is set up).  Release with ipkgpu_host_free. */
+int  ipkgpu_host_alloc(int device, size_t bytes, void** out);
+void ipkgpu_host_free(void* p);
+
 /* Enumeration strategy (no reference counterpart; the output is identical either way).  mode 0: list-join kernel, the
  * depth-first kernel takes the tiles whose lists overflow the shared-memory pool; mode 1: depth-first kernel only.
  * pool_cap: list-pool capacity in 8-byte elements (0 = default for the alphabet, at most 65000). */

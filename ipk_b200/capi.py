@@ -109,6 +109,10 @@ def load() -> C.CDLL:
     lib.ipkgpu_last_error.restype = C.c_char_p
     lib.ipkgpu_stream.argtypes = [C.c_void_p]
     lib.ipkgpu_stream.restype = C.c_void_p
+    lib.ipkgpu_host_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.ipkgpu_host_alloc.restype = C.c_int
+    lib.ipkgpu_host_free.argtypes = [C.c_void_p]
+    lib.ipkgpu_host_free.restype = None
     lib.ipkgpu_set_workspace_limit.argtypes = [C.c_void_p, C.c_uint64]
     lib.ipkgpu_set_workspace_limit.restype = C.c_int
     lib.ipkgpu_set_enumeration.argtypes = [C.c_void_p, C.c_int, C.c_uint32]

@@ -1181,6 +1181,20 @@ int ipkgpu_set_workspace_limit(ipkgpu_ctx* ctx, uint64_t bytes)
     return IPKGPU_OK;
 }
 
+int ipkgpu_host_alloc(int device, size_t bytes, void** out)
+{
+    if (!out) return IPKGPU_EINVAL;
+    *out = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return IPKGPU_ENODEV; }
+    if (cudaMallocHost(out, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return IPKGPU_ENOMEM; }
+    return IPKGPU_OK;
+}
+
+void ipkgpu_host_free(void* p)
+{
+    if (p && cudaFreeHost(p) != cudaSuccess) cudaGetLastError();
+}
+
 int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out)
 {
     return guarded(ctx, [&] {

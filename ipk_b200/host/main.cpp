@@ -21,6 +21,7 @@
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <memory>
 #include <vector>
 
 namespace
@@ -117,8 +118,12 @@ int main(int argc, char** argv)
         const uint32_t width = ipkhost_ar_width(ar);
         std::vector<const char*> label_ptrs;
         for (auto& s : labels) label_ptrs.push_back(s.c_str());
-        std::vector<float> logp(size_t(labels.size()) * width * sigma);
-        if (ipkhost_ar_read_nodes(ar, label_ptrs.data(), uint32_t(labels.size()), logp.data()) != IPKHOST_OK)
+        // page-locked, so that the library uploads in node chunks under its first kernels
+        void* logp_mem = nullptr;
+        if (ipkgpu_host_alloc(o.device, size_t(labels.size()) * width * sigma * sizeof(float), &logp_mem) != IPKGPU_OK)
+            throw std::runtime_error("cannot allocate page-locked memory for the posteriors (no CUDA device?)");
+        std::unique_ptr<float, void (*)(float*)> logp(static_cast<float*>(logp_mem), [](float* p) { ipkgpu_host_free(p); });
+        if (ipkhost_ar_read_nodes(ar, label_ptrs.data(), uint32_t(labels.size()), logp.get()) != IPKHOST_OK)
             throw std::runtime_error(ipkhost_last_error());
         ipkhost_ar_close(ar);
         fprintf(stderr, "Loaded %zu ghost-node matrices x %u sites x %u states in %.3f s\n", labels.size(), width, sigma, seconds_since(t0));
@@ -129,7 +134,7 @@ int main(int argc, char** argv)
         if (ipkgpu_create(&ctx, o.device, nullptr) != IPKGPU_OK) throw std::runtime_error(ipkgpu_last_error(nullptr));
         ipkgpu_input in;
         memset(&in, 0, sizeof in);
-        in.logp = logp.data();
+        in.logp = logp.get();
         in.node_branch = node_branch.data();
         in.n_nodes = uint32_t(labels.size());
         in.width = width; in.sigma = sigma; in.bits = bits; in.k = o.k;
