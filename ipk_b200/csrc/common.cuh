@@ -111,11 +111,11 @@ struct ipkgpu_ctx
     // IPKGPU_PART_MIN), each range's entries queued on the copy stream as soon as it is merged
     // host posteriors of at least h2d_chunk_min bytes go up in h2d_chunks node ranges (env IPKGPU_H2D_CHUNKS, IPKGPU_H2D_CHUNK_MIN)
     uint32_t h2d_chunks = 4;
-    uint64_t h2d_chunk_min = 64ull << 20;
+    uint64_t h2d_chunk_min = 256ull << 20;
     std::vector<cudaEvent_t> ev_h2d;
     uint32_t n_parts = 8;
     uint32_t first_part_div = 1;       // first part this much smaller than the others (env IPKGPU_FIRST_PART_DIV); 4 and 8 measured 4 ms SLOWER on cfg3 (r02e)
-    uint64_t part_min = 1ull << 25;
+    uint64_t part_min = 1ull << 27;
     bool entries_streamed = false, streamed_branch16 = false;
     cudaStream_t copy_stream = nullptr;   // indexed host results: the entries leave under the filter / ordering kernels
 

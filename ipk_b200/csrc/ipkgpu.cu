@@ -481,7 +481,12 @@ namespace
     /// Host-bound indexed results of at least ctx->part_min records are sorted and merged in k-mer ranges.
     bool parts_eligible(const ipkgpu_ctx* ctx, uint64_t n, uint32_t key_bits, uint32_t n_bits, int result_mode)
     {
-        return (result_mode & 3) == IPKGPU_RESULT_HOST_INDEXED && ctx->n_parts > 1 && n >= ctx->part_min && key_bits >= 8 && n_bits > 8 && n <= 0xffffffffull;
+        if ((result_mode & 3) != IPKGPU_RESULT_HOST_INDEXED || ctx->n_parts <= 1 || n < ctx->part_min || key_bits < 8 || n_bits <= 8 || n > 0xffffffffull)
+            return false;
+        // the sort below the top digit runs per unit of 2^slack digit ranges (sort_merge_parts): launches of a few million
+        // records leave the device half idle (cfg5: 64 units of 4.8 M records doubled the sort time and the build lost 9 ms)
+        const uint32_t low_bits = n_bits - 8, n_units = 256u >> (8 * div_up<uint32_t>(low_bits, 8) - low_bits);
+        return n / n_units >= ctx->part_min / 12;
     }
 
     /// Sort + max-merge + CSR of n records in k-mer RANGES, so that the entries start crossing PCIe while later ranges are
