@@ -103,6 +103,7 @@ struct ipkgpu_ctx
     uint32_t* s1_scores = nullptr;
     uint64_t hint_side = 0;            // ... and of its side stream
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
+    uint64_t hint_kmers = 0, hint_kmers_records = 0;   // k-mers of the previous result and the records it was merged from (parts_eligible)
     // pinned host staging
     ipkgpu::hbuf h_small, h_keys, h_fv, h_offs, h_branch, h_score, h_cnt;
     uint32_t max_branch = 0;           // largest branch id of the current build (16-bit branch results)

@@ -478,15 +478,19 @@ namespace
         float ms_sort = 0, ms_merge = 0;
     };
 
-    /// Host-bound indexed results of at least ctx->part_min records are sorted and merged in k-mer ranges.
-    bool parts_eligible(const ipkgpu_ctx* ctx, uint64_t n, uint32_t key_bits, uint32_t n_bits, int result_mode)
+    /// Host-bound indexed results of at least ctx->part_min records are sorted and merged in k-mer ranges -- when the ENTRIES
+    /// are what crosses PCIe.  The k-mer heads (24 bytes each) only exist after the ordering, at the very end; a database
+    /// of few entries per k-mer (cfg5: 2.5) gains nothing from streaming its entries and pays for the shorter launches
+    /// (110 -> 119 ms), so ranges need >= 8 records per expected k-mer: the previous build's count on this context if it was
+    /// of similar size, else the bound the caller knows (sigma^k or 2^key_bits).  r02i / r02k A/B runs under profiles/.
+    bool parts_eligible(const ipkgpu_ctx* ctx, uint64_t n, uint32_t key_bits, uint32_t n_bits, int result_mode, uint64_t kmer_bound)
     {
         if ((result_mode & 3) != IPKGPU_RESULT_HOST_INDEXED || ctx->n_parts <= 1 || n < ctx->part_min || key_bits < 8 || n_bits <= 8 || n > 0xffffffffull)
             return false;
-        // the sort below the top digit runs per unit of 2^slack digit ranges (sort_merge_parts): launches of a few million
-        // records leave the device half idle (cfg5: 64 units of 4.8 M records doubled the sort time and the build lost 9 ms)
-        const uint32_t low_bits = n_bits - 8, n_units = 256u >> (8 * div_up<uint32_t>(low_bits, 8) - low_bits);
-        return n / n_units >= ctx->part_min / 12;
+        uint64_t kmers = std::min(n, kmer_bound);
+        if (ctx->hint_kmers_records && n / 2 <= ctx->hint_kmers_records && ctx->hint_kmers_records <= 2 * n)
+            kmers = std::min<uint64_t>(kmers, uint64_t(double(ctx->hint_kmers) * double(n) / double(ctx->hint_kmers_records)) + 1);
+        return n / 8 >= kmers || ctx->part_min <= 1;
     }
 
     /// Sort + max-merge + CSR of n records in k-mer RANGES, so that the entries start crossing PCIe while later ranges are
@@ -744,7 +748,7 @@ namespace
             const size_t eb = tm.mark();
             ctx->reserve(ctx->keys_b, b.n * 8 + 8);
             ctx->reserve(ctx->vals_b, b.n * 4 + 4);
-            if (single && want_csr && !use_side && parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode))
+            if (single && want_csr && !use_side && parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode, uint64_t(std::min(1e18, std::pow(double(in->sigma), double(in->k))))))
             {
                 const parts_out po = sort_merge_parts(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
                                                       ctx->vals_b.as<uint32_t>(), b.n, key_bits, bbits, group_bits, group_base + b.g0, result_mode, tm);
@@ -816,6 +820,7 @@ namespace
                          ipkgpu_result* out, stage_timer& tm)
     {
         if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard", (unsigned long long)n_entries);
+        ctx->hint_kmers = n_kmers;
         ipkgpu_stats& st = out->stats;
         const bool on_device = (result_on_device & 1) != 0, indexed = (result_on_device & 2) != 0;
         // 16-bit branch ids for host results whose every branch id fits: 6 instead of 8 bytes per entry over PCIe
@@ -991,11 +996,12 @@ namespace
         {
             ctx->reserve(ctx->keys_b, n * 8 + 8);
             ctx->reserve(ctx->vals_b, n * 4 + 4);
-            if (!group_ordered && parts_eligible(ctx, n, sp.key_bits, sp.key_bits + sp.group_bits, result_on_device))
+            if (!group_ordered && parts_eligible(ctx, n, sp.key_bits, sp.key_bits + sp.group_bits, result_on_device, sp.key_bits < 63 ? 1ull << sp.key_bits : ~0ull))
             {
                 const parts_out po = sort_merge_parts(ctx, keys, reinterpret_cast<uint32_t*>(scores), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(),
                                                       n, sp.key_bits, sp.group_bits, sp.group_bits, 0, result_on_device, tm);
                 out->stats.sort_passes += po.passes;
+                ctx->hint_kmers_records = n;
                 finish_from_csr(ctx, po.m.n_kmers, po.m.n_records, sp, result_on_device, out, tm);
                 out->stats.ms_sort += po.ms_sort;
                 out->stats.ms_merge += po.ms_merge;
@@ -1019,6 +1025,7 @@ namespace
             IPK_CUDA(cudaMemsetAsync(ctx->kmer_offs.p, 0, 8, ctx->stream));
         }
         const size_t e2 = tm.mark();
+        ctx->hint_kmers_records = n;
         finish_from_csr(ctx, m.n_kmers, m.n_records, sp, result_on_device, out, tm);
         out->stats.ms_sort += tm.ms(e0, e1);
         out->stats.ms_merge += tm.ms(e1, e2);
@@ -1220,6 +1227,7 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         st.sort_passes = s1.sort_passes;
         st.enum_launches = s1.enum_launches;
         st.ms_h2d = s1.ms_h2d; st.ms_prefix = s1.ms_prefix; st.ms_enumerate = s1.ms_enumerate; st.ms_sort = s1.ms_sort; st.ms_merge = s1.ms_merge;
+        if (s1.csr_done) ctx->hint_kmers_records = s1.n_emitted;
         if (s1.csr_done) finish_from_csr(ctx, s1.n_kmers, s1.n_unique, sp, result_on_device, out, tm);
         else run_stage2(ctx, ctx->u_keys.as<uint64_t>(), ctx->u_scores.as<float>(), s1.n_unique, true, sp, result_on_device, out, tm);
         const size_t t1 = tm.mark();
