@@ -160,6 +160,33 @@ def score_threshold(omega: float, sigma: int, k: int) -> tuple[float, float]:
     return float(t.value), float(lt.value)
 
 
+class PinnedArray:
+    """float32 numpy array in page-locked memory from ipkgpu_host_alloc (include/ipkgpu.h): what a loader fills so that
+    ipkgpu_build can upload in node chunks under its first kernels.  Freed by close() / the context manager."""
+
+    def __init__(self, shape, device: int = 0):
+        self._lib = load()
+        n = int(np.prod(shape))
+        p = C.c_void_p(0)
+        rc = self._lib.ipkgpu_host_alloc(device, n * 4, C.byref(p))
+        if rc != 0 or not p.value:
+            raise IpkGpuError(rc, "ipkgpu_host_alloc failed")
+        self._p = p
+        self.array = np.ctypeslib.as_array((C.c_float * max(n, 1)).from_address(p.value))[:n].reshape(shape)
+
+    def close(self):
+        if self._p:
+            self.array = None
+            self._lib.ipkgpu_host_free(self._p)
+            self._p = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
 def _ptr(a) -> int:
     """address of a numpy array / torch tensor / raw int"""
     if a is None:
