@@ -509,9 +509,9 @@ namespace
         // everything the copies touch is sized now, by the record count (an upper bound of the entry count)
         if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
         if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
-        ctx->reserve_host(ctx->h_branch, n * 4 + 4);
+        ctx->reserve_host(ctx->h_branch, n * (b16 ? 2 : 4) + 8);
         ctx->reserve_host(ctx->h_score, n * 4 + 4);
-        if (b16) ctx->reserve(ctx->out_branch, n * 2 + 4);
+        if (b16) ctx->reserve(ctx->out_branch, n * 2 + 8);
 
         uint32_t start[257];
         const size_t e0 = tm.mark();
