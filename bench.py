@@ -301,6 +301,9 @@ def run_b200(args):
 
     ms_dev, ms_e2e = reduce_max(ms_dev), reduce_max(ms_e2e)
     n_entries = reduce_sum(last_dev[0]); n_kmers = reduce_sum(last_dev[1])
+    if (n_entries, n_kmers) != (reduce_sum(last_e2e[0]), reduce_sum(last_e2e[1])):
+        raise SystemExit(f"bench.py: the host-bound build disagrees with the device-resident one: {reduce_sum(last_e2e[0])} entries / "
+                         f"{reduce_sum(last_e2e[1])} k-mers vs {n_entries} / {n_kmers}")
     st = last_dev[2]
     n_emitted = reduce_sum(int(st["n_emitted"]))
     h2d = reduce_sum(int(last_e2e[2]["h2d_bytes"])); d2h = reduce_sum(last_e2e[3])
