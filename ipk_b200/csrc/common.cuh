@@ -79,6 +79,7 @@ struct ipkgpu_ctx
     ipkgpu::dbuf mif_tab;              // MIF0: bucket table of mif_log2 (mif_math.cuh)
     ipkgpu::dbuf mif_chunks;           // MIF0: first k-mer of every chunk of entries
     ipkgpu::dbuf rs_status;            // radix sort: look-back status words [tile][digit]
+    ipkgpu::dbuf ps_hist;              // packed sort: per-bucket digit bases of the LSD passes [256][passes][256] + tickets
     ipkgpu::dbuf mg_status;            // merge: look-back status words [tile][2]
     uint32_t mg_epoch = 0;
     int rs_shape = 2;                  // tile shape of the sweep kernel (index into RS_SHAPES; env IPKGPU_RS_SHAPE)

@@ -10,6 +10,7 @@
 #include "join.cuh"
 #include "radix_sort.cuh"
 #include "merge.cuh"
+#include "packed_sort.cuh"
 #include "filter.cuh"
 
 #include <cmath>
@@ -586,6 +587,154 @@ namespace
 
 namespace
 {
+    /// queues the D2H copy of the entries [ent_base, ent_base + n) of the CSR on the copy stream, behind whatever the main
+    /// stream has done so far (host-bound indexed results: the entries leave while later k-mer ranges are still sorted)
+    void queue_entry_copy(ipkgpu_ctx* ctx, uint64_t ent_base, uint64_t n, bool b16)
+    {
+        if (n == 0) return;
+        IPK_CUDA(cudaEventRecord(ctx->ev_merged, ctx->stream));
+        IPK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_merged, 0));
+        if (b16)
+        {
+            k6_narrow_branch<<<uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, 1024), 1u << 20)), 256, 0, ctx->copy_stream>>>(
+                ctx->ent_branch.as<uint32_t>(), ent_base, ent_base + n, ctx->out_branch.as<uint16_t>());
+            check_launch(ctx, "k6_narrow_branch", 0);
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.as<uint16_t>() + ent_base, ctx->out_branch.as<uint16_t>() + ent_base, n * 2,
+                                     cudaMemcpyDeviceToHost, ctx->copy_stream));
+        }
+        else
+            IPK_CUDA(cudaMemcpyAsync(ctx->h_branch.as<uint32_t>() + ent_base, ctx->ent_branch.as<uint32_t>() + ent_base, n * 4,
+                                     cudaMemcpyDeviceToHost, ctx->copy_stream));
+        IPK_CUDA(cudaMemcpyAsync(ctx->h_score.as<float>() + ent_base, ctx->ent_score.as<float>() + ent_base, n * 4,
+                                 cudaMemcpyDeviceToHost, ctx->copy_stream));
+    }
+
+    /// K3 + K3' over the sorted packed records of buckets [d0, d1) (packed_sort.cuh), appended to the CSR at (ent_base, kmer_base)
+    merge_out run_merge_packed(ipkgpu_ctx* ctx, const uint64_t* recs, ps_table& T, uint32_t d0, uint32_t d1, uint32_t key_bits, uint32_t gbits,
+                               uint32_t group_add, uint64_t ent_base, uint64_t kmer_base, uint64_t n_total)
+    {
+        merge_out r;
+        const uint64_t n = uint64_t(T.start[d1]) - T.start[d0];
+        if (n == 0) return r;
+        ps_fill_tiles(T, d0, d1, MP_TILE);
+        const uint32_t tiles = T.tile_first[d1];
+        const uint64_t n_cap = std::max(n_total, ent_base + n);
+        const uint64_t kmer_bound = key_bits < 40 ? std::min<uint64_t>(n_cap, 1ull << key_bits) : n_cap;
+        ctx->reserve(ctx->kmer_keys, kmer_bound * 8 + 8);
+        ctx->reserve(ctx->kmer_offs, (kmer_bound + 1) * 8);
+        ctx->reserve(ctx->ent_branch, n_cap * 4 + 4);
+        ctx->reserve(ctx->ent_score, n_cap * 4 + 4);
+        ctx->reserve(ctx->counters, 128);
+        const size_t status_bytes = size_t(tiles) * 16;
+        if (status_bytes > ctx->mg_status.cap)
+        {
+            ctx->reserve(ctx->mg_status, status_bytes);
+            IPK_CUDA(cudaMemsetAsync(ctx->mg_status.p, 0, ctx->mg_status.cap, ctx->stream));
+            ctx->mg_epoch = 0;
+        }
+        if (++ctx->mg_epoch >= (1u << 30))
+        {
+            IPK_CUDA(cudaMemsetAsync(ctx->mg_status.p, 0, ctx->mg_status.cap, ctx->stream));
+            ctx->mg_epoch = 1;
+        }
+        unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;      // [2], [3]: totals; [4]: ticket
+        IPK_CUDA(cudaMemsetAsync(totals, 0, 24, ctx->stream));
+        mergep_args M;
+        M.recs = recs; M.group_bits = gbits; M.kmer_low_bits = key_bits - 8; M.group_add = group_add;
+        M.group_branch = ctx->group_branch.as<uint32_t>();
+        M.kmer_keys = ctx->kmer_keys.as<uint64_t>() + kmer_base;
+        M.kmer_offs = ctx->kmer_offs.as<uint64_t>() + kmer_base;
+        M.ent_branch = ctx->ent_branch.as<uint32_t>() + ent_base;
+        M.ent_score = ctx->ent_score.as<float>() + ent_base;
+        M.status = ctx->mg_status.as<uint64_t>();
+        M.ticket = reinterpret_cast<uint32_t*>(totals + 2);
+        M.totals = totals;
+        M.offs_add = ent_base;
+        M.epoch = ctx->mg_epoch;
+        M.n_tiles = tiles;
+        IPK_LAUNCH(ctx, "mg_merge_packed", n * 8, mg_merge_packed<<<tiles, MP_THREADS, 0, ctx->stream>>>(M, T));
+        uint64_t h[2];
+        IPK_CUDA(cudaMemcpyAsync(h, totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        r.n_records = h[0];
+        r.n_kmers = h[1];
+        ctx->kprof_add_bytes("mg_merge_packed", r.n_records * 8 + r.n_kmers * 16);
+        const uint64_t end = ent_base + r.n_records;
+        IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + kmer_base + r.n_kmers, &end, 8, cudaMemcpyHostToDevice, ctx->stream));
+        return r;
+    }
+
+    /// The merge sort on packed records (packed_sort.cuh): top-byte histogram -> MSD pass (ka, va) -> 8-byte records in p0 ->
+    /// segmented LSD passes p0 <-> p1 (p1 = ka's memory, free once the MSD pass has read it) -> max-merge + CSR.
+    /// stream_parts: host-bound indexed result -- buckets are sorted and merged in runs of about n / n_parts records and each
+    /// run's entries are queued on the copy stream at once (the role sort_merge_parts has for the pair sort).
+    parts_out sort_merge_packed(ipkgpu_ctx* ctx, uint64_t* ka, uint32_t* va, uint64_t* p0, uint64_t n, uint32_t key_bits, uint32_t gbits,
+                                uint32_t group_add, int result_mode, bool stream_parts, stage_timer& tm)
+    {
+        parts_out R;
+        const uint32_t low_bits = key_bits + gbits - 8;
+        uint64_t* p1 = ka;
+        const bool b16 = stream_parts && (result_mode & 4) != 0 && ctx->max_branch < 65536u;
+        if (stream_parts)
+        {
+            if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+            if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
+            ctx->reserve_host(ctx->h_branch, n * (b16 ? 2 : 4) + 8);
+            ctx->reserve_host(ctx->h_score, n * 4 + 4);
+            if (b16) ctx->reserve(ctx->out_branch, n * 2 + 8);
+        }
+        ps_table T;
+        memset(&T, 0, sizeof T);
+        const size_t e0 = tm.mark();
+        ps_top_histogram(ctx, ka, n, low_bits);
+        IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(ctx->hist.as<uint32_t>()));
+        IPK_CUDA(cudaMemcpyAsync(T.start, ctx->hist.p, RS_RADIX * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        ps_dest D;
+        memset(&D, 0, sizeof D);
+        D.out[0] = p0;
+        ps_msd_pack(ctx, ka, va, n, low_bits, ctx->hist.as<uint32_t>(), D, false);
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));           // T.start is on the host now (and ka is free: it becomes p1)
+        T.start[PS_BUCKETS] = uint32_t(n);
+        const size_t e1 = tm.mark();
+        R.passes = 1 + div_up<uint32_t>(low_bits, 8);
+        struct mark3 { size_t a, b, c; };
+        std::vector<mark3> marks;
+        const uint64_t target = stream_parts ? div_up<uint64_t>(n, ctx->n_parts) : n;
+        uint64_t ent_base = 0, kmer_base = 0;
+        for (uint32_t d0 = 0; d0 < PS_BUCKETS;)
+        {
+            uint32_t d1 = d0 + 1;
+            while (d1 < PS_BUCKETS && uint64_t(T.start[d1]) - T.start[d0] < target) ++d1;
+            if (!stream_parts) d1 = PS_BUCKETS;
+            const uint32_t first = d0;
+            d0 = d1;
+            if (T.start[d1] == T.start[first]) continue;
+            const size_t ea = tm.mark();
+            const bool in1 = ps_sort_buckets(ctx, p0, p1, T, first, d1, low_bits);
+            const size_t eb = tm.mark();
+            const merge_out m = run_merge_packed(ctx, in1 ? p1 : p0, T, first, d1, key_bits, gbits, group_add, ent_base, kmer_base, n);
+            marks.push_back({ ea, eb, tm.mark() });
+            if (stream_parts) queue_entry_copy(ctx, ent_base, m.n_records, b16);
+            ent_base += m.n_records;
+            kmer_base += m.n_kmers;
+        }
+        if (stream_parts)
+        {
+            IPK_CUDA(cudaEventRecord(ctx->ev_copied, ctx->copy_stream));
+            ctx->entries_streamed = true;
+            ctx->streamed_branch16 = b16;
+        }
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        R.m.n_records = ent_base;
+        R.m.n_kmers = kmer_base;
+        R.ms_sort = tm.ms(e0, e1);
+        for (const mark3& k : marks) { R.ms_sort += tm.ms(k.a, k.b); R.ms_merge += tm.ms(k.b, k.c); }
+        return R;
+    }
+}
+
+namespace
+{
     struct stage1_out
     {
         uint64_t n_emitted = 0, n_unique = 0, n_kmers = 0;
@@ -747,6 +896,19 @@ namespace
             else if (!timed_first) { ea = e1; timed_first = true; }
             const size_t eb = tm.mark();
             ctx->reserve(ctx->keys_b, b.n * 8 + 8);
+            if (single && want_csr && !use_side && ps_eligible(key_bits, bbits, b.n))
+            {
+                // 8-byte packed records: one MSD pass, then segmented LSD passes and the merge (packed_sort.cuh)
+                const bool parts = parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode, uint64_t(std::min(1e18, std::pow(double(in->sigma), double(in->k)))));
+                const parts_out po = sort_merge_packed(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(), b.n, key_bits, bbits,
+                                                       group_base + b.g0, result_mode, parts, tm);
+                o.sort_passes += po.passes;
+                o.csr_done = true; o.n_kmers = po.m.n_kmers;
+                u_off += po.m.n_records;
+                ms_enum += tm.ms(ea, eb); ms_sort += po.ms_sort; ms_merge += po.ms_merge;
+                e_prev = tm.mark();
+                continue;
+            }
             ctx->reserve(ctx->vals_b, b.n * 4 + 4);
             if (single && want_csr && !use_side && parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode, uint64_t(std::min(1e18, std::pow(double(in->sigma), double(in->k))))))
             {
@@ -995,6 +1157,18 @@ namespace
         if (n)
         {
             ctx->reserve(ctx->keys_b, n * 8 + 8);
+            if (ps_eligible(sp.key_bits, sp.group_bits, n))
+            {
+                const bool parts = parts_eligible(ctx, n, sp.key_bits, sp.key_bits + sp.group_bits, result_on_device, sp.key_bits < 63 ? 1ull << sp.key_bits : ~0ull);
+                const parts_out po = sort_merge_packed(ctx, keys, reinterpret_cast<uint32_t*>(scores), ctx->keys_b.as<uint64_t>(), n, sp.key_bits, sp.group_bits, 0,
+                                                       result_on_device, parts, tm);
+                out->stats.sort_passes += po.passes;
+                ctx->hint_kmers_records = n;
+                finish_from_csr(ctx, po.m.n_kmers, po.m.n_records, sp, result_on_device, out, tm);
+                out->stats.ms_sort += po.ms_sort;
+                out->stats.ms_merge += po.ms_merge;
+                return;
+            }
             ctx->reserve(ctx->vals_b, n * 4 + 4);
             if (!group_ordered && parts_eligible(ctx, n, sp.key_bits, sp.key_bits + sp.group_bits, result_on_device, sp.key_bits < 63 ? 1ull << sp.key_bits : ~0ull))
             {
@@ -1141,7 +1315,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
-                            &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split };
+                            &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);

@@ -1,0 +1,595 @@
+// packed_sort.cuh -- the merge sort of the emitted records on 8-byte PACKED records, sm_100a.
+//
+// Same job as radix_sort.cuh + merge.cuh (ipk::put, branch_group.cpp:88-101, and the unsafe_insert regroup,
+// db_builder.cpp:685-693, as one sort on (k-mer, group) + segmented max), with less memory traffic:
+//
+//   1. ONE most-significant-digit pass on the top 8 bits of the composite key  ckey = (kmer << group_bits) | group
+//      splits the (u64 key, f32 score) pairs into 256 buckets.  Inside a bucket the top byte is implied by the position,
+//      so what is stored is  rec = (ckey & low_mask) << 32 | score bits : 8 bytes instead of 12 (needs
+//      key_bits + group_bits - 8 <= 32; every DNA configuration of BASELINE.json qualifies, the amino-acid one keeps the
+//      pair sort).
+//   2. The remaining ceil(low_bits / 8) LSD passes run on ONE u64 array, segmented by bucket: tiles are cut at bucket
+//      boundaries, every bucket has its own digit histogram and its own look-back chain, one launch per pass covers a
+//      run of buckets.  16 bytes of traffic per record and pass instead of 24, and one staging round through shared
+//      memory instead of two.
+//   3. The max-merge reads the packed records (8 bytes) and writes the CSR by k-mer as merge.cuh does.
+//
+// With several GPUs pass 1 IS the exchange: the buckets are dealt to owner ranks as contiguous k-mer ranges and the MSD
+// pass stores each bucket straight into its owner's receive buffer (peer memory over NVLink), so a rank pays no extra
+// pass for the all-to-all and sorts 8 bits less afterwards (ipkgpu_stage1_scatter_packed).
+#pragma once
+#include "common.cuh"
+#include "radix_sort.cuh"
+#include "merge.cuh"
+
+namespace ipkgpu
+{
+    constexpr int PS_BUCKETS = 256;
+
+    /// bucket geometry of one segmented launch (kernel parameter, 2 KB)
+    struct ps_table
+    {
+        uint32_t start[PS_BUCKETS + 1];        // first record of every bucket in the packed array
+        uint32_t tile_first[PS_BUCKETS + 1];   // id of the first tile of every bucket of THIS launch (tiles cut at bucket boundaries)
+        uint32_t d0, d1;                       // buckets [d0, d1) take part
+    };
+
+    /// destinations of the MSD pass: bucket d goes to out[owner[d]] (this rank's buffer or a peer's, mapped through CUDA IPC)
+    struct ps_dest
+    {
+        uint64_t* out[RS_MAX_PEERS];
+        uint8_t owner[PS_BUCKETS];
+    };
+
+    inline void ps_fill_tiles(ps_table& T, uint32_t d0, uint32_t d1, uint32_t tile)
+    {
+        for (uint32_t d = 0; d <= PS_BUCKETS; ++d) T.tile_first[d] = 0;
+        uint32_t t = 0;
+        for (uint32_t d = d0; d < d1; ++d) { T.tile_first[d] = t; t += (T.start[d + 1] - T.start[d] + tile - 1) / tile; }
+        for (uint32_t d = d1; d <= PS_BUCKETS; ++d) T.tile_first[d] = t;
+        T.d0 = d0; T.d1 = d1;
+    }
+
+    /// bucket of a tile: the b in [d0, d1) with tile_first[b] <= tile < tile_first[b + 1]
+    __device__ __forceinline__ uint32_t ps_bucket_of_tile(const ps_table& T, uint32_t tile)
+    {
+        uint32_t lo = T.d0, hi = T.d1;
+        while (hi - lo > 1)
+        {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (T.tile_first[mid] <= tile) lo = mid; else hi = mid;
+        }
+        return lo;
+    }
+
+    template<int THREADS, int ITEMS> constexpr size_t ps_smem_bytes(bool digits) { return size_t(THREADS / 32) * RS_RADIX * 4 + 2 * RS_RADIX * 4 + 64 + size_t(THREADS) * ITEMS * (digits ? 9 : 8); }
+
+    // -----------------------------------------------------------------------------------------------------------------
+    // Ranking core shared by the two sweeps: the tile's items in (warp, round, lane) order carry a digit each; afterwards
+    // pos[i] = position of item i in the tile's digit-sorted order, dbase / goff as in rs_onesweep.
+    // -----------------------------------------------------------------------------------------------------------------
+    template<int THREADS, int ITEMS>
+    struct ps_smem_view
+    {
+        uint64_t* sk;                       // [TILE] staged records
+        uint32_t (*wh)[RS_RADIX];           // [WARPS][256]
+        uint32_t* dbase;                    // [256]
+        uint32_t* goff;                     // [256]
+        uint32_t* misc;                     // [16]
+        uint8_t* sd;                        // [TILE] staged digits (MSD pass only)
+        __device__ explicit ps_smem_view(unsigned char* raw)
+        {
+            constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
+            sk = reinterpret_cast<uint64_t*>(raw);
+            wh = reinterpret_cast<uint32_t (*)[RS_RADIX]>(sk + TILE);
+            dbase = &wh[0][0] + WARPS * RS_RADIX;
+            goff = dbase + RS_RADIX;
+            misc = goff + RS_RADIX;
+            sd = reinterpret_cast<uint8_t*>(misc + 16);
+        }
+    };
+
+    /// One pass over one tile.  MSD = true: (keys_in, vals_in) pairs -> packed records, digit = top byte of the composite key,
+    /// destination per digit from D, tiles are plain runs of THREADS * ITEMS pairs.  MSD = false: packed -> packed, digit =
+    /// byte `shift / 8` of the record, tiles cut at bucket boundaries (T), digit bases per bucket.
+    template<int THREADS, int ITEMS, bool MSD, int MINB>
+    __global__ void __launch_bounds__(THREADS, MINB) ps_sweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                              uint64_t* __restrict__ out, const uint32_t* __restrict__ digit_base, uint64_t n,
+                                                              uint32_t shift /* MSD: low_bits; else: bit of the record where the digit starts */,
+                                                              uint32_t base_stride /* LSD: words between two buckets' digit bases */,
+                                                              uint64_t* status, uint32_t* ticket, uint32_t epoch,
+                                                              const __grid_constant__ ps_table T, const __grid_constant__ ps_dest D)
+    {
+        constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
+        static_assert(THREADS >= RS_RADIX && THREADS % 32 == 0 && ITEMS % 4 == 0, "tile shape");
+        extern __shared__ __align__(16) unsigned char ps_smem[];
+        const ps_smem_view<THREADS, ITEMS> S(ps_smem);
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const unsigned full = 0xffffffffu;
+        if (tid == 0)
+        {
+            const uint32_t t = atomicAdd(ticket, 1u);
+            S.misc[15] = t;
+            if (!MSD) S.misc[14] = ps_bucket_of_tile(T, t);
+        }
+        for (int i = tid; i < WARPS * RS_RADIX; i += THREADS) (&S.wh[0][0])[i] = 0;
+        __syncthreads();
+        const uint32_t tile = S.misc[15];
+        uint64_t tile_base;
+        uint32_t tile_n;
+        bool first_of_chain;
+        const uint32_t* dbase_g = digit_base;
+        if (MSD)
+        {
+            tile_base = uint64_t(tile) * TILE;
+            tile_n = uint32_t(min(uint64_t(TILE), n - tile_base));
+            first_of_chain = tile == 0;
+        }
+        else
+        {
+            const uint32_t b = S.misc[14];
+            const uint32_t lt = tile - T.tile_first[b];
+            tile_base = uint64_t(T.start[b]) + uint64_t(lt) * TILE;
+            tile_n = uint32_t(min(uint64_t(TILE), uint64_t(T.start[b + 1]) - tile_base));
+            first_of_chain = lt == 0;
+            dbase_g = digit_base + size_t(b) * base_stride;
+        }
+
+        uint64_t rec[ITEMS];
+        uint32_t dpk[ITEMS / 4];            // the items' digits, four per word
+        uint32_t rkp[ITEMS / 2];            // their ranks among the warp's earlier items of the same digit, two per word
+#pragma unroll
+        for (int i = 0; i < ITEMS / 4; ++i) dpk[i] = 0;
+#pragma unroll
+        for (int i = 0; i < ITEMS / 2; ++i) rkp[i] = 0;
+        if (MSD)
+        {
+            const uint64_t low_mask = shift >= 64 ? ~0ull : ((1ull << shift) - 1);
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+            {
+                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                rec[i] = li < tile_n ? keys_in[tile_base + li] : 0ull;
+            }
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+            {
+                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                const uint32_t v = li < tile_n ? vals_in[tile_base + li] : 0u;
+                dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
+                rec[i] = ((rec[i] & low_mask) << 32) | v;
+            }
+        }
+        else
+        {
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i)
+            {
+                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                rec[i] = li < tile_n ? keys_in[tile_base + li] : 0ull;
+                dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+        {
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+            const bool valid = li < tile_n;
+            const uint32_t d = valid ? (dpk[i / 4] >> (8 * (i & 3))) & 0xffu : RS_RADIX;
+            const unsigned peers = __match_any_sync(full, d);
+            const int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (lane == leader && valid)
+            {
+                old = S.wh[warp][d];
+                S.wh[warp][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(full, old, leader);
+            rkp[i / 2] |= ((old + __popc(peers & ((1u << lane) - 1))) & 0xffffu) << (16 * (i & 1));
+            __syncwarp();
+        }
+        __syncthreads();
+        const bool is_digit = tid < RS_RADIX;
+        uint32_t cnt = 0;
+        if (is_digit)
+        {
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w)
+            {
+                const uint32_t t = S.wh[w][tid];
+                S.wh[w][tid] = cnt;
+                cnt += t;
+            }
+        }
+        uint64_t* my_status = status + uint64_t(tile) * RS_RADIX + (is_digit ? tid : 0);
+        if (is_digit)
+            *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, first_of_chain ? RS_FLAG_INCL : RS_FLAG_LOCAL, cnt);
+        const uint32_t inc = warp_incl_scan(cnt, lane);
+        if (is_digit && lane == 31) S.misc[warp] = inc;
+        __syncthreads();
+        if (warp == 0)
+        {
+            const uint32_t w = lane < 8 ? S.misc[lane] : 0;
+            const uint32_t winc = warp_incl_scan(w, lane);
+            if (lane < 8) S.misc[lane] = winc - w;
+        }
+        __syncthreads();
+        if (is_digit)
+        {
+            const uint32_t ex_local = S.misc[warp] + inc - cnt;
+            uint32_t before = 0;
+            if (!first_of_chain)
+            {
+                // the chain ends at the first tile of the bucket (MSD: of the launch), which published an inclusive word
+                const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
+                while (true)
+                {
+                    const uint64_t w = *p;
+                    if (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0) continue;
+                    before += uint32_t(w);
+                    if (((w >> 32) & 3) == RS_FLAG_INCL) break;
+                    p -= RS_RADIX;
+                }
+                *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
+            }
+            S.dbase[tid] = ex_local;
+            S.goff[tid] = dbase_g[tid] + before - ex_local;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+        {
+            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+            if (li < tile_n)
+            {
+                const uint32_t d = (dpk[i / 4] >> (8 * (i & 3))) & 0xffu;
+                const uint32_t pos = S.dbase[d] + S.wh[warp][d] + ((rkp[i / 2] >> (16 * (i & 1))) & 0xffffu);
+                S.sk[pos] = rec[i];
+                if (MSD) S.sd[pos] = uint8_t(d);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i)
+        {
+            const uint32_t q = uint32_t(i) * THREADS + tid;
+            if (q < tile_n)
+            {
+                const uint64_t r = S.sk[q];
+                if (MSD)
+                {
+                    const uint32_t d = S.sd[q];
+                    D.out[D.owner[d]][S.goff[d] + q] = r;            // a store over NVLink when the owner is a peer
+                }
+                else
+                {
+                    const uint32_t d = uint32_t(r >> shift) & 0xffu;
+                    out[S.goff[d] + q] = r;
+                }
+            }
+        }
+    }
+
+    /// Digit histograms of every LSD pass and bucket from ONE read of the packed records: hist[b][p][d] += ...
+    /// CTA c walks records [c * chunk, (c + 1) * chunk) of the launch's bucket range and flushes its shared counters
+    /// whenever it crosses a bucket boundary.
+    constexpr int PS_HIST_THREADS = 256;
+    constexpr int PS_HIST_ITEMS = 16;
+    __global__ void __launch_bounds__(PS_HIST_THREADS) ps_seg_hist(const uint64_t* __restrict__ recs, uint32_t n_passes, uint64_t chunk,
+                                                                  uint32_t* __restrict__ hist, const __grid_constant__ ps_table T)
+    {
+        extern __shared__ uint32_t ps_sh[];              // [2 copies][n_passes][256]
+        const uint32_t per_copy = n_passes * RS_RADIX;
+        uint32_t* mine = ps_sh + ((threadIdx.x >> 5) & 1) * per_copy;
+        const uint64_t lo = uint64_t(T.start[T.d0]) + uint64_t(blockIdx.x) * chunk;
+        const uint64_t hi = min(lo + chunk, uint64_t(T.start[T.d1]));
+        if (lo >= hi) return;
+        // bucket of the first record: largest b in [d0, d1) with start[b] <= lo
+        uint32_t b = T.d0;
+        {
+            uint32_t l = T.d0, h = T.d1;
+            while (h - l > 1) { const uint32_t m = (l + h) >> 1; if (uint64_t(T.start[m]) <= lo) l = m; else h = m; }
+            b = l;
+        }
+        uint64_t pos = lo;
+        while (pos < hi)
+        {
+            while (uint64_t(T.start[b + 1]) <= pos) ++b;         // skips empty buckets
+            const uint64_t seg_end = min(hi, uint64_t(T.start[b + 1]));
+            for (uint32_t i = threadIdx.x; i < 2 * per_copy; i += PS_HIST_THREADS) ps_sh[i] = 0;
+            __syncthreads();
+            for (uint64_t base = pos; base < seg_end; base += uint64_t(PS_HIST_THREADS) * PS_HIST_ITEMS)
+            {
+                uint64_t r[PS_HIST_ITEMS];
+#pragma unroll
+                for (int i = 0; i < PS_HIST_ITEMS; ++i)
+                {
+                    const uint64_t idx = base + uint64_t(i) * PS_HIST_THREADS + threadIdx.x;
+                    r[i] = idx < seg_end ? recs[idx] : 0;
+                }
+#pragma unroll
+                for (int i = 0; i < PS_HIST_ITEMS; ++i)
+                {
+                    const uint64_t idx = base + uint64_t(i) * PS_HIST_THREADS + threadIdx.x;
+                    if (idx < seg_end)
+                    {
+                        const uint32_t kk = uint32_t(r[i] >> 32);
+                        for (uint32_t p = 0; p < n_passes; ++p) atomicAdd(&mine[p * RS_RADIX + ((kk >> (8 * p)) & 0xffu)], 1u);
+                    }
+                }
+            }
+            __syncthreads();
+            uint32_t* g = hist + size_t(b) * per_copy;
+            for (uint32_t i = threadIdx.x; i < per_copy; i += PS_HIST_THREADS)
+            {
+                const uint32_t v = ps_sh[i] + ps_sh[per_copy + i];
+                if (v) atomicAdd(&g[i], v);
+            }
+            __syncthreads();
+            pos = seg_end;
+        }
+    }
+
+    /// in place: hist[b][p][0..256) -> start[b] + exclusive scan; grid = (n_passes, buckets of the launch)
+    __global__ void __launch_bounds__(RS_RADIX) ps_seg_scan(uint32_t* __restrict__ hist, uint32_t n_passes, const __grid_constant__ ps_table T)
+    {
+        __shared__ uint32_t s_warp[9];
+        const uint32_t b = T.d0 + blockIdx.y;
+        uint32_t* h = hist + (size_t(b) * n_passes + blockIdx.x) * RS_RADIX;
+        const uint32_t v = h[threadIdx.x];
+        h[threadIdx.x] = T.start[b] + block_excl_scan_256(v, s_warp, nullptr);
+    }
+
+    // -----------------------------------------------------------------------------------------------------------------
+    // max-merge + CSR by k-mer over sorted PACKED records (see merge.cuh for the semantics); tiles cut at bucket boundaries
+    // -----------------------------------------------------------------------------------------------------------------
+    constexpr int MP_THREADS = 256;
+    constexpr int MP_ITEMS = 12;
+    constexpr int MP_TILE = MP_THREADS * MP_ITEMS;
+    constexpr int MP_WARPS = MP_THREADS / 32;
+
+    struct mergep_args
+    {
+        const uint64_t* recs;              // packed, sorted inside every bucket
+        uint32_t group_bits;               // width of the group field inside the packed key
+        uint32_t kmer_low_bits;            // k-mer bits below the bucket byte (key_bits - 8)
+        uint32_t group_add;
+        const uint32_t* group_branch;
+        uint64_t* kmer_keys; uint64_t* kmer_offs; uint32_t* ent_branch; float* ent_score;
+        uint64_t* status; uint32_t* ticket; unsigned long long* totals;
+        uint64_t offs_add;
+        uint32_t epoch, n_tiles;
+    };
+
+    __global__ void __launch_bounds__(MP_THREADS, 4) mg_merge_packed(const __grid_constant__ mergep_args A, const __grid_constant__ ps_table T)
+    {
+        __shared__ uint64_t sk[MP_TILE + 1];            // sk[0] = the record before the tile (same bucket)
+        __shared__ uint32_t s_cnt[2][MP_ITEMS][MP_WARPS];
+        __shared__ uint32_t s_tile, s_bucket, s_before[2];
+
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const unsigned full = 0xffffffffu;
+        if (tid == 0)
+        {
+            const uint32_t t = atomicAdd(A.ticket, 1u);
+            s_tile = t;
+            s_bucket = ps_bucket_of_tile(T, t);
+        }
+        __syncthreads();
+        const uint32_t tile = s_tile, bucket = s_bucket;
+        const uint32_t lt = tile - T.tile_first[bucket];
+        const uint64_t base = uint64_t(T.start[bucket]) + uint64_t(lt) * MP_TILE, bucket_end = T.start[bucket + 1];
+        const uint32_t tile_n = uint32_t(min(uint64_t(MP_TILE), bucket_end - base));
+        const bool first_in_bucket = lt == 0;
+        {
+            const uint64_t* __restrict__ g = A.recs + base;
+            uint64_t r[MP_ITEMS];
+#pragma unroll
+            for (int j = 0; j < MP_ITEMS; ++j)
+            {
+                const uint32_t q = uint32_t(j) * MP_THREADS + tid;
+                r[j] = q < tile_n ? __ldg(g + q) : 0ull;
+            }
+#pragma unroll
+            for (int j = 0; j < MP_ITEMS; ++j)
+            {
+                const uint32_t q = uint32_t(j) * MP_THREADS + tid;
+                if (q < tile_n) sk[q + 1] = r[j];
+            }
+            if (tid == 0) sk[0] = first_in_bucket ? 0ull : A.recs[base - 1];
+        }
+        __syncthreads();
+        const uint32_t kshift = 32 + A.group_bits;
+        unsigned hb[MP_ITEMS], kb[MP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < MP_ITEMS; ++j)
+        {
+            const uint32_t q = uint32_t(j) * MP_THREADS + tid;
+            bool head = false, khead = false;
+            if (q < tile_n)
+            {
+                const uint64_t cur = sk[q + 1], prev = sk[q];
+                const bool very_first = q == 0 && first_in_bucket;
+                head = (cur >> 32) != (prev >> 32) || very_first;
+                khead = (cur >> kshift) != (prev >> kshift) || very_first;
+            }
+            hb[j] = __ballot_sync(full, head);
+            kb[j] = __ballot_sync(full, khead);
+            if (lane == 0) { s_cnt[0][j][warp] = __popc(hb[j]); s_cnt[1][j][warp] = __popc(kb[j]); }
+        }
+        __syncthreads();
+        uint32_t total = 0;
+        uint64_t* mine = A.status + uint64_t(tile) * 2 + (warp < 2 ? warp : 0);
+        if (warp < 2)
+        {
+            uint32_t* c = &s_cnt[warp][0][0];
+            constexpr int N = MP_ITEMS * MP_WARPS, PER = (N + 31) / 32;
+            uint32_t v[PER], sum = 0;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; v[i] = e < N ? c[e] : 0; sum += v[i]; }
+            const uint32_t inc = warp_incl_scan(sum, lane);
+            total = __shfl_sync(full, inc, 31);
+            uint32_t run = inc - sum;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) { const int e = lane * PER + i; if (e < N) c[e] = run; run += v[i]; }
+            if (lane == 0) *reinterpret_cast<volatile uint64_t*>(mine) = rs_status(A.epoch, tile == 0 ? RS_FLAG_INCL : RS_FLAG_LOCAL, total);
+        }
+        // maximum score of every run that starts in this tile (a run may leave the tile, never the bucket)
+        float best[MP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < MP_ITEMS; ++j)
+        {
+            best[j] = 0.0f;
+            if (!((hb[j] >> lane) & 1)) continue;
+            const uint32_t q = uint32_t(j) * MP_THREADS + tid;
+            const uint64_t cur = sk[q + 1];
+            const uint32_t ck = uint32_t(cur >> 32);
+            float m = __uint_as_float(uint32_t(cur));
+            uint32_t r = q + 1;
+            for (; r < tile_n; ++r)
+            {
+                const uint64_t o = sk[r + 1];
+                if (uint32_t(o >> 32) != ck) break;
+                const float v = __uint_as_float(uint32_t(o));
+                if (m < v) m = v;                                   // branch_group.cpp:92 `it->second < kmer.score`
+            }
+            if (r == tile_n)
+                for (uint64_t g = base + tile_n; g < bucket_end; ++g)
+                {
+                    const uint64_t o = A.recs[g];
+                    if (uint32_t(o >> 32) != ck) break;
+                    const float v = __uint_as_float(uint32_t(o));
+                    if (m < v) m = v;
+                }
+            best[j] = m;
+        }
+        if (warp < 2)
+        {
+            uint32_t before = 0;
+            if (tile > 0)
+            {
+                before = warp_look_back(A.status + warp, tile, 2, A.epoch, lane);
+                if (lane == 0) *reinterpret_cast<volatile uint64_t*>(mine) = rs_status(A.epoch, RS_FLAG_INCL, before + total);
+            }
+            if (lane == 0)
+            {
+                s_before[warp] = before;
+                if (tile + 1 == A.n_tiles) A.totals[warp] = (unsigned long long)(before) + total;
+            }
+        }
+        __syncthreads();
+        const uint32_t group_mask = A.group_bits >= 32 ? ~0u : ((1u << A.group_bits) - 1);
+        const uint64_t kmer_top = uint64_t(bucket) << A.kmer_low_bits;
+        const uint32_t lt_mask = (1u << lane) - 1;
+#pragma unroll
+        for (int j = 0; j < MP_ITEMS; ++j)
+        {
+            if (!((hb[j] >> lane) & 1)) continue;
+            const uint32_t q = uint32_t(j) * MP_THREADS + tid;
+            const uint32_t ck = uint32_t(sk[q + 1] >> 32);
+            const uint64_t r1 = uint64_t(s_before[0]) + s_cnt[0][j][warp] + __popc(hb[j] & lt_mask);
+            const uint32_t group = (ck & group_mask) + A.group_add;
+            A.ent_branch[r1] = A.group_branch[group];
+            A.ent_score[r1] = best[j];
+            if ((kb[j] >> lane) & 1)
+            {
+                const uint64_t r2 = uint64_t(s_before[1]) + s_cnt[1][j][warp] + __popc(kb[j] & lt_mask);
+                A.kmer_keys[r2] = kmer_top | uint64_t(A.group_bits >= 32 ? 0u : (ck >> A.group_bits));
+                A.kmer_offs[r2] = r1 + A.offs_add;
+            }
+        }
+    }
+
+    // -----------------------------------------------------------------------------------------------------------------
+    // host side
+    // -----------------------------------------------------------------------------------------------------------------
+    constexpr int PS_THREADS = 384, PS_ITEMS = 16, PS_TILE = PS_THREADS * PS_ITEMS;
+
+    /// true when the packed path applies to composite keys of key_bits + group_bits
+    inline bool ps_eligible(uint32_t key_bits, uint32_t group_bits, uint64_t n)
+    {
+        static const bool off = getenv("IPKGPU_PACKED") && atoi(getenv("IPKGPU_PACKED")) == 0;
+        return !off && n > 0 && n <= 0xffffffffull && key_bits >= 8 && key_bits + group_bits - 8 <= 32;
+    }
+
+    /// status words + tickets for launches of up to n_tiles tiles (shares ctx->rs_status with radix_sort.cuh)
+    inline void ps_reserve_status(ipkgpu_ctx* ctx, uint64_t n_tiles)
+    {
+        const size_t want = n_tiles * RS_RADIX * 8;
+        if (want > ctx->rs_status.cap)
+        {
+            ctx->reserve(ctx->rs_status, want);
+            IPK_CUDA(cudaMemsetAsync(ctx->rs_status.p, 0, ctx->rs_status.cap, ctx->stream));
+            ctx->rs_epoch = 0;
+        }
+    }
+
+    /// top-byte histogram of the composite keys -> hist[0..256) (device, in ctx->hist) ; not yet scanned
+    inline void ps_top_histogram(ipkgpu_ctx* ctx, const uint64_t* keys, uint64_t n, uint32_t low_bits)
+    {
+        ctx->reserve(ctx->hist, (RS_MAX_PASSES * RS_RADIX + 16) * 4);
+        IPK_CUDA(cudaMemsetAsync(ctx->hist.p, 0, (RS_MAX_PASSES * RS_RADIX + 16) * 4, ctx->stream));
+        if (n == 0) return;
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, RS_HIST_THREADS * RS_HIST_ITEMS), uint64_t(ctx->num_sms) * 8));
+        IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_bits<<<hgrid, RS_HIST_THREADS, 2 * RS_RADIX * 4, ctx->stream>>>(keys, n, low_bits, 8, 1, ctx->hist.as<uint32_t>()));
+    }
+
+    /// MSD pass: n (key, score) pairs -> packed records in D's buffers; d_base[256] (device) = where this rank's records of
+    /// each bucket start inside the owner's buffer.  Uses tickets[15] of ctx->hist.
+    inline void ps_msd_pack(ipkgpu_ctx* ctx, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t low_bits,
+                            const uint32_t* d_base, const ps_dest& D, bool peers)
+    {
+        if (n == 0) return;
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_TILE));
+        ps_reserve_status(ctx, n_tiles);
+        uint32_t* ticket = ctx->hist.as<uint32_t>() + RS_MAX_PASSES * RS_RADIX + 15;
+        IPK_CUDA(cudaMemsetAsync(ticket, 0, 4, ctx->stream));
+        ps_table none;
+        memset(&none, 0, sizeof none);
+        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(true);
+        auto kern = ps_sweep<PS_THREADS, PS_ITEMS, true, 2>;
+        IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        IPK_LAUNCH(ctx, peers ? "ps_msd_scatter_peers" : "ps_msd_pack", n * 20 + uint64_t(n_tiles) * RS_RADIX * 8,
+                   kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(keys, vals, nullptr, d_base, n, low_bits, 0, ctx->rs_status.as<uint64_t>(), ticket,
+                                                                    rs_next_epoch(ctx), none, D));
+    }
+
+    /// LSD passes on the packed records of buckets [d0, d1) (T.start filled by the caller): ping-pongs between p0 and p1,
+    /// returns true when the sorted records end up in p1.  ctx->ps_hist holds the per-bucket digit bases.
+    inline bool ps_sort_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint32_t d0, uint32_t d1, uint32_t low_bits)
+    {
+        const uint32_t passes = div_up<uint32_t>(low_bits, 8);
+        const uint64_t n = uint64_t(T.start[d1]) - T.start[d0];
+        if (n == 0 || passes == 0) return false;
+        ps_fill_tiles(T, d0, d1, PS_TILE);
+        const uint32_t n_tiles = T.tile_first[d1];
+        ps_reserve_status(ctx, n_tiles);
+        const size_t hist_words = size_t(PS_BUCKETS) * passes * RS_RADIX;
+        ctx->reserve(ctx->ps_hist, hist_words * 4 + 64);
+        uint32_t* hist = ctx->ps_hist.as<uint32_t>();
+        uint32_t* tickets = hist + hist_words;
+        IPK_CUDA(cudaMemsetAsync(hist + size_t(d0) * passes * RS_RADIX, 0, size_t(d1 - d0) * passes * RS_RADIX * 4, ctx->stream));
+        IPK_CUDA(cudaMemsetAsync(tickets, 0, 64, ctx->stream));
+        const uint32_t hgrid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, PS_HIST_THREADS * PS_HIST_ITEMS), uint64_t(ctx->num_sms) * 8));
+        uint64_t chunk = div_up<uint64_t>(n, hgrid);
+        chunk = div_up<uint64_t>(chunk, PS_HIST_THREADS * PS_HIST_ITEMS) * (PS_HIST_THREADS * PS_HIST_ITEMS);
+        IPK_LAUNCH(ctx, "ps_seg_hist", n * 8,
+                   ps_seg_hist<<<uint32_t(div_up<uint64_t>(n, chunk)), PS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(p0, passes, chunk, hist, T));
+        IPK_LAUNCH(ctx, "ps_seg_scan", uint64_t(d1 - d0) * passes * 2048,
+                   ps_seg_scan<<<dim3(passes, d1 - d0), RS_RADIX, 0, ctx->stream>>>(hist, passes, T));
+        ps_dest none;
+        memset(&none, 0, sizeof none);
+        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(false);
+        auto kern = ps_sweep<PS_THREADS, PS_ITEMS, false, 2>;
+        IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        bool in1 = false;
+        for (uint32_t p = 0; p < passes; ++p)
+        {
+            IPK_LAUNCH(ctx, "ps_sweep", n * 16 + uint64_t(n_tiles) * RS_RADIX * 8,
+                       kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(in1 ? p1 : p0, nullptr, in1 ? p0 : p1, hist + size_t(p) * RS_RADIX, n, 32 + 8 * p,
+                                                                        passes * RS_RADIX, ctx->rs_status.as<uint64_t>(), tickets + p, rs_next_epoch(ctx), T, none));
+            in1 = !in1;
+        }
+        return in1;
+    }
+}
