@@ -135,6 +135,23 @@ int  ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name
 int  ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out);
 void ipkgpu_free_result(ipkgpu_ctx* ctx, ipkgpu_result* res);
 
+/* Order-independent digest of the database the last ipkgpu_build / ipkgpu_stage2 of ctx produced (it is still resident
+ * on the device whatever result mode was asked for).  No reference counterpart -- the reference compares databases entry by
+ * entry (tools/src/diff.cpp:129-295); the digest does the same for builds that never share a memory: sums (mod 2^64) and
+ * xors of mix64 over every (k-mer, branch, score bits), every (k-mer, entry count) and every (k-mer, filter-value bits).
+ * The digests of the key shards of a multi-GPU build add / xor up to the digest of the single-GPU database.
+ * n_boundary_above: entries with log_threshold < score < log_threshold + band -- the emitted side of the boundary cases
+ * BASELINE.json names (|score - threshold| < 1e-5); the full two-sided list is ipkgpu_boundary_list. */
+typedef struct ipkgpu_digest
+{
+    uint64_t entries_sum, entries_xor;   /* over (key, branch, score bits) */
+    uint64_t kmers_sum, kmers_xor;       /* over (key, number of entries) */
+    uint64_t fv_sum, fv_xor;             /* over (key, filter-value bits) */
+    uint64_t n_boundary_above;
+    uint64_t n_kmers, n_entries;
+} ipkgpu_digest;
+int  ipkgpu_result_digest(ipkgpu_ctx* ctx, float log_threshold, float band, ipkgpu_digest* out);
+
 /* ---- stage-level entry points (parity tests; multi-GPU build, where the caller runs the exchange) ---------------- */
 
 /* matrix::preprocess (window.cpp:16-27) for every node: B_out[n_nodes][W+1] (host). */

@@ -88,6 +88,14 @@ class Result(C.Structure):
     ]
 
 
+class Digest(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("entries_sum", "entries_xor", "kmers_sum", "kmers_xor", "fv_sum", "fv_xor",
+                                           "n_boundary_above", "n_kmers", "n_entries")]
+
+    def as_dict(self) -> dict:
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
 _lib = None
 
 
@@ -123,6 +131,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_kernel_profile_get.restype = C.c_int
     lib.ipkgpu_build.argtypes = [C.c_void_p, P(Input), C.c_int, P(Result)]
     lib.ipkgpu_build.restype = C.c_int
+    lib.ipkgpu_result_digest.argtypes = [C.c_void_p, C.c_float, C.c_float, P(Digest)]
+    lib.ipkgpu_result_digest.restype = C.c_int
     lib.ipkgpu_free_result.argtypes = [C.c_void_p, P(Result)]
     lib.ipkgpu_free_result.restype = None
     lib.ipkgpu_best_prefix.argtypes = [C.c_void_p, P(Input), C.c_void_p]
@@ -314,6 +324,12 @@ class Context:
         mode = (int(result_on_device) & 7) | (2 if indexed else 0) | (4 if branch16 else 0)
         self._check(self._lib.ipkgpu_build(self._h, C.byref(inp), mode, C.byref(res)))
         return res
+
+    def result_digest(self, log_threshold: float = 0.0, band: float = 1e-5) -> dict:
+        """order-independent digest of the database the last build / stage2 of this context left on the device"""
+        d = Digest()
+        self._check(self._lib.ipkgpu_result_digest(self._h, log_threshold, band, C.byref(d)))
+        return d.as_dict()
 
     @staticmethod
     def to_db(res: Result) -> PhyloKmerDB:

@@ -102,6 +102,8 @@ struct ipkgpu_ctx
     std::vector<ipc_mapping> ipc_open;  // peers' receive buffers mapped into this process
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;
+    uint64_t res_n_kmers = 0, res_n_entries = 0;      // the CSR the last build / stage 2 left in kmer_keys / kmer_offs / ent_* / fv
+    bool res_valid = false;
     uint64_t hint_side = 0;            // ... and of its side stream
     uint64_t hint_emitted = 0;         // emitted volume of the previous build: sizes the first enumeration attempt
     uint64_t hint_kmers = 0, hint_kmers_records = 0;   // k-mers of the previous result and the records it was merged from (parts_eligible)

@@ -1,0 +1,74 @@
+// digest.cuh -- order-independent digest of the database a build left on the device, sm_100a.
+//
+// No reference counterpart: the reference compares databases entry by entry with tools/src/diff.cpp:129-295.  A digest is
+// what lets two builds that never meet in one memory (device-resident vs host-bound, 1 GPU vs the shards of G processes)
+// be compared entry for entry: sums and xors of a 64-bit mix of every (k-mer, branch, score bits), every (k-mer, entry
+// count) and every (k-mer, filter value bits).  Sums / xors over shards add / xor up to the digest of the whole database.
+// tests/parity.py holds the same definition in numpy.
+#pragma once
+#include "common.cuh"
+
+namespace ipkgpu
+{
+    __host__ __device__ __forceinline__ uint64_t dg_mix64(uint64_t x)
+    {
+        x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+        x ^= x >> 27; x *= 0x94d049bb133111ebull;
+        x ^= x >> 31;
+        return x;
+    }
+    __host__ __device__ __forceinline__ uint64_t dg_key(uint64_t kmer) { return dg_mix64(kmer + 0x9e3779b97f4a7c15ull); }
+    __host__ __device__ __forceinline__ uint64_t dg_entry(uint64_t hk, uint32_t branch, uint32_t score_bits) { return dg_mix64(hk ^ (uint64_t(branch) << 32 | score_bits)); }
+    __host__ __device__ __forceinline__ uint64_t dg_count(uint64_t hk, uint64_t count) { return dg_mix64(hk ^ (count + 0x632be59bd9b4e019ull)); }
+    __host__ __device__ __forceinline__ uint64_t dg_fv(uint64_t hk, uint32_t fv_bits) { return dg_mix64(hk ^ (uint64_t(fv_bits) | 0x5bd1e99500000000ull)); }
+
+    constexpr int DG_THREADS = 256;
+    constexpr int DG_LANES = 8;             // lanes that share one k-mer
+
+    /// acc[0..5] = entries sum / xor, k-mers sum / xor, filter values sum / xor; acc[6] = entries whose score lies
+    /// within `band` above log_threshold (the emitted side of the north star's boundary cases)
+    __global__ void __launch_bounds__(DG_THREADS) k7_digest(const uint64_t* __restrict__ kmer_keys, const uint64_t* __restrict__ kmer_offs,
+                                                            const uint32_t* __restrict__ ent_branch, const float* __restrict__ ent_score,
+                                                            const float* __restrict__ fv, uint64_t n_kmers, float log_threshold, float band,
+                                                            unsigned long long* __restrict__ acc)
+    {
+        uint64_t es = 0, ex = 0, ks = 0, kx = 0, fs = 0, fx = 0, nb = 0;
+        const int gl = threadIdx.x & (DG_LANES - 1);
+        const float hi = __fadd_rn(log_threshold, band);
+        for (uint64_t q = (blockIdx.x * uint64_t(DG_THREADS) + threadIdx.x) / DG_LANES; q < n_kmers; q += uint64_t(gridDim.x) * (DG_THREADS / DG_LANES))
+        {
+            const uint64_t hk = dg_key(kmer_keys[q]);
+            const uint64_t a = kmer_offs[q], b = kmer_offs[q + 1];
+            if (gl == 0)
+            {
+                const uint64_t h = dg_count(hk, b - a);
+                ks += h; kx ^= h;
+                const uint64_t g = dg_fv(hk, __float_as_uint(fv[q]));
+                fs += g; fx ^= g;
+            }
+            for (uint64_t i = a + gl; i < b; i += DG_LANES)
+            {
+                const float s = ent_score[i];
+                const uint64_t h = dg_entry(hk, ent_branch[i], __float_as_uint(s));
+                es += h; ex ^= h;
+                nb += s < hi ? 1 : 0;
+            }
+        }
+        uint64_t v[7] = { es, ex, ks, kx, fs, fx, nb };
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1)
+#pragma unroll
+            for (int j = 0; j < 7; ++j)
+            {
+                const uint64_t t = __shfl_xor_sync(0xffffffffu, v[j], o);
+                if (j == 1 || j == 3 || j == 5) v[j] ^= t; else v[j] += t;
+            }
+        if ((threadIdx.x & 31) == 0)
+        {
+            atomicAdd(acc + 0, (unsigned long long)v[0]); atomicXor(acc + 1, (unsigned long long)v[1]);
+            atomicAdd(acc + 2, (unsigned long long)v[2]); atomicXor(acc + 3, (unsigned long long)v[3]);
+            atomicAdd(acc + 4, (unsigned long long)v[4]); atomicXor(acc + 5, (unsigned long long)v[5]);
+            atomicAdd(acc + 6, (unsigned long long)v[6]);
+        }
+    }
+}

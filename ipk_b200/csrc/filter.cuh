@@ -202,13 +202,15 @@ namespace ipkgpu
 
     /// filter.cpp:137-144 with libstdc++'s std::default_random_engine (minstd_rand0: x <- 16807 x mod 2^31-1, seed 42) and
     /// std::uniform_real_distribution<double>(0,1) (generate_canonical: two draws, (g1 + g2*R) / R^2, R = 2^31-2).
-    /// The i-th k-mer IN ASCENDING KEY ORDER takes draws 2i+1 and 2i+2 (the reference draws in hash-map iteration
-    /// order, which is unknowable here: parity unpinned).  The LCG is jumped ahead by modular exponentiation.
-    __global__ void k4_random(uint64_t n_kmers, float* __restrict__ fv)
+    /// The reference draws in hash-map iteration order, which is unknowable here (parity unpinned); the canonical order of
+    /// this repo is a function of the k-mer alone, so that key shards on several GPUs draw what one GPU draws: the k-mer
+    /// with key K takes draws 2e+1 and 2e+2 of the stream, e = K mod (2^31-2) (the period).  The LCG is jumped ahead by
+    /// modular exponentiation.
+    __global__ void k4_random(uint64_t n_kmers, const uint64_t* __restrict__ kmer_keys, float* __restrict__ fv)
     {
         const uint64_t q = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
         if (q >= n_kmers) return;
-        uint64_t e = 2 * q + 1, base = 16807, acc = 1;
+        uint64_t e = 2 * (kmer_keys[q] % 2147483646ull) + 1, base = 16807, acc = 1;
         while (e)
         {
             if (e & 1) acc = mulmod31(acc, base);

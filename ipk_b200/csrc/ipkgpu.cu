@@ -12,6 +12,7 @@
 #include "merge.cuh"
 #include "packed_sort.cuh"
 #include "filter.cuh"
+#include "digest.cuh"
 
 #include <cmath>
 #include <numeric>
@@ -757,6 +758,7 @@ namespace
                           bool want_csr, ipkgpu_stats* st, stage_timer& tm, bool raw = false, int result_mode = 0)
     {
         stage1_out o;
+        ctx->res_valid = false;
         o.n_groups = uint32_t(T.group_branch.size());
         const uint32_t key_bits = in->k * in->bits;
         if (key_bits + group_bits > 64) fail(IPKGPU_EINVAL, "k*bits + group bits = %u exceeds 64", key_bits + group_bits);
@@ -1062,7 +1064,7 @@ namespace
             }
             else
             {
-                IPK_LAUNCH(ctx, "k4_random", n_kmers * 4, k4_random<<<grid, 256, 0, ctx->stream>>>(n_kmers, ctx->fv.as<float>()));
+                IPK_LAUNCH(ctx, "k4_random", n_kmers * 12, k4_random<<<grid, 256, 0, ctx->stream>>>(n_kmers, ctx->kmer_keys.as<uint64_t>(), ctx->fv.as<float>()));
             }
             e1 = tm.mark();
             // K5: stable sort on the 32-bit order-preserving image of fv; k-mers are in ascending key order, so ties keep it
@@ -1144,6 +1146,7 @@ namespace
         st.ms_d2h = tm.ms(e2, e3);
         st.n_kmers = n_kmers;
         st.n_entries = n_entries;
+        ctx->res_n_kmers = n_kmers; ctx->res_n_entries = n_entries; ctx->res_valid = true;
     }
 
     /// Stage 2 on unique records (composite keys with the GLOBAL group field): regroup by k-mer -> CSR -> finish.
@@ -1151,6 +1154,7 @@ namespace
     void run_stage2(ipkgpu_ctx* ctx, uint64_t* keys, float* scores, uint64_t n, bool group_ordered, const stage2_params& sp,
                     int result_on_device, ipkgpu_result* out, stage_timer& tm)
     {
+        ctx->res_valid = false;
         const size_t e0 = tm.mark();
         const uint64_t* sk = keys;
         const float* sv = scores;
@@ -1409,6 +1413,30 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         st.ms_total = tm.ms(t0, t1);
         st.kernel_launches = ctx->launches;
         st.n_tiles = ctx->last_tiles; st.n_deferred_tiles = ctx->last_deferred_tiles;
+    });
+}
+
+int ipkgpu_result_digest(ipkgpu_ctx* ctx, float log_threshold, float band, ipkgpu_digest* out)
+{
+    return guarded(ctx, [&] {
+        if (!out) fail(IPKGPU_EINVAL, "digest is null");
+        if (!ctx->res_valid) fail(IPKGPU_EINVAL, "no database on this context: call ipkgpu_build / ipkgpu_stage2 first");
+        memset(out, 0, sizeof *out);
+        out->n_kmers = ctx->res_n_kmers; out->n_entries = ctx->res_n_entries;
+        if (ctx->res_n_kmers == 0) return;
+        ctx->reserve(ctx->counters, 128);
+        unsigned long long* acc = ctx->counters.as<unsigned long long>() + 8;
+        IPK_CUDA(cudaMemsetAsync(acc, 0, 56, ctx->stream));
+        const uint64_t groups = div_up<uint64_t>(ctx->res_n_kmers * DG_LANES, DG_THREADS);
+        const uint32_t grid = uint32_t(std::min<uint64_t>(groups, uint64_t(ctx->num_sms) * 32));
+        IPK_LAUNCH(ctx, "k7_digest", ctx->res_n_kmers * 20 + ctx->res_n_entries * 8,
+                   k7_digest<<<grid, DG_THREADS, 0, ctx->stream>>>(ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->ent_branch.as<uint32_t>(),
+                                                                   ctx->ent_score.as<float>(), ctx->fv.as<float>(), ctx->res_n_kmers, log_threshold, band, acc));
+        uint64_t h[7];
+        IPK_CUDA(cudaMemcpyAsync(h, acc, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        out->entries_sum = h[0]; out->entries_xor = h[1]; out->kmers_sum = h[2]; out->kmers_xor = h[3];
+        out->fv_sum = h[4]; out->fv_xor = h[5]; out->n_boundary_above = h[6];
     });
 }
 

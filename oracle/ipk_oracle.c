@@ -267,16 +267,18 @@ float ipko_mif0(const float* log_scores, size_t n, uint32_t total_num_groups, fl
 /* random_filter, filter.cpp:133-146: std::default_random_engine(42) (libstdc++: minstd_rand0, x <- 16807 x mod 2^31-1)
  * feeding std::uniform_real_distribution<double>(0,1) (libstdc++ generate_canonical<double,53>: two draws,
  * ((g1-1) + (g2-1)*R) / R^2 with R = 2^31-2, result 1.0 mapped to nextafter(1,0)), cast to float.
- * Draw order: the reference iterates its hash map (unknowable, PARITY UNPINNED); here i-th k-mer in ascending key. */
-void ipko_random_fv(size_t n, float* fv)
+ * Draw order: the reference iterates its hash map (unknowable, PARITY UNPINNED); canonical here: the k-mer with key K takes
+ * draws 2e+1 and 2e+2 of the stream, e = K mod (2^31-2) -- a function of the k-mer alone, so key shards agree with the whole. */
+static uint64_t mulmod31(uint64_t a, uint64_t b) { return (a * b) % 2147483647ull; }
+void ipko_random_fv(size_t n, const uint64_t* keys, float* fv)
 {
-    uint64_t x = 42;
     const double R = 2147483646.0;
     for (size_t i = 0; i < n; ++i)
     {
-        x = (x * 16807ull) % 2147483647ull; const double g1 = (double)(x - 1);
-        x = (x * 16807ull) % 2147483647ull; const double g2 = (double)(x - 1);
-        double r = (g1 + g2 * R) / (R * R);
+        uint64_t e = 2 * (keys[i] % 2147483646ull) + 1, base = 16807, acc = 1;
+        for (; e; e >>= 1) { if (e & 1) acc = mulmod31(acc, base); base = mulmod31(base, base); }
+        const uint64_t x1 = mulmod31(42, acc), x2 = mulmod31(x1, 16807);
+        double r = ((double)(x1 - 1) + (double)(x2 - 1) * R) / (R * R);
         if (r >= 1.0) r = nextafter(1.0, 0.0);
         fv[i] = (float)r;
     }
@@ -383,7 +385,14 @@ ipko_db* ipko_build(const float* logp, const uint32_t* node_branch, uint32_t n_n
     start[n_kmers] = n_entries;
     ord_t* ord = (ord_t*)malloc((n_kmers ? n_kmers : 1) * sizeof(ord_t));
     float* rnd = NULL;
-    if (filter != 0) { rnd = (float*)malloc((n_kmers ? n_kmers : 1) * sizeof(float)); ipko_random_fv(n_kmers, rnd); }
+    if (filter != 0)
+    {
+        rnd = (float*)malloc((n_kmers ? n_kmers : 1) * sizeof(float));
+        uint64_t* ks = (uint64_t*)malloc((n_kmers ? n_kmers : 1) * sizeof(uint64_t));
+        for (size_t q = 0; q < n_kmers; ++q) ks[q] = recs[start[q]].key;
+        ipko_random_fv(n_kmers, ks, rnd);
+        free(ks);
+    }
 #ifdef _OPENMP
 #pragma omp parallel num_threads(threads > 0 ? threads : 1)
 #endif

@@ -203,14 +203,18 @@ extern "C"
         else
         {
             // random_filter (filter.cpp:133-146).  The reference draws in hash-map iteration order, which is
-            // unknowable without i2l::hash_map: PARITY UNPINNED.  This repo's canonical order is key-ascending.
-            std::vector<key_type> ks;
-            ks.reserve(db.size());
-            for (const auto& kv : db) ks.push_back(kv.first);
-            std::sort(ks.begin(), ks.end());
-            std::default_random_engine generator(42);
-            std::uniform_real_distribution<double> distribution(0, 1);
-            for (auto key : ks) order.push_back({ key, (float)distribution(generator) });
+            // unknowable without i2l::hash_map: PARITY UNPINNED.  This repo's canonical draw is a function of the k-mer:
+            // key K takes draws 2e+1, 2e+2 of std::default_random_engine(42), e = K mod (2^31-2); the engine is jumped
+            // there (x <- 42 * 16807^(2e) mod 2^31-1) and std::uniform_real_distribution does the rest.
+            for (const auto& kv : db)
+            {
+                const uint64_t M = 2147483647ull;
+                uint64_t e = 2 * (uint64_t(kv.first) % (M - 1)), base = 16807, acc = 42;
+                for (; e; e >>= 1) { if (e & 1) acc = acc * base % M; base = base * base % M; }
+                std::default_random_engine generator(static_cast<std::default_random_engine::result_type>(acc));
+                std::uniform_real_distribution<double> distribution(0, 1);
+                order.push_back({ kv.first, (float)distribution(generator) });
+            }
         }
         // db_builder.cpp:284 std::sort(kmer_order) -- tie order unspecified there; canonical here: key ascending
         std::sort(order.begin(), order.end(), [](const kmer_fv& a, const kmer_fv& b) {

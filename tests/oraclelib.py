@@ -62,7 +62,7 @@ def port() -> C.CDLL:
             f.restype = C.c_int64
         lib.ipko_mif0.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_float]
         lib.ipko_mif0.restype = C.c_float
-        lib.ipko_random_fv.argtypes = [C.c_size_t, C.c_void_p]
+        lib.ipko_random_fv.argtypes = [C.c_size_t, C.c_void_p, C.c_void_p]
         lib.ipko_random_fv.restype = None
         lib.ipko_build.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                    C.c_float, C.c_float, C.c_uint32, C.c_int, C.c_int]
@@ -144,9 +144,11 @@ def mif0(log_scores, total_num_groups: int, threshold: float) -> float:
     return float(port().ipko_mif0(s.ctypes.data, s.shape[0], total_num_groups, threshold))
 
 
-def random_fv(n: int) -> np.ndarray:
-    fv = np.empty(n, np.float32)
-    port().ipko_random_fv(n, fv.ctypes.data)
+def random_fv(keys) -> np.ndarray:
+    """the canonical random filter value of every k-mer key (a function of the key alone)"""
+    keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    fv = np.empty(len(keys), np.float32)
+    port().ipko_random_fv(len(keys), keys.ctypes.data, fv.ctypes.data)
     return fv
 
 

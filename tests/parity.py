@@ -42,3 +42,27 @@ def assert_db_equal(got, want, check_fv=True, exact_fv=False):
         assert np.all(fv[1:] >= fv[:-1]), "k-mers are not in ascending filter-value order"
         tie = fv[1:] == fv[:-1]
         assert np.all(got.keys[1:][tie] > got.keys[:-1][tie]), "ties are not in ascending key order"
+
+
+# ---- the digest of ipk_b200/csrc/digest.cuh in numpy (uint64 arithmetic wraps) ---------------------------------------
+def _mix64(x):
+    x = x.astype(np.uint64)
+    x ^= x >> np.uint64(30); x *= np.uint64(0xbf58476d1ce4e5b9)
+    x ^= x >> np.uint64(27); x *= np.uint64(0x94d049bb133111eb)
+    x ^= x >> np.uint64(31)
+    return x
+
+
+def db_digest(db, log_threshold=0.0, band=1e-5):
+    """the dict Context.result_digest returns, computed from a host database (any k-mer order)"""
+    with np.errstate(over="ignore"):
+        hk = _mix64(db.keys.astype(np.uint64) + np.uint64(0x9e3779b97f4a7c15))
+        cnt = np.diff(db.offsets.astype(np.uint64))
+        he = _mix64(np.repeat(hk, cnt.astype(np.int64)) ^ ((db.branch.astype(np.uint64) << np.uint64(32)) | db.score.view(np.uint32).astype(np.uint64)))
+        hc = _mix64(hk ^ (cnt + np.uint64(0x632be59bd9b4e019)))
+        hf = _mix64(hk ^ (db.fv.view(np.uint32).astype(np.uint64) | np.uint64(0x5bd1e99500000000)))
+        xor = lambda a: int(np.bitwise_xor.reduce(a)) if a.size else 0
+        add = lambda a: int(a.sum(dtype=np.uint64)) if a.size else 0
+        hi = np.float32(log_threshold) + np.float32(band)
+        return {"entries_sum": add(he), "entries_xor": xor(he), "kmers_sum": add(hc), "kmers_xor": xor(hc), "fv_sum": add(hf), "fv_xor": xor(hf),
+                "n_boundary_above": int((db.score < hi).sum()), "n_kmers": db.n_kmers, "n_entries": db.n_entries}

@@ -124,6 +124,32 @@ def test_build_matches_oracle(ctx, mode, name, n_taxa, W, sigma, bits, k, omega,
         assert got.stats["n_deferred_tiles"] < got.stats["n_tiles"]       # the fast path really ran
 
 
+@pytest.mark.parametrize("name,n_taxa,W,sigma,bits,k,omega", [BUILD_CASES[1], BUILD_CASES[4]])
+@pytest.mark.parametrize("result_mode", ["host", "device_indexed"])
+def test_result_digest_is_the_numpy_digest_of_the_database(ctx, name, n_taxa, W, sigma, bits, k, omega, result_mode):
+    """ipkgpu_result_digest (digest.cuh) == the same definition in numpy (parity.db_digest) over the database the build
+    handed back, and its entry / k-mer parts == the digest of the ORACLE's database: the order-independent check bench.py
+    uses where two builds never share a memory (device-resident vs host-bound, 1 GPU vs G shards)"""
+    from ipk_b200 import capi as libipkgpu
+    from parity import db_digest
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    got = ctx.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+    if result_mode == "device_indexed":
+        inp, keep = libipkgpu.make_input(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+        res = ctx.build_raw(inp, result_on_device=True, indexed=True)
+        assert int(res.n_entries) == got.n_entries
+    d = ctx.result_digest(lthr, 1e-5)
+    assert d == db_digest(got, lthr, 1e-5)
+    want = db_digest(O.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0, 4), lthr, 1e-5)
+    for f in ("entries_sum", "entries_xor", "kmers_sum", "kmers_xor", "n_boundary_above", "n_kmers", "n_entries"):
+        assert d[f] == want[f], f
+    # one flipped score bit must show
+    got.score.view(np.uint32)[got.n_entries // 2] ^= 1
+    assert db_digest(got, lthr, 1e-5)["entries_xor"] != d["entries_xor"]
+
+
 def test_build_interleaved_groups_and_singletons(ctx):
     """ghost nodes of one branch need not be adjacent; a branch may have one ghost only (--inner-only/--outer-only)"""
     logp, nb = _synth(10, 150, 4)

@@ -122,8 +122,8 @@ def test_mif0_known_answers():
 
 
 def test_random_fv_is_libstdcxx_minstd():
-    fv = O.random_fv(4)
-    # std::default_random_engine(42) + uniform_real_distribution<double>(0,1), libstdc++: first values
+    fv = O.random_fv(np.arange(4))
+    # std::default_random_engine(42) + uniform_real_distribution<double>(0,1), libstdc++: keys 0..3 take draws (1,2), (3,4), ...
     x = 42; out = []
     for _ in range(4):
         x = x * 16807 % 2147483647; g1 = x - 1
@@ -131,6 +131,10 @@ def test_random_fv_is_libstdcxx_minstd():
         out.append(np.float32((g1 + g2 * 2147483646.0) / (2147483646.0 ** 2)))
     assert np.array_equal(fv, np.array(out, np.float32))
     assert np.all((fv >= 0) & (fv < 1))
+    # a function of the key alone (key shards of a multi-GPU build draw what one GPU draws), periodic in 2^31-2
+    big = np.array([3, 2**40 + 12345, (2**31 - 2) + 3], np.uint64)
+    got = O.random_fv(big)
+    assert got[0] == fv[3] == got[2] and 0 <= got[1] < 1
 
 
 @pytest.mark.skipif(not (O.have_ref(4) and O.have_ref(20)), reason="oracle/_ref not built (needs /root/reference)")
