@@ -90,6 +90,9 @@ struct ipkgpu_ctx
     uint32_t small_list = 64;          // join kernel: longest list its owner thread fills and sorts alone (env IPKGPU_SMALL_LIST)
     uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet
     uint64_t last_tiles = 0, last_deferred_tiles = 0;   // of the current call
+    ipkgpu::dbuf runs, runs_scratch;   // commits of the join kernel (enumerate.cuh: emit_run) and their group-ordered index (packed_sort.cuh)
+    uint64_t runs_n = 0;               // runs recorded by the current enumeration
+    bool runs_valid = false;           // ... and whether they cover every emitted record (join kernel only, nothing deferred to the depth-first kernel)
     uint64_t enum_join_emitted = 0;    // records the join kernel of the last enumeration launch emitted
     ipkgpu::dbuf u_keys, u_scores;                 // unique (kmer,group) records, composite keys
     ipkgpu::dbuf kmer_keys, kmer_offs, ent_branch, ent_score, fv, ord_keys_a, ord_keys_b, ord_vals_a, ord_vals_b;

@@ -127,6 +127,15 @@ namespace ipkgpu
     // K2: enumeration
     // ----------------------------------------------------------------------------------------------------------
 
+    /// One commit of the join kernel: `count` records at `offset` of the emission stream, all of branch group `group`
+    /// (a tile lies inside one node).  Read in group order, the runs ARE the stream sorted by group: the first pass of the
+    /// merge sort walks them in that order (packed_sort.cuh), so no radix pass is ever spent on the group bits.
+    struct emit_run
+    {
+        unsigned long long offset;
+        uint32_t count, group;
+    };
+
     struct enum_args
     {
         const float* logp;            // [n_nodes][W][sigma]
@@ -156,6 +165,9 @@ namespace ipkgpu
         // sum over all tiles BEFORE it (decoupled look-back), so the record stream is in tile order = branch-group order
         unsigned long long* tile_status;
         unsigned long long* phase_clocks;   // debug (IPKGPU_PHASE_CLOCKS): cycles of thread 0 per phase of the join kernel, summed over tiles
+        emit_run* runs;               // join kernel: one entry per committing item (null: not recorded) ...
+        unsigned long long* run_counter;   // ... their number so far
+        uint32_t run_cap;
         uint32_t group_min;           // join kernel: lists of at least this many elements are built by a lane group
         uint32_t small_list;          // join kernel: lists up to this length are filled and sorted by their owner thread
     };

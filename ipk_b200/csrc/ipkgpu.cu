@@ -201,6 +201,7 @@ namespace
         // enumerated into this side stream (any order).  side_keys == nullptr: one stream, any order.
         uint64_t* side_keys = nullptr; float* side_scores = nullptr; uint64_t side_cap = 0;
         uint64_t emitted_before = 0;       // records already in (out_keys, out_scores): a later node chunk of the same enumeration
+        bool want_runs = false;            // record every commit of the join kernel in ctx->runs (counters[5] = their number, zeroed by the caller)
     };
 
     uint64_t read_u64(ipkgpu_ctx* ctx, const void* d);
@@ -280,6 +281,8 @@ namespace
         }
         const bool ordered = use_join && !L.debug && L.side_keys != nullptr;
         unsigned long long* const counters = ctx->counters.as<unsigned long long>();
+        const bool record_runs = L.want_runs && use_join && !ordered && !L.debug;
+        if (L.want_runs && !record_runs) ctx->runs_valid = false;
         if (ordered)
         {
             ctx->reserve(ctx->tile_status, grid * 8);
@@ -312,6 +315,14 @@ namespace
                 ctx->reserve(out_list, lvl_grid * 4);
                 lists[level & 1] = out_list.as<uint32_t>();
                 A.deferred_tiles = lists[level & 1];
+                if (record_runs)
+                {
+                    // every item of this level commits at most once
+                    ctx->reserve_keep(ctx->runs, (ctx->runs_n + lvl_grid) * sizeof(emit_run), ctx->runs_n * sizeof(emit_run));
+                    A.runs = ctx->runs.as<emit_run>();
+                    A.run_counter = counters + 5;
+                    A.run_cap = uint32_t(std::min<uint64_t>(ctx->runs.cap / sizeof(emit_run), 0xffffffffull));
+                }
                 IPK_CUDA(cudaMemsetAsync(A.counter + 1, 0, 8, ctx->stream));
                 const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
                 if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
@@ -326,9 +337,10 @@ namespace
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
                     IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
-                uint64_t h[2] = { 0, 0 };
-                IPK_CUDA(cudaMemcpyAsync(h, A.counter, 16, cudaMemcpyDeviceToHost, ctx->stream));
+                uint64_t h[6] = { 0, 0, 0, 0, 0, 0 };
+                IPK_CUDA(cudaMemcpyAsync(h, A.counter, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
                 IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+                if (record_runs) ctx->runs_n = h[5];
                 ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], A.cap) - std::min<uint64_t>(emitted_before, A.cap)));
                 emitted_before = h[0];
                 n_items = h[1];
@@ -361,6 +373,7 @@ namespace
         }
         if (!use_join) { ctx->last_deferred_tiles += grid; ctx->last_tiles += grid; }
         if (n_deferred == 0) return;
+        ctx->runs_valid = false;           // the depth-first kernel commits per warp, unrecorded
         const size_t smem = enum_smem_bytes(int(in->k), int(in->sigma), L.debug);
         const uint64_t dfs_in_bytes = use_join ? n_deferred * uint64_t(ENUM_THREADS + in->k) * (in->sigma + 1) * 4 : in_bytes;
         if (L.debug)
@@ -670,10 +683,14 @@ namespace
     /// stream_parts: host-bound indexed result -- buckets are sorted and merged in runs of about n / n_parts records and each
     /// run's entries are queued on the copy stream at once (the role sort_merge_parts has for the pair sort).
     parts_out sort_merge_packed(ipkgpu_ctx* ctx, uint64_t* ka, uint32_t* va, uint64_t* p0, uint64_t n, uint32_t key_bits, uint32_t gbits,
-                                uint32_t group_add, int result_mode, bool stream_parts, stage_timer& tm)
+                                uint32_t group_add, int result_mode, bool stream_parts, stage_timer& tm, bool use_runs = false)
     {
+        // use_runs: ctx->runs lists the commits of the enumeration (one branch group each, together all n records).  The MSD
+        // pass reads them in group order, so its output is group-ordered inside every bucket and the LSD passes only have the
+        // k-mer bits left: 1 + ceil((key_bits - 8) / 8) passes instead of 1 + ceil((key_bits + gbits - 8) / 8).
         parts_out R;
         const uint32_t low_bits = key_bits + gbits - 8;
+        const uint32_t skip_bits = use_runs ? gbits : 0;
         uint64_t* p1 = ka;
         const bool b16 = stream_parts && (result_mode & 4) != 0 && ctx->max_branch < 65536u;
         if (stream_parts)
@@ -687,17 +704,20 @@ namespace
         ps_table T;
         memset(&T, 0, sizeof T);
         const size_t e0 = tm.mark();
+        ps_runs Rn;
+        memset(&Rn, 0, sizeof Rn);
+        if (use_runs) Rn = ps_order_runs(ctx, n, gbits);          // (uses ctx->hist as sort scratch: before the top histogram)
         ps_top_histogram(ctx, ka, n, low_bits);
         IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(ctx->hist.as<uint32_t>()));
         IPK_CUDA(cudaMemcpyAsync(T.start, ctx->hist.p, RS_RADIX * 4, cudaMemcpyDeviceToHost, ctx->stream));
         ps_dest D;
         memset(&D, 0, sizeof D);
         D.out[0] = p0;
-        ps_msd_pack(ctx, ka, va, n, low_bits, ctx->hist.as<uint32_t>(), D, false);
+        ps_msd_pack(ctx, ka, va, n, low_bits, ctx->hist.as<uint32_t>(), D, false, Rn);
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));           // T.start is on the host now (and ka is free: it becomes p1)
         T.start[PS_BUCKETS] = uint32_t(n);
         const size_t e1 = tm.mark();
-        R.passes = 1 + div_up<uint32_t>(low_bits, 8);
+        R.passes = 1 + div_up<uint32_t>(low_bits - skip_bits, 8);
         struct mark3 { size_t a, b, c; };
         std::vector<mark3> marks;
         const uint64_t target = stream_parts ? div_up<uint64_t>(n, ctx->n_parts) : n;
@@ -711,7 +731,7 @@ namespace
             d0 = d1;
             if (T.start[d1] == T.start[first]) continue;
             const size_t ea = tm.mark();
-            const bool in1 = ps_sort_buckets(ctx, p0, p1, T, first, d1, low_bits);
+            const bool in1 = ps_sort_buckets(ctx, p0, p1, T, first, d1, low_bits, skip_bits);
             const size_t eb = tm.mark();
             const merge_out m = run_merge_packed(ctx, in1 ? p1 : p0, T, first, d1, key_bits, gbits, group_add, ent_base, kmer_base, n);
             marks.push_back({ ea, eb, tm.mark() });
@@ -803,6 +823,12 @@ namespace
         // instead of (key_bits + group_bits) / 8.  The few tiles that level defers go to a side stream that is sorted on
         // all bits and merged in by the max-merge kernel.
         const bool ordered = ctx->ordered && !raw && in->k >= 2 && ctx->enum_mode != 1;
+        // commits of the join kernel recorded as runs of one branch group each: read in group order by the first pass of the
+        // packed sort they spare it every pass on the group bits (packed_sort.cuh)
+        static const bool runs_off = getenv("IPKGPU_RUNS") && atoi(getenv("IPKGPU_RUNS")) == 0;
+        L.want_runs = !runs_off && !ordered && !raw && want_csr && key_bits >= 8 && key_bits + all_bits - 8 <= 32;
+        ctx->runs_n = 0;
+        ctx->runs_valid = L.want_runs;
         uint64_t side_cap = 0;
         if (ordered)
         {
@@ -837,6 +863,7 @@ namespace
         if (first_valid) batches.push_back({ 0, o.n_groups, n_main });
         else
         {
+            ctx->runs_valid = false;
             // the first attempt overflowed its buffer: it still counted every node exactly -> plan batches of whole groups
             std::vector<unsigned long long> counts(in->n_nodes);
             IPK_CUDA(cudaMemcpyAsync(counts.data(), ctx->node_counts.p, size_t(in->n_nodes) * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -903,7 +930,7 @@ namespace
                 // 8-byte packed records: one MSD pass, then segmented LSD passes and the merge (packed_sort.cuh)
                 const bool parts = parts_eligible(ctx, b.n, key_bits, key_bits + bbits, result_mode, uint64_t(std::min(1e18, std::pow(double(in->sigma), double(in->k)))));
                 const parts_out po = sort_merge_packed(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(), b.n, key_bits, bbits,
-                                                       group_base + b.g0, result_mode, parts, tm);
+                                                       group_base + b.g0, result_mode, parts, tm, ctx->runs_valid && ctx->runs_n > 0);
                 o.sort_passes += po.passes;
                 o.csr_done = true; o.n_kmers = po.m.n_kmers;
                 u_off += po.m.n_records;
@@ -1319,7 +1346,8 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
-                            &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist };
+                            &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
+                            &ctx->runs, &ctx->runs_scratch };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto* b : all) ctx->release(*b);

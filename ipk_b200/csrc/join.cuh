@@ -809,7 +809,15 @@ namespace ipkgpu
                 wbase[ENUM_THREADS] = total;
                 rbase[ENUM_THREADS] = br + ir;
                 // ONE global atomic per tile reserves the tile's exact output range ...
-                if (!A.tile_status) s_base = total ? atomicAdd(A.counter, (unsigned long long)total) : 0ull;
+                if (!A.tile_status)
+                {
+                    s_base = total ? atomicAdd(A.counter, (unsigned long long)total) : 0ull;
+                    if (A.runs && total)
+                    {
+                        const unsigned long long r = atomicAdd(A.run_counter, 1ull);
+                        if (r < A.run_cap) A.runs[r] = emit_run{ s_base, total, A.node_group[node] - A.group_sub };
+                    }
+                }
                 else
                 {
                     // ... or, in ordered mode, only counts; the range follows from the look-back below

@@ -21,10 +21,12 @@
 #include "common.cuh"
 #include "radix_sort.cuh"
 #include "merge.cuh"
+#include "enumerate.cuh"
 
 namespace ipkgpu
 {
     constexpr int PS_BUCKETS = 256;
+    constexpr int PS_THREADS = 384, PS_ITEMS = 16, PS_TILE = PS_THREADS * PS_ITEMS;      // tile shape of the sweeps
 
     /// bucket geometry of one segmented launch (kernel parameter, 2 KB)
     struct ps_table
@@ -39,6 +41,33 @@ namespace ipkgpu
     {
         uint64_t* out[RS_MAX_PEERS];
         uint8_t owner[PS_BUCKETS];
+    };
+
+    /// The emission stream read in branch-group order: run r (one commit of the join kernel, enumerate.cuh: emit_run) holds
+    /// the logical positions [lstart[r], lstart[r + 1]) and lies at off[r] of the physical stream; runs ascend by group.
+    struct ps_runs
+    {
+        const uint32_t* lstart;                // [n_runs + 1], lstart[n_runs] = n; null: the stream is read as it lies
+        const uint32_t* off;                   // [n_runs]
+        const uint32_t* tile_first;            // [tiles of the MSD pass] run that holds the tile's first logical position
+        uint32_t n_runs;
+    };
+    constexpr int PS_RUN_WIN = 64;             // run boundaries a tile stages in shared memory (runs average thousands of records)
+
+    /// logical -> physical position for ascending logical positions of one thread; the staged window covers the runs
+    /// first .. first + PS_RUN_WIN - 1 of the tile, anything beyond is looked up in global memory
+    struct ps_run_cursor
+    {
+        uint32_t j, hi, delta;
+        __device__ __forceinline__ void init(const uint32_t* s_rs, const uint32_t* s_ro) { j = 0; hi = s_rs[1]; delta = s_ro[0] - s_rs[0]; }
+        __device__ __forceinline__ uint32_t map(uint32_t L, const uint32_t* s_rs, const uint32_t* s_ro, const ps_runs& R, uint32_t first)
+        {
+            while (L >= hi && j + 1 < uint32_t(PS_RUN_WIN)) { ++j; hi = s_rs[j + 1]; delta = s_ro[j] - s_rs[j]; }
+            if (L < hi) return L + delta;
+            uint32_t lo = first + PS_RUN_WIN - 1, up = R.n_runs;          // last r in [lo, up) with lstart[r] <= L
+            while (up - lo > 1) { const uint32_t mid = (lo + up) >> 1; if (R.lstart[mid] <= L) lo = mid; else up = mid; }
+            return R.off[lo] + (L - R.lstart[lo]);
+        }
     };
 
     inline void ps_fill_tiles(ps_table& T, uint32_t d0, uint32_t d1, uint32_t tile)
@@ -92,13 +121,14 @@ namespace ipkgpu
     /// One pass over one tile.  MSD = true: (keys_in, vals_in) pairs -> packed records, digit = top byte of the composite key,
     /// destination per digit from D, tiles are plain runs of THREADS * ITEMS pairs.  MSD = false: packed -> packed, digit =
     /// byte `shift / 8` of the record, tiles cut at bucket boundaries (T), digit bases per bucket.
-    template<int THREADS, int ITEMS, bool MSD, int MINB>
+    template<int THREADS, int ITEMS, bool MSD, int MINB, bool RUNS = false>
     __global__ void __launch_bounds__(THREADS, MINB) ps_sweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                               uint64_t* __restrict__ out, const uint32_t* __restrict__ digit_base, uint64_t n,
                                                               uint32_t shift /* MSD: low_bits; else: bit of the record where the digit starts */,
                                                               uint32_t base_stride /* LSD: words between two buckets' digit bases */,
                                                               uint64_t* status, uint32_t* ticket, uint32_t epoch,
-                                                              const __grid_constant__ ps_table T, const __grid_constant__ ps_dest D)
+                                                              const __grid_constant__ ps_table T, const __grid_constant__ ps_dest D,
+                                                              const __grid_constant__ ps_runs R)
     {
         constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
         static_assert(THREADS >= RS_RADIX && THREADS % 32 == 0 && ITEMS % 4 == 0, "tile shape");
@@ -116,7 +146,7 @@ namespace ipkgpu
         __syncthreads();
         const uint32_t tile = S.misc[15];
         uint64_t tile_base;
-        uint32_t tile_n;
+        uint32_t tile_n, chain_pos;                     // chain_pos: tiles before this one in its look-back chain
         bool first_of_chain;
         const uint32_t* dbase_g = digit_base;
         if (MSD)
@@ -124,6 +154,7 @@ namespace ipkgpu
             tile_base = uint64_t(tile) * TILE;
             tile_n = uint32_t(min(uint64_t(TILE), n - tile_base));
             first_of_chain = tile == 0;
+            chain_pos = tile;
         }
         else
         {
@@ -132,6 +163,7 @@ namespace ipkgpu
             tile_base = uint64_t(T.start[b]) + uint64_t(lt) * TILE;
             tile_n = uint32_t(min(uint64_t(TILE), uint64_t(T.start[b + 1]) - tile_base));
             first_of_chain = lt == 0;
+            chain_pos = lt;
             dbase_g = digit_base + size_t(b) * base_stride;
         }
 
@@ -145,19 +177,52 @@ namespace ipkgpu
         if (MSD)
         {
             const uint64_t low_mask = shift >= 64 ? ~0ull : ((1ull << shift) - 1);
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i)
+            if (RUNS)
             {
-                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
-                rec[i] = li < tile_n ? keys_in[tile_base + li] : 0ull;
+                // the tile's logical positions, mapped run by run to where the enumeration put them
+                __shared__ uint32_t s_rs[PS_RUN_WIN + 1], s_ro[PS_RUN_WIN];
+                const uint32_t first = R.tile_first[tile];
+                if (tid <= PS_RUN_WIN)
+                {
+                    const uint32_t r = first + tid;
+                    s_rs[tid] = r <= R.n_runs ? R.lstart[r] : 0xffffffffu;
+                    if (tid < PS_RUN_WIN) s_ro[tid] = r < R.n_runs ? R.off[r] : 0u;
+                }
+                __syncthreads();
+                ps_run_cursor c;
+                c.init(s_rs, s_ro);
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i)
+                {
+                    const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                    rec[i] = li < tile_n ? keys_in[c.map(uint32_t(tile_base) + li, s_rs, s_ro, R, first)] : 0ull;
+                }
+                c.init(s_rs, s_ro);
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i)
+                {
+                    const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                    const uint32_t v = li < tile_n ? vals_in[c.map(uint32_t(tile_base) + li, s_rs, s_ro, R, first)] : 0u;
+                    dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
+                    rec[i] = ((rec[i] & low_mask) << 32) | v;
+                }
             }
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i)
+            else
             {
-                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
-                const uint32_t v = li < tile_n ? vals_in[tile_base + li] : 0u;
-                dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
-                rec[i] = ((rec[i] & low_mask) << 32) | v;
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i)
+                {
+                    const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                    rec[i] = li < tile_n ? keys_in[tile_base + li] : 0ull;
+                }
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i)
+                {
+                    const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                    const uint32_t v = li < tile_n ? vals_in[tile_base + li] : 0u;
+                    dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
+                    rec[i] = ((rec[i] & low_mask) << 32) | v;
+                }
             }
         }
         else
@@ -220,15 +285,27 @@ namespace ipkgpu
             uint32_t before = 0;
             if (!first_of_chain)
             {
-                // the chain ends at the first tile of the bucket (MSD: of the launch), which published an inclusive word
+                // the chain ends at the first tile of the bucket (MSD: of the launch), which published an inclusive word.
+                // Four predecessors are polled at a time: their loads overlap, and a walk over LOCAL words costs one
+                // memory latency per four tiles instead of one per tile (ncu r03c: a quarter of the stall samples sat here).
                 const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
-                while (true)
+                uint32_t left = chain_pos;                      // predecessors in the chain, nearest first
+                bool done = false;
+                while (!done)
                 {
-                    const uint64_t w = *p;
-                    if (uint32_t(w >> 34) != epoch || ((w >> 32) & 3) == 0) continue;
-                    before += uint32_t(w);
-                    if (((w >> 32) & 3) == RS_FLAG_INCL) break;
-                    p -= RS_RADIX;
+                    uint64_t w[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) w[j] = uint32_t(j) < left ? p[-int64_t(j) * RS_RADIX] : 0ull;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                    {
+                        if (done || uint32_t(j) >= left) break;
+                        if (uint32_t(w[j] >> 34) != epoch || ((w[j] >> 32) & 3) == 0) { left -= j; p -= int64_t(j) * RS_RADIX; goto again; }
+                        before += uint32_t(w[j]);
+                        if (((w[j] >> 32) & 3) == RS_FLAG_INCL) done = true;
+                    }
+                    if (!done) { left -= 4; p -= 4 * int64_t(RS_RADIX); }
+                again:;
                 }
                 *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
             }
@@ -275,7 +352,7 @@ namespace ipkgpu
     /// whenever it crosses a bucket boundary.
     constexpr int PS_HIST_THREADS = 256;
     constexpr int PS_HIST_ITEMS = 16;
-    __global__ void __launch_bounds__(PS_HIST_THREADS) ps_seg_hist(const uint64_t* __restrict__ recs, uint32_t n_passes, uint64_t chunk,
+    __global__ void __launch_bounds__(PS_HIST_THREADS) ps_seg_hist(const uint64_t* __restrict__ recs, uint32_t n_passes, uint32_t skip_bits, uint64_t chunk,
                                                                   uint32_t* __restrict__ hist, const __grid_constant__ ps_table T)
     {
         extern __shared__ uint32_t ps_sh[];              // [2 copies][n_passes][256]
@@ -313,7 +390,7 @@ namespace ipkgpu
                     const uint64_t idx = base + uint64_t(i) * PS_HIST_THREADS + threadIdx.x;
                     if (idx < seg_end)
                     {
-                        const uint32_t kk = uint32_t(r[i] >> 32);
+                        const uint32_t kk = uint32_t(r[i] >> 32) >> skip_bits;
                         for (uint32_t p = 0; p < n_passes; ++p) atomicAdd(&mine[p * RS_RADIX + ((kk >> (8 * p)) & 0xffu)], 1u);
                     }
                 }
@@ -503,8 +580,6 @@ namespace ipkgpu
     // -----------------------------------------------------------------------------------------------------------------
     // host side
     // -----------------------------------------------------------------------------------------------------------------
-    constexpr int PS_THREADS = 384, PS_ITEMS = 16, PS_TILE = PS_THREADS * PS_ITEMS;
-
     /// true when the packed path applies to composite keys of key_bits + group_bits
     inline bool ps_eligible(uint32_t key_bits, uint32_t group_bits, uint64_t n)
     {
@@ -524,6 +599,54 @@ namespace ipkgpu
         }
     }
 
+    __global__ void ps_runs_keys(const emit_run* __restrict__ runs, uint32_t n_runs, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+    {
+        const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i < n_runs) { keys[i] = runs[i].group; vals[i] = i; }
+    }
+    __global__ void ps_runs_gather(const emit_run* __restrict__ runs, const uint32_t* __restrict__ perm, uint32_t n_runs, uint32_t n_total,
+                                   uint32_t* __restrict__ cnt, uint32_t* __restrict__ off, uint32_t* __restrict__ lstart)
+    {
+        const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i == 0) lstart[n_runs] = n_total;
+        if (i < n_runs) { const emit_run r = runs[perm[i]]; cnt[i] = r.count; off[i] = uint32_t(r.offset); }
+    }
+
+    /// tile_first[t] = last run r with lstart[r] <= t * tile (one thread per tile of the MSD pass)
+    __global__ void ps_runs_tile_first(const uint32_t* __restrict__ lstart, uint32_t n_runs, uint32_t n_tiles, uint32_t tile, uint32_t* __restrict__ tile_first)
+    {
+        const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+        if (t >= n_tiles) return;
+        const uint32_t target = t * tile;
+        uint32_t lo = 0, up = n_runs;
+        while (up - lo > 1) { const uint32_t mid = (lo + up) >> 1; if (lstart[mid] <= target) lo = mid; else up = mid; }
+        tile_first[t] = lo;
+    }
+
+    /// ctx->runs (ctx->runs_n commits of the enumeration, any order) -> the group-ordered index the MSD pass reads through.
+    /// A stable sort of the run ids by group, then a scan of the counts.  Uses ctx->hist / ctx->scan_tmp as sort scratch.
+    inline ps_runs ps_order_runs(ipkgpu_ctx* ctx, uint64_t n, uint32_t group_bits)
+    {
+        const uint32_t nr = uint32_t(ctx->runs_n);
+        const size_t a8 = (size_t(nr) * 8 + 255) & ~size_t(255), a4 = (size_t(nr + 1) * 4 + 255) & ~size_t(255);
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_TILE));
+        ctx->reserve(ctx->runs_scratch, 2 * a8 + 5 * a4 + size_t(n_tiles) * 4);
+        char* base = ctx->runs_scratch.as<char>();
+        uint64_t* ka = reinterpret_cast<uint64_t*>(base); uint64_t* kb = reinterpret_cast<uint64_t*>(base + a8);
+        uint32_t* va = reinterpret_cast<uint32_t*>(base + 2 * a8); uint32_t* vb = va + a4 / 4;
+        uint32_t* cnt = vb + a4 / 4; uint32_t* off = cnt + a4 / 4; uint32_t* lstart = off + a4 / 4;
+        const uint32_t grid = div_up<uint32_t>(nr, 256);
+        IPK_LAUNCH(ctx, "ps_runs_keys", uint64_t(nr) * 28, ps_runs_keys<<<grid, 256, 0, ctx->stream>>>(ctx->runs.as<emit_run>(), nr, ka, va));
+        const bool in_b = radix_sort_pairs(ctx, ka, va, kb, vb, nr, group_bits, ctx->hist, ctx->scan_tmp);
+        IPK_LAUNCH(ctx, "ps_runs_gather", uint64_t(nr) * 28,
+                   ps_runs_gather<<<grid, 256, 0, ctx->stream>>>(ctx->runs.as<emit_run>(), in_b ? vb : va, nr, uint32_t(n), cnt, off, lstart));
+        exclusive_scan_u32(ctx, cnt, lstart, nr, ctx->scan_tmp);
+        uint32_t* tile_first = lstart + a4 / 4;
+        IPK_LAUNCH(ctx, "ps_runs_tile_first", uint64_t(n_tiles) * 80,
+                   ps_runs_tile_first<<<div_up<uint32_t>(n_tiles, 256), 256, 0, ctx->stream>>>(lstart, nr, n_tiles, PS_TILE, tile_first));
+        return ps_runs{ lstart, off, tile_first, nr };
+    }
+
     /// top-byte histogram of the composite keys -> hist[0..256) (device, in ctx->hist) ; not yet scanned
     inline void ps_top_histogram(ipkgpu_ctx* ctx, const uint64_t* keys, uint64_t n, uint32_t low_bits)
     {
@@ -537,7 +660,7 @@ namespace ipkgpu
     /// MSD pass: n (key, score) pairs -> packed records in D's buffers; d_base[256] (device) = where this rank's records of
     /// each bucket start inside the owner's buffer.  Uses tickets[15] of ctx->hist.
     inline void ps_msd_pack(ipkgpu_ctx* ctx, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t low_bits,
-                            const uint32_t* d_base, const ps_dest& D, bool peers)
+                            const uint32_t* d_base, const ps_dest& D, bool peers, const ps_runs& Rn)
     {
         if (n == 0) return;
         const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_TILE));
@@ -547,18 +670,20 @@ namespace ipkgpu
         ps_table none;
         memset(&none, 0, sizeof none);
         constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(true);
-        auto kern = ps_sweep<PS_THREADS, PS_ITEMS, true, 2>;
+        auto kern = Rn.lstart ? ps_sweep<PS_THREADS, PS_ITEMS, true, 2, true> : ps_sweep<PS_THREADS, PS_ITEMS, true, 2, false>;
         IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         IPK_LAUNCH(ctx, peers ? "ps_msd_scatter_peers" : "ps_msd_pack", n * 20 + uint64_t(n_tiles) * RS_RADIX * 8,
                    kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(keys, vals, nullptr, d_base, n, low_bits, 0, ctx->rs_status.as<uint64_t>(), ticket,
-                                                                    rs_next_epoch(ctx), none, D));
+                                                                    rs_next_epoch(ctx), none, D, Rn));
     }
 
     /// LSD passes on the packed records of buckets [d0, d1) (T.start filled by the caller): ping-pongs between p0 and p1,
     /// returns true when the sorted records end up in p1.  ctx->ps_hist holds the per-bucket digit bases.
-    inline bool ps_sort_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint32_t d0, uint32_t d1, uint32_t low_bits)
+    /// skip_bits: low bits of the key field the input is already ordered on (the group field, when the MSD pass read the
+    /// emission in group order): the passes start above them.
+    inline bool ps_sort_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint32_t d0, uint32_t d1, uint32_t low_bits, uint32_t skip_bits = 0)
     {
-        const uint32_t passes = div_up<uint32_t>(low_bits, 8);
+        const uint32_t passes = div_up<uint32_t>(low_bits - skip_bits, 8);
         const uint64_t n = uint64_t(T.start[d1]) - T.start[d0];
         if (n == 0 || passes == 0) return false;
         ps_fill_tiles(T, d0, d1, PS_TILE);
@@ -574,11 +699,13 @@ namespace ipkgpu
         uint64_t chunk = div_up<uint64_t>(n, hgrid);
         chunk = div_up<uint64_t>(chunk, PS_HIST_THREADS * PS_HIST_ITEMS) * (PS_HIST_THREADS * PS_HIST_ITEMS);
         IPK_LAUNCH(ctx, "ps_seg_hist", n * 8,
-                   ps_seg_hist<<<uint32_t(div_up<uint64_t>(n, chunk)), PS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(p0, passes, chunk, hist, T));
+                   ps_seg_hist<<<uint32_t(div_up<uint64_t>(n, chunk)), PS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(p0, passes, skip_bits, chunk, hist, T));
         IPK_LAUNCH(ctx, "ps_seg_scan", uint64_t(d1 - d0) * passes * 2048,
                    ps_seg_scan<<<dim3(passes, d1 - d0), RS_RADIX, 0, ctx->stream>>>(hist, passes, T));
         ps_dest none;
         memset(&none, 0, sizeof none);
+        ps_runs no_runs;
+        memset(&no_runs, 0, sizeof no_runs);
         constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(false);
         auto kern = ps_sweep<PS_THREADS, PS_ITEMS, false, 2>;
         IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
@@ -586,8 +713,8 @@ namespace ipkgpu
         for (uint32_t p = 0; p < passes; ++p)
         {
             IPK_LAUNCH(ctx, "ps_sweep", n * 16 + uint64_t(n_tiles) * RS_RADIX * 8,
-                       kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(in1 ? p1 : p0, nullptr, in1 ? p0 : p1, hist + size_t(p) * RS_RADIX, n, 32 + 8 * p,
-                                                                        passes * RS_RADIX, ctx->rs_status.as<uint64_t>(), tickets + p, rs_next_epoch(ctx), T, none));
+                       kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(in1 ? p1 : p0, nullptr, in1 ? p0 : p1, hist + size_t(p) * RS_RADIX, n, 32 + skip_bits + 8 * p,
+                                                                        passes * RS_RADIX, ctx->rs_status.as<uint64_t>(), tickets + p, rs_next_epoch(ctx), T, none, no_runs));
             in1 = !in1;
         }
         return in1;
