@@ -29,6 +29,7 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, _p)
 
 METRIC = "phylo-k-mers/s"
+NVLINK_GBS = 900.0          # NVLink 5 per direction per GPU (BASELINE.json north_star)
 DEFAULT_WORKLOAD = "cfg3_16s_10k"
 
 
@@ -42,6 +43,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-branches", type=int, default=0, help="branch groups in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=42)
+    ap.add_argument("--write-digest", action="store_true", help="record this run's database digest in profiles/digests.json")
     return ap.parse_args()
 
 
@@ -112,12 +114,12 @@ def host_cores() -> int:
         return os.cpu_count() or 1
 
 
-def cpu_build_sample(wl, seed, b0, b1, threads):
-    """one CPU build over branch groups [b0, b1) of the workload; returns (n_entries, n_emitted, seconds, kind)"""
+def cpu_build_sample(wl, seed, b0, b1, threads, keep_db=False):
+    """one CPU build over branch groups [b0, b1) of the workload; returns (n_entries, n_emitted, seconds, kind[, db])"""
     import oraclelib as O
-    from ipk_b200 import capi, synth
+    from ipk_b200 import synth                      # libipksynth.so only: the CPU arm maps no GPU library
     logp, nb = synth.posteriors(wl.n_taxa, wl.width, wl.sigma, seed=seed, branch_begin=b0, branch_end=b1)
-    thr, lthr = capi.score_threshold(wl.omega, wl.sigma, wl.k)
+    thr, lthr = synth.score_threshold(wl.omega, wl.sigma, wl.k)
     filt = 0 if wl.filter == "mif0" else 1
     t = time.perf_counter()
     if O.have_ref(wl.sigma):
@@ -125,6 +127,8 @@ def cpu_build_sample(wl, seed, b0, b1, threads):
     else:
         db, kind = O.build(logp, nb, wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt, threads), "port"
     dt = time.perf_counter() - t
+    if keep_db:
+        return db.n_entries, db.n_emitted, dt, kind, db
     return db.n_entries, db.n_emitted, dt, kind
 
 
@@ -139,18 +143,26 @@ def cpu_sample_size(wl, seed, threads, target_s, forced=0):
     return min(n, wl.n_branches)
 
 
-def cpu_baseline(wl, seed, target_s=15.0, forced=0):
+def cpu_baseline(wl, seed, target_s=15.0, forced=0, gpu_check=None):
+    """gpu_check(nb, cpu_db) -> str: the B200 arm builds the same slice and compares the two databases entry for entry"""
     threads = host_cores()
     nb = cpu_sample_size(wl, seed, threads, target_s, forced)
-    n_entries, n_emitted, dt, kind = cpu_build_sample(wl, seed, 0, nb, threads)
-    return {"value": n_entries / dt, "unit": METRIC, "cores": threads, "kind": kind,
-            "sample": f"branch groups [0,{nb}) of {wl.n_branches} ({2 * nb} ghost matrices, {2 * nb * (wl.width - wl.k + 1)} windows): "
-                      f"{n_entries} entries, {n_emitted} emitted in {dt:.2f} s; OpenMP over branch groups "
-                      f"(the loop db_builder.cpp:602-605 once marked parallel), in-RAM stages 1+2, no serialization"}
+    n_entries, n_emitted, dt, kind, db = cpu_build_sample(wl, seed, 0, nb, threads, keep_db=True)
+    out = {"value": n_entries / dt, "unit": METRIC, "cores": threads, "kind": kind,
+           "sample": f"branch groups [0,{nb}) of {wl.n_branches} ({2 * nb} ghost matrices, {2 * nb * (wl.width - wl.k + 1)} windows): "
+                     f"{n_entries} entries, {n_emitted} emitted in {dt:.2f} s; OpenMP over branch groups "
+                     f"(the loop db_builder.cpp:602-605 once marked parallel), in-RAM stages 1+2, no serialization"}
+    if gpu_check is not None:
+        out["parity"] = gpu_check(nb, db)
+    return out
 
 
-def workload_config(wl, n_gpus):
-    return {"workload": wl.name, "n_taxa": wl.n_taxa, "alignment_columns": wl.width, "k": wl.k, "omega": wl.omega,
+def workload_config(wl, n_gpus, seed=42):
+    """identical in both arms (the driver compares the two dicts)"""
+    return {"seed": seed, "l2": "B200 arm: flushed between steps (256 MiB write)",
+            "timing": "B200 arm: CUDA events on the launching stream, per step, summed, max over ranks; CPU arm: wall clock",
+            "result": "B200 arm: indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries",
+            "workload": wl.name, "n_taxa": wl.n_taxa, "alignment_columns": wl.width, "k": wl.k, "omega": wl.omega,
             "states": wl.sigma, "filter": wl.filter, "branch_groups": wl.n_branches, "ghost_matrices": wl.n_ghost_nodes,
             "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", records bucketed by k-mer hash and stored into the owners' buffers over NVLink peer memory, sorted once by the owner"
                                                                    if n_gpus > 1 and os.environ.get("IPK_EXCHANGE", "peer") == "peer" else
@@ -178,7 +190,7 @@ def run_reference(args):
               f"OpenMP over branch groups on {threads} threads")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(args.steps, 1), "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, args.gpus),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, args.gpus, args.seed),
             "cpu_baseline": {"value": value, "unit": METRIC, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -296,8 +308,31 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     ms_dev, last_dev, rows = timed(False, args.steps, True)
+    dig_dev = ctx.result_digest(lthr, 1e-5)                 # the database the last device-resident step left (this rank's shard)
     ms_e2e, last_e2e, _ = timed(True, args.steps, False)
+    dig_e2e = ctx.result_digest(lthr, 1e-5)
     clocks = sampler.stop() if rank == 0 else None
+
+    def reduce_digest(d: dict) -> dict:
+        """digests of key shards add / xor up to the digest of the whole database (ipkgpu.h: ipkgpu_result_digest)"""
+        if world == 1:
+            return d
+        names = list(d)
+        t = torch.tensor([d[n] - (1 << 64) if d[n] >= (1 << 63) else d[n] for n in names], dtype=torch.int64, device=dev)
+        parts = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(parts, t)
+        out = {}
+        for i, n in enumerate(names):
+            vals = [int(p_[i].item()) & ((1 << 64) - 1) for p_ in parts]
+            acc = 0
+            for v in vals:
+                acc = (acc ^ v) if n.endswith("_xor") else ((acc + v) & ((1 << 64) - 1))
+            out[n] = acc
+        return out
+
+    dig_dev, dig_e2e = reduce_digest(dig_dev), reduce_digest(dig_e2e)
+    if dig_dev != dig_e2e:
+        raise SystemExit(f"bench.py: the host-bound build is not the database of the device-resident one: digest {dig_e2e} vs {dig_dev}")
 
     ms_dev, ms_e2e = reduce_max(ms_dev), reduce_max(ms_e2e)
     n_entries = reduce_sum(last_dev[0]); n_kmers = reduce_sum(last_dev[1])
@@ -313,6 +348,27 @@ def run_b200(args):
         if world > 1:
             dist.destroy_process_group()
         return 0
+
+    # ---- the database itself: entry-for-entry identical at every N -- the digest of this run against the one
+    # a single-GPU run of the same workload and seed committed under profiles/
+    digest_path = os.path.join(ROOT, "profiles", "digests.json")
+    digest_key = f"{wl.name}/seed{args.seed}"
+    try:
+        with open(digest_path) as f:
+            known = json.load(f)
+    except Exception:
+        known = {}
+    digest_check = "no committed digest for this workload"
+    if digest_key in known:
+        want = {k_: int(v) for k_, v in known[digest_key]["digest"].items()}
+        if want != dig_dev:
+            raise SystemExit(f"bench.py: the database built on {world} GPU(s) differs from the committed single-GPU one ({digest_key}): {dig_dev} vs {want}")
+        digest_check = f"equal to profiles/digests.json[{digest_key}] (written by a {known[digest_key]['n_gpus']}-GPU run)"
+    if args.write_digest:
+        known[digest_key] = {"n_gpus": world, "digest": {k_: str(v) for k_, v in dig_dev.items()}}
+        with open(digest_path, "w") as f:
+            json.dump(known, f, indent=1, sort_keys=True)
+        digest_check += "; written"
 
     # ---- roofline of the dominant kernel: algorithmic bytes (summed by the library at each launch site, DESIGN.md
     # kernel table) / device time measured live with CUDA events around every launch of the timed region
@@ -340,32 +396,42 @@ def run_b200(args):
                     "share_of_step": round(top["ms"] / max(ms_dev, 1e-9), 4)}
     # whole-path roofline as north_star defines it: emitted-plus-sorted bytes over HBM vs all-to-all bytes over NVLink
     passes = int(st["sort_passes"])
+    exch_bytes_per_record = 12.0                         # (u64 composite key, f32 score) stored into the owner's buffers
     path_bytes = sum(r["bytes"] for r in rows) / max(args.steps, 1)
-    t_hbm = path_bytes / world / (peak * 1e9)
-    t_nvl = (12.0 * sent_remote / world) / 770e9 if world > 1 else 0.0
+    t_hbm = path_bytes / (peak * 1e9)                     # `rows` are rank 0's own kernels: its share of the path already
+    t_nvl = (exch_bytes_per_record * sent_remote / world) / (NVLINK_GBS * 1e9) if world > 1 else 0.0
     t_bound = max(t_hbm, t_nvl)
     value = n_entries * args.steps / (ms_dev * 1e-3)
     e2e_value = n_entries * args.steps / (ms_e2e * 1e-3)
     line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {**workload_config(wl, world), "seed": args.seed, "l2": "flushed between steps (256 MiB write)",
-                       "timing": "CUDA events on the launching stream, per step, summed; max over ranks",
-                       "result": "indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries",
-                       "host": "rank processes bound to the CPUs next to their GPU (NVML affinity)" if numa_bound else "unbound"},
+            "config": workload_config(wl, world, args.seed),
+            "host": "rank processes bound to the CPUs next to their GPU (NVML affinity)" if numa_bound else "unbound",
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "build_time_s": ms_e2e / args.steps * 1e-3},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
             "path_roofline": {"algo_bytes_per_step": int(path_bytes), "t_hbm_ms": round(t_hbm * 1e3, 3), "t_nvlink_ms": round(t_nvl * 1e3, 3),
-                              "frac": round(t_bound / (ms_dev / args.steps * 1e-3), 4), "nvlink_peak_gbs": 770.0},
+                              "frac": round(t_bound / (ms_dev / args.steps * 1e-3), 4), "nvlink_peak_gbs": NVLINK_GBS,
+                              "bound": "nvlink" if t_nvl > t_hbm else "hbm"},
             "counts": {"windows": wl.n_windows, "emitted": n_emitted, "entries": n_entries, "kmers": n_kmers, "sort_passes": passes,
                        "tiles_rank0": int(st.get("n_tiles", 0)), "deferred_tiles_rank0": int(st.get("n_deferred_tiles", 0)),
                        "emitted_per_s": n_emitted * args.steps / (ms_dev * 1e-3)},
             "stages_e2e_ms_rank0": {k_: round(float(last_e2e[2][k_]), 3) for k_ in ("ms_h2d", "ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order", "ms_d2h", "ms_total", "ms_partition", "ms_exchange") if k_ in last_e2e[2]},
             "stages_ms_rank0": {k_: round(float(st[k_]), 3) for k_ in ("ms_prefix", "ms_enumerate", "ms_sort", "ms_merge", "ms_filter", "ms_order", "ms_partition", "ms_exchange") if k_ in st},
             "kernels": kernels}
+    line["digest"] = {**{k_: str(v) for k_, v in dig_dev.items()}, "check": digest_check,
+                      "e2e_equal": True}        # (checked above: the run aborts otherwise)
     if not args.no_cpu_baseline and world == 1:
-        line["cpu_baseline"] = cpu_baseline(wl, args.seed, 15.0, args.cpu_sample_branches)
+        def gpu_check(nb, cpu_db):
+            """the same [0, nb) branch-group slice through ipkgpu_build, compared with the CPU arm's database entry for entry"""
+            from parity import assert_db_equal
+            got = ctx.build(h_logp.numpy()[: 2 * nb], node_branch[: 2 * nb], wl.width, wl.sigma, wl.bits, wl.k, lthr, thr, wl.n_tree_nodes, filt)
+            assert got.stats["n_emitted"] == cpu_db.n_emitted, (got.stats["n_emitted"], cpu_db.n_emitted)
+            assert_db_equal(got, cpu_db, exact_fv=(filt != capi.FILTER_MIF0))
+            return (f"ipkgpu_build of branch groups [0,{nb}) == the CPU arm's database: {got.n_kmers} k-mers, {got.n_entries} entries, "
+                    f"(k-mer, branch) set / order / scores bit-exact, filter values within 2e-5 relative")
+        line["cpu_baseline"] = cpu_baseline(wl, args.seed, 15.0, args.cpu_sample_branches, gpu_check)
     else:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)

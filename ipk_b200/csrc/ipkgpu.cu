@@ -327,21 +327,23 @@ namespace
                 const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
                 if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
                 const uint64_t lvl_in_bytes = level == 0 ? in_bytes : lvl_grid * uint64_t(width + in->k) * (in->sigma + 1) * 4;
+                // (the retries of deferred items are their own launch class in the kernel profile: a few thousand CTAs against half a million)
+                const char* const kname = level == 0 ? "k2_join" : "k2_join_retry";
                 if (L.debug)
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<true><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, kname, lvl_in_bytes, k2_join<true><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 else
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-                    IPK_LAUNCH(ctx, "k2_join", lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
+                    IPK_LAUNCH(ctx, kname, lvl_in_bytes, k2_join<false><<<uint32_t(lvl_grid), JOIN_THREADS, smem, ctx->stream>>>(A, P, J));
                 }
                 uint64_t h[6] = { 0, 0, 0, 0, 0, 0 };
                 IPK_CUDA(cudaMemcpyAsync(h, A.counter, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
                 IPK_CUDA(cudaStreamSynchronize(ctx->stream));
                 if (record_runs) ctx->runs_n = h[5];
-                ctx->kprof_add_bytes("k2_join", 12 * (std::min<uint64_t>(h[0], A.cap) - std::min<uint64_t>(emitted_before, A.cap)));
+                ctx->kprof_add_bytes(kname, 12 * (std::min<uint64_t>(h[0], A.cap) - std::min<uint64_t>(emitted_before, A.cap)));
                 emitted_before = h[0];
                 n_items = h[1];
                 prev_width = width;

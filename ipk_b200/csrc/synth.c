@@ -152,3 +152,13 @@ int ipk_synth_posteriors(uint32_t n_taxa, uint32_t W, uint32_t sigma, uint64_t s
     free(st); free(parent);
     return 0;
 }
+
+/* i2l::score_threshold(omega, k) and its log10 as the call sites' types imply (float powf / log10f; db_builder.cpp:260,640) --
+ * the same two lines as ipkgpu_score_threshold (include/ipkgpu.h), so that the CPU arm of bench.py and the fixture
+ * generators get the constants without mapping the GPU library. */
+void ipk_synth_score_threshold(float omega, uint32_t sigma, uint32_t k, float* threshold, float* log_threshold)
+{
+    const float t = powf(omega / (float)sigma, (float)k);
+    if (threshold) *threshold = t;
+    if (log_threshold) *log_threshold = log10f(t);
+}

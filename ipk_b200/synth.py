@@ -40,6 +40,8 @@ def load() -> C.CDLL:
         lib.ipk_synth_posteriors.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(SynthParams),
                                              C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         lib.ipk_synth_posteriors.restype = C.c_int
+        lib.ipk_synth_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        lib.ipk_synth_score_threshold.restype = None
         _lib = lib
     return _lib
 
@@ -83,6 +85,13 @@ WORKLOADS = {
     "cfg4_aa_2k": Workload("cfg4_aa_2k", 2000, 800, 6, 1.5, 20, 5),
     "cfg5_viral": Workload("cfg5_viral", 500, 9700, 14, 2.0, 4, 2),
 }
+
+
+def score_threshold(omega: float, sigma: int, k: int) -> tuple[float, float]:
+    """(threshold, log10 threshold): the same float powf / log10f as ipkgpu_score_threshold, without loading libipkgpu.so"""
+    t, lt = C.c_float(0), C.c_float(0)
+    load().ipk_synth_score_threshold(omega, sigma, k, C.byref(t), C.byref(lt))
+    return float(t.value), float(lt.value)
 
 
 def tree(n_taxa: int, seed: int = 42):

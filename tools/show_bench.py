@@ -10,4 +10,6 @@ for f in sys.argv[1:]:
     print("  counts", d.get("counts")); print("  stages", d.get("stages_ms_rank0")); print("  stages e2e", d.get("stages_e2e_ms_rank0")); print("  path", d.get("path_roofline")); print("  clocks", d.get("clocks"))
     for k in d.get("kernels", [])[:12]:
         print(f"   {k['kernel']:20s} n={k['launches']:3d} ms={k['ms']:9.3f} algoGB/s={k['algo_gbs']:8.1f} share={k['share']:.3f}")
-    if d.get("cpu_baseline"): print("  cpu", d["cpu_baseline"]["value"], d["cpu_baseline"]["cores"], d["cpu_baseline"]["kind"])
+    if d.get("cpu_baseline"): print("  cpu", d["cpu_baseline"]["value"], d["cpu_baseline"]["cores"], d["cpu_baseline"]["kind"], "|", d["cpu_baseline"].get("parity"))
+    if d.get("digest"): print("  digest", d["digest"].get("check"), d["digest"].get("entries_xor"))
+    print("  roofline", d.get("roofline"))
