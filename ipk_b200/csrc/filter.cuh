@@ -16,13 +16,6 @@ namespace ipkgpu
         const double p = (log_score > -300.0f && log_score <= 0.0f) ? mif_exp10(log_score) : exp10(double(log_score));
         return float(p < 1.0 ? p : 1.0);
     }
-    __device__ __forceinline__ double shannon(double x) { return -x * log2(x); }    // filter.cpp:55-58 (once per k-mer)
-    /// the same for the per-entry terms: mif_log2 for normal positive arguments, libdevice for anything else
-    __device__ __forceinline__ double shannon_fast(double x, const mif_log2_entry* tab)
-    {
-        return (x >= 2.3e-308 && x < 1.0e300) ? -x * mif_log2(x, tab) : -x * log2(x);
-    }
-
     __device__ __forceinline__ double shfl_xor_f64(unsigned mask, double v, int lane_mask)
     {
         int lo = __double2loint(v), hi = __double2hiint(v);
@@ -30,26 +23,26 @@ namespace ipkgpu
         hi = __shfl_xor_sync(mask, hi, lane_mask);
         return __hiloint2double(hi, lo);
     }
-    __device__ __forceinline__ double shfl_f64(unsigned mask, double v, int src, int width)
-    {
-        int lo = __double2loint(v), hi = __double2hiint(v);
-        lo = __shfl_sync(mask, lo, src, width);
-        hi = __shfl_sync(mask, hi, src, width);
-        return __hiloint2double(hi, lo);
-    }
 
     // ----------------------------------------------------------------------------------------------------------
-    // K4 MIF0.  A CTA owns the k-mers whose first entry lies in its chunk of MIF_CHUNK entries, i.e. a contiguous run of
-    // entries.  The transcendental work (exp10, the division, log2) is done one ENTRY per thread into shared memory;
-    // the two fp64 running sums are then advanced one K-MER per thread, sequentially over that k-mer's entries in stored
-    // (group processing) order -- exactly the order of filter.cpp:78-82,101-108 -- so the accumulation is the
-    // reference's while no lane ever waits for another k-mer's chain.
+    // K4 MIF0.  filter.cpp:60-119 per k-mer with entries x_1..x_n (x = logscore_to_score), T groups, threshold t:
+    //     ss = sum x_i + (T - n) t;   H = T h(t/ss) + sum (h(x_i/ss) - h(t/ss)),  h(w) = -w log2 w;   fv = ss (H - log2 T)
+    // Multiplied out, every division by ss cancels:
+    //     fv = ss (log2 ss - log2 T)  -  sum x_i log2 x_i  -  (T - n) t log2 t
+    // so an entry contributes two numbers that depend on its score alone, x_i and x_i log2 x_i, and a k-mer needs ONE pass
+    // over its entries (the reference's two: the sum, then the weighted terms) and no division.  Same value up to fp64
+    // rounding (~1e-15 relative); the rounding to fp32 differs from the reference's in ~1e-7 of the k-mers, as any other
+    // libm would (tests/parity.py: FV_RTOL).
+    // A CTA owns the k-mers whose first entry lies in its chunk of MIF_CHUNK entries, i.e. a contiguous run of entries.
+    // The transcendental work is done one ENTRY per thread into shared memory; the two fp64 sums are then taken one K-MER
+    // per thread in stored order, or -- from MIF_LONG entries on -- by a warp in a fixed lane order (lane l adds entries
+    // l, l+32, ..., then the xor butterfly): a fixed association per k-mer, whichever path, chunk or GPU it falls into.
     // ----------------------------------------------------------------------------------------------------------
     constexpr int MIF_THREADS = 256;
     constexpr int MIF_CHUNK = 1024;          // entries per CTA chunk (k-mers are assigned by their first entry)
     constexpr int MIF_LONG = 16;             // k-mers with at least this many entries are summed by a warp (fixed lane order)
     constexpr int MIF_CAP = 2048;            // entries a CTA can stage; longer runs take the streaming path
-    constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CHUNK) * 8 + size_t(MIF_CHUNK + 2) * 4 + size_t(MIF_CAP) * 2;
+    constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CAP) * 4 + size_t(MIF_CHUNK + 2) * 4;
 
     /// chunk_first[b] = first k-mer whose entries start at or after b * MIF_CHUNK  (b = 0 .. n_chunks; last = n_kmers)
     __global__ void k4_chunk_first(const uint64_t* __restrict__ offs, uint64_t n_kmers, uint64_t n_chunks, uint32_t* __restrict__ chunk_first)
@@ -69,17 +62,21 @@ namespace ipkgpu
 
     struct mif0_consts
     {
-        double threshold, Hc, T;
+        double threshold, Hc, T, tlog;       // tlog = threshold * log2(threshold)
     };
 
-    /// filter.cpp:86-115 for one k-mer, given the sequential sum of its scores and a callable that yields the
-    /// shannon terms of its entries in stored order
-    __device__ __forceinline__ double mif0_tail_begin(double& score_sum, uint64_t n_entries_kmer, const mif0_consts& C, double& target_threshold)
+    /// x log2 x of an entry's score x in [0, 1] (a float widened to double)
+    __device__ __forceinline__ double mif_xlog2x(double x, const mif_log2_entry* tab)
     {
-        score_sum = __dadd_rn(score_sum, __dmul_rn(C.T - double(n_entries_kmer), C.threshold));            // :86
-        const double weighted_threshold = C.threshold / score_sum;
-        target_threshold = shannon(weighted_threshold);
-        return __dmul_rn(C.T, target_threshold);                                                            // :93
+        return x >= 2.3e-308 ? x * mif_log2(x, tab) : x * log2(x);      // x == 0: 0 * -inf = NaN, as the reference's shannon(0)
+    }
+    /// the filter value from the two sums of a k-mer with n entries
+    __device__ __forceinline__ float mif0_value(double S, double A, uint64_t n, const mif0_consts& C, const mif_log2_entry* tab)
+    {
+        const double rest = C.T - double(n);
+        const double ss = __dadd_rn(S, __dmul_rn(rest, C.threshold));                                       // filter.cpp:86
+        const double l = (ss >= 2.3e-308 && ss < 1.0e300) ? mif_log2(ss, tab) : log2(ss);
+        return float(__dsub_rn(__dsub_rn(__dmul_rn(ss, __dsub_rn(l, C.Hc)), A), __dmul_rn(rest, C.tlog)));
     }
 
     __global__ void __launch_bounds__(MIF_THREADS) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores,
@@ -88,113 +85,75 @@ namespace ipkgpu
     {
         __shared__ mif_log2_entry s_tab[MIF_LOG2_BUCKETS];
         extern __shared__ __align__(16) unsigned char mif_smem[];
-        double* slot = reinterpret_cast<double*>(mif_smem);                     // [MIF_CAP] x (float, low word) while summing; then the entry's shannon term
-        double* ssum = slot + MIF_CAP;                                          // [MIF_CHUNK] per k-mer: score_sum
-        uint32_t* koff = reinterpret_cast<uint32_t*>(ssum + MIF_CHUNK);         // [MIF_CHUNK + 2] per k-mer: first entry, relative to the run
-        uint16_t* seg = reinterpret_cast<uint16_t*>(koff + MIF_CHUNK + 2);      // [MIF_CAP] per entry: its k-mer, relative to the CTA's first
+        double* st = reinterpret_cast<double*>(mif_smem);                       // [MIF_CAP] x log2 x per entry
+        float* sx = reinterpret_cast<float*>(st + MIF_CAP);                     // [MIF_CAP] x per entry
+        uint32_t* koff = reinterpret_cast<uint32_t*>(sx + MIF_CAP);             // [MIF_CHUNK + 2] per k-mer: first entry, relative to the run
         const uint32_t q0 = chunk_first[blockIdx.x], q1 = chunk_first[blockIdx.x + 1];
         if (q0 == q1) return;
         const int tid = threadIdx.x;
-        if (tid < MIF_LOG2_BUCKETS) s_tab[tid] = log2_tab[tid];          // visible after the first barrier below
+        if (tid < MIF_LOG2_BUCKETS) s_tab[tid] = log2_tab[tid];
         const uint32_t nk = q1 - q0;
         const uint64_t e0 = offs[q0], e1 = offs[q1];
         const uint64_t span = e1 - e0;
-        const mif0_consts C{ double(threshold), log2(double(total_num_groups)), double(total_num_groups) };
-        float* xs = reinterpret_cast<float*>(slot);    // xs[2*i] = x of entry i
+        const double thr = double(threshold);
+        const mif0_consts C{ thr, log2(double(total_num_groups)), double(total_num_groups), thr * log2(thr) };
         const int lane = tid & 31, warp = tid >> 5;
         constexpr int MIF_WARPS = MIF_THREADS / 32;
         const unsigned full = 0xffffffffu;
+        __syncthreads();                                           // s_tab
         if (span <= uint64_t(MIF_CAP))
         {
             for (uint32_t j = tid; j <= nk; j += MIF_THREADS) koff[j] = uint32_t(offs[q0 + j] - e0);
-            for (uint32_t i = tid; i < uint32_t(span); i += MIF_THREADS) xs[2 * i] = logscore_to_score(scores[e0 + i]);
-            __syncthreads();
-            // score sums.  Short k-mers: one thread, stored order (filter.cpp:78-82).  Long ones (>= MIF_LONG entries): one
-            // warp, lane l adds entries l, l+32, ... in order, then the xor butterfly -- a fixed association per k-mer,
-            // whichever path or chunk the k-mer falls into.
-            for (uint32_t j = tid; j < nk; j += MIF_THREADS)
-            {
-                const uint32_t a = koff[j], b = koff[j + 1];
-                if (b - a >= uint32_t(MIF_LONG)) continue;
-                double s = 0;
-                for (uint32_t i = a; i < b; ++i) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
-                ssum[j] = s;
-            }
-            for (uint32_t j = warp; j < nk; j += MIF_WARPS)
-            {
-                const uint32_t a = koff[j], b = koff[j + 1];
-                if (b - a < uint32_t(MIF_LONG)) continue;
-                double s = 0;
-                for (uint32_t i = a + lane; i < b; i += 32) { s = __dadd_rn(s, double(xs[2 * i])); seg[i] = uint16_t(j); }
-#pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) s = __dadd_rn(s, shfl_xor_f64(full, s, o));
-                if (lane == 0) ssum[j] = s;
-            }
-            __syncthreads();
-            // every k-mer's score_sum gets its threshold share (:86) -- recomputed by whoever needs it, it is one fp64 fma
             for (uint32_t i = tid; i < uint32_t(span); i += MIF_THREADS)
             {
-                const uint32_t j = seg[i];
-                const double ss = __dadd_rn(ssum[j], __dmul_rn(C.T - double(koff[j + 1] - koff[j]), C.threshold));
-                const double weighted_score = double(xs[2 * i]) / ss;
-                slot[i] = shannon_fast(weighted_score, s_tab);                                                                    // :103-105
+                const float x = logscore_to_score(scores[e0 + i]);
+                sx[i] = x;
+                st[i] = mif_xlog2x(double(x), s_tab);
             }
             __syncthreads();
             for (uint32_t j = tid; j < nk; j += MIF_THREADS)
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
                 if (b - a >= uint32_t(MIF_LONG)) continue;
-                double ss = ssum[j], tt;
-                double H = mif0_tail_begin(ss, b - a, C, tt);
-                for (uint32_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), slot[i]);                        // :107
-                fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));                                            // :115
+                double S = 0, A = 0;
+                for (uint32_t i = a; i < b; ++i) { S = __dadd_rn(S, double(sx[i])); A = __dadd_rn(A, st[i]); }       // stored order (filter.cpp:78-82)
+                fv[q0 + j] = mif0_value(S, A, b - a, C, s_tab);
             }
             for (uint32_t j = warp; j < nk; j += MIF_WARPS)
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
                 if (b - a < uint32_t(MIF_LONG)) continue;
-                double ss = ssum[j], tt;
-                const double H0 = mif0_tail_begin(ss, b - a, C, tt);
-                double d = 0;                                      // sum of (term - target_threshold), same lane order as above
-                for (uint32_t i = a + lane; i < b; i += 32) d = __dadd_rn(d, __dsub_rn(slot[i], tt));
+                double S = 0, A = 0;
+                for (uint32_t i = a + lane; i < b; i += 32) { S = __dadd_rn(S, double(sx[i])); A = __dadd_rn(A, st[i]); }
 #pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) d = __dadd_rn(d, shfl_xor_f64(full, d, o));
-                if (lane == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(__dadd_rn(H0, d), C.Hc)));
+                for (int o = 16; o >= 1; o >>= 1) { S = __dadd_rn(S, shfl_xor_f64(full, S, o)); A = __dadd_rn(A, shfl_xor_f64(full, A, o)); }
+                if (lane == 0) fv[q0 + j] = mif0_value(S, A, b - a, C, s_tab);
             }
             return;
         }
         // streaming path: a run longer than the staging buffer (a k-mer present on thousands of branches).  Straight from
         // global memory, one warp per k-mer, in the same two orders.
-        __syncthreads();                                           // s_tab
         for (uint32_t j = warp; j < nk; j += MIF_WARPS)
         {
             const uint64_t a = offs[q0 + j], b = offs[q0 + j + 1];
-            const bool is_long = b - a >= uint64_t(MIF_LONG);
-            double s = 0;
-            if (is_long)
+            double S = 0, A = 0;
+            if (b - a >= uint64_t(MIF_LONG))
             {
-                for (uint64_t i = a + lane; i < b; i += 32) s = __dadd_rn(s, double(logscore_to_score(scores[i])));
-#pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) s = __dadd_rn(s, shfl_xor_f64(full, s, o));
-            }
-            else if (lane == 0)
-                for (uint64_t i = a; i < b; ++i) s = __dadd_rn(s, double(logscore_to_score(scores[i])));
-            s = shfl_f64(full, s, 0, 32);
-            double ss = s, tt;
-            const double H0 = mif0_tail_begin(ss, b - a, C, tt);
-            double H = H0;
-            if (is_long)
-            {
-                double d = 0;
                 for (uint64_t i = a + lane; i < b; i += 32)
-                    d = __dadd_rn(d, __dsub_rn(shannon_fast(double(logscore_to_score(scores[i])) / ss, s_tab), tt));
+                {
+                    const double x = double(logscore_to_score(scores[i]));
+                    S = __dadd_rn(S, x); A = __dadd_rn(A, mif_xlog2x(x, s_tab));
+                }
 #pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) d = __dadd_rn(d, shfl_xor_f64(full, d, o));
-                H = __dadd_rn(H0, d);
+                for (int o = 16; o >= 1; o >>= 1) { S = __dadd_rn(S, shfl_xor_f64(full, S, o)); A = __dadd_rn(A, shfl_xor_f64(full, A, o)); }
             }
             else if (lane == 0)
-                for (uint64_t i = a; i < b; ++i) H = __dadd_rn(__dsub_rn(H, tt), shannon_fast(double(logscore_to_score(scores[i])) / ss, s_tab));
-            if (lane == 0) fv[q0 + j] = float(__dmul_rn(ss, __dsub_rn(H, C.Hc)));
+                for (uint64_t i = a; i < b; ++i)
+                {
+                    const double x = double(logscore_to_score(scores[i]));
+                    S = __dadd_rn(S, x); A = __dadd_rn(A, mif_xlog2x(x, s_tab));
+                }
+            if (lane == 0) fv[q0 + j] = mif0_value(S, A, b - a, C, s_tab);
         }
     }
 
