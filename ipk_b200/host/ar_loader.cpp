@@ -21,6 +21,10 @@
 namespace
 {
     thread_local std::string g_error;
+}
+namespace ipkhost { void set_last_error(const std::string& s) { g_error = s; } }      // plan.cpp, ipk_file.cpp
+namespace
+{
 
     int fail(int code, const std::string& what)
     {

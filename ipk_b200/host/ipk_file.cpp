@@ -5,10 +5,13 @@
 // buffered in 8 MiB blocks: the reference's per-field Boost archive calls are its stage-3 bottleneck.
 #include "ipkhost.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
+#include <unistd.h>
 
 namespace
 {
@@ -21,10 +24,12 @@ namespace
         FILE* f;
         std::vector<unsigned char> buf;
         bool ok = true;
+        uint64_t total = 0;               // bytes flushed so far
         explicit writer(FILE* f_) : f(f_) { buf.reserve(8u << 20); }
         void flush()
         {
             if (!buf.empty() && fwrite(buf.data(), 1, buf.size(), f) != buf.size()) ok = false;
+            total += buf.size();
             buf.clear();
         }
         void raw(const void* p, size_t n)
@@ -63,46 +68,122 @@ struct ipkhost_db_file
     std::vector<uint32_t> branch;
 };
 
+namespace
+{
+    /// bytes of the part of the file before the first k-mer record
+    void put_header(writer& w, const ipkhost_db* db)
+    {
+        // boost::archive::binary_oarchive with default flags (db_builder.cpp:176-177): basic_binary_oarchive::init writes the
+        // signature string and the library version, basic_binary_oprimitive::init the sizes of int / long / float / double as
+        // one byte each and int(1) for the endianness check.
+        w.put<uint64_t>(sizeof PREAMBLE - 1);
+        w.raw(PREAMBLE, sizeof PREAMBLE - 1);
+        w.put<uint16_t>(ARCHIVE_VERSION);
+        w.put<uint8_t>(sizeof(int)); w.put<uint8_t>(sizeof(long)); w.put<uint8_t>(sizeof(float)); w.put<uint8_t>(sizeof(double));
+        w.put<int32_t>(1);
+        // ipk_header (db_builder.cpp:297-305): sequence_type, tree_index, tree, kmer_size, omega, num_kmers, num_entries
+        w.str(db->sequence_type);
+        w.put<uint64_t>(db->n_index);
+        for (uint64_t i = 0; i < db->n_index; ++i)
+        {
+            w.put<uint64_t>(db->index_num_nodes[i]);
+            w.put<double>(db->index_subtree_branch_length[i]);
+        }
+        w.str(db->tree);
+        w.put<uint64_t>(db->kmer_size);
+        w.put<float>(db->omega);
+        w.put<uint64_t>(db->n_kmers);
+        w.put<uint64_t>(db->n_entries);
+    }
+
+    inline uint64_t entries_of(const ipkhost_db* db, uint64_t q) { return db->counts ? db->counts[q] : db->offsets[q + 1] - db->offsets[q]; }
+
+    /// k-mers [q0, q1) formatted into private blocks and written at file offset `at` (record = 20 + 8 n bytes)
+    bool write_range(int fd, const ipkhost_db* db, uint64_t q0, uint64_t q1, uint64_t at)
+    {
+        const size_t BLOCK = 8u << 20;
+        std::vector<unsigned char> buf(BLOCK + 64);
+        size_t fill = 0;
+        auto flush = [&]() -> bool {
+            size_t done = 0;
+            while (done < fill)
+            {
+                const ssize_t r = pwrite(fd, buf.data() + done, fill - done, off_t(at + done));
+                if (r <= 0) return false;
+                done += size_t(r);
+            }
+            at += fill; fill = 0;
+            return true;
+        };
+        for (uint64_t q = q0; q < q1; ++q)
+        {
+            const uint64_t a = db->offsets[q], n = entries_of(db, q);
+            if (fill + 20 > BLOCK && !flush()) return false;
+            unsigned char* p = buf.data() + fill;
+            memcpy(p, &db->keys[q], 8); memcpy(p + 8, &db->fv[q], 4); memcpy(p + 12, &n, 8);
+            fill += 20;
+            for (uint64_t e = a; e < a + n;)
+            {
+                if (fill + 8 > BLOCK && !flush()) return false;
+                const uint64_t room = (BLOCK - fill) / 8, m = std::min<uint64_t>(room, a + n - e);
+                unsigned char* o = buf.data() + fill;
+                if (db->branch16) for (uint64_t i = 0; i < m; ++i) { const uint32_t b = db->branch16[e + i]; memcpy(o + 8 * i, &b, 4); memcpy(o + 8 * i + 4, &db->score[e + i], 4); }
+                else for (uint64_t i = 0; i < m; ++i) { memcpy(o + 8 * i, &db->branch[e + i], 4); memcpy(o + 8 * i + 4, &db->score[e + i], 4); }
+                fill += size_t(m) * 8;
+                e += m;
+            }
+        }
+        return flush();
+    }
+}
+
 extern "C"
 {
 
-int ipkhost_write_ipk(const char* path, const ipkhost_db* db)
+int ipkhost_write_ipk_mt(const char* path, const ipkhost_db* db, int n_threads)
 {
     if (!path || !db) return IPKHOST_EINVAL;
     if (db->n_kmers && (!db->keys || !db->fv || !db->offsets)) return IPKHOST_EINVAL;
     if (db->n_entries && ((!db->branch && !db->branch16) || !db->score)) return IPKHOST_EINVAL;
     FILE* f = fopen(path, "wb");
     if (!f) return IPKHOST_EIO;
-    writer w(f);
-    w.put<uint64_t>(sizeof PREAMBLE - 1);
-    w.raw(PREAMBLE, sizeof PREAMBLE - 1);
-    w.put<uint16_t>(ARCHIVE_VERSION);
-    // ipk_header (db_builder.cpp:297-305): sequence_type, tree_index, tree, kmer_size, omega, num_kmers, num_entries
-    w.str(db->sequence_type);
-    w.put<uint64_t>(db->n_index);
-    for (uint64_t i = 0; i < db->n_index; ++i)
+    uint64_t header_bytes = 0;
     {
-        w.put<uint64_t>(db->index_num_nodes[i]);
-        w.put<double>(db->index_subtree_branch_length[i]);
+        writer w(f);
+        put_header(w, db);
+        header_bytes = w.total + w.buf.size();
+        w.flush();
+        if (!w.ok || fflush(f) != 0) { fclose(f); return IPKHOST_EIO; }
     }
-    w.str(db->tree);
-    w.put<uint64_t>(db->kmer_size);
-    w.put<float>(db->omega);
-    w.put<uint64_t>(db->n_kmers);
-    w.put<uint64_t>(db->n_entries);
-    // save_phylo_kmer(kmer, filter_value, entries) in the order handed over (db_builder.cpp:323-332)
-    for (uint64_t q = 0; q < db->n_kmers; ++q)
+    // save_phylo_kmer(kmer, filter_value, entries) in the order handed over (db_builder.cpp:323-332): the k-mers are cut
+    // into runs of about equal bytes, one thread formats and pwrites each run at its prefix-summed offset
+    unsigned T = n_threads > 0 ? unsigned(n_threads) : std::max(1u, std::thread::hardware_concurrency());
+    T = unsigned(std::min<uint64_t>(T, std::max<uint64_t>(1, db->n_kmers / 4096)));
+    const uint64_t total = db->n_kmers * 20 + db->n_entries * 8;
+    std::vector<uint64_t> cut(T + 1, db->n_kmers), at(T + 1, total);
+    cut[0] = 0; at[0] = 0;
     {
-        const uint64_t a = db->offsets[q], b = db->counts ? a + db->counts[q] : db->offsets[q + 1];
-        w.put<uint64_t>(db->keys[q]);
-        w.put<float>(db->fv[q]);
-        w.put<uint64_t>(b - a);
-        for (uint64_t e = a; e < b; ++e) { w.put<uint32_t>(db->branch16 ? uint32_t(db->branch16[e]) : db->branch[e]); w.put<float>(db->score[e]); }
+        uint64_t acc = 0, next = 1;
+        for (uint64_t q = 0; q < db->n_kmers && next < T; ++q)
+        {
+            while (next < T && acc >= total / T * next) { cut[next] = q; at[next] = acc; ++next; }
+            acc += 20 + 8 * entries_of(db, q);
+        }
+        // cuts never reached (the last k-mers are long) stay at the end: empty ranges
     }
-    w.flush();
-    const bool ok = w.ok && fclose(f) == 0;
-    return ok ? IPKHOST_OK : IPKHOST_EIO;
+    const int fd = fileno(f);
+    std::vector<char> ok(T, 1);
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < T; ++t)
+        th.emplace_back([&, t] { ok[t] = write_range(fd, db, cut[t], cut[t + 1], header_bytes + at[t]) ? 1 : 0; });
+    for (auto& x : th) x.join();
+    bool good = true;
+    for (char c : ok) good = good && c;
+    good = fclose(f) == 0 && good;
+    return good ? IPKHOST_OK : IPKHOST_EIO;
 }
+
+int ipkhost_write_ipk(const char* path, const ipkhost_db* db) { return ipkhost_write_ipk_mt(path, db, 0); }
 
 int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
 {
@@ -115,7 +196,10 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
     auto d = new ipkhost_db_file();
     const std::string pre = r.str();
     const uint16_t ver = r.get<uint16_t>();
-    if (!r.ok || pre != PREAMBLE || ver != ARCHIVE_VERSION) { fclose(f); delete d; return IPKHOST_EFORMAT; }
+    const uint8_t s_int = r.get<uint8_t>(), s_long = r.get<uint8_t>(), s_float = r.get<uint8_t>(), s_double = r.get<uint8_t>();
+    const int32_t one = r.get<int32_t>();
+    if (!r.ok || pre != PREAMBLE || ver != ARCHIVE_VERSION || s_int != sizeof(int) || s_long != sizeof(long) || s_float != sizeof(float) ||
+        s_double != sizeof(double) || one != 1) { fclose(f); delete d; return IPKHOST_EFORMAT; }
     d->sequence_type = r.str();
     const uint64_t n_index = r.get<uint64_t>();
     if (!r.ok || n_index > (1ull << 32)) { fclose(f); delete d; return IPKHOST_EFORMAT; }

@@ -37,10 +37,33 @@ int  ipkhost_ar_read_nodes(ipkhost_ar* ar, const char* const* labels, uint32_t n
 /* the csv reader's float parser alone (known-answer tests against the reference's own csv.h) */
 int  ipkhost_parse_float(const char* text, float* out);
 
+/* ---- build plan: everything ipk::build is handed besides the posteriors (ipk/src/main.cpp:145-198) -----------------
+ * original tree (newick text) -> ghost-node injection (extended_tree.cpp:76-155) -> ghost selection and grouping
+ * (db_builder.cpp:495-553) -> extended label -> AR label through the AR tree (ar::map_nodes, ar.cpp:790-834; the AR tree
+ * is re-rooted first when raxml-ng unrooted it, extended_tree.cpp:186-205) -> tree index (db_builder.cpp:191-197).
+ * ar_tree_newick may be NULL: the posteriors are then keyed by the extended labels themselves.
+ * ghost_strategy: 0 both (default), 1 inner only (_X0), 2 outer only (_X1).  An unrooted original tree is IPKHOST_EINVAL
+ * unless use_unrooted (extended_tree.cpp:169-177). */
+typedef struct ipkhost_plan ipkhost_plan;
+int  ipkhost_plan_create(const char* original_newick, const char* ar_tree_newick, int ghost_strategy, int use_unrooted, ipkhost_plan** out);
+void ipkhost_plan_free(ipkhost_plan* p);
+uint32_t ipkhost_plan_num_ghosts(const ipkhost_plan* p);                  /* ghost matrices to load, in processing order */
+uint32_t ipkhost_plan_num_groups(const ipkhost_plan* p);
+const char* ipkhost_plan_ext_label(const ipkhost_plan* p, uint32_t i);    /* label in the extended tree ("17_X1") */
+const char* ipkhost_plan_ar_label(const ipkhost_plan* p, uint32_t i);     /* label of the same node in the AR output */
+const uint32_t* ipkhost_plan_node_branch(const ipkhost_plan* p);          /* [num_ghosts] post-order id of the ORIGINAL node */
+uint32_t ipkhost_plan_node_count(const ipkhost_plan* p);                  /* original_tree.get_node_count() */
+const uint64_t* ipkhost_plan_index_num_nodes(const ipkhost_plan* p);      /* [node_count] tree index, post-order */
+const double* ipkhost_plan_index_lengths(const ipkhost_plan* p);
+const char* ipkhost_plan_newick(const ipkhost_plan* p);                   /* to_newick(original_tree): the header's tree */
+const char* ipkhost_plan_extended_newick(const ipkhost_plan* p);          /* what save_extended_tree writes (main.cpp:39-46) */
+
 /* ---- .ipk database file ------------------------------------------------------------------------------------
  * Layout (UNVERIFIED against i2l, whose source is absent here -- SURVEY.md 8f1; everything below is written and read
  * through this one module so that a correction is local):
- *   "serialization::archive" preamble of a Boost binary_oarchive: u64 length 22, the 22 bytes, u16 version 19,
+ *   preamble of a boost::archive::binary_oarchive with default flags (db_builder.cpp:176-177): u64 length 22, the 22 bytes
+ *   "serialization::archive", u16 library version 19 (BOOST_ARCHIVE_VERSION of Boost 1.76 - 1.8x), then what
+ *   basic_binary_oprimitive::init adds: u8 sizeof(int), u8 sizeof(long), u8 sizeof(float), u8 sizeof(double), i32 1;
  *   then raw little-endian primitives:
  *   header   string sequence_type ("DNA" | "Proteins"); u64 n_index, n_index x { u64 num_nodes; f64 subtree_branch_length };
  *            string tree (newick); u64 kmer_size; f32 omega; u64 num_kmers; u64 num_entries
@@ -66,7 +89,10 @@ typedef struct ipkhost_db
     const uint16_t* branch16;                  /* NULL, or the branch ids as 16-bit values (ipkgpu's IPKGPU_RESULT_BRANCH16) */
 } ipkhost_db;
 
-int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);
+int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);                 /* all cores */
+/* n_threads <= 0: all cores.  The k-mers are cut into runs of equal bytes (a record is 20 + 8 n bytes), every thread
+ * formats its run into private 8 MiB blocks and pwrites them at the prefix-summed offset. */
+int  ipkhost_write_ipk_mt(const char* path, const ipkhost_db* db, int n_threads);
 /* reads a file written by ipkhost_write_ipk; arrays are owned by the returned handle */
 typedef struct ipkhost_db_file ipkhost_db_file;
 int  ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view);

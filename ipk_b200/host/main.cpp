@@ -1,14 +1,20 @@
-// main.cpp -- ipk-b200: the database-build half of `ipk-dna` / `ipk-aa` (ipk/src/main.cpp:76-246, ipk::build) on a B200.
+// main.cpp -- ipk-b200: the database build of `ipk-dna` / `ipk-aa` (ipk/src/main.cpp:76-246, ipk::build) on a B200.
 //
-// It starts where the reference's hot path starts -- ancestral reconstruction done, ghost nodes mapped to branches --
-// and ends where it ends, with the serialized database:
-//     raxml-ng ancestralProbs (--ar-probs)  +  ghost node -> branch table (--node-map)
-//         -> libipkgpu (include/ipkgpu.h): enumerate, per-branch max, regroup, filter values, order
-//         -> DB.ipk (--output)
-// Options keep the reference's names and defaults where it has them (ipk/src/command_line.cpp:83-147): -k (8), --omega
-// (1.5), --mif0 | --random, -o/--output (<workdir>/DB.ipk), -w/--workdir.  Tree extension, alignment reduction and the
-// raxml-ng run itself stay upstream (out of scope); --node-map is what extended_tree + ar::mapping boil
-// down to for this path: one line `AR-node-label <TAB> post-order id of the original branch`, in processing order.
+// Two ways in:
+//  (1) the reference's own command line (ipk/src/command_line.cpp:83-147), exactly as ipk.py:292-329 spawns it:
+//          ipk-dna --ar-binary X --refalign A.fasta -t TREE -w DIR -k K --model M --alpha A --categories C
+//                  --reduction-ratio R --omega W --mif0|--random --both|--inner-only|--outer-only -u MU -j N -o OUT -v V
+//                  [--ar-dir DIR] [--ar-only] [--ar-parameters "..."] [--no-reduction] [--use-unrooted] [--uncompressed] [--on-disk]
+//      Ancestral reconstruction stays the upstream CPU stage it is in BASELINE.json: --ar-dir must point at raxml-ng's
+//      `*.raxml.ancestralProbs` / `*.raxml.ancestralTree` (the reference's own resume point, ar.cpp:610-640); everything
+//      after it is done here: original tree -> ghost nodes -> extended/AR label mapping -> ghost selection and grouping ->
+//      posteriors -> libipkgpu -> tree index + DB.ipk.  Options that only steer raxml-ng or the alignment reduction are
+//      parsed and ignored (the alignment is only needed to RUN the reconstruction); -u/--mu and --BB/--DC/--DCLA/--DCCW are
+//      parsed and ignored as the reference build itself ignores them; --on-disk needs no flag here (the device
+//      path batches by itself when the emitted volume exceeds its memory) and is accepted.
+//      The alphabet comes from the executable's name like the reference's three binaries (ipk-dna, ipk-aa), or --states.
+//  (2) the build half alone: --ar-probs FILE --node-map FILE (`AR-node-label <TAB> post-order id of the branch`, in
+//      processing order), for callers that have done the tree work themselves.
 // Errors: message on stderr, exit status 1 (main.cpp:225-246).
 #include "ipkhost.h"
 #include "../../include/ipkgpu.h"
@@ -23,33 +29,46 @@
 #include <string>
 #include <memory>
 #include <vector>
+#include <dirent.h>
+#include <sys/stat.h>
 
 namespace
 {
     struct options
     {
-        std::string ar_probs, node_map, tree_file, output, workdir = ".";
-        std::string states = "dna";
+        std::string ar_probs, node_map, tree_file, output, workdir = ".", ar_dir, refalign;
+        std::string states;
         uint32_t k = 8;
         float omega = 1.5f;
         int filter = IPKGPU_FILTER_MIF0;
         uint32_t node_count = 0;
-        int device = 0, threads = 0;
-        bool dump = false;
+        int device = 0, threads = 0, verbosity = 1;
+        int ghosts = 0;                    // 0 both, 1 inner only, 2 outer only
+        bool dump = false, use_unrooted = false, ar_only = false, merge_branches = false;
     };
 
     [[noreturn]] void usage(const char* why)
     {
         if (why) fprintf(stderr, "ipk-b200: %s\n", why);
         fprintf(stderr,
-                "usage: ipk-b200 --ar-probs FILE --node-map FILE [--states dna|aa] [-k K] [--omega W] [--mif0|--random]\n"
-                "                [--tree NEWICK] [--node-count N] [-w DIR] [-o DB.ipk] [--device N] [-j THREADS] [--dump]\n");
+                "usage: ipk-b200 --refalign FASTA -t|--reftree NEWICK --ar-dir DIR [-k K] [--omega W] [--mif0|--random]\n"
+                "                [--both|--inner-only|--outer-only] [--use-unrooted] [-w DIR] [-o DB.ipk] [--states dna|aa]\n"
+                "                [-j THREADS] [-v N] [--device N] [--dump]   (and every other ipk-dna / ipk-aa option, see main.cpp)\n"
+                "   or: ipk-b200 --ar-probs FILE --node-map FILE [--tree NEWICK] [--node-count N] [...]\n");
         exit(1);
     }
 
     options parse(int argc, char** argv)
     {
         options o;
+        {
+            // ipk-dna / ipk-aa / ipk-aa-pos pick the alphabet at compile time (ipk/CMakeLists.txt); here by the name invoked
+            std::string self = argc ? argv[0] : "";
+            const size_t slash = self.find_last_of('/');
+            if (slash != std::string::npos) self = self.substr(slash + 1);
+            if (self.find("-pos") != std::string::npos) { fprintf(stderr, "ipk-b200: --keep-positions builds are not supported\n"); exit(1); }
+            o.states = self.find("aa") != std::string::npos ? "aa" : "dna";
+        }
         auto need = [&](int& i) -> const char* { if (i + 1 >= argc) usage((std::string("missing value for ") + argv[i]).c_str()); return argv[++i]; };
         for (int i = 1; i < argc; ++i)
         {
@@ -57,25 +76,81 @@ namespace
             if (a == "--ar-probs") o.ar_probs = need(i);
             else if (a == "--node-map") o.node_map = need(i);
             else if (a == "--tree" || a == "-t" || a == "--reftree") o.tree_file = need(i);
+            else if (a == "--refalign") o.refalign = need(i);
+            else if (a == "--ar-dir") o.ar_dir = need(i);
             else if (a == "--states") o.states = need(i);
             else if (a == "-k" || a == "--k") o.k = uint32_t(atoi(need(i)));
             else if (a == "--omega") o.omega = float(atof(need(i)));
             else if (a == "--mif0") o.filter = IPKGPU_FILTER_MIF0;
             else if (a == "--random") o.filter = IPKGPU_FILTER_RANDOM;
+            else if (a == "--both") o.ghosts = 0;
+            else if (a == "--inner-only") o.ghosts = 1;
+            else if (a == "--outer-only") o.ghosts = 2;
+            else if (a == "--use-unrooted") o.use_unrooted = true;
+            else if (a == "--ar-only") o.ar_only = true;
+            else if (a == "--merge-branches") o.merge_branches = true;
             else if (a == "--node-count") o.node_count = uint32_t(atoll(need(i)));
             else if (a == "-w" || a == "--workdir") o.workdir = need(i);
             else if (a == "-o" || a == "--output") o.output = need(i);
             else if (a == "--device") o.device = atoi(need(i));
             else if (a == "-j" || a == "--num-threads") o.threads = atoi(need(i));
+            else if (a == "-v" || a == "--verbosity") o.verbosity = atoi(need(i));
             else if (a == "--dump") o.dump = true;
-            else if (a == "-u" || a == "--mu") need(i);                 // accepted and ignored, as the reference build does
+            // parsed and ignored: they steer raxml-ng / the alignment reduction (upstream), or nothing at all in the reference build
+            else if (a == "--ar-binary" || a == "-m" || a == "--model" || a == "-a" || a == "--alpha" || a == "--categories" ||
+                     a == "--reduction-ratio" || a == "-u" || a == "--mu") need(i);
+            else if (a == "--ar-parameters")
+            {
+                // ipk.py passes the value inside literal quotes, possibly split by the shell: swallow up to the closing quote (command_line.cpp:170-207)
+                std::string v = need(i);
+                if (!v.empty() && (v[0] == '"' || v[0] == '\''))
+                {
+                    const char q = v[0];
+                    while ((v.size() < 2 || v.back() != q) && i + 1 < argc) v = argv[++i];
+                }
+            }
+            else if (a == "--no-reduction" || a == "--uncompressed" || a == "--on-disk" || a == "--BB" || a == "--DC" || a == "--DCLA" || a == "--DCCW") {}
             else if (a == "--help" || a == "-h") usage(nullptr);
             else usage(("unknown option " + a).c_str());
         }
-        if (o.ar_probs.empty() || o.node_map.empty()) usage("--ar-probs and --node-map are required");
         if (o.states != "dna" && o.states != "aa") usage("--states must be dna or aa");
+        const bool reference_mode = o.ar_probs.empty() && o.node_map.empty();
+        if (reference_mode)
+        {
+            if (o.tree_file.empty()) usage("the option '--reftree' is required but missing");       // boost::program_options' wording
+            if (o.ar_dir.empty())
+                usage("--ar-dir is required: ancestral reconstruction is the upstream CPU stage (run raxml-ng through the reference's --ar-only, "
+                      "then point --ar-dir at its *.raxml.ancestralProbs / *.raxml.ancestralTree)");
+        }
+        else if (o.ar_probs.empty() || o.node_map.empty()) usage("--ar-probs and --node-map go together");
+        if (o.merge_branches) { fprintf(stderr, "ipk-b200: --merge-branches is not supported by this build\n"); exit(1); }
         if (o.output.empty()) o.output = o.workdir + "/DB.ipk";         // command_line.cpp:259-263
         return o;
+    }
+
+    std::string read_text(const std::string& path)
+    {
+        std::ifstream in(path);
+        if (!in) throw std::runtime_error("cannot open " + path);
+        std::stringstream ss;
+        ss << in.rdbuf();
+        return ss.str();
+    }
+
+    /// find_file_by_suffix (ar.cpp:594-608); the lexicographically first match, so that the choice does not depend on readdir order
+    std::string find_by_suffix(const std::string& dir, const std::string& suffix)
+    {
+        DIR* d = opendir(dir.c_str());
+        if (!d) throw std::runtime_error("Error! No such directory: " + dir);
+        std::string best;
+        while (const dirent* e = readdir(d))
+        {
+            const std::string name = e->d_name;
+            if (name.size() >= suffix.size() && name.compare(name.size() - suffix.size(), suffix.size(), suffix) == 0 && (best.empty() || name < best)) best = name;
+        }
+        closedir(d);
+        if (best.empty()) throw std::runtime_error("Could not find \"*" + suffix + "\" in the folder provided by --ar-dir: " + dir);
+        return dir + "/" + best;
     }
 
     double seconds_since(std::chrono::steady_clock::time_point t0)
@@ -91,10 +166,44 @@ int main(int argc, char** argv)
         const options o = parse(argc, argv);
         const uint32_t sigma = o.states == "dna" ? 4 : 20, bits = o.states == "dna" ? 2 : 5;
 
-        // ---- node map: processing order of the ghost nodes and the branch each belongs to (db_builder.cpp:495-553)
         std::vector<std::string> labels;
         std::vector<uint32_t> node_branch;
+        std::vector<uint64_t> index_num_nodes;
+        std::vector<double> index_lengths;
+        std::string tree, ar_probs = o.ar_probs;
+        uint32_t node_count = 0;
+        if (o.node_map.empty())
         {
+            // ---- the reference's path from the tree to ipk::build's arguments (main.cpp:145-198)
+            ar_probs = find_by_suffix(o.ar_dir, ".raxml.ancestralProbs");
+            const std::string ar_tree_file = find_by_suffix(o.ar_dir, ".raxml.ancestralTree");
+            if (o.verbosity > 0)
+                fprintf(stderr, "Ancestral reconstruction results have been found:\n\t%s\n\t%s\n", ar_probs.c_str(), ar_tree_file.c_str());
+            if (o.ar_only)
+            {
+                if (o.verbosity > 0) fprintf(stderr, "--ar-only requested. Finishing after ancestral reconstruction.\n");
+                return 0;
+            }
+            ipkhost_plan* plan = nullptr;
+            if (ipkhost_plan_create(read_text(o.tree_file).c_str(), read_text(ar_tree_file).c_str(), o.ghosts, o.use_unrooted ? 1 : 0, &plan) != IPKHOST_OK)
+                throw std::runtime_error(ipkhost_last_error());
+            const uint32_t n = ipkhost_plan_num_ghosts(plan);
+            for (uint32_t i = 0; i < n; ++i) labels.push_back(ipkhost_plan_ar_label(plan, i));
+            node_branch.assign(ipkhost_plan_node_branch(plan), ipkhost_plan_node_branch(plan) + n);
+            node_count = ipkhost_plan_node_count(plan);
+            index_num_nodes.assign(ipkhost_plan_index_num_nodes(plan), ipkhost_plan_index_num_nodes(plan) + node_count);
+            index_lengths.assign(ipkhost_plan_index_lengths(plan), ipkhost_plan_index_lengths(plan) + node_count);
+            tree = ipkhost_plan_newick(plan);
+            // save_extended_tree (main.cpp:39-46)
+            const std::string ext_dir = o.workdir + "/extended_trees";
+            mkdir(ext_dir.c_str(), 0777);
+            std::ofstream(ext_dir + "/extended_tree.newick") << ipkhost_plan_extended_newick(plan) << "\n";
+            if (o.verbosity > 0) fprintf(stderr, "%u ghost nodes in %u branch groups of a %u-node tree\n", n, ipkhost_plan_num_groups(plan), node_count);
+            ipkhost_plan_free(plan);
+        }
+        else
+        {
+            // ---- node map: processing order of the ghost nodes and the branch each belongs to (db_builder.cpp:495-553)
             std::ifstream in(o.node_map);
             if (!in) throw std::runtime_error("cannot open " + o.node_map);
             std::string line;
@@ -106,15 +215,31 @@ int main(int argc, char** argv)
                 labels.push_back(line.substr(0, tab));
                 node_branch.push_back(uint32_t(std::stoul(line.substr(tab + 1))));
             }
+            uint32_t max_branch = 0;
+            for (uint32_t b : node_branch) max_branch = std::max(max_branch, b);
+            node_count = o.node_count ? o.node_count : max_branch + 2;      // original_tree.get_node_count(): branches + root
+            if (!o.tree_file.empty())
+            {
+                // with a tree the header gets its index and the canonical newick; without, both stay empty
+                tree = read_text(o.tree_file);
+                ipkhost_plan* plan = nullptr;
+                if (ipkhost_plan_create(tree.c_str(), nullptr, 0, 1, &plan) == IPKHOST_OK)
+                {
+                    const uint32_t nc = ipkhost_plan_node_count(plan);
+                    index_num_nodes.assign(ipkhost_plan_index_num_nodes(plan), ipkhost_plan_index_num_nodes(plan) + nc);
+                    index_lengths.assign(ipkhost_plan_index_lengths(plan), ipkhost_plan_index_lengths(plan) + nc);
+                    tree = ipkhost_plan_newick(plan);
+                    if (!o.node_count) node_count = nc;
+                    ipkhost_plan_free(plan);
+                }
+                else while (!tree.empty() && (tree.back() == '\n' || tree.back() == '\r')) tree.pop_back();
+            }
         }
-        uint32_t max_branch = 0;
-        for (uint32_t b : node_branch) max_branch = std::max(max_branch, b);
-        const uint32_t node_count = o.node_count ? o.node_count : max_branch + 2;      // original_tree.get_node_count(): branches + root
 
         // ---- posteriors
         auto t0 = std::chrono::steady_clock::now();
         ipkhost_ar* ar = nullptr;
-        if (ipkhost_ar_open(o.ar_probs.c_str(), sigma, o.threads, &ar) != IPKHOST_OK) throw std::runtime_error(ipkhost_last_error());
+        if (ipkhost_ar_open(ar_probs.c_str(), sigma, o.threads, &ar) != IPKHOST_OK) throw std::runtime_error(ipkhost_last_error());
         const uint32_t width = ipkhost_ar_width(ar);
         std::vector<const char*> label_ptrs;
         for (auto& s : labels) label_ptrs.push_back(s.c_str());
@@ -154,26 +279,20 @@ int main(int argc, char** argv)
 
         // ---- serialize
         t0 = std::chrono::steady_clock::now();
-        std::string tree;
-        if (!o.tree_file.empty())
-        {
-            std::ifstream tf(o.tree_file);
-            if (!tf) throw std::runtime_error("cannot open " + o.tree_file);
-            std::stringstream ss;
-            ss << tf.rdbuf();
-            tree = ss.str();
-            while (!tree.empty() && (tree.back() == '\n' || tree.back() == '\r')) tree.pop_back();
-        }
         ipkhost_db db;
         memset(&db, 0, sizeof db);
         db.sequence_type = sigma == 4 ? "DNA" : "Proteins";
         db.tree = tree.c_str();
+        db.n_index = index_num_nodes.size();
+        db.index_num_nodes = index_num_nodes.data();
+        db.index_subtree_branch_length = index_lengths.data();
         db.kmer_size = o.k;
         db.omega = o.omega;
         db.n_kmers = res.n_kmers; db.n_entries = res.n_entries;
         db.keys = res.keys; db.fv = res.fv; db.offsets = res.offsets; db.counts = res.counts; db.branch = res.branch; db.branch16 = res.branch16; db.score = res.score;
-        if (ipkhost_write_ipk(o.output.c_str(), &db) != IPKHOST_OK) throw std::runtime_error("cannot write " + o.output);
-        fprintf(stderr, "Wrote %s in %.3f s\n", o.output.c_str(), seconds_since(t0));
+        if (ipkhost_write_ipk_mt(o.output.c_str(), &db, o.threads) != IPKHOST_OK) throw std::runtime_error("cannot write " + o.output);
+        fprintf(stderr, "Wrote %s in %.3f s (record layout as documented in ipkhost.h: UNVERIFIED against i2l's serializer, whose source is not available)\n",
+                o.output.c_str(), seconds_since(t0));
         if (o.dump)
             for (uint64_t q = 0; q < res.n_kmers; ++q)
                 for (uint64_t e = res.offsets[q]; e < (res.counts ? res.offsets[q] + res.counts[q] : res.offsets[q + 1]); ++e)

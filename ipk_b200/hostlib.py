@@ -47,6 +47,19 @@ def load() -> C.CDLL:
         lib.ipkhost_read_ipk.argtypes = [C.c_char_p, P(C.c_void_p), P(HostDb)]
         lib.ipkhost_free_ipk.argtypes = [C.c_void_p]
         lib.ipkhost_free_ipk.restype = None
+        lib.ipkhost_write_ipk_mt.argtypes = [C.c_char_p, P(HostDb), C.c_int]
+        lib.ipkhost_plan_create.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, P(C.c_void_p)]
+        lib.ipkhost_plan_free.argtypes = [C.c_void_p]
+        lib.ipkhost_plan_free.restype = None
+        for name, res in (("num_ghosts", C.c_uint32), ("num_groups", C.c_uint32), ("node_count", C.c_uint32), ("node_branch", P(C.c_uint32)),
+                          ("index_num_nodes", P(C.c_uint64)), ("index_lengths", P(C.c_double)), ("newick", C.c_char_p), ("extended_newick", C.c_char_p)):
+            fn = getattr(lib, "ipkhost_plan_" + name)
+            fn.argtypes = [C.c_void_p]
+            fn.restype = res
+        for name in ("ext_label", "ar_label"):
+            fn = getattr(lib, "ipkhost_plan_" + name)
+            fn.argtypes = [C.c_void_p, C.c_uint32]
+            fn.restype = C.c_char_p
         _lib = lib
     return _lib
 
@@ -86,8 +99,29 @@ def read_ar(path: str, sigma: int, labels: list[str] | None = None, threads: int
         lib.ipkhost_ar_close(h)
 
 
+def plan(newick: str, ar_tree: str | None = None, ghosts: str = "both", use_unrooted: bool = False) -> dict:
+    """the build plan of ipkhost.h: ghost nodes in processing order (extended / AR labels, branch of each), tree index, trees"""
+    lib = load()
+    h = C.c_void_p(0)
+    rc = lib.ipkhost_plan_create(newick.encode(), ar_tree.encode() if ar_tree is not None else None,
+                                 {"both": 0, "inner-only": 1, "outer-only": 2}[ghosts], 1 if use_unrooted else 0, C.byref(h))
+    if rc != 0:
+        raise HostError(rc, lib.ipkhost_last_error().decode())
+    try:
+        n, nc = lib.ipkhost_plan_num_ghosts(h), lib.ipkhost_plan_node_count(h)
+        return dict(n_groups=lib.ipkhost_plan_num_groups(h), node_count=nc,
+                    ext_labels=[lib.ipkhost_plan_ext_label(h, i).decode() for i in range(n)],
+                    ar_labels=[lib.ipkhost_plan_ar_label(h, i).decode() for i in range(n)],
+                    node_branch=np.ctypeslib.as_array(lib.ipkhost_plan_node_branch(h), (n,)).copy() if n else np.zeros(0, np.uint32),
+                    index_num_nodes=np.ctypeslib.as_array(lib.ipkhost_plan_index_num_nodes(h), (nc,)).copy(),
+                    index_len=np.ctypeslib.as_array(lib.ipkhost_plan_index_lengths(h), (nc,)).copy(),
+                    newick=lib.ipkhost_plan_newick(h).decode(), extended_newick=lib.ipkhost_plan_extended_newick(h).decode())
+    finally:
+        lib.ipkhost_plan_free(h)
+
+
 def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega: float, sequence_type: str = "DNA",
-              tree: str = "", index_num_nodes=None, index_len=None) -> None:
+              tree: str = "", index_num_nodes=None, index_len=None, threads: int = 0) -> None:
     keys = np.ascontiguousarray(keys, np.uint64); fv = np.ascontiguousarray(fv, np.float32)
     offsets = np.ascontiguousarray(offsets, np.uint64)
     branch = np.ascontiguousarray(branch, np.uint32); score = np.ascontiguousarray(score, np.float32)
@@ -98,7 +132,7 @@ def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega
                 keys.ctypes.data_as(C.POINTER(C.c_uint64)), fv.ctypes.data_as(C.POINTER(C.c_float)),
                 offsets.ctypes.data_as(C.POINTER(C.c_uint64)), None, branch.ctypes.data_as(C.POINTER(C.c_uint32)),
                 score.ctypes.data_as(C.POINTER(C.c_float)), None)
-    rc = load().ipkhost_write_ipk(path.encode(), C.byref(db))
+    rc = load().ipkhost_write_ipk_mt(path.encode(), C.byref(db), threads)
     if rc != 0:
         raise HostError(rc, "cannot write " + path)
 

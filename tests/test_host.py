@@ -134,13 +134,194 @@ def test_ipk_round_trip(tmp_path):
     assert list(d["index_num_nodes"]) == [1, 1, 3, 1, 5] and list(d["index_len"]) == [1, 2, 3.5, 3, 6.5]
     for name, a in (("keys", keys), ("fv", fv), ("offsets", offsets), ("branch", branch), ("score", score)):
         assert np.array_equal(d[name], a), name
-    assert os.path.getsize(path) == 8 + 22 + 2 + (8 + 3) + 8 + 5 * 16 + (8 + 20) + 8 + 4 + 8 + 8 + nk * 20 + ne * 8
+    assert os.path.getsize(path) == 8 + 22 + 2 + 4 + 4 + (8 + 3) + 8 + 5 * 16 + (8 + 20) + 8 + 4 + 8 + 8 + nk * 20 + ne * 8
     with open(path, "r+b") as f:              # truncated file -> format error, not a crash
         f.truncate(os.path.getsize(path) - 5)
     with pytest.raises(hostlib.HostError):
         hostlib.read_ipk(path)
     hostlib.write_ipk(path, [], [], [0], [], [], 8, 1.5)
     assert len(hostlib.read_ipk(path)["keys"]) == 0
+    # the preamble of a boost binary_oarchive with default flags (db_builder.cpp:176-177)
+    raw = open(path, "rb").read(40)
+    assert raw[:8] == (22).to_bytes(8, "little") and raw[8:30] == b"serialization::archive" and raw[30:32] == (19).to_bytes(2, "little")
+    assert raw[32:36] == bytes([4, 8, 4, 8]) and raw[36:40] == (1).to_bytes(4, "little")
+
+
+def test_db_tools_diff_and_dump(tmp_path):
+    """ipk-b200-db: the checks of tools/src/diff.cpp:24-295 (+ BASELINE.json's boundary rule) and the listing of dump.cpp:18-33"""
+    from ipk_b200 import hostlib
+    tool = os.path.join(os.path.dirname(hostlib.EXE_PATH), "ipk-b200-db")
+    tree = "((a:1,b:2):0.5,c:3);"                    # post-order a0 b1 (ab)2 c3 root4; pre-order root0 (ab)1 a2 b3 c4
+    k, omega = 3, 1.5
+    thr = float(np.log10(np.float32((omega / 4) ** k)))
+    keys = np.array([5, 9, 27], np.uint64)          # AAC.. in base 4: 5 = 0,1,1 -> "ACC"; 9 = "AGC"; 27 = "CGT"
+    offsets = np.array([0, 2, 3, 5], np.uint64)
+    branch = np.array([0, 3, 1, 2, 0], np.uint32)
+    score = np.array([-0.5, -1.0, -0.25, thr + 2e-6, -0.75], np.float32)
+    fv = np.array([0.1, 0.2, 0.3], np.float32)
+    pa, pb, pc = (str(tmp_path / n) for n in ("A.ipk", "B.ipk", "C.ipk"))
+    hostlib.write_ipk(pa, keys, fv, offsets, branch, score, k, omega, "DNA", tree, [1, 1, 3, 1, 5], [0, 0, 3, 0, 6.5])
+    # B: same database, k-mers in another order, one score off by 1e-3 (inside the reference's EPS), the boundary entry missing
+    order = [2, 0, 1]
+    cnt = np.diff(offsets.astype(np.int64))
+    sel = np.concatenate([np.arange(offsets[q], offsets[q + 1]) for q in order]).astype(np.int64)
+    b_branch, b_score = branch[sel].copy(), score[sel].copy()
+    b_score[np.where((b_branch == 3))[0][0]] += np.float32(1e-3)
+    drop = int(np.where(b_score == np.float32(thr + 2e-6))[0][0])
+    b_cnt = cnt[order].copy(); b_cnt[0] -= 1
+    hostlib.write_ipk(pb, keys[order], fv[order], np.concatenate(([0], np.cumsum(b_cnt))), np.delete(b_branch, drop), np.delete(b_score, drop),
+                      k, omega, "DNA", tree, [1, 1, 3, 1, 5], [0, 0, 3, 0, 6.5])
+    r = subprocess.run([tool, "diff", pa, pa], capture_output=True, text=True)
+    assert r.returncode == 0 and "Phylo-k-mer scores:\tOK\t0" in r.stdout and "Sequence type:\tOK\tDNA\tDNA" in r.stdout
+    r = subprocess.run([tool, "diff", pa, pb, "-v"], capture_output=True, text=True)
+    assert r.returncode == 2 and "Number of phylo-k-mers:\tDIFF\t5\t4" in r.stdout and "Phylo-k-mer scores:\tDIFF\t1" in r.stdout
+    assert "\t27\tCGT\t2\t" in r.stdout                 # the entry B lacks, decoded
+    r = subprocess.run([tool, "diff", pa, pb, "--boundary", "1e-5"], capture_output=True, text=True)
+    assert "Phylo-k-mer scores:\tOK\t0" in r.stdout and "Boundary cases (a score within 1e-05 of the threshold):\t1" in r.stdout
+    r = subprocess.run([tool, "diff", pa, pb, "--boundary", "1e-5", "--eps", "0"], capture_output=True, text=True)
+    assert "Phylo-k-mer scores:\tDIFF\t1" in r.stdout      # bit equality: the 1e-3 shift shows
+    r = subprocess.run([tool, "dump", pa], capture_output=True, text=True)
+    assert r.returncode == 0
+    lines = r.stdout.splitlines()
+    assert lines[0] == "ACC" and lines[1].split("\t")[1:] == [f"{10 ** -0.5:g}", "2"] and lines[2].split("\t")[2] == "4"      # branches as pre-order ids
+    assert lines[3] == "AGC" and lines[5] == "CGT"
+    r = subprocess.run([tool, "diff", pa, str(tmp_path / "missing.ipk")], capture_output=True, text=True)
+    assert r.returncode == 1 and "Exception" in r.stderr
+
+
+def test_ipk_writer_threads_agree(tmp_path):
+    """the multi-threaded writer (runs of k-mers at prefix-summed offsets) produces the bytes of the single-threaded one"""
+    from ipk_b200 import hostlib
+    rng = np.random.default_rng(11)
+    nk = 50000
+    cnt = rng.integers(0, 40, nk)
+    cnt[rng.integers(0, nk, 20)] = 5000                 # a few long k-mers straddle block and thread boundaries
+    offsets = np.concatenate(([0], np.cumsum(cnt))).astype(np.uint64)
+    ne = int(offsets[-1])
+    keys = rng.permutation(1 << 20)[:nk].astype(np.uint64)
+    fv = np.sort(rng.random(nk).astype(np.float32))
+    branch = rng.integers(0, 60000, ne).astype(np.uint32)
+    score = (-5 * rng.random(ne)).astype(np.float32)
+    files = []
+    for t in (1, 3, 16):
+        path = str(tmp_path / f"DB{t}.ipk")
+        hostlib.write_ipk(path, keys, fv, offsets, branch, score, 10, 1.5, "DNA", "(a:1,b:2);", [1, 1, 3], [0, 0, 3], threads=t)
+        files.append(open(path, "rb").read())
+    assert files[0] == files[1] == files[2]
+    d = hostlib.read_ipk(str(tmp_path / "DB16.ipk"))
+    assert np.array_equal(d["branch"], branch) and np.array_equal(d["score"], score) and np.array_equal(d["offsets"], offsets)
+
+
+# ---- host orchestration: tree -> ghost nodes -> groups -> AR labels -> tree index (ipkhost.h build plan) ---------------
+FIVE = "((A:1,B:2)n1:0.5,(C:3,(D:4,E:5)n3:0.25)n2:0.75)root;"
+
+
+def test_plan_five_taxa_by_hand():
+    """extended_tree.cpp:76-155 + db_builder.cpp:495-553 + :191-197 on a tree small enough to do on paper.
+    Original post-order: A0 B1 n1=2 C3 D4 E5 n3=6 n2=7 root8; ghost names count from node_count + 1 = 10 in that order."""
+    from ipk_b200 import hostlib
+    p = hostlib.plan(FIVE)
+    assert p["node_count"] == 9 and p["n_groups"] == 8
+    # post-order of the EXTENDED tree: X1 of a node comes before the ghosts of its descendants, X0 after them
+    assert p["ext_labels"] == ["19_X1", "18_X0", "11_X1", "10_X0", "15_X1", "14_X0", "39_X1", "38_X0", "23_X1", "22_X0",
+                               "35_X1", "34_X0", "27_X1", "26_X0", "31_X1", "30_X0"]
+    assert list(p["node_branch"]) == [2, 2, 0, 0, 1, 1, 7, 7, 3, 3, 6, 6, 4, 4, 5, 5]
+    assert p["ar_labels"] == p["ext_labels"]              # no AR tree given
+    assert list(p["index_num_nodes"]) == [1, 1, 3, 1, 1, 1, 3, 5, 9]
+    assert list(p["index_len"]) == [0, 0, 3, 0, 0, 0, 9, 12.25, 16.5]
+    assert p["newick"] == FIVE.replace(":0.5,", ":0.5,")       # round trip of labels, lengths and child order
+    # ghost branch lengths (extended_tree.cpp:35-73): leaf A (1): x0 = x1 = 0.5; n1 (0.5, two leaves, 3 below): x0 0.25, x1 (3 + 0.25 * 2) / 2
+    ext = p["extended_newick"]
+    for piece in ("11_X1:0.5", "A:0.5)10_X0:0.5", "19_X1:1.75", "18_X0:0.25", "12_X2:0.01,13_X3:0.01"):
+        assert piece in ext, (piece, ext)
+    inner, outer = hostlib.plan(FIVE, ghosts="inner-only"), hostlib.plan(FIVE, ghosts="outer-only")
+    assert list(inner["node_branch"]) == [0, 1, 2, 3, 4, 5, 6, 7] and all(l.endswith("_X0") for l in inner["ext_labels"])
+    assert list(outer["node_branch"]) == [2, 0, 1, 7, 3, 6, 4, 5] and all(l.endswith("_X1") for l in outer["ext_labels"])
+
+
+def _relabel(newick, fn):
+    """every label of a newick string through fn (labels here contain no quotes)"""
+    import re
+    return re.sub(r"([(),])([^(),:;]+)", lambda m: m.group(1) + fn(m.group(2)), newick)
+
+
+def _top_children(newick):
+    """texts of the root's children"""
+    body = newick[1:newick.rindex(")")]
+    out, depth, start = [], 0, 0
+    for i, c in enumerate(body):
+        depth += c == "("
+        depth -= c == ")"
+        if c == "," and depth == 0:
+            out.append(body[start:i]); start = i + 1
+    out.append(body[start:])
+    return out
+
+
+def test_plan_maps_ar_labels_and_reroots():
+    """ar::map_nodes (ar.cpp:790-834) over a relabelled copy of the extended tree; and the same tree as raxml-ng returns it,
+    unrooted ((X, Y)root -> (Y, x1, x2), main.cpp:166-178), which reroot_tree (extended_tree.cpp:186-205) restores"""
+    from ipk_b200 import hostlib
+    ext = hostlib.plan(FIVE)["extended_newick"]
+    ar_rooted = _relabel(ext, lambda l: "AR" + l)
+    p = hostlib.plan(FIVE, ar_rooted)
+    assert p["ar_labels"] == ["AR" + l for l in p["ext_labels"]]
+    x, y = _top_children(ar_rooted)                     # x = (...)AR18_X0:len
+    x_kids = _top_children(x[: x.rindex(")") + 1])
+    unrooted = "(" + ",".join([y] + x_kids) + ")ARroot;"
+    q = hostlib.plan(FIVE, unrooted)
+    want = ["AR" + l for l in p["ext_labels"]]
+    want[p["ext_labels"].index("18_X0")] = "ARroot"     # the dropped node's place is taken by the old root, the new one is "added_root"
+    assert q["ar_labels"] == want
+    with pytest.raises(hostlib.HostError, match="differ in the number of nodes"):
+        hostlib.plan(FIVE, "(a,b);")
+
+
+def test_plan_rejects_unrooted_reference_tree():
+    from ipk_b200 import hostlib
+    with pytest.raises(hostlib.HostError, match="not rooted"):
+        hostlib.plan("(A:1,B:1,C:1);")
+    assert hostlib.plan("(A:1,B:1,C:1);", use_unrooted=True)["n_groups"] == 3
+    with pytest.raises(hostlib.HostError, match="newick"):
+        hostlib.plan("((A:1,B:1);")
+
+
+def _ipk_py_argv(exe, tmp_path, ar_dir, extra=()):
+    """the command ipk.py:292-329 builds"""
+    return [exe, "--ar-binary", "raxml-ng", "--refalign", str(tmp_path / "ref.fasta"), "-t", str(tmp_path / "tree.newick"), "-w", str(tmp_path),
+            "-k", "6", "--model", "GTR", "--alpha", "1.0", "--categories", "4", "--reduction-ratio", "0.99", "--omega", "1.5", "--mif0", "--both",
+            "-u", "1.0", "-j", "2", "-o", str(tmp_path / "DB.ipk"), "-v", "1", "--ar-dir", ar_dir, *extra]
+
+
+def test_executable_accepts_the_command_line_ipk_py_builds(tmp_path):
+    """CPU: every option of ipk/src/command_line.cpp:83-147 parses; without a GPU the run ends at the device, not at the argv"""
+    from ipk_b200 import hostlib
+    exe = os.path.join(os.path.dirname(hostlib.EXE_PATH), "ipk-dna")
+    assert os.path.exists(exe)
+    (tmp_path / "tree.newick").write_text(FIVE + "\n")
+    ar_dir = tmp_path / "AR"
+    ar_dir.mkdir()
+    p = hostlib.plan(FIVE)
+    rng = np.random.default_rng(2)
+    write_tsv(str(ar_dir / "x.raxml.ancestralProbs"), random_probs(rng, len(p["ext_labels"]), 30, 4), p["ext_labels"], 4)
+    (ar_dir / "x.raxml.ancestralTree").write_text(p["extended_newick"] + "\n")
+    extra = ["--ar-parameters", '"--blopt', 'nr_safe"', "--no-reduction", "--use-unrooted", "--uncompressed", "--on-disk", "--DCLA"]
+    r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(ar_dir), extra), capture_output=True, text=True)
+    assert "unknown option" not in r.stderr and "usage:" not in r.stderr, r.stderr
+    assert "16 ghost nodes in 8 branch groups of a 9-node tree" in r.stderr, r.stderr
+    assert (tmp_path / "extended_trees" / "extended_tree.newick").read_text().strip() == p["extended_newick"]
+    import torch
+    if not torch.cuda.is_available():
+        assert r.returncode == 1 and "Exception" in r.stderr            # no CPU fallback: the device is where it stops
+    # --ar-only ends after locating the reconstruction; a missing --ar-dir and unsupported modes are errors with exit status 1
+    r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(ar_dir), ["--ar-only"]), capture_output=True, text=True)
+    assert r.returncode == 0 and "--ar-only requested" in r.stderr
+    r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(tmp_path / "nope")), capture_output=True, text=True)
+    assert r.returncode == 1 and "No such directory" in r.stderr
+    r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(ar_dir), ["--merge-branches"]), capture_output=True, text=True)
+    assert r.returncode == 1 and "not supported" in r.stderr
+    r = subprocess.run([exe, "--refalign", "a", "-t", str(tmp_path / "tree.newick")], capture_output=True, text=True)
+    assert r.returncode == 1 and "--ar-dir is required" in r.stderr
 
 
 @pytest.mark.gpu
@@ -179,3 +360,61 @@ def test_ipk_b200_executable_end_to_end(sigma, bits, k, omega, filt, tmp_path):
     # error convention of the reference binary: message on stderr, exit status 1 (main.cpp:225-246)
     r = subprocess.run([hostlib.EXE_PATH, "--ar-probs", tsv + ".missing", "--node-map", nmap], capture_output=True, text=True)
     assert r.returncode == 1 and "Exception" in r.stderr
+
+
+def _synth_newick(n_taxa, seed=5):
+    """the generator's tree (post-order ids = branch ids of synth.posteriors) as newick; children in ascending id order keep the ids"""
+    from ipk_b200 import synth
+    parent, blen = synth.tree(n_taxa, seed)
+    kids = {}
+    for v, p in enumerate(parent):
+        if p != 0xffffffff:
+            kids.setdefault(int(p), []).append(v)
+    def text(v):
+        if v not in kids:
+            return f"T{v}:{float(blen[v]):.6g}"
+        inner = ",".join(text(c) for c in sorted(kids[v]))
+        return f"({inner})" + ("" if parent[v] == 0xffffffff else f":{float(blen[v]):.6g}")
+    return text(len(parent) - 1) + ";"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ghosts", ["both", "outer-only"])
+def test_reference_command_line_end_to_end(ghosts, tmp_path):
+    """tree + raxml-ng outputs -> `ipk-dna <the argv of ipk.py:292-329>` -> DB.ipk: ghost injection, grouping, AR label mapping,
+    posteriors, the device path and the header's tree index, against the oracle build over the same plan"""
+    import oraclelib as O
+    from parity import assert_db_equal
+    from types import SimpleNamespace
+    from ipk_b200 import hostlib, capi, synth
+    n_taxa, W, sigma, k, omega = 7, 50, 4, 6, 1.5
+    newick = _synth_newick(n_taxa)
+    (tmp_path / "tree.newick").write_text(newick + "\n")
+    plan0 = hostlib.plan(newick, ghosts=ghosts)
+    assert plan0["node_count"] == 2 * n_taxa - 1
+    logp, nb = synth.posteriors(n_taxa, W, sigma, seed=5)               # rows 2b (X0), 2b + 1 (X1) of branch b
+    all_ext = hostlib.plan(newick)["ext_labels"]
+    all_branch = hostlib.plan(newick)["node_branch"]
+    row_of = {l: 2 * int(b) + (1 if l.endswith("_X1") else 0) for l, b in zip(all_ext, all_branch)}
+    ar_dir = tmp_path / "AR"
+    ar_dir.mkdir()
+    file_labels = sorted(row_of, key=row_of.get)                         # the file lists the nodes in ITS order, not the build's
+    write_tsv(str(ar_dir / "ext.phylip.raxml.ancestralProbs"), np.power(10.0, logp.astype(np.float64))[[row_of[l] for l in file_labels]],
+              ["AR" + l for l in file_labels], sigma)
+    (ar_dir / "ext.phylip.raxml.ancestralTree").write_text(_relabel(hostlib.plan(newick)["extended_newick"], lambda l: "AR" + l) + "\n")
+    exe = os.path.join(os.path.dirname(hostlib.EXE_PATH), "ipk-dna")
+    argv = _ipk_py_argv(exe, tmp_path, str(ar_dir))
+    argv[argv.index("--both")] = "--" + ghosts
+    r = subprocess.run(argv, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    d = hostlib.read_ipk(str(tmp_path / "DB.ipk"))
+    assert d["tree"] == plan0["newick"] and d["kmer_size"] == 6 and d["sequence_type"] == "DNA"
+    assert np.array_equal(d["index_num_nodes"], plan0["index_num_nodes"]) and np.array_equal(d["index_len"], plan0["index_len"])
+    assert len(d["index_num_nodes"]) == 2 * n_taxa - 1 and d["index_num_nodes"][-1] == 2 * n_taxa - 1
+    _, parsed = hostlib.read_ar(str(ar_dir / "ext.phylip.raxml.ancestralProbs"), sigma, ["AR" + l for l in plan0["ext_labels"]])
+    thr, lthr = capi.score_threshold(omega, sigma, k)
+    want = O.build(parsed, plan0["node_branch"], W, sigma, 2, k, lthr, thr, 2 * n_taxa - 1, 0, 2)
+    got = SimpleNamespace(keys=d["keys"], fv=d["fv"], offsets=d["offsets"], branch=d["branch"], score=d["score"],
+                          n_kmers=len(d["keys"]), n_entries=len(d["branch"]))
+    assert want.n_entries > 100
+    assert_db_equal(got, want)
