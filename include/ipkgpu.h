@@ -193,6 +193,39 @@ int  ipkgpu_open_peer(ipkgpu_ctx* ctx, const unsigned char* handle /*[64]*/, voi
 int  ipkgpu_stage1_scatter(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* peer_keys, float* const* peer_scores,
                            const uint64_t* base_offsets);
 
+/* ---- the same exchange on PACKED records: the first pass of the merge sort IS the exchange -------------------------
+ * The merge sort of the single-GPU build starts with a most-significant-digit pass on the top 8 bits of the k-mer that
+ * turns (u64 key, f32 score) pairs into 8-byte packed records (packed_sort.cuh).  With G ranks the 256 buckets of that
+ * pass are dealt to the ranks as contiguous k-mer ranges of about equal size and every rank's MSD pass stores each bucket
+ * straight into its owner's receive buffer over NVLink: no separate partition pass, 8 instead of 12 bytes per record on
+ * the wire, and the owner sorts 8 bits less.  A rank reads its emission in branch-group order (the runs the enumeration
+ * recorded) and the sources land in rank order inside every bucket, so the owner's sort skips the group bits altogether.
+ * Needs k*bits >= 8, k*bits + group_bits - 8 <= 32 and < 2^32 records per rank; otherwise use the pair exchange above.
+ * 1. every rank:  ipkgpu_stage1_raw, then ipkgpu_stage1_bucket_counts -> counts[256]; the caller all-gathers G x 256
+ * 2. every rank:  ipkgpu_exchange_plan (host arithmetic only) -> owner[256], base[256] (where THIS rank's records of each
+ *                 bucket start inside the owner's buffer), bucket_start[257] and n_recv (this rank's own buffer)
+ * 3. every rank:  ipkgpu_recv_packed(n_recv) -> buffer + CUDA IPC handle; handles all-gathered, mapped with
+ *                 ipkgpu_open_peer_slot(rank of the peer, ...) (a changed handle replaces the stale mapping)
+ * 4. every rank:  ipkgpu_stage1_scatter_packed; *group_ordered tells whether this rank's records went out in group order
+ *                 (false after a depth-first or batched enumeration): the caller ANDs it over the ranks
+ * 5. a barrier, then ipkgpu_stage2_packed on the rank's own receive buffer. */
+int  ipkgpu_stage1_bucket_counts(ipkgpu_ctx* ctx, uint64_t* counts /*[256]*/);
+int  ipkgpu_exchange_plan(uint32_t n_parts, uint32_t rank, const uint64_t* counts /*[n_parts][256]*/, uint8_t* owner /*[256]*/,
+                          uint64_t* base /*[256]*/, uint64_t* bucket_start /*[257]*/, uint64_t* n_recv);
+int  ipkgpu_recv_packed(ipkgpu_ctx* ctx, uint64_t n_records, uint64_t** d_recs, unsigned char* handle /*[64] or NULL*/);
+int  ipkgpu_open_peer_slot(ipkgpu_ctx* ctx, uint32_t slot, const unsigned char* handle /*[64]*/, void** d_ptr);
+int  ipkgpu_stage1_scatter_packed(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* peer_recs, const uint8_t* owner, const uint64_t* base,
+                                  int32_t* group_ordered);
+int  ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_start /*[257]*/, uint32_t group_bits, int32_t group_ordered,
+                          const uint32_t* group_branch, uint32_t n_groups_total, uint32_t key_bits, float threshold,
+                          uint32_t total_num_groups, int32_t filter, int result_mode, ipkgpu_result* out);
+
+/* Entries of host results (ipkgpu_result.branch / branch16 / score) go to the caller's PAGE-LOCKED buffers instead of the
+ * context's own -- e.g. shared memory that another process maps, so that the shards of a multi-GPU build meet in one
+ * address space without a second copy.  The buffers are never grown or freed by the library (a result that does not fit is
+ * IPKGPU_ENOMEM); NULL, 0, NULL, 0 returns to the context's own staging. */
+int  ipkgpu_set_entry_staging(ipkgpu_ctx* ctx, void* branch_buf, size_t branch_bytes, void* score_buf, size_t score_bytes);
+
 /* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
  * values -> order (equal composite keys are merged by maximum score).  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
  * chunks_group_ordered != 0 promises that the records are a concatenation of chunks in ascending group ranges, each

@@ -157,10 +157,39 @@ def load() -> C.CDLL:
     lib.ipkgpu_stage2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
                                   C.c_uint32, C.c_float, C.c_uint32, C.c_int32, C.c_int32, C.c_int, P(Result)]
     lib.ipkgpu_stage2.restype = C.c_int
+    lib.ipkgpu_stage1_bucket_counts.argtypes = [C.c_void_p, P(C.c_uint64)]
+    lib.ipkgpu_stage1_bucket_counts.restype = C.c_int
+    lib.ipkgpu_exchange_plan.argtypes = [C.c_uint32, C.c_uint32, P(C.c_uint64), P(C.c_uint8), P(C.c_uint64), P(C.c_uint64), P(C.c_uint64)]
+    lib.ipkgpu_exchange_plan.restype = C.c_int
+    lib.ipkgpu_recv_packed.argtypes = [C.c_void_p, C.c_uint64, P(C.c_void_p), C.c_void_p]
+    lib.ipkgpu_recv_packed.restype = C.c_int
+    lib.ipkgpu_open_peer_slot.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, P(C.c_void_p)]
+    lib.ipkgpu_open_peer_slot.restype = C.c_int
+    lib.ipkgpu_stage1_scatter_packed.argtypes = [C.c_void_p, C.c_uint32, P(C.c_void_p), P(C.c_uint8), P(C.c_uint64), P(C.c_int32)]
+    lib.ipkgpu_stage1_scatter_packed.restype = C.c_int
+    lib.ipkgpu_stage2_packed.argtypes = [C.c_void_p, C.c_uint64, P(C.c_uint64), C.c_uint32, C.c_int32, C.c_void_p, C.c_uint32, C.c_uint32,
+                                         C.c_float, C.c_uint32, C.c_int32, C.c_int, P(Result)]
+    lib.ipkgpu_stage2_packed.restype = C.c_int
+    lib.ipkgpu_set_entry_staging.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    lib.ipkgpu_set_entry_staging.restype = C.c_int
     lib.ipkgpu_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, P(C.c_float), P(C.c_float)]
     lib.ipkgpu_score_threshold.restype = None
     _lib = lib
     return lib
+
+
+def exchange_plan(n_parts: int, rank: int, counts: np.ndarray):
+    """ipkgpu_exchange_plan: counts [n_parts, 256] -> (owner[256] u8, base[256] u64, bucket_start[257] u64, n_recv)"""
+    counts = np.ascontiguousarray(counts, np.uint64)
+    assert counts.shape == (n_parts, 256)
+    owner = np.zeros(256, np.uint8); base = np.zeros(256, np.uint64); start = np.zeros(257, np.uint64)
+    n_recv = C.c_uint64(0)
+    P = C.POINTER
+    rc = load().ipkgpu_exchange_plan(n_parts, rank, counts.ctypes.data_as(P(C.c_uint64)), owner.ctypes.data_as(P(C.c_uint8)),
+                                     base.ctypes.data_as(P(C.c_uint64)), start.ctypes.data_as(P(C.c_uint64)), C.byref(n_recv))
+    if rc != 0:
+        raise IpkGpuError(rc, "ipkgpu_exchange_plan: bad arguments or a shard above 2^32-1 records")
+    return owner, base, start, int(n_recv.value)
 
 
 def score_threshold(omega: float, sigma: int, k: int) -> tuple[float, float]:
@@ -418,6 +447,50 @@ class Context:
         ps = (C.c_void_p * n)(*peer_scores)
         base = (C.c_uint64 * n)(*[int(b) for b in base_offsets])
         self._check(self._lib.ipkgpu_stage1_scatter(self._h, n, pk, ps, base))
+
+    # ---- the exchange on packed records: the MSD pass of the merge sort stores into the owners' buffers (include/ipkgpu.h) ----
+    def stage1_bucket_counts(self) -> np.ndarray:
+        counts = np.zeros(256, np.uint64)
+        self._check(self._lib.ipkgpu_stage1_bucket_counts(self._h, counts.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return counts
+
+    def recv_packed(self, n_records: int) -> tuple[int, bytes]:
+        """-> (device address of this rank's receive buffer, its CUDA IPC handle)"""
+        p = C.c_void_p(0)
+        h = C.create_string_buffer(64)
+        self._check(self._lib.ipkgpu_recv_packed(self._h, n_records, C.byref(p), h))
+        return int(p.value or 0), h.raw
+
+    def open_peer_slot(self, slot: int, handle: bytes) -> int:
+        p = C.c_void_p(0)
+        self._check(self._lib.ipkgpu_open_peer_slot(self._h, slot, C.create_string_buffer(handle, 64), C.byref(p)))
+        return int(p.value or 0)
+
+    def stage1_scatter_packed(self, peer_recs: list[int], owner: np.ndarray, base: np.ndarray) -> bool:
+        """-> whether this rank's records went out in branch-group order"""
+        n = len(peer_recs)
+        pr = (C.c_void_p * n)(*peer_recs)
+        owner = np.ascontiguousarray(owner, np.uint8); base = np.ascontiguousarray(base, np.uint64)
+        ordered = C.c_int32(0)
+        self._check(self._lib.ipkgpu_stage1_scatter_packed(self._h, n, pr, owner.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                           base.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(ordered)))
+        return bool(ordered.value)
+
+    def stage2_packed(self, n: int, bucket_start: np.ndarray, group_bits: int, group_ordered: bool, group_branch: np.ndarray, key_bits: int,
+                      threshold: float, total_num_groups: int, filter: int = FILTER_MIF0, result_on_device: bool | int = False,
+                      indexed: bool = False, branch16: bool = False) -> Result:
+        group_branch = np.ascontiguousarray(group_branch, dtype=np.uint32)
+        bucket_start = np.ascontiguousarray(bucket_start, np.uint64)
+        res = Result()
+        mode = (int(result_on_device) & 7) | (2 if indexed else 0) | (4 if branch16 else 0)
+        self._check(self._lib.ipkgpu_stage2_packed(self._h, n, bucket_start.ctypes.data_as(C.POINTER(C.c_uint64)), group_bits, 1 if group_ordered else 0,
+                                                   group_branch.ctypes.data, int(group_branch.shape[0]), key_bits, threshold, total_num_groups, filter,
+                                                   mode, C.byref(res)))
+        return res
+
+    def set_entry_staging(self, branch_buf, branch_bytes: int, score_buf, score_bytes: int) -> None:
+        """entries of host results go to the caller's page-locked buffers (e.g. shared memory another process maps); None resets"""
+        self._check(self._lib.ipkgpu_set_entry_staging(self._h, _ptr(branch_buf), branch_bytes, _ptr(score_buf), score_bytes))
 
     def stage2(self, d_keys, d_scores, n: int, group_bits: int, group_branch: np.ndarray, key_bits: int, threshold: float,
                total_num_groups: int, filter: int = FILTER_MIF0, chunks_group_ordered: bool = True,

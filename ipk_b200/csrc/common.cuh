@@ -51,6 +51,7 @@ namespace ipkgpu
     {
         void* p = nullptr;
         size_t cap = 0;
+        bool external = false;             // the caller's page-locked memory (ipkgpu_set_entry_staging): never grown or freed here
         template<class T> T* as() const { return static_cast<T*>(p); }
     };
 
@@ -101,8 +102,11 @@ struct ipkgpu_ctx
     uint64_t s1_n = 0;
     uint32_t s1_group_bits = 0;
     ipkgpu::dbuf recv_keys, recv_scores, peer_base;   // receive side of the fused partition + exchange (exported through CUDA IPC)
-    struct ipc_mapping { unsigned char handle[64]; void* ptr; };
+    struct ipc_mapping { unsigned char handle[64]; void* ptr = nullptr; };
     std::vector<ipc_mapping> ipc_open;  // peers' receive buffers mapped into this process
+    std::vector<ipc_mapping> ipc_slots; // ... one per peer rank for the packed exchange: a changed handle replaces the mapping (ipkgpu_open_peer_slot)
+    uint32_t s1_key_bits = 0;          // k * bits of the stage-1 build
+    ipkgpu::dbuf recv_old;             // a receive buffer that was outgrown: freed one exchange later, once no peer maps it any more
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;
     uint64_t res_n_kmers = 0, res_n_entries = 0;      // the CSR the last build / stage 2 left in kmer_keys / kmer_offs / ent_* / fv
@@ -211,6 +215,7 @@ struct ipkgpu_ctx
     void reserve_host(ipkgpu::hbuf& b, size_t bytes)
     {
         if (bytes <= b.cap) return;
+        if (b.external) ipkgpu::fail(IPKGPU_ENOMEM, "the caller's staging buffer holds %zu bytes, the result needs %zu (ipkgpu_set_entry_staging)", b.cap, bytes);
         if (b.p) cudaFreeHost(b.p);
         b.p = nullptr; b.cap = 0;
         size_t want = bytes + bytes / 16 + 256;

@@ -680,6 +680,20 @@ namespace
         return r;
     }
 
+    parts_out sort_merge_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint64_t n, uint32_t key_bits, uint32_t gbits,
+                                 uint32_t skip_bits, uint32_t group_add, int result_mode, bool stream_parts, bool b16, stage_timer& tm,
+                                 size_t e_before0, size_t e_before1, uint32_t passes_before);
+
+    /// copy stream, events and pinned staging for entries that leave part by part
+    void prepare_entry_stream(ipkgpu_ctx* ctx, uint64_t n, bool b16)
+    {
+        if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
+        ctx->reserve_host(ctx->h_branch, n * (b16 ? 2 : 4) + 8);
+        ctx->reserve_host(ctx->h_score, n * 4 + 4);
+        if (b16) ctx->reserve(ctx->out_branch, n * 2 + 8);
+    }
+
     /// The merge sort on packed records (packed_sort.cuh): top-byte histogram -> MSD pass (ka, va) -> 8-byte records in p0 ->
     /// segmented LSD passes p0 <-> p1 (p1 = ka's memory, free once the MSD pass has read it) -> max-merge + CSR.
     /// stream_parts: host-bound indexed result -- buckets are sorted and merged in runs of about n / n_parts records and each
@@ -690,19 +704,11 @@ namespace
         // use_runs: ctx->runs lists the commits of the enumeration (one branch group each, together all n records).  The MSD
         // pass reads them in group order, so its output is group-ordered inside every bucket and the LSD passes only have the
         // k-mer bits left: 1 + ceil((key_bits - 8) / 8) passes instead of 1 + ceil((key_bits + gbits - 8) / 8).
-        parts_out R;
         const uint32_t low_bits = key_bits + gbits - 8;
         const uint32_t skip_bits = use_runs ? gbits : 0;
         uint64_t* p1 = ka;
         const bool b16 = stream_parts && (result_mode & 4) != 0 && ctx->max_branch < 65536u;
-        if (stream_parts)
-        {
-            if (!ctx->copy_stream) IPK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-            if (!ctx->ev_merged) { IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_merged, cudaEventDisableTiming)); IPK_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming)); }
-            ctx->reserve_host(ctx->h_branch, n * (b16 ? 2 : 4) + 8);
-            ctx->reserve_host(ctx->h_score, n * 4 + 4);
-            if (b16) ctx->reserve(ctx->out_branch, n * 2 + 8);
-        }
+        if (stream_parts) prepare_entry_stream(ctx, n, b16);
         ps_table T;
         memset(&T, 0, sizeof T);
         const size_t e0 = tm.mark();
@@ -719,7 +725,19 @@ namespace
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));           // T.start is on the host now (and ka is free: it becomes p1)
         T.start[PS_BUCKETS] = uint32_t(n);
         const size_t e1 = tm.mark();
-        R.passes = 1 + div_up<uint32_t>(low_bits - skip_bits, 8);
+        return sort_merge_buckets(ctx, p0, p1, T, n, key_bits, gbits, skip_bits, group_add, result_mode, stream_parts, b16, tm, e0, e1, 1);
+    }
+
+    /// Second half of the packed sort: packed records bucketed by their top k-mer byte (T.start) -> segmented LSD passes on
+    /// the bits above skip_bits -> max-merge + CSR, in runs of buckets of about n / n_parts records when stream_parts.
+    /// Also what an owner rank runs on the records its peers stored into its receive buffer (ipkgpu_stage2_packed).
+    parts_out sort_merge_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint64_t n, uint32_t key_bits, uint32_t gbits,
+                                 uint32_t skip_bits, uint32_t group_add, int result_mode, bool stream_parts, bool b16, stage_timer& tm,
+                                 size_t e_before0, size_t e_before1, uint32_t passes_before)
+    {
+        parts_out R;
+        const uint32_t low_bits = key_bits + gbits - 8;
+        R.passes = passes_before + div_up<uint32_t>(low_bits - skip_bits, 8);
         struct mark3 { size_t a, b, c; };
         std::vector<mark3> marks;
         const uint64_t target = stream_parts ? div_up<uint64_t>(n, ctx->n_parts) : n;
@@ -750,7 +768,7 @@ namespace
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));
         R.m.n_records = ent_base;
         R.m.n_kmers = kmer_base;
-        R.ms_sort = tm.ms(e0, e1);
+        R.ms_sort = tm.ms(e_before0, e_before1);
         for (const mark3& k : marks) { R.ms_sort += tm.ms(k.a, k.b); R.ms_merge += tm.ms(k.b, k.c); }
         return R;
     }
@@ -828,7 +846,7 @@ namespace
         // commits of the join kernel recorded as runs of one branch group each: read in group order by the first pass of the
         // packed sort they spare it every pass on the group bits (packed_sort.cuh)
         static const bool runs_off = getenv("IPKGPU_RUNS") && atoi(getenv("IPKGPU_RUNS")) == 0;
-        L.want_runs = !runs_off && !ordered && !raw && want_csr && key_bits >= 8 && key_bits + all_bits - 8 <= 32;
+        L.want_runs = !runs_off && !ordered && (raw || want_csr) && key_bits >= 8 && key_bits + (raw ? group_bits : all_bits) - 8 <= 32;
         ctx->runs_n = 0;
         ctx->runs_valid = L.want_runs;
         uint64_t side_cap = 0;
@@ -895,6 +913,7 @@ namespace
             o.n_unique = o.n_emitted;
             o.n_batches = 1;
             ctx->s1_n = o.n_emitted;
+            ctx->s1_key_bits = key_bits;
             ctx->s1_group_bits = group_bits;
             ctx->s1_keys = ctx->keys_a.as<uint64_t>();
             ctx->s1_scores = ctx->vals_a.as<uint32_t>();
@@ -985,7 +1004,9 @@ namespace
         o.n_unique = u_off;
         o.ms_enumerate = ms_enum; o.ms_sort = ms_sort; o.ms_merge = ms_merge;
         ctx->s1_n = o.csr_done ? 0 : u_off;
+        ctx->s1_key_bits = key_bits;
         ctx->s1_group_bits = group_bits;
+        if (!o.csr_done) ctx->runs_valid = false;          // merged records: no longer the emission the runs describe
         ctx->s1_keys = ctx->u_keys.as<uint64_t>();
         ctx->s1_scores = ctx->u_scores.as<uint32_t>();
         return o;
@@ -1349,14 +1370,16 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
                             &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
-                            &ctx->runs, &ctx->runs_scratch };
+                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
+    for (auto& m : ctx->ipc_slots) if (m.ptr) cudaIpcCloseMemHandle(m.ptr);
+    ctx->ipc_slots.clear();
     for (auto* b : all) ctx->release(*b);
     ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score, &ctx->h_cnt };
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev_merged) { cudaEventDestroy(ctx->ev_merged); cudaEventDestroy(ctx->ev_copied); }
-    for (auto* b : hall) if (b->p) cudaFreeHost(b->p);
+    for (auto* b : hall) if (b->p && !b->external) cudaFreeHost(b->p);
     for (auto e : ctx->events) cudaEventDestroy(e);
     for (auto e : ctx->ev_h2d) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -1691,6 +1714,213 @@ int ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t n
         for (uint32_t g = 0; g < n_groups_total; ++g) ctx->max_branch = std::max(ctx->max_branch, group_branch[g]);
         const stage2_params sp{ group_bits, key_bits, total_num_groups, threshold, filter };
         run_stage2(ctx, d_keys, d_scores, n, chunks_group_ordered != 0, sp, result_on_device, out, tm);
+        const size_t t1 = tm.mark();
+        IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
+        out->stats.ms_total = tm.ms(t0, t1);
+        out->stats.n_groups = n_groups_total;
+        out->stats.kernel_launches = ctx->launches;
+    });
+}
+
+
+// ---- multi-GPU build on packed records: the MSD pass of the merge sort is the exchange (include/ipkgpu.h) ------------
+
+int ipkgpu_set_entry_staging(ipkgpu_ctx* ctx, void* branch_buf, size_t branch_bytes, void* score_buf, size_t score_bytes)
+{
+    return guarded(ctx, [&] {
+        if ((branch_buf == nullptr) != (score_buf == nullptr)) fail(IPKGPU_EINVAL, "both buffers or neither");
+        for (ipkgpu::hbuf* b : { &ctx->h_branch, &ctx->h_score })
+        {
+            if (b->p && !b->external) cudaFreeHost(b->p);
+            b->p = nullptr; b->cap = 0; b->external = false;
+        }
+        if (!branch_buf) return;
+        ctx->h_branch.p = branch_buf; ctx->h_branch.cap = branch_bytes; ctx->h_branch.external = true;
+        ctx->h_score.p = score_buf; ctx->h_score.cap = score_bytes; ctx->h_score.external = true;
+    });
+}
+
+int ipkgpu_stage1_bucket_counts(ipkgpu_ctx* ctx, uint64_t* counts)
+{
+    return guarded(ctx, [&] {
+        if (!counts) fail(IPKGPU_EINVAL, "counts is null");
+        for (int d = 0; d < PS_BUCKETS; ++d) counts[d] = 0;
+        const uint64_t n = ctx->s1_n;
+        if (n == 0) return;
+        if (!ps_eligible(ctx->s1_key_bits, ctx->s1_group_bits, n))
+            fail(IPKGPU_EINVAL, "packed exchange needs k*bits >= 8, k*bits + group bits - 8 <= 32 and fewer than 2^32 records per rank (have %u + %u bits, %llu records)",
+                 ctx->s1_key_bits, ctx->s1_group_bits, (unsigned long long)n);
+        ps_top_histogram(ctx, ctx->s1_keys, n, ctx->s1_key_bits + ctx->s1_group_bits - 8);
+        uint32_t h[PS_BUCKETS];
+        IPK_CUDA(cudaMemcpyAsync(h, ctx->hist.p, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int d = 0; d < PS_BUCKETS; ++d) counts[d] = h[d];
+    });
+}
+
+int ipkgpu_exchange_plan(uint32_t n_parts, uint32_t rank, const uint64_t* counts, uint8_t* owner, uint64_t* base, uint64_t* bucket_start, uint64_t* n_recv)
+{
+    if (!counts || !owner || !base || !bucket_start || !n_recv || n_parts < 1 || n_parts > uint32_t(RS_MAX_PEERS) || rank >= n_parts) return IPKGPU_EINVAL;
+    uint64_t total[PS_BUCKETS], grand = 0;
+    for (int d = 0; d < PS_BUCKETS; ++d)
+    {
+        total[d] = 0;
+        for (uint32_t r = 0; r < n_parts; ++r) total[d] += counts[size_t(r) * PS_BUCKETS + d];
+        grand += total[d];
+    }
+    // contiguous k-mer ranges of about grand / n_parts records: a bucket goes to the rank its midpoint falls to
+    uint64_t cum = 0;
+    for (int d = 0; d < PS_BUCKETS; ++d)
+    {
+        const long double mid = (long double)cum + (long double)total[d] / 2;
+        uint32_t o = grand ? uint32_t(mid * n_parts / (long double)grand) : 0;
+        owner[d] = uint8_t(std::min(o, n_parts - 1));
+        if (d && owner[d] < owner[d - 1]) owner[d] = owner[d - 1];
+        cum += total[d];
+    }
+    // an owner's buffer: its buckets in ascending order, inside a bucket the source ranks in ascending order (= ascending groups)
+    uint64_t fill[RS_MAX_PEERS];
+    for (uint32_t r = 0; r < n_parts; ++r) fill[r] = 0;
+    for (int d = 0; d < PS_BUCKETS; ++d)
+    {
+        const uint32_t o = owner[d];
+        uint64_t before = 0;
+        for (uint32_t r = 0; r < rank; ++r) before += counts[size_t(r) * PS_BUCKETS + d];
+        base[d] = fill[o] + before;
+        bucket_start[d] = fill[rank];            // where bucket d begins in THIS rank's buffer (empty range when another rank owns it)
+        fill[o] += total[d];
+    }
+    bucket_start[PS_BUCKETS] = fill[rank];
+    *n_recv = fill[rank];
+    for (uint32_t r = 0; r < n_parts; ++r) if (fill[r] > 0xffffffffull) return IPKGPU_EINVAL;
+    return IPKGPU_OK;
+}
+
+int ipkgpu_recv_packed(ipkgpu_ctx* ctx, uint64_t n_records, uint64_t** d_recs, unsigned char* handle)
+{
+    return guarded(ctx, [&] {
+        if (!d_recs) fail(IPKGPU_EINVAL, "output pointer is null");
+        if (n_records * 8 + 8 > ctx->recv_keys.cap)
+        {
+            // peers may still map the buffer being outgrown: it is kept for one more exchange (they re-open on a changed
+            // handle before they store, ipkgpu_open_peer_slot) and only then freed
+            ctx->release(ctx->recv_old);
+            ctx->recv_old = ctx->recv_keys;
+            ctx->recv_keys = dbuf();
+            ctx->reserve(ctx->recv_keys, (n_records + n_records / 4) * 8 + 8);
+        }
+        *d_recs = ctx->recv_keys.as<uint64_t>();
+        if (handle)
+        {
+            cudaIpcMemHandle_t h;
+            IPK_CUDA(cudaIpcGetMemHandle(&h, ctx->recv_keys.p));
+            memcpy(handle, &h, sizeof h);
+        }
+    });
+}
+
+int ipkgpu_open_peer_slot(ipkgpu_ctx* ctx, uint32_t slot, const unsigned char* handle, void** d_ptr)
+{
+    return guarded(ctx, [&] {
+        if (!handle || !d_ptr || slot >= uint32_t(RS_MAX_PEERS)) fail(IPKGPU_EINVAL, "bad argument");
+        if (ctx->ipc_slots.size() <= slot) ctx->ipc_slots.resize(slot + 1);
+        auto& m = ctx->ipc_slots[slot];
+        if (m.ptr && !memcmp(m.handle, handle, sizeof m.handle)) { *d_ptr = m.ptr; return; }
+        if (m.ptr) { cudaIpcCloseMemHandle(m.ptr); m.ptr = nullptr; }      // the peer reallocated: drop the stale mapping first
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handle, sizeof h);
+        void* p = nullptr;
+        IPK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        memcpy(m.handle, handle, sizeof m.handle);
+        m.ptr = p;
+        *d_ptr = p;
+    });
+}
+
+int ipkgpu_stage1_scatter_packed(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* peer_recs, const uint8_t* owner, const uint64_t* base,
+                                 int32_t* group_ordered)
+{
+    return guarded(ctx, [&] {
+        if (n_parts < 1 || n_parts > uint32_t(RS_MAX_PEERS)) fail(IPKGPU_EINVAL, "n_parts = %u outside [1, %d]", n_parts, RS_MAX_PEERS);
+        if (!peer_recs || !owner || !base || !group_ordered) fail(IPKGPU_EINVAL, "null argument");
+        const uint64_t n = ctx->s1_n;
+        const bool ordered = n == 0 || (ctx->runs_valid && ctx->runs_n > 0);
+        *group_ordered = ordered ? 1 : 0;
+        if (n == 0) return;
+        if (!ps_eligible(ctx->s1_key_bits, ctx->s1_group_bits, n)) fail(IPKGPU_EINVAL, "records do not fit the packed form");
+        ps_dest D;
+        memset(&D, 0, sizeof D);
+        uint32_t b32[PS_BUCKETS];
+        for (int d = 0; d < PS_BUCKETS; ++d)
+        {
+            if (owner[d] >= n_parts) fail(IPKGPU_EINVAL, "owner of bucket %d is rank %u of %u", d, owner[d], n_parts);
+            if (base[d] > 0xffffffffull) fail(IPKGPU_EINVAL, "offset into rank %u's receive buffer exceeds 2^32-1", owner[d]);
+            D.owner[d] = owner[d];
+            b32[d] = uint32_t(base[d]);
+        }
+        for (uint32_t p = 0; p < n_parts; ++p)
+        {
+            if (!peer_recs[p]) fail(IPKGPU_EINVAL, "receive buffer of rank %u is null", p);
+            D.out[p] = peer_recs[p];
+        }
+        ps_runs Rn;
+        memset(&Rn, 0, sizeof Rn);
+        if (ordered) Rn = ps_order_runs(ctx, n, ctx->s1_group_bits);
+        ctx->reserve(ctx->peer_base, sizeof b32);
+        IPK_CUDA(cudaMemcpyAsync(ctx->peer_base.p, b32, sizeof b32, cudaMemcpyHostToDevice, ctx->stream));
+        ps_msd_pack(ctx, ctx->s1_keys, ctx->s1_scores, n, ctx->s1_key_bits + ctx->s1_group_bits - 8, ctx->peer_base.as<uint32_t>(), D, true, Rn);
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));          // the caller's barrier may only follow completed stores (and b32 is a stack array)
+    });
+}
+
+int ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_start, uint32_t group_bits, int32_t group_ordered,
+                         const uint32_t* group_branch, uint32_t n_groups_total, uint32_t key_bits, float threshold, uint32_t total_num_groups,
+                         int32_t filter, int result_mode, ipkgpu_result* out)
+{
+    return guarded(ctx, [&] {
+        if (!out || !bucket_start) fail(IPKGPU_EINVAL, "null argument");
+        if (!group_branch && n_groups_total) fail(IPKGPU_EINVAL, "group_branch is null");
+        if (filter != IPKGPU_FILTER_MIF0 && filter != IPKGPU_FILTER_RANDOM) fail(IPKGPU_EINVAL, "unknown filter %d", filter);
+        if (n && !ps_eligible(key_bits, group_bits, n)) fail(IPKGPU_EINVAL, "records do not fit the packed form");
+        if (n * 8 > ctx->recv_keys.cap) fail(IPKGPU_EINVAL, "%llu records exceed the receive buffer (ipkgpu_recv_packed)", (unsigned long long)n);
+        memset(out, 0, sizeof *out);
+        ctx->res_valid = false;
+        stage_timer tm(ctx);
+        const size_t t0 = tm.mark();
+        ctx->reserve(ctx->group_branch, size_t(n_groups_total) * 4 + 4);
+        IPK_CUDA(cudaMemcpyAsync(ctx->group_branch.p, group_branch, size_t(n_groups_total) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->max_branch = 0;
+        for (uint32_t g = 0; g < n_groups_total; ++g) ctx->max_branch = std::max(ctx->max_branch, group_branch[g]);
+        const stage2_params sp{ group_bits, key_bits, total_num_groups, threshold, filter };
+        if (n == 0)
+        {
+            ctx->reserve(ctx->kmer_offs, 8);
+            IPK_CUDA(cudaMemsetAsync(ctx->kmer_offs.p, 0, 8, ctx->stream));
+            finish_from_csr(ctx, 0, 0, sp, result_mode, out, tm);
+        }
+        else
+        {
+            ps_table T;
+            memset(&T, 0, sizeof T);
+            for (int d = 0; d <= PS_BUCKETS; ++d)
+            {
+                if (bucket_start[d] > n || (d && bucket_start[d] < bucket_start[d - 1])) fail(IPKGPU_EINVAL, "bucket_start is not an ascending table ending at n");
+                T.start[d] = uint32_t(bucket_start[d]);
+            }
+            if (bucket_start[PS_BUCKETS] != n) fail(IPKGPU_EINVAL, "bucket_start[256] must equal n");
+            ctx->reserve(ctx->keys_a, n * 8 + 8);
+            const bool parts = parts_eligible(ctx, n, key_bits, key_bits + group_bits, result_mode, key_bits < 63 ? 1ull << key_bits : ~0ull);
+            const bool b16 = parts && (result_mode & 4) != 0 && ctx->max_branch < 65536u;
+            if (parts) prepare_entry_stream(ctx, n, b16);
+            const size_t e0 = tm.mark();
+            const parts_out po = sort_merge_buckets(ctx, ctx->recv_keys.as<uint64_t>(), ctx->keys_a.as<uint64_t>(), T, n, key_bits, group_bits,
+                                                    group_ordered ? group_bits : 0, 0, result_mode, parts, b16, tm, e0, e0, 0);
+            out->stats.sort_passes = po.passes;
+            ctx->hint_kmers_records = n;
+            finish_from_csr(ctx, po.m.n_kmers, po.m.n_records, sp, result_mode, out, tm);
+            out->stats.ms_sort = po.ms_sort;
+            out->stats.ms_merge = po.ms_merge;
+        }
         const size_t t1 = tm.mark();
         IPK_CUDA(cudaEventSynchronize(ctx->event(t1)));
         out->stats.ms_total = tm.ms(t0, t1);

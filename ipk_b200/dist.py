@@ -19,7 +19,6 @@ this module is only the torch.distributed plumbing around it and never computes 
 """
 from __future__ import annotations
 
-import heapq
 from dataclasses import dataclass
 
 import numpy as np
@@ -141,6 +140,35 @@ def peer_exchange(ctx, device, group=None):
     return rk, rs, n_recv, counts
 
 
+def packed_eligible(key_bits: int, group_bits: int) -> bool:
+    """the exchange on packed records (include/ipkgpu.h) needs the low k-mer bits and the group to fit 32 bits"""
+    return key_bits >= 8 and key_bits + group_bits - 8 <= 32
+
+
+def packed_exchange(ctx, device, group=None):
+    """The exchange as the first pass of the merge sort (include/ipkgpu.h): per-rank counts of the 256 top-byte buckets
+    all-gathered, owners = contiguous k-mer ranges of about equal size (ipkgpu_exchange_plan, host arithmetic in the
+    library), every rank's MSD pass stores 8-byte packed records straight into the owners' receive buffers over NVLink.
+    Returns (bucket_start[257] of this rank's buffer, n_received, group_ordered over all ranks, records sent to other ranks)."""
+    from . import capi
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    counts = ctx.stage1_bucket_counts()
+    mine = torch.from_numpy(counts.astype(np.int64)).to(device)
+    rows = [torch.zeros(256, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)             # also orders this build after every rank's previous stage 2
+    matrix = torch.stack(rows).cpu().numpy().astype(np.uint64)
+    owner, base, start, n_recv = capi.exchange_plan(world, rank, matrix)
+    rp, handle = ctx.recv_packed(max(n_recv, 1))
+    h_all = [torch.zeros(64, dtype=torch.uint8, device=device) for _ in range(world)]
+    dist.all_gather(h_all, torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(device), group=group)
+    peers = [rp if r == rank else ctx.open_peer_slot(r, bytes(h_all[r].cpu().numpy().tobytes())) for r in range(world)]
+    ordered = ctx.stage1_scatter_packed(peers, owner, base)        # returns once this rank's stores have completed
+    flag = torch.tensor([1 if ordered else 0], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)       # the barrier: every rank's stores have landed; and the AND of the flags
+    sent_remote = int(counts[owner != rank].sum())
+    return start, n_recv, bool(int(flag.item())), sent_remote
+
+
 def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: float, total_num_groups: int, filter: int,
                   device, result_on_device: bool = False, group=None, table: GroupTable | None = None, raw: bool = True,
                   exchange: str = "peer", indexed: bool = False, branch16: bool = False):
@@ -152,7 +180,17 @@ def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: f
     cuda = torch.device(device).type == "cuda"
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if cuda else None
     n_unique, st1 = ctx.stage1(inp, table.group_base, table.group_bits, raw)
-    if exchange == "peer" and cuda and hasattr(ctx, "stage1_scatter"):
+    if exchange in ("peer", "packed") and raw and cuda and hasattr(ctx, "stage1_scatter_packed") and packed_eligible(key_bits, table.group_bits) \
+            and exchange != "peer-pairs":
+        ev[0].record()
+        start, n_recv, ordered, sent_remote = packed_exchange(ctx, device, group)
+        ev[2].record()
+        res = ctx.stage2_packed(n_recv, start, table.group_bits, ordered, table.group_branch, key_bits, threshold, total_num_groups, filter,
+                                result_on_device, **({"indexed": True, "branch16": branch16} if indexed else {}))
+        info = dict(stage1=st1, n_unique_local=int(n_unique), n_received=n_recv, keep=None, ms_partition=0.0, n_sent_remote=sent_remote,
+                    ms_exchange=ev[0].elapsed_time(ev[2]), exchange="packed MSD pass into peer memory", group_ordered=ordered, bytes_per_record=8)
+        return res, info
+    if exchange in ("peer", "peer-pairs") and cuda and hasattr(ctx, "stage1_scatter"):
         ev[0].record()
         rk, rs, n_recv, counts = peer_exchange(ctx, device, group)
         ev[2].record()
@@ -186,23 +224,8 @@ def sharded_build(ctx, inp, node_branch: np.ndarray, key_bits: int, threshold: f
 
 def merge_shards(shards):
     """G-way merge of per-rank databases (each in ascending (fv, key) order) into one, the shape of merge_stage2
-    (db_builder.cpp:392-458).  shards: objects with keys / fv / offsets / branch / score numpy arrays.
-    Host-side, run while serializing; returns the five arrays of the merged database."""
-    heads = []
-    for s, d in enumerate(shards):
-        if len(d.keys):
-            heads.append((float(d.fv[0]), int(d.keys[0]), s, 0))
-    heapq.heapify(heads)
-    keys, fv, cnt, br, sc = [], [], [], [], []
-    while heads:
-        f, k, s, i = heapq.heappop(heads)
-        d = shards[s]
-        a, b = int(d.offsets[i]), int(d.offsets[i + 1])
-        keys.append(k); fv.append(f); cnt.append(b - a); br.append(d.branch[a:b]); sc.append(d.score[a:b])
-        if i + 1 < len(d.keys):
-            heapq.heappush(heads, (float(d.fv[i + 1]), int(d.keys[i + 1]), s, i + 1))
-    offsets = np.zeros(len(keys) + 1, np.uint64)
-    offsets[1:] = np.cumsum(np.asarray(cnt, dtype=np.uint64)) if keys else 0
-    return (np.asarray(keys, np.uint64), np.asarray(fv, np.float32), offsets,
-            np.concatenate(br).astype(np.uint32) if br else np.zeros(0, np.uint32),
-            np.concatenate(sc).astype(np.float32) if sc else np.zeros(0, np.float32))
+    (db_builder.cpp:392-458): the native N-way merge of libipkhost (host/ipk_file.cpp: ipkhost_merge_order, worker threads
+    over disjoint filter-value ranges) materialised as the five arrays of the merged database.  Shards may be contiguous
+    (offsets[i+1] ends k-mer i) or indexed (a `counts` array)."""
+    from . import hostlib
+    return hostlib.merge_shards(shards)

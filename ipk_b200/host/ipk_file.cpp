@@ -98,8 +98,18 @@ namespace
 
     inline uint64_t entries_of(const ipkhost_db* db, uint64_t q) { return db->counts ? db->counts[q] : db->offsets[q + 1] - db->offsets[q]; }
 
-    /// k-mers [q0, q1) formatted into private blocks and written at file offset `at` (record = 20 + 8 n bytes)
-    bool write_range(int fd, const ipkhost_db* db, uint64_t q0, uint64_t q1, uint64_t at)
+    /// where the k-mer at output position q lives: one database, or k-mer order_index[q] of shard order_shard[q]
+    struct source
+    {
+        const ipkhost_db* dbs;
+        const uint8_t* order_shard;        // null: dbs[0], position q itself
+        const uint32_t* order_index;
+        const ipkhost_db* db(uint64_t q) const { return order_shard ? dbs + order_shard[q] : dbs; }
+        uint64_t at(uint64_t q) const { return order_shard ? order_index[q] : q; }
+    };
+
+    /// output positions [q0, q1) formatted into private blocks and written at file offset `at` (record = 20 + 8 n bytes)
+    bool write_range(int fd, const source& S, uint64_t q0, uint64_t q1, uint64_t at)
     {
         const size_t BLOCK = 8u << 20;
         std::vector<unsigned char> buf(BLOCK + 64);
@@ -117,23 +127,76 @@ namespace
         };
         for (uint64_t q = q0; q < q1; ++q)
         {
-            const uint64_t a = db->offsets[q], n = entries_of(db, q);
+            const ipkhost_db* db = S.db(q);
+            const uint64_t i = S.at(q);
+            const uint64_t a = db->offsets[i], n = entries_of(db, i);
             if (fill + 20 > BLOCK && !flush()) return false;
             unsigned char* p = buf.data() + fill;
-            memcpy(p, &db->keys[q], 8); memcpy(p + 8, &db->fv[q], 4); memcpy(p + 12, &n, 8);
+            memcpy(p, &db->keys[i], 8); memcpy(p + 8, &db->fv[i], 4); memcpy(p + 12, &n, 8);
             fill += 20;
             for (uint64_t e = a; e < a + n;)
             {
                 if (fill + 8 > BLOCK && !flush()) return false;
                 const uint64_t room = (BLOCK - fill) / 8, m = std::min<uint64_t>(room, a + n - e);
                 unsigned char* o = buf.data() + fill;
-                if (db->branch16) for (uint64_t i = 0; i < m; ++i) { const uint32_t b = db->branch16[e + i]; memcpy(o + 8 * i, &b, 4); memcpy(o + 8 * i + 4, &db->score[e + i], 4); }
-                else for (uint64_t i = 0; i < m; ++i) { memcpy(o + 8 * i, &db->branch[e + i], 4); memcpy(o + 8 * i + 4, &db->score[e + i], 4); }
+                if (db->branch16) for (uint64_t j = 0; j < m; ++j) { const uint32_t b = db->branch16[e + j]; memcpy(o + 8 * j, &b, 4); memcpy(o + 8 * j + 4, &db->score[e + j], 4); }
+                else for (uint64_t j = 0; j < m; ++j) { memcpy(o + 8 * j, &db->branch[e + j], 4); memcpy(o + 8 * j + 4, &db->score[e + j], 4); }
                 fill += size_t(m) * 8;
                 e += m;
             }
         }
         return flush();
+    }
+
+    /// header + all records of `S` (n_kmers output positions, n_entries entries in total) with T threads
+    int write_all(const char* path, const ipkhost_db* header, const source& S, uint64_t n_kmers, uint64_t n_entries, int n_threads)
+    {
+        FILE* f = fopen(path, "wb");
+        if (!f) return IPKHOST_EIO;
+        uint64_t header_bytes = 0;
+        {
+            ipkhost_db h = *header;
+            h.n_kmers = n_kmers; h.n_entries = n_entries;
+            writer w(f);
+            put_header(w, &h);
+            header_bytes = w.total + w.buf.size();
+            w.flush();
+            if (!w.ok || fflush(f) != 0) { fclose(f); return IPKHOST_EIO; }
+        }
+        // save_phylo_kmer(kmer, filter_value, entries) in the order handed over (db_builder.cpp:323-332): the k-mers are cut
+        // into runs of about equal bytes, one thread formats and pwrites each run at its prefix-summed offset
+        unsigned T = n_threads > 0 ? unsigned(n_threads) : std::max(1u, std::thread::hardware_concurrency());
+        T = unsigned(std::min<uint64_t>(T, std::max<uint64_t>(1, n_kmers / 4096)));
+        const uint64_t total = n_kmers * 20 + n_entries * 8;
+        std::vector<uint64_t> cut(T + 1, n_kmers), at(T + 1, total);
+        cut[0] = 0; at[0] = 0;
+        {
+            uint64_t acc = 0, next = 1;
+            for (uint64_t q = 0; q < n_kmers && next < T; ++q)
+            {
+                while (next < T && acc >= total / T * next) { cut[next] = q; at[next] = acc; ++next; }
+                acc += 20 + 8 * entries_of(S.db(q), S.at(q));
+            }
+            // cuts never reached (the last k-mers are long) stay at the end: empty ranges
+        }
+        const int fd = fileno(f);
+        std::vector<char> ok(T, 1);
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < T; ++t)
+            th.emplace_back([&, t] { ok[t] = write_range(fd, S, cut[t], cut[t + 1], header_bytes + at[t]) ? 1 : 0; });
+        for (auto& x : th) x.join();
+        bool good = true;
+        for (char c : ok) good = good && c;
+        good = fclose(f) == 0 && good;
+        return good ? IPKHOST_OK : IPKHOST_EIO;
+    }
+
+    /// the order the device sorts filter values in (filter.cuh: k5_order_keys): sign-flipped bit image, ties by key
+    inline uint32_t fv_image(float f) { uint32_t b; memcpy(&b, &f, 4); return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u); }
+    inline bool head_less(const ipkhost_db& a, uint64_t i, const ipkhost_db& b, uint64_t j)
+    {
+        const uint32_t x = fv_image(a.fv[i]), y = fv_image(b.fv[j]);
+        return x != y ? x < y : a.keys[i] < b.keys[j];
     }
 }
 
@@ -145,42 +208,71 @@ int ipkhost_write_ipk_mt(const char* path, const ipkhost_db* db, int n_threads)
     if (!path || !db) return IPKHOST_EINVAL;
     if (db->n_kmers && (!db->keys || !db->fv || !db->offsets)) return IPKHOST_EINVAL;
     if (db->n_entries && ((!db->branch && !db->branch16) || !db->score)) return IPKHOST_EINVAL;
-    FILE* f = fopen(path, "wb");
-    if (!f) return IPKHOST_EIO;
-    uint64_t header_bytes = 0;
+    const source S{ db, nullptr, nullptr };
+    return write_all(path, db, S, db->n_kmers, db->n_entries, n_threads);
+}
+
+int ipkhost_merge_order(uint32_t n_shards, const ipkhost_db* shards, int n_threads, uint8_t* out_shard, uint32_t* out_index)
+{
+    if (!shards || n_shards < 1 || n_shards > 255) return IPKHOST_EINVAL;
+    uint64_t total = 0;
+    uint32_t biggest = 0;
+    for (uint32_t s = 0; s < n_shards; ++s)
     {
-        writer w(f);
-        put_header(w, db);
-        header_bytes = w.total + w.buf.size();
-        w.flush();
-        if (!w.ok || fflush(f) != 0) { fclose(f); return IPKHOST_EIO; }
+        if (shards[s].n_kmers > 0xffffffffull) return IPKHOST_EINVAL;
+        total += shards[s].n_kmers;
+        if (shards[s].n_kmers > shards[biggest].n_kmers) biggest = s;
     }
-    // save_phylo_kmer(kmer, filter_value, entries) in the order handed over (db_builder.cpp:323-332): the k-mers are cut
-    // into runs of about equal bytes, one thread formats and pwrites each run at its prefix-summed offset
+    if (total == 0) return IPKHOST_OK;
+    if (!out_shard || !out_index) return IPKHOST_EINVAL;
     unsigned T = n_threads > 0 ? unsigned(n_threads) : std::max(1u, std::thread::hardware_concurrency());
-    T = unsigned(std::min<uint64_t>(T, std::max<uint64_t>(1, db->n_kmers / 4096)));
-    const uint64_t total = db->n_kmers * 20 + db->n_entries * 8;
-    std::vector<uint64_t> cut(T + 1, db->n_kmers), at(T + 1, total);
-    cut[0] = 0; at[0] = 0;
+    T = unsigned(std::min<uint64_t>(T, std::max<uint64_t>(1, total / 65536)));
+    // splitters: T - 1 evenly spaced k-mers of the largest shard; lower bounds of each in every shard give the threads
+    // disjoint input ranges and their output offsets (keys are unique across shards, so no tie straddles a cut)
+    std::vector<std::vector<uint64_t>> lo(T + 1, std::vector<uint64_t>(n_shards, 0));
+    for (uint32_t s = 0; s < n_shards; ++s) lo[T][s] = shards[s].n_kmers;
+    const ipkhost_db& B = shards[biggest];
+    for (unsigned t = 1; t < T; ++t)
     {
-        uint64_t acc = 0, next = 1;
-        for (uint64_t q = 0; q < db->n_kmers && next < T; ++q)
+        const uint64_t pivot = B.n_kmers * t / T;
+        for (uint32_t s = 0; s < n_shards; ++s)
         {
-            while (next < T && acc >= total / T * next) { cut[next] = q; at[next] = acc; ++next; }
-            acc += 20 + 8 * entries_of(db, q);
+            uint64_t a = 0, b = shards[s].n_kmers;           // first i with !(shard[i] < pivot)
+            while (a < b) { const uint64_t m = (a + b) / 2; if (head_less(shards[s], m, B, pivot)) a = m + 1; else b = m; }
+            lo[t][s] = a;
         }
-        // cuts never reached (the last k-mers are long) stay at the end: empty ranges
     }
-    const int fd = fileno(f);
-    std::vector<char> ok(T, 1);
     std::vector<std::thread> th;
     for (unsigned t = 0; t < T; ++t)
-        th.emplace_back([&, t] { ok[t] = write_range(fd, db, cut[t], cut[t + 1], header_bytes + at[t]) ? 1 : 0; });
+        th.emplace_back([&, t] {
+            uint64_t out = 0;
+            for (uint32_t s = 0; s < n_shards; ++s) out += lo[t][s];
+            std::vector<uint64_t> cur(lo[t]);
+            const std::vector<uint64_t>& end = lo[t + 1];
+            while (true)
+            {
+                int best = -1;
+                for (uint32_t s = 0; s < n_shards; ++s)
+                    if (cur[s] < end[s] && (best < 0 || head_less(shards[s], cur[s], shards[best], cur[best]))) best = int(s);
+                if (best < 0) break;
+                out_shard[out] = uint8_t(best);
+                out_index[out] = uint32_t(cur[best]++);
+                ++out;
+            }
+        });
     for (auto& x : th) x.join();
-    bool good = true;
-    for (char c : ok) good = good && c;
-    good = fclose(f) == 0 && good;
-    return good ? IPKHOST_OK : IPKHOST_EIO;
+    return IPKHOST_OK;
+}
+
+int ipkhost_write_ipk_sharded(const char* path, const ipkhost_db* header, uint32_t n_shards, const ipkhost_db* shards,
+                              const uint8_t* order_shard, const uint32_t* order_index, int n_threads)
+{
+    if (!path || !header || !shards || n_shards < 1) return IPKHOST_EINVAL;
+    uint64_t n_kmers = 0, n_entries = 0;
+    for (uint32_t s = 0; s < n_shards; ++s) { n_kmers += shards[s].n_kmers; n_entries += shards[s].n_entries; }
+    if (n_kmers && (!order_shard || !order_index)) return IPKHOST_EINVAL;
+    const source S{ shards, order_shard, order_index };
+    return write_all(path, header, S, n_kmers, n_entries, n_threads);
 }
 
 int ipkhost_write_ipk(const char* path, const ipkhost_db* db) { return ipkhost_write_ipk_mt(path, db, 0); }

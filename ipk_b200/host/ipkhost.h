@@ -93,6 +93,14 @@ int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);                 
 /* n_threads <= 0: all cores.  The k-mers are cut into runs of equal bytes (a record is 20 + 8 n bytes), every thread
  * formats its run into private 8 MiB blocks and pwrites them at the prefix-summed offset. */
 int  ipkhost_write_ipk_mt(const char* path, const ipkhost_db* db, int n_threads);
+/* The shards of a multi-GPU build (one per rank: disjoint k-mer sets, each in ascending (filter value, key)) as ONE database:
+ * ipkhost_merge_order is the N-way merge by (filter value, key) of merge_stage2 (db_builder.cpp:392-458) over the k-mer
+ * heads only -- the k-mer at merged position i is k-mer out_index[i] of shard out_shard[i], its entries stay where they are;
+ * n_threads workers own disjoint filter-value ranges.  ipkhost_write_ipk_sharded streams that order into one file (header
+ * fields from `header`, counts summed over the shards), as merge_stage2 does while it merges. */
+int  ipkhost_merge_order(uint32_t n_shards, const ipkhost_db* shards, int n_threads, uint8_t* out_shard, uint32_t* out_index);
+int  ipkhost_write_ipk_sharded(const char* path, const ipkhost_db* header, uint32_t n_shards, const ipkhost_db* shards,
+                               const uint8_t* order_shard, const uint32_t* order_index, int n_threads);
 /* reads a file written by ipkhost_write_ipk; arrays are owned by the returned handle */
 typedef struct ipkhost_db_file ipkhost_db_file;
 int  ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view);

@@ -48,6 +48,8 @@ def load() -> C.CDLL:
         lib.ipkhost_free_ipk.argtypes = [C.c_void_p]
         lib.ipkhost_free_ipk.restype = None
         lib.ipkhost_write_ipk_mt.argtypes = [C.c_char_p, P(HostDb), C.c_int]
+        lib.ipkhost_merge_order.argtypes = [C.c_uint32, P(HostDb), C.c_int, C.c_void_p, C.c_void_p]
+        lib.ipkhost_write_ipk_sharded.argtypes = [C.c_char_p, P(HostDb), C.c_uint32, P(HostDb), C.c_void_p, C.c_void_p, C.c_int]
         lib.ipkhost_plan_create.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, P(C.c_void_p)]
         lib.ipkhost_plan_free.argtypes = [C.c_void_p]
         lib.ipkhost_plan_free.restype = None
@@ -153,3 +155,68 @@ def read_ipk(path: str) -> dict:
                     branch=arr(v.branch, ne), score=arr(v.score, ne))
     finally:
         lib.ipkhost_free_ipk(h)
+
+
+def _host_db(d, keep: list) -> HostDb:
+    """ipkhost_db view of an object with keys / fv / offsets / branch (or branch16) / score (+ counts for indexed shards)"""
+    def arr(name, dtype):
+        a = getattr(d, name, None)
+        if a is None:
+            return None
+        a = np.ascontiguousarray(a, dtype)
+        keep.append(a)
+        return a
+    keys, fv, offsets = arr("keys", np.uint64), arr("fv", np.float32), arr("offsets", np.uint64)
+    counts, branch, b16, score = arr("counts", np.uint32), arr("branch", np.uint32), arr("branch16", np.uint16), arr("score", np.float32)
+    ptr = lambda a, t: a.ctypes.data_as(C.POINTER(t)) if a is not None else None
+    n_entries = len(score) if score is not None else 0
+    return HostDb(b"", b"", 0, None, None, 0, 0.0, len(keys), n_entries, ptr(keys, C.c_uint64), ptr(fv, C.c_float), ptr(offsets, C.c_uint64),
+                  ptr(counts, C.c_uint32), ptr(branch, C.c_uint32), ptr(score, C.c_float), ptr(b16, C.c_uint16))
+
+
+def merge_order(shards, threads: int = 0):
+    """N-way merge of shard heads by (filter value, key) (merge_stage2, db_builder.cpp:392-458): -> (shard[u8], index[u32]) per merged k-mer"""
+    keep: list = []
+    views = (HostDb * len(shards))(*[_host_db(d, keep) for d in shards])
+    total = sum(len(d.keys) for d in shards)
+    out_shard, out_index = np.zeros(total, np.uint8), np.zeros(total, np.uint32)
+    rc = load().ipkhost_merge_order(len(shards), views, threads, out_shard.ctypes.data, out_index.ctypes.data)
+    if rc != 0:
+        raise HostError(rc, "ipkhost_merge_order")
+    return out_shard, out_index
+
+
+def merge_shards(shards, threads: int = 0):
+    """the merged database as five arrays (keys, fv, offsets, branch, score): what a reader of the one file would see"""
+    sh, ix = merge_order(shards, threads)
+    total = len(sh)
+    keys, fv, cnt = np.zeros(total, np.uint64), np.zeros(total, np.float32), np.zeros(total, np.int64)
+    starts = np.zeros(total, np.int64)
+    bases = np.concatenate(([0], np.cumsum([len(d.score) for d in shards]))).astype(np.int64)
+    for s, d in enumerate(shards):
+        m = sh == s
+        i = ix[m].astype(np.int64)
+        keys[m] = np.asarray(d.keys)[i]; fv[m] = np.asarray(d.fv)[i]
+        off = np.asarray(d.offsets).astype(np.int64)
+        c = np.asarray(d.counts).astype(np.int64)[i] if getattr(d, "counts", None) is not None else off[i + 1] - off[i]
+        cnt[m] = c; starts[m] = off[i] + bases[s]
+    offsets = np.zeros(total + 1, np.uint64)
+    offsets[1:] = np.cumsum(cnt)
+    branch_all = np.concatenate([np.asarray(d.branch if getattr(d, "branch", None) is not None else d.branch16).astype(np.uint32) for d in shards]) if shards else np.zeros(0, np.uint32)
+    score_all = np.concatenate([np.asarray(d.score, np.float32) for d in shards]) if shards else np.zeros(0, np.float32)
+    idx = np.repeat(starts - offsets[:-1].astype(np.int64), cnt) + np.arange(int(cnt.sum()), dtype=np.int64)
+    return keys, fv, offsets, branch_all[idx], score_all[idx]
+
+
+def write_ipk_sharded(path: str, shards, kmer_size: int, omega: float, sequence_type: str = "DNA", tree: str = "",
+                      index_num_nodes=None, index_len=None, threads: int = 0) -> None:
+    keep: list = []
+    views = (HostDb * len(shards))(*[_host_db(d, keep) for d in shards])
+    sh, ix = merge_order(shards, threads)
+    inn = np.ascontiguousarray(index_num_nodes if index_num_nodes is not None else [], np.uint64)
+    il = np.ascontiguousarray(index_len if index_len is not None else [], np.float64)
+    header = HostDb(sequence_type.encode(), tree.encode(), len(inn), inn.ctypes.data_as(C.POINTER(C.c_uint64)), il.ctypes.data_as(C.POINTER(C.c_double)),
+                    kmer_size, omega, 0, 0, None, None, None, None, None, None, None)
+    rc = load().ipkhost_write_ipk_sharded(path.encode(), C.byref(header), len(shards), views, sh.ctypes.data, ix.ctypes.data, threads)
+    if rc != 0:
+        raise HostError(rc, "cannot write " + path)

@@ -244,6 +244,69 @@ def test_sharded_stages_equal_single(world, sigma, bits, k, n_taxa, W, raw):
             c.close()
 
 
+@pytest.mark.parametrize("world", [2, 3, 5])
+@pytest.mark.parametrize("k,n_taxa,W,enum_mode", [(8, 20, 200, 0), (10, 12, 150, 0), (4, 16, 120, 0), (8, 20, 200, 1)])
+@pytest.mark.parametrize("streamed,filt", [(False, 0), (True, 0), (False, 1)])
+def test_packed_exchange_equals_single(world, k, n_taxa, W, enum_mode, streamed, filt, monkeypatch):
+    """The exchange as the MSD pass of the merge sort (ipkgpu_stage1_bucket_counts / ipkgpu_exchange_plan / recv_packed /
+    stage1_scatter_packed / stage2_packed), ranks emulated as contexts of ONE process on one device so that the "peer"
+    buffers are plain device pointers (the IPC mapping is exercised by bench.py --gpus N, whose database digest must equal
+    the single-GPU one).  Entry-for-entry equal to the single-GPU build, filter values bit for bit -- also under the random
+    filter, whose draw is a function of the k-mer.  enum_mode 1 (depth-first kernel: no runs) takes the unordered path."""
+    from types import SimpleNamespace
+    from ipk_b200 import capi as libipkgpu, dist as ipkdist, hostlib
+    if streamed:
+        monkeypatch.setenv("IPKGPU_PART_MIN", "1")
+        monkeypatch.setenv("IPKGPU_PARTS", "3")
+    sigma, bits, omega = 4, 2, 1.5
+    logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    with libipkgpu.Context(0) as c1:
+        want = c1.build(logp, nb, W, sigma, bits, k, lthr, thr, T, filt)
+    parts = ipkdist.split_branches(2 * n_taxa - 2, world)
+    group_branch = ipkdist.local_groups(nb)
+    group_bits = max(int(np.ceil(np.log2(len(group_branch)))), 0)
+    assert ipkdist.packed_eligible(k * bits, group_bits)
+    ctxs = [libipkgpu.Context(0) for _ in range(world)]
+    try:
+        matrix = np.zeros((world, 256), np.uint64)
+        for r, (b0, b1) in enumerate(parts):
+            ctxs[r].set_enumeration(enum_mode, 0)
+            sl = slice(2 * b0, 2 * b1)
+            inp, keep = libipkgpu.make_input(np.ascontiguousarray(logp[sl]), nb[sl], W, sigma, bits, k, lthr, thr, T, filt)
+            n1, _ = ctxs[r].stage1(inp, b0, group_bits, True)
+            matrix[r] = ctxs[r].stage1_bucket_counts()
+            assert int(matrix[r].sum()) == n1
+        plans = [libipkgpu.exchange_plan(world, r, matrix) for r in range(world)]
+        assert all(np.array_equal(plans[0][0], p[0]) for p in plans) and np.all(np.diff(plans[0][0].astype(int)) >= 0)     # owners: the same contiguous ranges everywhere
+        assert sum(p[3] for p in plans) == int(matrix.sum())
+        bufs = [ctxs[r].recv_packed(max(plans[r][3], 1)) for r in range(world)]
+        ordered = all([ctxs[r].stage1_scatter_packed([b[0] for b in bufs], plans[r][0], plans[r][1]) for r in range(world)])
+        assert ordered == (enum_mode == 0)
+        shards = []
+        for r in range(world):
+            res = ctxs[r].stage2_packed(plans[r][3], plans[r][2], group_bits, ordered, group_branch, k * bits, thr, T, filt, False,
+                                        indexed=streamed, branch16=streamed)
+            assert bool(res.branch16) == (streamed and plans[r][3] > 0)
+            if ordered and plans[r][3]:
+                assert res.stats.sort_passes == (k * bits - 8 + 7) // 8           # the owner sorts the k-mer bits below the bucket byte, nothing else
+            shards.append(libipkgpu.Context.to_db(res))
+            d = ctxs[r].result_digest(lthr)
+            assert d["n_entries"] == shards[-1].n_entries
+        assert sum(s.n_entries for s in shards) == want.n_entries
+        # key RANGES: every k-mer of shard r lies below every k-mer of shard r + 1
+        tops = [(int(s.keys.min()), int(s.keys.max())) for s in shards if s.n_kmers]
+        assert all(a[1] < b[0] for a, b in zip(tops, tops[1:]))
+        merged = hostlib.merge_shards(shards)
+        got = SimpleNamespace(keys=merged[0], fv=merged[1], offsets=merged[2], branch=merged[3], score=merged[4],
+                              n_kmers=len(merged[0]), n_entries=len(merged[3]))
+        assert_db_equal(got, want, exact_fv=True)
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 @pytest.mark.parametrize("raw", [True, False])
 @pytest.mark.parametrize("world", [2, 3])
 @pytest.mark.parametrize("sigma,bits,k,n_taxa,W", [(4, 2, 8, 20, 200), (20, 5, 4, 8, 90)])

@@ -418,3 +418,72 @@ def test_reference_command_line_end_to_end(ghosts, tmp_path):
                           n_kmers=len(d["keys"]), n_entries=len(d["branch"]))
     assert want.n_entries > 100
     assert_db_equal(got, want)
+
+
+def _random_shards(rng, n_shards, n_kmers_each, with_ties=True):
+    """disjoint key sets, each shard in ascending (fv, key); a few exactly equal filter values across and inside shards"""
+    from types import SimpleNamespace
+    keys_all = rng.permutation(1 << 20)[: n_shards * n_kmers_each].astype(np.uint64)
+    shards = []
+    for s in range(n_shards):
+        keys = keys_all[s * n_kmers_each:(s + 1) * n_kmers_each]
+        fv = rng.normal(size=n_kmers_each).astype(np.float32)
+        if with_ties:
+            fv[rng.integers(0, n_kmers_each, n_kmers_each // 10)] = np.float32(0.125)
+            fv[:3] = [-0.0, 0.0, -1.5]
+        img = fv.view(np.uint32).astype(np.int64)
+        o = np.lexsort((keys, np.where(img >> 31, img ^ 0xffffffff, img ^ 0x80000000)))     # the order the device leaves a shard in
+        keys, fv = keys[o], fv[o]
+        cnt = rng.integers(1, 6, n_kmers_each)
+        offsets = np.concatenate(([0], np.cumsum(cnt))).astype(np.uint64)
+        ne = int(offsets[-1])
+        shards.append(SimpleNamespace(keys=keys, fv=fv, offsets=offsets, branch=rng.integers(0, 900, ne).astype(np.uint32),
+                                      score=(-4 * rng.random(ne)).astype(np.float32)))
+    return shards
+
+
+@pytest.mark.parametrize("n_shards,threads", [(1, 1), (2, 1), (3, 4), (8, 16)])
+def test_merge_order_is_the_sort_by_filter_value_and_key(n_shards, threads, tmp_path):
+    """ipkhost_merge_order (the N-way merge of merge_stage2, db_builder.cpp:392-458) against one global sort, and the sharded
+    writer against the single-database writer byte for byte"""
+    from ipk_b200 import hostlib
+    rng = np.random.default_rng(40 + n_shards)
+    shards = _random_shards(rng, n_shards, 70000)
+    keys, fv, offsets, branch, score = hostlib.merge_shards(shards, threads)
+    all_keys = np.concatenate([s.keys for s in shards]); all_fv = np.concatenate([s.fv for s in shards])
+    img = all_fv.view(np.uint32).astype(np.int64)
+    img = np.where(img >> 31, img ^ 0xffffffff, img ^ 0x80000000)            # the device's order of floats: -0.0 before 0.0
+    o = np.lexsort((all_keys, img))
+    assert np.array_equal(keys, all_keys[o]) and np.array_equal(fv.view(np.uint32), all_fv[o].view(np.uint32))
+    # entries follow their k-mer
+    k0 = int(keys[12345])
+    s0 = next(s for s in shards if k0 in set(s.keys[:].tolist()))
+    i0 = int(np.where(s0.keys == k0)[0][0])
+    a, b = int(offsets[12345]), int(offsets[12346])
+    assert np.array_equal(branch[a:b], s0.branch[int(s0.offsets[i0]):int(s0.offsets[i0 + 1])])
+    one, many = str(tmp_path / "one.ipk"), str(tmp_path / "many.ipk")
+    hostlib.write_ipk(one, keys, fv, offsets, branch, score, 9, 1.5, "DNA", "(a:1,b:2);", [1, 1, 3], [0, 0, 3])
+    hostlib.write_ipk_sharded(many, shards, 9, 1.5, "DNA", "(a:1,b:2);", [1, 1, 3], [0, 0, 3], threads)
+    assert open(one, "rb").read() == open(many, "rb").read()
+
+
+def test_exchange_plan_arithmetic():
+    """ipkgpu_exchange_plan (host-only, no device): owners are contiguous balanced bucket ranges, the bases tile every owner's
+    buffer exactly -- bucket after bucket, source rank after source rank"""
+    from ipk_b200 import capi
+    rng = np.random.default_rng(8)
+    for world in (1, 2, 3, 8):
+        counts = rng.integers(0, 5000, (world, 256)).astype(np.uint64)
+        counts[:, rng.integers(0, 256, 20)] = 0
+        plans = [capi.exchange_plan(world, r, counts) for r in range(world)]
+        owner = plans[0][0]
+        total = counts.sum(0)
+        assert all(np.array_equal(owner, p[0]) for p in plans) and np.all(np.diff(owner.astype(int)) >= 0) and owner.max() < world
+        load = np.array([int(total[owner == r].sum()) for r in range(world)])
+        assert [p[3] for p in plans] == list(load)
+        assert load.max() - load.min() <= 2 * int(total.max())                 # balanced to a bucket
+        for o in range(world):
+            spans = sorted((int(plans[r][1][d]), int(plans[r][1][d]) + int(counts[r, d])) for r in range(world) for d in range(256) if owner[d] == o and counts[r, d])
+            assert spans[0][0] == 0 and spans[-1][1] == load[o] and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            start = plans[o][2]
+            assert start[256] == load[o] and all(int(start[d + 1]) - int(start[d]) == (int(total[d]) if owner[d] == o else 0) for d in range(256))
