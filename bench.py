@@ -164,7 +164,7 @@ def workload_config(wl, n_gpus, seed=42):
             "result": "B200 arm: indexed CSR (ipkgpu.h IPKGPU_RESULT_*_INDEXED): k-mers in filter-value order, each pointing at its entries",
             "workload": wl.name, "n_taxa": wl.n_taxa, "alignment_columns": wl.width, "k": wl.k, "omega": wl.omega,
             "states": wl.sigma, "filter": wl.filter, "branch_groups": wl.n_branches, "ghost_matrices": wl.n_ghost_nodes,
-            "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", records bucketed by k-mer hash and stored into the owners' buffers over NVLink peer memory, sorted once by the owner"
+            "windows": wl.n_windows, "partition": f"branch groups over {n_gpus} GPU(s)" + (", the first pass of the merge sort stores 8-byte packed records into the k-mer-range owners' buffers over NVLink peer memory"
                                                                    if n_gpus > 1 and os.environ.get("IPK_EXCHANGE", "peer") == "peer" else
                                                                    ", NCCL all-to-all by k-mer hash" if n_gpus > 1 else "")}
 
@@ -241,6 +241,10 @@ def run_b200(args):
     table = ipkdist.exchange_group_table(node_branch, dev) if world > 1 else None
     key_bits = wl.k * wl.bits
 
+    arenas = {}          # N > 1: every rank's host result in a shared page-locked arena; rank 0 maps them all (set up after the warm-up)
+    merged = {}
+    exch_info = {}
+
     def step(host: bool):
         """one build; returns (n_entries of this rank's shard, n_kmers, stats dict, d2h bytes, launches)"""
         inp = inp_host if host else inp_dev
@@ -250,6 +254,15 @@ def run_b200(args):
             return int(res.n_entries), int(res.n_kmers), st, int(st["d2h_bytes"]), int(st["kernel_launches"]), 0
         res, info = ipkdist.sharded_build(ctx, inp, node_branch, key_bits, thr, wl.n_tree_nodes, filt, dev, result_on_device=not host, table=table,
                                           exchange=os.environ.get("IPK_EXCHANGE", "peer"), indexed=True, branch16=host)
+        exch_info.update(exchange=info.get("exchange", "NCCL all-to-all"), bytes_per_record=info.get("bytes_per_record", 12),
+                         n_received_rank0=int(info.get("n_received", 0)))
+        if host and arenas:
+            # the end-to-end build ends with ONE database in rank 0's memory: the shards (mapped in place) + their N-way merge order
+            t_m = time.perf_counter()
+            got = ipkdist.gather_database(res, arenas, dev)
+            if got is not None:
+                merged["shards"], merged["order"] = got
+                merged["ms_merge_order"] = (time.perf_counter() - t_m) * 1e3
         st = res.stats.as_dict()
         st1 = info["stage1"]
         for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):
@@ -302,7 +315,21 @@ def run_b200(args):
 
     # ---- warm-up (both paths: sizes every grow-only buffer, pins the result staging, settles clocks)
     for _ in range(args.warmup):
-        step(False)
+        last_w = step(False)
+    if world > 1:
+        # shared arenas sized by the shard this rank just built (the workload is deterministic; 5 % head room)
+        # (entries are staged by the RECEIVED record count, an upper bound of the unique entries known before the merge)
+        cap_e, cap_k = int(max(last_w[0], exch_info.get("n_received_rank0", 0)) * 1.05) + 4096, int(last_w[1] * 1.05) + 4096
+        caps = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(caps, torch.tensor([cap_e, cap_k], dtype=torch.int64, device=dev))
+        caps = [[int(x) for x in c.cpu().tolist()] for c in caps]
+        tag = os.environ.get("MASTER_PORT", "0")
+        mine = ipkdist.SharedArena(f"ipkb200_{tag}_{rank}", cap_e, cap_k, create=True)
+        mine.register()
+        ctx.set_result_arena(mine.address, cap_e, cap_k)
+        dist.barrier()
+        for r in range(world):
+            arenas[r] = mine if r == rank else (ipkdist.SharedArena(f"ipkb200_{tag}_{r}", caps[r][0], caps[r][1], create=False) if rank == 0 else None)
     step(True)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -346,6 +373,7 @@ def run_b200(args):
     sent_remote = reduce_sum(last_dev[5])
     if rank != 0:
         if world > 1:
+            _close_arenas(ctx, arenas, rank)
             dist.destroy_process_group()
         return 0
 
@@ -396,7 +424,24 @@ def run_b200(args):
                     "share_of_step": round(top["ms"] / max(ms_dev, 1e-9), 4)}
     # whole-path roofline as north_star defines it: emitted-plus-sorted bytes over HBM vs all-to-all bytes over NVLink
     passes = int(st["sort_passes"])
-    exch_bytes_per_record = 12.0                         # (u64 composite key, f32 score) stored into the owner's buffers
+    exch_bytes_per_record = float(exch_info.get("bytes_per_record", 12))     # 8: packed records; 12: (u64 composite key, f32 score)
+    host_check = None
+    if world > 1 and merged:
+        # what arrived in rank 0's memory IS the database the devices built: digest of the mapped shards, and the merge order ascends
+        from ipk_b200 import hostlib
+        hd = hostlib.digest(merged["shards"])
+        if any(hd[k_] != dig_e2e[k_] for k_ in hd):
+            raise SystemExit(f"bench.py: the shards in rank 0's memory are not the database the devices built: {hd} vs {dig_e2e}")
+        osh, oix = merged["order"]
+        fv_m, key_m = np.zeros(len(osh), np.float32), np.zeros(len(osh), np.uint64)
+        for r_, d_ in enumerate(merged["shards"]):
+            m_ = osh == r_
+            fv_m[m_] = np.asarray(d_.fv)[oix[m_]]; key_m[m_] = np.asarray(d_.keys)[oix[m_]]
+        tie = fv_m[1:] == fv_m[:-1]
+        if len(osh) != n_kmers or not np.all(fv_m[1:] >= fv_m[:-1]) or not np.all(key_m[1:][tie] > key_m[:-1][tie]):
+            raise SystemExit("bench.py: the N-way merge order of the shards is not ascending in (filter value, key)")
+        host_check = (f"{world} shards mapped into rank 0 (shared page-locked arenas), host digest == device digest, N-way merge order over "
+                      f"{len(osh)} k-mers in {merged.get('ms_merge_order', 0.0):.1f} ms (inside the timed region)")
     path_bytes = sum(r["bytes"] for r in rows) / max(args.steps, 1)
     t_hbm = path_bytes / (peak * 1e9)                     # `rows` are rank 0's own kernels: its share of the path already
     t_nvl = (exch_bytes_per_record * sent_remote / world) / (NVLINK_GBS * 1e9) if world > 1 else 0.0
@@ -422,6 +467,11 @@ def run_b200(args):
             "kernels": kernels}
     line["digest"] = {**{k_: str(v) for k_, v in dig_dev.items()}, "check": digest_check,
                       "e2e_equal": True}        # (checked above: the run aborts otherwise)
+    if world > 1:
+        line["e2e"]["artefact"] = host_check or "shards only (no shared arenas)"
+        line["exchange"] = exch_info
+    else:
+        line["e2e"]["artefact"] = "one indexed database in pinned host memory (ipkgpu_build, IPKGPU_RESULT_HOST_INDEXED | BRANCH16)"
     if not args.no_cpu_baseline and world == 1:
         def gpu_check(nb, cpu_db):
             """the same [0, nb) branch-group slice through ipkgpu_build, compared with the CPU arm's database entry for entry"""
@@ -436,8 +486,24 @@ def run_b200(args):
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)
     if world > 1:
+        _close_arenas(ctx, arenas, rank)
         dist.destroy_process_group()
     return 0
+
+
+def _close_arenas(ctx, arenas, rank):
+    import torch.distributed as dist
+    try:
+        ctx.set_result_arena(None, 0, 0)
+    except Exception:
+        pass
+    dist.barrier()
+    for r, a in arenas.items():
+        if a is not None and r != rank:
+            a.close()
+    dist.barrier()
+    if arenas.get(rank) is not None:
+        arenas[rank].close()
 
 
 def main():

@@ -220,11 +220,14 @@ int  ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_st
                           const uint32_t* group_branch, uint32_t n_groups_total, uint32_t key_bits, float threshold,
                           uint32_t total_num_groups, int32_t filter, int result_mode, ipkgpu_result* out);
 
-/* Entries of host results (ipkgpu_result.branch / branch16 / score) go to the caller's PAGE-LOCKED buffers instead of the
- * context's own -- e.g. shared memory that another process maps, so that the shards of a multi-GPU build meet in one
- * address space without a second copy.  The buffers are never grown or freed by the library (a result that does not fit is
- * IPKGPU_ENOMEM); NULL, 0, NULL, 0 returns to the context's own staging. */
-int  ipkgpu_set_entry_staging(ipkgpu_ctx* ctx, void* branch_buf, size_t branch_bytes, void* score_buf, size_t score_bytes);
+/* Host results of ctx (every array of ipkgpu_result) go to ONE caller-provided PAGE-LOCKED arena instead of the context's
+ * own staging -- e.g. a shared-memory segment that another process maps, so that the shards of a multi-GPU build meet in
+ * one address space without a second copy.  ipkgpu_result_arena_layout gives the arena size for the capacities and the byte
+ * offsets of its six arrays: [0] branch (u32, or u16 with IPKGPU_RESULT_BRANCH16) [1] score f32 [2] keys u64 [3] fv f32
+ * [4] offsets u64 [5] counts u32 -- any process can address a mapped arena with it.  The arena is never grown or freed by
+ * the library (a result that does not fit is IPKGPU_ENOMEM); base = NULL returns to the context's own staging. */
+size_t ipkgpu_result_arena_layout(uint64_t cap_entries, uint64_t cap_kmers, size_t* offsets /*[6] or NULL*/);
+int  ipkgpu_set_result_arena(ipkgpu_ctx* ctx, void* base, uint64_t cap_entries, uint64_t cap_kmers);
 
 /* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
  * values -> order (equal composite keys are merged by maximum score).  d_keys/d_scores are overwritten (one side of the sort's ping-pong).

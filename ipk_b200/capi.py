@@ -170,12 +170,21 @@ def load() -> C.CDLL:
     lib.ipkgpu_stage2_packed.argtypes = [C.c_void_p, C.c_uint64, P(C.c_uint64), C.c_uint32, C.c_int32, C.c_void_p, C.c_uint32, C.c_uint32,
                                          C.c_float, C.c_uint32, C.c_int32, C.c_int, P(Result)]
     lib.ipkgpu_stage2_packed.restype = C.c_int
-    lib.ipkgpu_set_entry_staging.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
-    lib.ipkgpu_set_entry_staging.restype = C.c_int
+    lib.ipkgpu_set_result_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64]
+    lib.ipkgpu_set_result_arena.restype = C.c_int
+    lib.ipkgpu_result_arena_layout.argtypes = [C.c_uint64, C.c_uint64, P(C.c_size_t)]
+    lib.ipkgpu_result_arena_layout.restype = C.c_size_t
     lib.ipkgpu_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, P(C.c_float), P(C.c_float)]
     lib.ipkgpu_score_threshold.restype = None
     _lib = lib
     return lib
+
+
+def result_arena_layout(cap_entries: int, cap_kmers: int) -> tuple[int, list[int]]:
+    """(bytes, byte offsets of branch / score / keys / fv / offsets / counts) of a result arena (ipkgpu_result_arena_layout)"""
+    off = (C.c_size_t * 6)()
+    total = load().ipkgpu_result_arena_layout(cap_entries, cap_kmers, off)
+    return int(total), [int(o) for o in off]
 
 
 def exchange_plan(n_parts: int, rank: int, counts: np.ndarray):
@@ -488,9 +497,9 @@ class Context:
                                                    mode, C.byref(res)))
         return res
 
-    def set_entry_staging(self, branch_buf, branch_bytes: int, score_buf, score_bytes: int) -> None:
-        """entries of host results go to the caller's page-locked buffers (e.g. shared memory another process maps); None resets"""
-        self._check(self._lib.ipkgpu_set_entry_staging(self._h, _ptr(branch_buf), branch_bytes, _ptr(score_buf), score_bytes))
+    def set_result_arena(self, base, cap_entries: int, cap_kmers: int) -> None:
+        """host results go to the caller's page-locked arena (e.g. shared memory another process maps); base None resets"""
+        self._check(self._lib.ipkgpu_set_result_arena(self._h, _ptr(base), cap_entries, cap_kmers))
 
     def stage2(self, d_keys, d_scores, n: int, group_bits: int, group_branch: np.ndarray, key_bits: int, threshold: float,
                total_num_groups: int, filter: int = FILTER_MIF0, chunks_group_ordered: bool = True,

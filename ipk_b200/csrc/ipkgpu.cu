@@ -1725,18 +1725,37 @@ int ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t n
 
 // ---- multi-GPU build on packed records: the MSD pass of the merge sort is the exchange (include/ipkgpu.h) ------------
 
-int ipkgpu_set_entry_staging(ipkgpu_ctx* ctx, void* branch_buf, size_t branch_bytes, void* score_buf, size_t score_bytes)
+size_t ipkgpu_result_arena_layout(uint64_t cap_entries, uint64_t cap_kmers, size_t* offsets)
+{
+    const size_t sizes[6] = { size_t(cap_entries) * 4 + 16, size_t(cap_entries) * 4 + 16, size_t(cap_kmers) * 8 + 16, size_t(cap_kmers) * 4 + 16,
+                              (size_t(cap_kmers) + 1) * 8 + 16, size_t(cap_kmers) * 4 + 16 };
+    size_t at = 0;
+    for (int i = 0; i < 6; ++i)
+    {
+        if (offsets) offsets[i] = at;
+        at += (sizes[i] + 255) & ~size_t(255);
+    }
+    return at;
+}
+
+int ipkgpu_set_result_arena(ipkgpu_ctx* ctx, void* base, uint64_t cap_entries, uint64_t cap_kmers)
 {
     return guarded(ctx, [&] {
-        if ((branch_buf == nullptr) != (score_buf == nullptr)) fail(IPKGPU_EINVAL, "both buffers or neither");
-        for (ipkgpu::hbuf* b : { &ctx->h_branch, &ctx->h_score })
+        ipkgpu::hbuf* bufs[6] = { &ctx->h_branch, &ctx->h_score, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_cnt };
+        for (ipkgpu::hbuf* b : bufs)
         {
             if (b->p && !b->external) cudaFreeHost(b->p);
             b->p = nullptr; b->cap = 0; b->external = false;
         }
-        if (!branch_buf) return;
-        ctx->h_branch.p = branch_buf; ctx->h_branch.cap = branch_bytes; ctx->h_branch.external = true;
-        ctx->h_score.p = score_buf; ctx->h_score.cap = score_bytes; ctx->h_score.external = true;
+        if (!base) return;
+        size_t off[6];
+        const size_t total = ipkgpu_result_arena_layout(cap_entries, cap_kmers, off);
+        for (int i = 0; i < 6; ++i)
+        {
+            bufs[i]->p = static_cast<char*>(base) + off[i];
+            bufs[i]->cap = (i + 1 < 6 ? off[i + 1] : total) - off[i];
+            bufs[i]->external = true;
+        }
     });
 }
 

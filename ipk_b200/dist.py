@@ -229,3 +229,68 @@ def merge_shards(shards):
     (offsets[i+1] ends k-mer i) or indexed (a `counts` array)."""
     from . import hostlib
     return hostlib.merge_shards(shards)
+
+
+# ---- one database in one address space: every rank's host result lands in a shared, page-locked arena that rank 0 maps ----
+class SharedArena:
+    """A POSIX shared-memory segment laid out by ipkgpu_result_arena_layout.  The owner rank creates it, page-locks it
+    (cudaHostRegister) and hands it to its context (ipkgpu_set_result_arena): the D2H copies of its shard land there.  Any
+    other process of the node attaches by name and reads the six arrays in place -- no second copy, no collective."""
+
+    def __init__(self, name: str, cap_entries: int, cap_kmers: int, create: bool):
+        from multiprocessing import shared_memory
+        from . import capi
+        self.cap_entries, self.cap_kmers = int(cap_entries), int(cap_kmers)
+        self.nbytes, self.offsets = capi.result_arena_layout(self.cap_entries, self.cap_kmers)
+        self.shm = shared_memory.SharedMemory(name=name, create=create, size=self.nbytes if create else 0)
+        self.buf = np.frombuffer(self.shm.buf, dtype=np.uint8, count=self.nbytes)
+        self.owner, self.registered = create, False
+
+    @property
+    def address(self) -> int:
+        return self.buf.ctypes.data
+
+    def register(self):
+        rc = torch.cuda.cudart().cudaHostRegister(self.address, self.nbytes, 0)
+        if int(rc) != 0:
+            raise RuntimeError(f"cudaHostRegister of the shared arena failed: {rc}")
+        self.registered = True
+
+    def shard(self, n_kmers: int, n_entries: int, branch16: bool):
+        """the arrays of a finished indexed host result, viewed in place"""
+        from types import SimpleNamespace
+        o = self.offsets
+        view = lambda off, dtype, n: np.frombuffer(self.shm.buf, dtype=dtype, count=n, offset=off)
+        d = SimpleNamespace(keys=view(o[2], np.uint64, n_kmers), fv=view(o[3], np.float32, n_kmers), offsets=view(o[4], np.uint64, n_kmers + 1),
+                            counts=view(o[5], np.uint32, n_kmers), score=view(o[1], np.float32, n_entries),
+                            branch=None if branch16 else view(o[0], np.uint32, n_entries), branch16=view(o[0], np.uint16, n_entries) if branch16 else None)
+        return d
+
+    def close(self):
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.address)
+            self.registered = False
+        self.buf = None
+        try:
+            self.shm.close()
+            if self.owner:
+                self.shm.unlink()
+        except Exception:
+            pass
+
+
+def gather_database(res, arenas, device, group=None, threads: int = 0):
+    """After sharded_build with host results in shared arenas: rank 0 learns every shard's sizes (one tiny all-gather) and
+    merges the k-mer heads of all shards by (filter value, key) -- the N-way merge of merge_stage2 (db_builder.cpp:392-458),
+    natively (hostlib.merge_order).  Returns on rank 0 (shards, (order_shard, order_index)): the whole database in rank 0's
+    address space, k-mer i of the build = k-mer order_index[i] of shards[order_shard[i]]; None elsewhere."""
+    from . import hostlib
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    mine = torch.tensor([int(res.n_kmers), int(res.n_entries), 1 if res.branch16 else 0], dtype=torch.int64, device=device)
+    rows = [torch.zeros(3, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)            # every rank's copies have completed (ipkgpu_stage2* is blocking) before it reports
+    if rank != 0:
+        return None
+    sizes = [[int(x) for x in r.cpu().tolist()] for r in rows]
+    shards = [arenas[r].shard(sizes[r][0], sizes[r][1], bool(sizes[r][2])) for r in range(world)]
+    return shards, hostlib.merge_order(shards, threads)

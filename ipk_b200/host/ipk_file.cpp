@@ -264,6 +264,46 @@ int ipkhost_merge_order(uint32_t n_shards, const ipkhost_db* shards, int n_threa
     return IPKHOST_OK;
 }
 
+int ipkhost_digest(uint32_t n_shards, const ipkhost_db* shards, int n_threads, uint64_t* out)
+{
+    // the digest of ipk_b200/csrc/digest.cuh over host databases: out[0..5] = entries sum / xor, k-mers sum / xor, fv sum / xor
+    if (!shards || !out) return IPKHOST_EINVAL;
+    auto mix = [](uint64_t x) { x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31; return x; };
+    unsigned T = n_threads > 0 ? unsigned(n_threads) : std::max(1u, std::thread::hardware_concurrency());
+    std::vector<std::vector<uint64_t>> acc(T, std::vector<uint64_t>(6, 0));
+    for (uint32_t s = 0; s < n_shards; ++s)
+    {
+        const ipkhost_db* d = shards + s;
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < T; ++t)
+            th.emplace_back([&, t] {
+                std::vector<uint64_t>& a = acc[t];
+                for (uint64_t q = d->n_kmers * t / T; q < d->n_kmers * (t + 1) / T; ++q)
+                {
+                    const uint64_t hk = mix(d->keys[q] + 0x9e3779b97f4a7c15ull);
+                    const uint64_t b = d->offsets[q], n = entries_of(d, q);
+                    const uint64_t hc = mix(hk ^ (n + 0x632be59bd9b4e019ull));
+                    a[2] += hc; a[3] ^= hc;
+                    uint32_t fb; memcpy(&fb, &d->fv[q], 4);
+                    const uint64_t hf = mix(hk ^ (uint64_t(fb) | 0x5bd1e99500000000ull));
+                    a[4] += hf; a[5] ^= hf;
+                    for (uint64_t e = b; e < b + n; ++e)
+                    {
+                        uint32_t sb; memcpy(&sb, &d->score[e], 4);
+                        const uint32_t br = d->branch16 ? uint32_t(d->branch16[e]) : d->branch[e];
+                        const uint64_t he = mix(hk ^ (uint64_t(br) << 32 | sb));
+                        a[0] += he; a[1] ^= he;
+                    }
+                }
+            });
+        for (auto& x : th) x.join();
+    }
+    for (int i = 0; i < 6; ++i) out[i] = 0;
+    for (unsigned t = 0; t < T; ++t)
+        for (int i = 0; i < 6; ++i) { if (i & 1) out[i] ^= acc[t][i]; else out[i] += acc[t][i]; }
+    return IPKHOST_OK;
+}
+
 int ipkhost_write_ipk_sharded(const char* path, const ipkhost_db* header, uint32_t n_shards, const ipkhost_db* shards,
                               const uint8_t* order_shard, const uint32_t* order_index, int n_threads)
 {

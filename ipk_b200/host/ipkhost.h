@@ -101,6 +101,9 @@ int  ipkhost_write_ipk_mt(const char* path, const ipkhost_db* db, int n_threads)
 int  ipkhost_merge_order(uint32_t n_shards, const ipkhost_db* shards, int n_threads, uint8_t* out_shard, uint32_t* out_index);
 int  ipkhost_write_ipk_sharded(const char* path, const ipkhost_db* header, uint32_t n_shards, const ipkhost_db* shards,
                                const uint8_t* order_shard, const uint32_t* order_index, int n_threads);
+/* the order-independent digest of include/ipkgpu.h (ipkgpu_result_digest) over databases in HOST memory:
+ * out[0..5] = entries sum / xor, k-mers sum / xor, filter values sum / xor -- what arrived on the host is what the device built */
+int  ipkhost_digest(uint32_t n_shards, const ipkhost_db* shards, int n_threads, uint64_t* out /*[6]*/);
 /* reads a file written by ipkhost_write_ipk; arrays are owned by the returned handle */
 typedef struct ipkhost_db_file ipkhost_db_file;
 int  ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view);

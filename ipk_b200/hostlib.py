@@ -50,6 +50,7 @@ def load() -> C.CDLL:
         lib.ipkhost_write_ipk_mt.argtypes = [C.c_char_p, P(HostDb), C.c_int]
         lib.ipkhost_merge_order.argtypes = [C.c_uint32, P(HostDb), C.c_int, C.c_void_p, C.c_void_p]
         lib.ipkhost_write_ipk_sharded.argtypes = [C.c_char_p, P(HostDb), C.c_uint32, P(HostDb), C.c_void_p, C.c_void_p, C.c_int]
+        lib.ipkhost_digest.argtypes = [C.c_uint32, P(HostDb), C.c_int, P(C.c_uint64)]
         lib.ipkhost_plan_create.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, P(C.c_void_p)]
         lib.ipkhost_plan_free.argtypes = [C.c_void_p]
         lib.ipkhost_plan_free.restype = None
@@ -220,3 +221,15 @@ def write_ipk_sharded(path: str, shards, kmer_size: int, omega: float, sequence_
     rc = load().ipkhost_write_ipk_sharded(path.encode(), C.byref(header), len(shards), views, sh.ctypes.data, ix.ctypes.data, threads)
     if rc != 0:
         raise HostError(rc, "cannot write " + path)
+
+
+def digest(shards, threads: int = 0) -> dict:
+    """ipkhost_digest: the device's database digest (ipkgpu_result_digest) recomputed from host arrays"""
+    keep: list = []
+    views = (HostDb * len(shards))(*[_host_db(d, keep) for d in shards])
+    out = (C.c_uint64 * 6)()
+    rc = load().ipkhost_digest(len(shards), views, threads, out)
+    if rc != 0:
+        raise HostError(rc, "ipkhost_digest")
+    names = ("entries_sum", "entries_xor", "kmers_sum", "kmers_xor", "fv_sum", "fv_xor")
+    return {n: int(v) for n, v in zip(names, out)}
