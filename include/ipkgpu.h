@@ -209,6 +209,9 @@ int  ipkgpu_stage1_scatter(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* p
  * 4. every rank:  ipkgpu_stage1_scatter_packed; *group_ordered tells whether this rank's records went out in group order
  *                 (false after a depth-first or batched enumeration): the caller ANDs it over the ranks
  * 5. a barrier, then ipkgpu_stage2_packed on the rank's own receive buffer. */
+/* ranks that are contexts of ONE process (ipk-b200 --devices): direct access from ctx's device to memory of peer_device,
+ * so that the receive buffer pointers of ipkgpu_recv_packed can be handed over as they are (no IPC handle) */
+int  ipkgpu_enable_peer(ipkgpu_ctx* ctx, int peer_device);
 int  ipkgpu_stage1_bucket_counts(ipkgpu_ctx* ctx, uint64_t* counts /*[256]*/);
 int  ipkgpu_exchange_plan(uint32_t n_parts, uint32_t rank, const uint64_t* counts /*[n_parts][256]*/, uint8_t* owner /*[256]*/,
                           uint64_t* base /*[256]*/, uint64_t* bucket_start /*[257]*/, uint64_t* n_recv);

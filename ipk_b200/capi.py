@@ -157,6 +157,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_stage2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
                                   C.c_uint32, C.c_float, C.c_uint32, C.c_int32, C.c_int32, C.c_int, P(Result)]
     lib.ipkgpu_stage2.restype = C.c_int
+    lib.ipkgpu_enable_peer.argtypes = [C.c_void_p, C.c_int]
+    lib.ipkgpu_enable_peer.restype = C.c_int
     lib.ipkgpu_stage1_bucket_counts.argtypes = [C.c_void_p, P(C.c_uint64)]
     lib.ipkgpu_stage1_bucket_counts.restype = C.c_int
     lib.ipkgpu_exchange_plan.argtypes = [C.c_uint32, C.c_uint32, P(C.c_uint64), P(C.c_uint8), P(C.c_uint64), P(C.c_uint64), P(C.c_uint64)]

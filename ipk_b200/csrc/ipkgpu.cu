@@ -1759,6 +1759,19 @@ int ipkgpu_set_result_arena(ipkgpu_ctx* ctx, void* base, uint64_t cap_entries, u
     });
 }
 
+int ipkgpu_enable_peer(ipkgpu_ctx* ctx, int peer_device)
+{
+    return guarded(ctx, [&] {
+        if (peer_device == ctx->device) return;
+        int can = 0;
+        IPK_CUDA(cudaDeviceCanAccessPeer(&can, ctx->device, peer_device));
+        if (!can) fail(IPKGPU_ENODEV, "device %d cannot access device %d directly (no NVLink / PCIe peer path)", ctx->device, peer_device);
+        const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return; }
+        IPK_CUDA(e);
+    });
+}
+
 int ipkgpu_stage1_bucket_counts(ipkgpu_ctx* ctx, uint64_t* counts)
 {
     return guarded(ctx, [&] {

@@ -29,6 +29,10 @@
 #include <string>
 #include <memory>
 #include <vector>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+#include <unordered_map>
 #include <dirent.h>
 #include <sys/stat.h>
 
@@ -43,6 +47,7 @@ namespace
         int filter = IPKGPU_FILTER_MIF0;
         uint32_t node_count = 0;
         int device = 0, threads = 0, verbosity = 1;
+        std::vector<int> devices;          // --devices 0,1,...: one rank per device, the multi-GPU build of include/ipkgpu.h
         int ghosts = 0;                    // 0 both, 1 inner only, 2 outer only
         bool dump = false, use_unrooted = false, ar_only = false, merge_branches = false;
     };
@@ -53,7 +58,7 @@ namespace
         fprintf(stderr,
                 "usage: ipk-b200 --refalign FASTA -t|--reftree NEWICK --ar-dir DIR [-k K] [--omega W] [--mif0|--random]\n"
                 "                [--both|--inner-only|--outer-only] [--use-unrooted] [-w DIR] [-o DB.ipk] [--states dna|aa]\n"
-                "                [-j THREADS] [-v N] [--device N] [--dump]   (and every other ipk-dna / ipk-aa option, see main.cpp)\n"
+                "                [-j THREADS] [-v N] [--device N | --devices 0,1,...] [--dump]   (and every other ipk-dna / ipk-aa option, see main.cpp)\n"
                 "   or: ipk-b200 --ar-probs FILE --node-map FILE [--tree NEWICK] [--node-count N] [...]\n");
         exit(1);
     }
@@ -93,6 +98,13 @@ namespace
             else if (a == "-w" || a == "--workdir") o.workdir = need(i);
             else if (a == "-o" || a == "--output") o.output = need(i);
             else if (a == "--device") o.device = atoi(need(i));
+            else if (a == "--devices")
+            {
+                const std::string v = need(i);
+                for (size_t p = 0; p < v.size();) { size_t q = v.find(',', p); if (q == std::string::npos) q = v.size(); o.devices.push_back(atoi(v.substr(p, q - p).c_str())); p = q + 1; }
+                if (o.devices.empty() || o.devices.size() > 16) usage("--devices takes 1 to 16 comma-separated device ordinals");
+                o.device = o.devices[0];
+            }
             else if (a == "-j" || a == "--num-threads") o.threads = atoi(need(i));
             else if (a == "-v" || a == "--verbosity") o.verbosity = atoi(need(i));
             else if (a == "--dump") o.dump = true;
@@ -156,6 +168,114 @@ namespace
     double seconds_since(std::chrono::steady_clock::time_point t0)
     {
         return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+}
+
+namespace
+{
+    /// all threads wait until `n` have arrived (C++17: no std::barrier)
+    struct thread_barrier
+    {
+        std::mutex m; std::condition_variable cv; unsigned n, waiting = 0, phase = 0;
+        explicit thread_barrier(unsigned n_) : n(n_) {}
+        void wait()
+        {
+            std::unique_lock<std::mutex> l(m);
+            const unsigned p = phase;
+            if (++waiting == n) { waiting = 0; ++phase; cv.notify_all(); }
+            else cv.wait(l, [&] { return phase != p; });
+        }
+    };
+
+    struct shard_result
+    {
+        ipkgpu_ctx* ctx = nullptr;
+        ipkgpu_result res;
+        std::string error;
+        ipkgpu_stats stage1;
+    };
+
+    /// The multi-GPU build of include/ipkgpu.h with the ranks as threads of this process, one per device: branch groups in
+    /// contiguous blocks -> stage 1 -> the MSD pass of the merge sort stores each k-mer range into its owner's buffer over
+    /// NVLink (direct peer access) -> every owner sorts / merges / filters its range -> shards in pinned host memory.
+    /// The caller merges them by (filter value, key) while it serializes (merge_stage2, db_builder.cpp:392-458).
+    void build_on_devices(const std::vector<int>& devices, const float* logp, const std::vector<uint32_t>& node_branch, uint32_t width, uint32_t sigma,
+                          uint32_t bits, uint32_t k, float omega, uint32_t node_count, int filter, std::vector<shard_result>& out)
+    {
+        const uint32_t G = uint32_t(devices.size()), n_nodes = uint32_t(node_branch.size());
+        // groups by first appearance; the nodes must come group after group so that a rank's matrices are one slice
+        std::vector<uint32_t> group_branch, group_first_node;
+        {
+            std::unordered_map<uint32_t, uint32_t> seen;
+            for (uint32_t i = 0; i < n_nodes; ++i)
+            {
+                const auto it = seen.find(node_branch[i]);
+                if (it == seen.end()) { seen[node_branch[i]] = uint32_t(group_branch.size()); group_branch.push_back(node_branch[i]); group_first_node.push_back(i); }
+                else if (it->second + 1 != group_branch.size()) throw std::runtime_error("--devices needs the ghost nodes listed branch group after branch group");
+            }
+            group_first_node.push_back(n_nodes);
+        }
+        const uint32_t n_groups = uint32_t(group_branch.size());
+        uint32_t group_bits = 0;
+        while ((1ull << group_bits) < n_groups) ++group_bits;
+        const uint32_t key_bits = k * bits;
+        if (key_bits < 8 || key_bits + group_bits - 8 > 32)
+            throw std::runtime_error("--devices: this alphabet / k / tree size does not fit the packed exchange (k*bits >= 8, k*bits + group bits <= 40)");
+        float threshold = 0, log_threshold = 0;
+        ipkgpu_score_threshold(omega, sigma, k, &threshold, &log_threshold);
+        out.assign(G, shard_result());
+        std::vector<uint64_t> counts(size_t(G) * 256, 0);
+        std::vector<uint64_t*> recv(G, nullptr);
+        std::vector<int32_t> ordered(G, 0);
+        thread_barrier bar(G);
+        std::vector<std::thread> th;
+        for (uint32_t r = 0; r < G; ++r)
+            th.emplace_back([&, r] {
+                shard_result& S = out[r];
+                auto check = [&](int rc, const char* what) {
+                    if (rc != IPKGPU_OK && S.error.empty()) S.error = std::string(what) + ": " + ipkgpu_last_error(S.ctx);
+                    return rc == IPKGPU_OK;
+                };
+                bool ok = true;
+                if (ipkgpu_create(&S.ctx, devices[r], nullptr) != IPKGPU_OK) { S.error = ipkgpu_last_error(nullptr); ok = false; }
+                for (uint32_t p = 0; ok && p < G; ++p) ok = check(ipkgpu_enable_peer(S.ctx, devices[p]), "peer access");
+                const uint32_t g0 = uint32_t(uint64_t(n_groups) * r / G), g1 = uint32_t(uint64_t(n_groups) * (r + 1) / G);
+                const uint32_t n0 = group_first_node[g0], n1 = group_first_node[g1];
+                ipkgpu_input in;
+                memset(&in, 0, sizeof in);
+                in.logp = logp + size_t(n0) * width * sigma;
+                in.node_branch = node_branch.data() + n0;
+                in.n_nodes = n1 - n0;
+                in.width = width; in.sigma = sigma; in.bits = bits; in.k = k;
+                in.threshold = threshold; in.log_threshold = log_threshold;
+                in.total_num_groups = node_count; in.filter = filter;
+                uint64_t n_raw = 0;
+                memset(&S.stage1, 0, sizeof S.stage1);
+                if (ok) ok = check(ipkgpu_stage1_raw(S.ctx, &in, g0, group_bits, &n_raw, &S.stage1), "stage 1");
+                if (ok) ok = check(ipkgpu_stage1_bucket_counts(S.ctx, counts.data() + size_t(r) * 256), "bucket counts");
+                bar.wait();                                    // the G x 256 matrix is complete (a failed rank contributed zeros)
+                uint8_t owner[256]; uint64_t base[256], start[257], n_recv = 0;
+                if (ipkgpu_exchange_plan(G, r, counts.data(), owner, base, start, &n_recv) != IPKGPU_OK && S.error.empty()) { S.error = "a key range exceeds 2^32-1 records"; ok = false; }
+                if (ok) ok = check(ipkgpu_recv_packed(S.ctx, n_recv ? n_recv : 1, &recv[r], nullptr), "receive buffer");
+                bar.wait();                                    // every rank's buffer exists
+                bool all_ok = true;
+                for (uint32_t p = 0; p < G; ++p) all_ok = all_ok && out[p].error.empty();
+                if (ok && all_ok) ok = check(ipkgpu_stage1_scatter_packed(S.ctx, G, recv.data(), owner, base, &ordered[r]), "exchange");
+                bar.wait();                                    // every rank's stores have landed
+                int32_t all_ordered = 1;
+                for (uint32_t p = 0; p < G; ++p) { all_ordered &= ordered[p]; all_ok = all_ok && out[p].error.empty(); }
+                if (ok && all_ok)
+                    check(ipkgpu_stage2_packed(S.ctx, n_recv, start, group_bits, all_ordered, group_branch.data(), n_groups, key_bits, threshold, node_count, filter,
+                                               IPKGPU_RESULT_HOST_INDEXED | IPKGPU_RESULT_BRANCH16, &S.res), "stage 2");
+            });
+        for (auto& t : th) t.join();
+        for (uint32_t r = 0; r < G; ++r)
+            if (!out[r].error.empty())
+            {
+                const std::string msg = "device " + std::to_string(devices[r]) + ": " + out[r].error;
+                for (auto& s : out) if (s.ctx) ipkgpu_destroy(s.ctx);
+                throw std::runtime_error(msg);
+            }
     }
 }
 
@@ -255,6 +375,53 @@ int main(int argc, char** argv)
 
         // ---- the device path
         t0 = std::chrono::steady_clock::now();
+        ipkhost_db header;
+        memset(&header, 0, sizeof header);
+        header.sequence_type = sigma == 4 ? "DNA" : "Proteins";
+        header.tree = tree.c_str();
+        header.n_index = index_num_nodes.size();
+        header.index_num_nodes = index_num_nodes.data();
+        header.index_subtree_branch_length = index_lengths.data();
+        header.kmer_size = o.k;
+        header.omega = o.omega;
+        const char* const layout_note = "(record layout as documented in ipkhost.h: UNVERIFIED against i2l's serializer, whose source is not available)";
+        if (o.devices.size() > 1)
+        {
+            std::vector<shard_result> shards;
+            build_on_devices(o.devices, logp.get(), node_branch, width, sigma, bits, o.k, o.omega, node_count, o.filter, shards);
+            std::vector<ipkhost_db> views(shards.size());
+            uint64_t n_kmers = 0, n_entries = 0, n_emitted = 0;
+            for (size_t r = 0; r < shards.size(); ++r)
+            {
+                const ipkgpu_result& res = shards[r].res;
+                ipkhost_db& v = views[r];
+                memset(&v, 0, sizeof v);
+                v.n_kmers = res.n_kmers; v.n_entries = res.n_entries;
+                v.keys = res.keys; v.fv = res.fv; v.offsets = res.offsets; v.counts = res.counts; v.branch = res.branch; v.branch16 = res.branch16; v.score = res.score;
+                n_kmers += res.n_kmers; n_entries += res.n_entries; n_emitted += shards[r].stage1.n_emitted;
+            }
+            fprintf(stderr, "Built %llu k-mers, %llu phylo-k-mers (%llu emitted) on %zu devices in %.3f s\n", (unsigned long long)n_kmers,
+                    (unsigned long long)n_entries, (unsigned long long)n_emitted, shards.size(), seconds_since(t0));
+            // ---- N-way merge by (filter value, key) while serializing (merge_stage2, db_builder.cpp:392-458)
+            t0 = std::chrono::steady_clock::now();
+            std::vector<uint8_t> order_shard(n_kmers);
+            std::vector<uint32_t> order_index(n_kmers);
+            if (ipkhost_merge_order(uint32_t(views.size()), views.data(), o.threads, order_shard.data(), order_index.data()) != IPKHOST_OK)
+                throw std::runtime_error("cannot merge the shards");
+            if (ipkhost_write_ipk_sharded(o.output.c_str(), &header, uint32_t(views.size()), views.data(), order_shard.data(), order_index.data(), o.threads) != IPKHOST_OK)
+                throw std::runtime_error("cannot write " + o.output);
+            fprintf(stderr, "Wrote %s in %.3f s %s\n", o.output.c_str(), seconds_since(t0), layout_note);
+            if (o.dump)
+                for (uint64_t i = 0; i < n_kmers; ++i)
+                {
+                    const ipkhost_db& v = views[order_shard[i]];
+                    const uint64_t q = order_index[i];
+                    for (uint64_t e = v.offsets[q]; e < v.offsets[q] + v.counts[q]; ++e)
+                        printf("%llu\t%.9g\t%u\t%.9g\n", (unsigned long long)v.keys[q], double(v.fv[q]), v.branch16 ? uint32_t(v.branch16[e]) : v.branch[e], double(v.score[e]));
+                }
+            for (auto& s : shards) ipkgpu_destroy(s.ctx);
+            return 0;
+        }
         ipkgpu_ctx* ctx = nullptr;
         if (ipkgpu_create(&ctx, o.device, nullptr) != IPKGPU_OK) throw std::runtime_error(ipkgpu_last_error(nullptr));
         ipkgpu_input in;
@@ -279,20 +446,11 @@ int main(int argc, char** argv)
 
         // ---- serialize
         t0 = std::chrono::steady_clock::now();
-        ipkhost_db db;
-        memset(&db, 0, sizeof db);
-        db.sequence_type = sigma == 4 ? "DNA" : "Proteins";
-        db.tree = tree.c_str();
-        db.n_index = index_num_nodes.size();
-        db.index_num_nodes = index_num_nodes.data();
-        db.index_subtree_branch_length = index_lengths.data();
-        db.kmer_size = o.k;
-        db.omega = o.omega;
+        ipkhost_db db = header;
         db.n_kmers = res.n_kmers; db.n_entries = res.n_entries;
         db.keys = res.keys; db.fv = res.fv; db.offsets = res.offsets; db.counts = res.counts; db.branch = res.branch; db.branch16 = res.branch16; db.score = res.score;
         if (ipkhost_write_ipk_mt(o.output.c_str(), &db, o.threads) != IPKHOST_OK) throw std::runtime_error("cannot write " + o.output);
-        fprintf(stderr, "Wrote %s in %.3f s (record layout as documented in ipkhost.h: UNVERIFIED against i2l's serializer, whose source is not available)\n",
-                o.output.c_str(), seconds_since(t0));
+        fprintf(stderr, "Wrote %s in %.3f s %s\n", o.output.c_str(), seconds_since(t0), layout_note);
         if (o.dump)
             for (uint64_t q = 0; q < res.n_kmers; ++q)
                 for (uint64_t e = res.offsets[q]; e < (res.counts ? res.offsets[q] + res.counts[q] : res.offsets[q + 1]); ++e)

@@ -418,6 +418,13 @@ def test_reference_command_line_end_to_end(ghosts, tmp_path):
                           n_kmers=len(d["keys"]), n_entries=len(d["branch"]))
     assert want.n_entries > 100
     assert_db_equal(got, want)
+    # the multi-GPU build of the same executable (ranks = threads, one per listed device; here three on the one device):
+    # key-range shards merged by (filter value, key) while serializing -- the same file, byte for byte
+    argv3 = argv + ["--devices", "0,0,0"]
+    argv3[argv3.index("-o") + 1] = str(tmp_path / "DB3.ipk")
+    r = subprocess.run(argv3, capture_output=True, text=True)
+    assert r.returncode == 0 and "on 3 devices" in r.stderr, r.stderr
+    assert open(tmp_path / "DB3.ipk", "rb").read() == open(tmp_path / "DB.ipk", "rb").read()
 
 
 def _random_shards(rng, n_shards, n_kmers_each, with_ties=True):
