@@ -152,6 +152,17 @@ typedef struct ipkgpu_digest
 } ipkgpu_digest;
 int  ipkgpu_result_digest(ipkgpu_ctx* ctx, float log_threshold, float band, ipkgpu_digest* out);
 
+/* Boundary cases (BASELINE.json: "k-mers whose reference score lies within 1e-5 of the threshold are listed separately"; the
+ * reference's own differ does it by hand, diff-plain-text.py:36-45).  log_threshold comes out of i2l::score_threshold
+ * (db_builder.cpp:640), whose rounding cannot be pinned here (source absent): an entry whose presence or value flips when the
+ * threshold moves by less than `band` cannot be held against either build.  The list is exact by construction: the input is
+ * enumerated and merged twice, at log_threshold - band and + band, and every (k-mer, branch) whose entry differs between
+ * the two -- missing from the tight build (score_tight = NaN), or there with another per-branch maximum -- is reported.
+ * Up to cap entries are written (any order), *n_out is their true number.  Costs two enumerations: a diagnostic, not a
+ * stage of the build. */
+int  ipkgpu_boundary_list(ipkgpu_ctx* ctx, const ipkgpu_input* in, float band, uint64_t cap, uint64_t* kmer_out, uint32_t* branch_out,
+                          float* score_loose_out, float* score_tight_out, uint64_t* n_out);
+
 /* ---- stage-level entry points (parity tests; multi-GPU build, where the caller runs the exchange) ---------------- */
 
 /* matrix::preprocess (window.cpp:16-27) for every node: B_out[n_nodes][W+1] (host). */

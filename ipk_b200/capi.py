@@ -133,6 +133,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_build.restype = C.c_int
     lib.ipkgpu_result_digest.argtypes = [C.c_void_p, C.c_float, C.c_float, P(Digest)]
     lib.ipkgpu_result_digest.restype = C.c_int
+    lib.ipkgpu_boundary_list.argtypes = [C.c_void_p, P(Input), C.c_float, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_uint64)]
+    lib.ipkgpu_boundary_list.restype = C.c_int
     lib.ipkgpu_free_result.argtypes = [C.c_void_p, P(Result)]
     lib.ipkgpu_free_result.restype = None
     lib.ipkgpu_best_prefix.argtypes = [C.c_void_p, P(Input), C.c_void_p]
@@ -370,6 +372,18 @@ class Context:
         d = Digest()
         self._check(self._lib.ipkgpu_result_digest(self._h, log_threshold, band, C.byref(d)))
         return d.as_dict()
+
+    def boundary_list(self, inp: Input, band: float = 1e-5, cap: int = 1 << 20):
+        """(k-mer, branch) entries whose presence or score flips when the threshold moves by less than `band`:
+        -> (n_total, kmer[u64], branch[u32], score at threshold - band, score at threshold + band or NaN), sorted by (k-mer, branch)"""
+        kmer, branch = np.empty(cap, np.uint64), np.empty(cap, np.uint32)
+        lo, hi = np.empty(cap, np.float32), np.empty(cap, np.float32)
+        n = C.c_uint64(0)
+        self._check(self._lib.ipkgpu_boundary_list(self._h, C.byref(inp), band, cap, kmer.ctypes.data, branch.ctypes.data, lo.ctypes.data,
+                                                   hi.ctypes.data, C.byref(n)))
+        m = min(int(n.value), cap)
+        o = np.lexsort((branch[:m], kmer[:m]))
+        return int(n.value), kmer[:m][o], branch[:m][o], lo[:m][o], hi[:m][o]
 
     @staticmethod
     def to_db(res: Result) -> PhyloKmerDB:

@@ -71,4 +71,35 @@ namespace ipkgpu
             atomicAdd(acc + 6, (unsigned long long)v[6]);
         }
     }
+
+    /// Boundary cases (BASELINE.json: k-mers whose score lies within a band of the threshold are listed separately): the
+    /// unique (k-mer, group) records of a build at threshold - band (`loose`, sorted by composite key) against those of a
+    /// build at threshold + band (`tight`, a subset as a set of keys).  A loose record that the tight build lacks, or holds
+    /// with another score (the per-branch maximum was taken over a different set of windows), depends on which side of the
+    /// band the threshold falls: it is appended to the list.
+    __global__ void __launch_bounds__(256) k8_boundary_diff(const uint64_t* __restrict__ loose_keys, const float* __restrict__ loose_scores, uint64_t n_loose,
+                                                            const uint64_t* __restrict__ tight_keys, const float* __restrict__ tight_scores, uint64_t n_tight,
+                                                            uint32_t group_bits, const uint32_t* __restrict__ group_branch, uint64_t cap,
+                                                            uint64_t* __restrict__ out_kmer, uint32_t* __restrict__ out_branch, float* __restrict__ out_loose,
+                                                            float* __restrict__ out_tight, unsigned long long* __restrict__ counter)
+    {
+        for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n_loose; i += uint64_t(gridDim.x) * blockDim.x)
+        {
+            const uint64_t key = loose_keys[i];
+            uint64_t lo = 0, hi = n_tight;                 // first j with tight_keys[j] >= key
+            while (lo < hi) { const uint64_t mid = (lo + hi) >> 1; if (tight_keys[mid] < key) lo = mid + 1; else hi = mid; }
+            const bool present = lo < n_tight && tight_keys[lo] == key;
+            const float sl = loose_scores[i];
+            const float st = present ? tight_scores[lo] : __uint_as_float(0x7fc00000u);
+            if (present && __float_as_uint(st) == __float_as_uint(sl)) continue;
+            const unsigned long long o = atomicAdd(counter, 1ull);
+            if (o < cap)
+            {
+                out_kmer[o] = key >> group_bits;
+                out_branch[o] = group_branch[uint32_t(key & ((1ull << group_bits) - 1))];
+                out_loose[o] = sl;
+                out_tight[o] = st;
+            }
+        }
+    }
 }

@@ -1493,6 +1493,55 @@ int ipkgpu_result_digest(ipkgpu_ctx* ctx, float log_threshold, float band, ipkgp
     });
 }
 
+int ipkgpu_boundary_list(ipkgpu_ctx* ctx, const ipkgpu_input* in, float band, uint64_t cap, uint64_t* kmer_out, uint32_t* branch_out,
+                         float* score_loose_out, float* score_tight_out, uint64_t* n_out)
+{
+    return guarded(ctx, [&] {
+        validate(in);
+        if (!n_out || (cap && (!kmer_out || !branch_out || !score_loose_out || !score_tight_out))) fail(IPKGPU_EINVAL, "output pointer is null");
+        if (!(band > 0.0f)) fail(IPKGPU_EINVAL, "band must be positive");
+        *n_out = 0;
+        const group_tables T = make_groups(in->node_branch, in->n_nodes, 0);
+        const uint32_t group_bits = ceil_log2(uint32_t(T.group_branch.size()));
+        stage_timer tm(ctx);
+        ipkgpu_input run = *in;
+        // loose: everything a threshold up to `band` lower would let in
+        run.log_threshold = in->log_threshold - band;
+        ctx->hint_emitted = 0;
+        const stage1_out lo = run_stage1(ctx, &run, T, 0, group_bits, false, nullptr, tm);
+        if (lo.n_batches > 1) fail(IPKGPU_ENOMEM, "the boundary analysis needs the emitted records of the input in one batch; pass fewer ghost nodes at a time");
+        const uint64_t n_loose = lo.n_unique;
+        ctx->reserve(ctx->side_keys_a, n_loose * 8 + 8);
+        ctx->reserve(ctx->side_vals_a, n_loose * 4 + 4);
+        IPK_CUDA(cudaMemcpyAsync(ctx->side_keys_a.p, ctx->u_keys.p, n_loose * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(ctx->side_vals_a.p, ctx->u_scores.p, n_loose * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        // tight: what survives a threshold up to `band` higher
+        run.log_threshold = in->log_threshold + band;
+        const stage1_out hi = run_stage1(ctx, &run, T, 0, group_bits, false, nullptr, tm);
+        if (hi.n_batches > 1) fail(IPKGPU_ENOMEM, "the boundary analysis needs the emitted records of the input in one batch");
+        ctx->hint_emitted = 0;
+        if (n_loose == 0) return;
+        ctx->reserve(ctx->out_keys, cap * 8 + 8); ctx->reserve(ctx->out_branch, cap * 4 + 4);
+        ctx->reserve(ctx->out_score, cap * 4 + 4); ctx->reserve(ctx->out_fv, cap * 4 + 4);
+        unsigned long long* counter = ctx->counters.as<unsigned long long>() + 8;
+        IPK_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
+        const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n_loose, 256), uint64_t(ctx->num_sms) * 16));
+        IPK_LAUNCH(ctx, "k8_boundary_diff", n_loose * 12,
+                   k8_boundary_diff<<<grid, 256, 0, ctx->stream>>>(ctx->side_keys_a.as<uint64_t>(), ctx->side_vals_a.as<float>(), n_loose, ctx->u_keys.as<uint64_t>(),
+                                                                   ctx->u_scores.as<float>(), hi.n_unique, group_bits, ctx->group_branch.as<uint32_t>(), cap,
+                                                                   ctx->out_keys.as<uint64_t>(), ctx->out_branch.as<uint32_t>(), ctx->out_score.as<float>(),
+                                                                   ctx->out_fv.as<float>(), counter));
+        const uint64_t n = read_u64(ctx, counter);
+        *n_out = n;
+        const uint64_t m = std::min(n, cap);
+        IPK_CUDA(cudaMemcpyAsync(kmer_out, ctx->out_keys.p, m * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(branch_out, ctx->out_branch.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(score_loose_out, ctx->out_score.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(score_tight_out, ctx->out_fv.p, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
 void ipkgpu_free_result(ipkgpu_ctx* ctx, ipkgpu_result* res)
 {
     (void)ctx;

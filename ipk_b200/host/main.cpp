@@ -47,6 +47,8 @@ namespace
         int filter = IPKGPU_FILTER_MIF0;
         uint32_t node_count = 0;
         int device = 0, threads = 0, verbosity = 1;
+        std::string boundary_file;         // --boundary-list FILE: the entries that depend on which side of +-band the threshold falls
+        float boundary_band = 1e-5f;
         std::vector<int> devices;          // --devices 0,1,...: one rank per device, the multi-GPU build of include/ipkgpu.h
         int ghosts = 0;                    // 0 both, 1 inner only, 2 outer only
         bool dump = false, use_unrooted = false, ar_only = false, merge_branches = false;
@@ -108,6 +110,8 @@ namespace
             else if (a == "-j" || a == "--num-threads") o.threads = atoi(need(i));
             else if (a == "-v" || a == "--verbosity") o.verbosity = atoi(need(i));
             else if (a == "--dump") o.dump = true;
+            else if (a == "--boundary-list") o.boundary_file = need(i);
+            else if (a == "--boundary-band") o.boundary_band = float(atof(need(i)));
             // parsed and ignored: they steer raxml-ng / the alignment reduction (upstream), or nothing at all in the reference build
             else if (a == "--ar-binary" || a == "-m" || a == "--model" || a == "-a" || a == "--alpha" || a == "--categories" ||
                      a == "--reduction-ratio" || a == "-u" || a == "--mu") need(i);
@@ -135,7 +139,8 @@ namespace
                       "then point --ar-dir at its *.raxml.ancestralProbs / *.raxml.ancestralTree)");
         }
         else if (o.ar_probs.empty() || o.node_map.empty()) usage("--ar-probs and --node-map go together");
-        if (o.merge_branches) { fprintf(stderr, "ipk-b200: --merge-branches is not supported by this build\n"); exit(1); }
+        // main.cpp:31-37 (check_parameters): ipk-dna / ipk-aa refuse it with exactly this message; only the KEEP_POSITIONS binary takes it
+        if (o.merge_branches) { fprintf(stderr, "Exception: --merge-branches is only supported for IPK compiled with the KEEP_POSITIONS flag.\n"); exit(1); }
         if (o.output.empty()) o.output = o.workdir + "/DB.ipk";         // command_line.cpp:259-263
         return o;
     }
@@ -455,6 +460,24 @@ int main(int argc, char** argv)
             for (uint64_t q = 0; q < res.n_kmers; ++q)
                 for (uint64_t e = res.offsets[q]; e < (res.counts ? res.offsets[q] + res.counts[q] : res.offsets[q + 1]); ++e)
                     printf("%llu\t%.9g\t%u\t%.9g\n", (unsigned long long)res.keys[q], double(res.fv[q]), res.branch16 ? uint32_t(res.branch16[e]) : res.branch[e], double(res.score[e]));
+        if (!o.boundary_file.empty())
+        {
+            // BASELINE.json: k-mers within 1e-5 of the threshold are listed separately (the threshold's rounding is i2l's, unpinned here)
+            const uint64_t cap = 1ull << 22;
+            std::vector<uint64_t> bk(cap);
+            std::vector<uint32_t> bb(cap);
+            std::vector<float> bl(cap), bt(cap);
+            uint64_t nb = 0;
+            if (ipkgpu_boundary_list(ctx, &in, o.boundary_band, cap, bk.data(), bb.data(), bl.data(), bt.data(), &nb) != IPKGPU_OK)
+                throw std::runtime_error(std::string("boundary list: ") + ipkgpu_last_error(ctx));
+            FILE* bf = fopen(o.boundary_file.c_str(), "w");
+            if (!bf) throw std::runtime_error("cannot write " + o.boundary_file);
+            fprintf(bf, "# entries whose presence or score changes when log10(threshold) = %.9g moves by less than %g: %llu\n# k-mer code\tbranch\tscore at threshold-band\tscore at threshold+band (nan: absent)\n",
+                    double(in.log_threshold), double(o.boundary_band), (unsigned long long)nb);
+            for (uint64_t i = 0; i < std::min(nb, cap); ++i) fprintf(bf, "%llu\t%u\t%.9g\t%.9g\n", (unsigned long long)bk[i], bb[i], double(bl[i]), double(bt[i]));
+            fclose(bf);
+            fprintf(stderr, "Boundary cases (within %g of the threshold): %llu, listed in %s\n", double(o.boundary_band), (unsigned long long)nb, o.boundary_file.c_str());
+        }
         ipkgpu_free_result(ctx, &res);
         ipkgpu_destroy(ctx);
         return 0;

@@ -150,6 +150,58 @@ def test_result_digest_is_the_numpy_digest_of_the_database(ctx, name, n_taxa, W,
     assert db_digest(got, lthr, 1e-5)["entries_xor"] != d["entries_xor"]
 
 
+def _threshold_columns(rng, n_nodes, W, k, omega):
+    """posteriors in which many k-mers score within rounding of the threshold: runs of columns whose two best states have
+    exactly p = omega / 4 each (a k-mer over k such columns scores k log10(omega / 4) = log10(threshold) up to fp32 rounding),
+    between ordinary peaked columns"""
+    logp = _rand_posteriors(rng, n_nodes, W, 4, peaked=0.8, zeros=False)
+    a = np.float32(np.log10(np.float32(omega / 4.0)))
+    b = np.float32(np.log10(np.float32((1.0 - 2 * omega / 4.0) / 2.0)))
+    for n in range(n_nodes):
+        for start in rng.integers(0, W - k - 3, 3):
+            for c in range(start, start + k + 2):
+                perm = rng.permutation(4)
+                logp[n, c, perm[:2]] = a
+                logp[n, c, perm[2:]] = b
+    return logp
+
+
+@pytest.mark.parametrize("k", [5, 8])
+def test_boundary_list_matches_oracle(ctx, k):
+    """ipkgpu_boundary_list: the entries whose presence or score flips when the threshold moves by less than the band (the
+    boundary cases BASELINE.json sets aside), against the same set taken from two ORACLE builds at threshold -/+ band"""
+    from ipk_b200 import capi as libipkgpu
+    from parity import by_key
+    rng = np.random.default_rng(70 + k)
+    n_taxa, W, omega, band = 5, 90, 1.5, 1e-5
+    n_nodes = 2 * (2 * n_taxa - 2)
+    logp = _threshold_columns(rng, n_nodes, W, k, omega)
+    nb = np.repeat(np.arange(n_nodes // 2, dtype=np.uint32), 2)
+    thr, lthr = _thr(omega, 4, k)
+    T = 2 * n_taxa - 1
+    inp, keep = libipkgpu.make_input(logp, nb, W, 4, 2, k, lthr, thr, T, 0)
+    n, kmer, branch, s_lo, s_hi = ctx.boundary_list(inp, band)
+    loose = O.build(logp, nb, W, 4, 2, k, np.float32(lthr) - np.float32(band), thr, T, 0, 4)
+    tight = O.build(logp, nb, W, 4, 2, k, np.float32(lthr) + np.float32(band), thr, T, 0, 4)
+    _, _, _, lk, lb, ls = by_key(loose)
+    _, _, _, tk, tb, ts = by_key(tight)
+    have = {(int(a), int(b_)): np.float32(c) for a, b_, c in zip(tk, tb, ts)}
+    want = sorted((int(a), int(b_), np.float32(c), have.get((int(a), int(b_)))) for a, b_, c in zip(lk, lb, ls)
+                  if have.get((int(a), int(b_))) is None or have[(int(a), int(b_))].view(np.uint32) != np.float32(c).view(np.uint32))
+    assert n == len(want) and n > 20, (n, len(want))          # the fixture does straddle the threshold
+    assert [(int(a), int(b_)) for a, b_ in zip(kmer, branch)] == [(w[0], w[1]) for w in want]
+    assert np.array_equal(s_lo.view(np.uint32), np.array([w[2] for w in want], np.float32).view(np.uint32))
+    absent = np.array([w[3] is None for w in want])
+    assert np.array_equal(np.isnan(s_hi), absent) and absent.any()
+    assert np.array_equal(s_hi[~absent].view(np.uint32), np.array([w[3] for w in want if w[3] is not None], np.float32).view(np.uint32))
+    # every listed score lies in the band around the threshold, on the emitted side of the loose build
+    assert np.all(np.abs(s_lo[absent] - np.float32(lthr)) <= np.float32(2 * band))
+    # the build itself is untouched by the analysis
+    got = ctx.build(logp, nb, W, 4, 2, k, lthr, thr, T, 0)
+    assert_db_equal(got, O.build(logp, nb, W, 4, 2, k, lthr, thr, T, 0, 4))
+    assert ctx.result_digest(lthr, band)["n_boundary_above"] >= int(absent.sum()) - n      # (a lower bound; just exercises the counter)
+
+
 def test_build_interleaved_groups_and_singletons(ctx):
     """ghost nodes of one branch need not be adjacent; a branch may have one ghost only (--inner-only/--outer-only)"""
     logp, nb = _synth(10, 150, 4)

@@ -319,7 +319,7 @@ def test_executable_accepts_the_command_line_ipk_py_builds(tmp_path):
     r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(tmp_path / "nope")), capture_output=True, text=True)
     assert r.returncode == 1 and "No such directory" in r.stderr
     r = subprocess.run(_ipk_py_argv(exe, tmp_path, str(ar_dir), ["--merge-branches"]), capture_output=True, text=True)
-    assert r.returncode == 1 and "not supported" in r.stderr
+    assert r.returncode == 1 and "only supported for IPK compiled with the KEEP_POSITIONS flag" in r.stderr      # main.cpp:31-37
     r = subprocess.run([exe, "--refalign", "a", "-t", str(tmp_path / "tree.newick")], capture_output=True, text=True)
     assert r.returncode == 1 and "--ar-dir is required" in r.stderr
 
