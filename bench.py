@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-branches", type=int, default=0, help="branch groups in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=42)
+    ap.add_argument("--no-file", action="store_true", help="skip the serialization leg (posteriors in RAM -> DB.ipk on /dev/shm, and the one-shot ipk-b200 run)")
     ap.add_argument("--write-digest", action="store_true", help="record this run's database digest in profiles/digests.json")
     return ap.parse_args()
 
@@ -195,6 +196,58 @@ def run_reference(args):
             "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+def file_leg(ctx, inp_host, h_logp, node_branch, wl, n_entries, n_kmers):
+    """BASELINE's metric is "phylo-k-mers/s & .ipk build time": (1) posteriors in pinned RAM -> ipkgpu_build -> the multi-threaded
+    writer -> DB.ipk closed on /dev/shm, in this process (warm); (2) the ipk-b200 executable, one shot and cold: raw float32
+    posteriors from /dev/shm -> DB.ipk on /dev/shm, wall clock of the whole process (context creation, first-touch allocations
+    and page-locking of 9.5 GB included).  Outside the timed legs; files are removed afterwards."""
+    import ctypes as C
+    import shutil
+    import tempfile
+    from ipk_b200 import capi, hostlib
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+    need = 20 * n_kmers + 8 * n_entries + h_logp.numel() * 4 + (1 << 28)
+    if shutil.disk_usage(base).free < need:
+        return {"skipped": f"{base} has less than {need >> 30} GiB free"}
+    d = tempfile.mkdtemp(prefix="ipkb200_bench_", dir=base)
+    out = {}
+    try:
+        lib = hostlib.load()
+        path = os.path.join(d, "DB.ipk")
+        t0 = time.perf_counter()
+        res = ctx.build_raw(inp_host, result_on_device=False, indexed=True, branch16=True)
+        t1 = time.perf_counter()
+        db = hostlib.HostDb(b"DNA" if wl.sigma == 4 else b"Proteins", b"", 0, None, None, wl.k, wl.omega, res.n_kmers, res.n_entries,
+                            C.cast(res.keys, C.POINTER(C.c_uint64)), C.cast(res.fv, C.POINTER(C.c_float)), C.cast(res.offsets, C.POINTER(C.c_uint64)),
+                            C.cast(res.counts, C.POINTER(C.c_uint32)), C.cast(res.branch, C.POINTER(C.c_uint32)), C.cast(res.score, C.POINTER(C.c_float)),
+                            C.cast(res.branch16, C.POINTER(C.c_uint16)))
+        rc = lib.ipkhost_write_ipk_mt(path.encode(), C.byref(db), 0)
+        t2 = time.perf_counter()
+        if rc != 0:
+            raise RuntimeError("ipkhost_write_ipk_mt failed")
+        size = os.path.getsize(path)
+        out.update(build_ms=round((t1 - t0) * 1e3, 1), write_ms=round((t2 - t1) * 1e3, 1), total_ms=round((t2 - t0) * 1e3, 1), file_bytes=size,
+                   writer_gbs=round(size / (t2 - t1) * 1e-9, 2), threads=host_cores(),
+                   what="pinned posteriors -> ipkgpu_build (indexed host result, 16-bit branches) -> ipkhost_write_ipk_mt -> file closed on " + base)
+        os.remove(path)
+        # one shot, cold
+        logp_path, map_path = os.path.join(d, "logp.f32"), os.path.join(d, "node_map.tsv")
+        h_logp.numpy().tofile(logp_path)
+        with open(map_path, "w") as f:
+            f.write("".join(f"n{i}\t{int(b)}\n" for i, b in enumerate(node_branch)))
+        argv = [hostlib.EXE_PATH, "--logp-f32", logp_path, "--width", str(wl.width), "--node-map", map_path, "--states", "dna" if wl.sigma == 4 else "aa",
+                "-k", str(wl.k), "--omega", str(wl.omega), "--mif0" if wl.filter == "mif0" else "--random", "--node-count", str(wl.n_tree_nodes), "-o", path]
+        t0 = time.perf_counter()
+        r = subprocess.run(argv, capture_output=True, text=True)
+        t1 = time.perf_counter()
+        out["one_shot"] = {"wall_s": round(t1 - t0, 3), "returncode": r.returncode, "file_bytes": os.path.getsize(path) if os.path.exists(path) else 0,
+                           "log": [l_ for l_ in r.stderr.splitlines() if l_.startswith(("Loaded", "Built", "Wrote", "Exception"))],
+                           "what": "ipk-b200 --logp-f32 ... -o DB.ipk: process start to exit, posteriors and database on " + base}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -472,6 +525,8 @@ def run_b200(args):
         line["exchange"] = exch_info
     else:
         line["e2e"]["artefact"] = "one indexed database in pinned host memory (ipkgpu_build, IPKGPU_RESULT_HOST_INDEXED | BRANCH16)"
+    if world == 1 and not args.no_file:
+        line["e2e_file"] = file_leg(ctx, inp_host, h_logp, node_branch, wl, n_entries, n_kmers)
     if not args.no_cpu_baseline and world == 1:
         def gpu_check(nb, cpu_db):
             """the same [0, nb) branch-group slice through ipkgpu_build, compared with the CPU arm's database entry for entry"""

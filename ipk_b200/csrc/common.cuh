@@ -56,6 +56,13 @@ namespace ipkgpu
     };
 
     constexpr int NUM_SMS_B200 = 148;
+
+    /// Page-locked host memory.  cudaMallocHost pins 4 KB pages one by one (measured on the B200 hosts: 4.4 s for 8 GiB, most of
+    /// a cold build); large blocks are instead anonymous mappings advised to transparent huge pages, first touched by several
+    /// threads and then registered (0.12 s + 0.25 s for the same 8 GiB, tools/probe/pin_probe.cu).  Small blocks, and hosts where
+    /// the mapping or the registration fails, take cudaMallocHost.  pinned_free takes either kind.
+    cudaError_t pinned_alloc(void** out, size_t bytes);
+    void pinned_free(void* p);
 }
 
 struct ipkgpu_ctx
@@ -216,10 +223,10 @@ struct ipkgpu_ctx
     {
         if (bytes <= b.cap) return;
         if (b.external) ipkgpu::fail(IPKGPU_ENOMEM, "the caller's staging buffer holds %zu bytes, the result needs %zu (ipkgpu_set_entry_staging)", b.cap, bytes);
-        if (b.p) cudaFreeHost(b.p);
+        if (b.p) ipkgpu::pinned_free(b.p);
         b.p = nullptr; b.cap = 0;
         size_t want = bytes + bytes / 16 + 256;
-        cudaError_t e = cudaMallocHost(&b.p, want);
+        cudaError_t e = ipkgpu::pinned_alloc(&b.p, want);
         if (e != cudaSuccess)
         {
             cudaGetLastError();

@@ -18,7 +18,69 @@
 #include <numeric>
 #include <unordered_map>
 
+#include <mutex>
+#include <thread>
+#include <sys/mman.h>
+
 using namespace ipkgpu;
+
+namespace ipkgpu
+{
+    static std::mutex g_pin_mutex;
+    static std::unordered_map<void*, std::pair<void*, size_t>> g_pin_maps;        // registered pointer -> (mapping base, mapping length)
+
+    cudaError_t pinned_alloc(void** out, size_t bytes)
+    {
+        *out = nullptr;
+        static const bool thp_off = getenv("IPKGPU_PIN_THP") && atoi(getenv("IPKGPU_PIN_THP")) == 0;
+        const size_t HUGE = size_t(2) << 20;
+        if (bytes >= (size_t(64) << 20) && !thp_off)
+        {
+            const size_t len = (bytes + HUGE - 1) & ~(HUGE - 1);
+            void* base = mmap(nullptr, len + HUGE, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+            if (base != MAP_FAILED)
+            {
+                char* q = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(base) + HUGE - 1) & ~uintptr_t(HUGE - 1));
+                madvise(q, len, MADV_HUGEPAGE);
+                const unsigned T = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+                std::vector<std::thread> th;
+                for (unsigned t = 0; t < T; ++t)
+                    th.emplace_back([=] {
+                        const size_t lo = len / T * t, hi = t + 1 == T ? len : len / T * (t + 1);
+                        for (size_t o = lo; o < hi; o += 4096) q[o] = 0;
+                    });
+                for (auto& x : th) x.join();
+                if (cudaHostRegister(q, len, cudaHostRegisterPortable) == cudaSuccess)
+                {
+                    std::lock_guard<std::mutex> l(g_pin_mutex);
+                    g_pin_maps[q] = { base, len + HUGE };
+                    *out = q;
+                    return cudaSuccess;
+                }
+                cudaGetLastError();
+                munmap(base, len + HUGE);
+            }
+        }
+        return cudaMallocHost(out, bytes ? bytes : 1);
+    }
+
+    void pinned_free(void* p)
+    {
+        if (!p) return;
+        std::pair<void*, size_t> m{ nullptr, 0 };
+        {
+            std::lock_guard<std::mutex> l(g_pin_mutex);
+            const auto it = g_pin_maps.find(p);
+            if (it != g_pin_maps.end()) { m = it->second; g_pin_maps.erase(it); }
+        }
+        if (m.first)
+        {
+            if (cudaHostUnregister(p) != cudaSuccess) cudaGetLastError();
+            munmap(m.first, m.second);
+        }
+        else if (cudaFreeHost(p) != cudaSuccess) cudaGetLastError();
+    }
+}
 
 namespace
 {
@@ -1379,7 +1441,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score, &ctx->h_cnt };
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev_merged) { cudaEventDestroy(ctx->ev_merged); cudaEventDestroy(ctx->ev_copied); }
-    for (auto* b : hall) if (b->p && !b->external) cudaFreeHost(b->p);
+    for (auto* b : hall) if (b->p && !b->external) ipkgpu::pinned_free(b->p);
     for (auto e : ctx->events) cudaEventDestroy(e);
     for (auto e : ctx->ev_h2d) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -1429,13 +1491,13 @@ int ipkgpu_host_alloc(int device, size_t bytes, void** out)
     if (!out) return IPKGPU_EINVAL;
     *out = nullptr;
     if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return IPKGPU_ENODEV; }
-    if (cudaMallocHost(out, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return IPKGPU_ENOMEM; }
+    if (ipkgpu::pinned_alloc(out, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); *out = nullptr; return IPKGPU_ENOMEM; }
     return IPKGPU_OK;
 }
 
 void ipkgpu_host_free(void* p)
 {
-    if (p && cudaFreeHost(p) != cudaSuccess) cudaGetLastError();
+    ipkgpu::pinned_free(p);
 }
 
 int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out)
@@ -1793,7 +1855,7 @@ int ipkgpu_set_result_arena(ipkgpu_ctx* ctx, void* base, uint64_t cap_entries, u
         ipkgpu::hbuf* bufs[6] = { &ctx->h_branch, &ctx->h_score, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_cnt };
         for (ipkgpu::hbuf* b : bufs)
         {
-            if (b->p && !b->external) cudaFreeHost(b->p);
+            if (b->p && !b->external) ipkgpu::pinned_free(b->p);
             b->p = nullptr; b->cap = 0; b->external = false;
         }
         if (!base) return;

@@ -26,7 +26,13 @@
 namespace ipkgpu
 {
     constexpr int PS_BUCKETS = 256;
-    constexpr int PS_THREADS = 384, PS_ITEMS = 16, PS_TILE = PS_THREADS * PS_ITEMS;      // tile shape of the sweeps
+    // Tile shapes of the two sweeps and of the merge, from an A/B of builds on one box (profiles/r03n_ab_shapes.txt; ms per step on
+    // cfg3): MSD pass 384x16 @2 CTAs/SM 16.7, 384x12 @3 15.4, 512x12 @2 15.8; LSD passes (two) 384x16 @2 29.9, 384x8 @4 29.0, 512x8 @2
+    // 33.5; merge 256x12 @4 12.05, 256x8 @6 11.4, 256x16 @3 12.9.  All within 8 %: the kernels are bound by per-record work, not by
+    // occupancy.
+    constexpr int PS_THREADS = 384;
+    constexpr int PS_MSD_ITEMS = 12, PS_MSD_MINB = 3, PS_MSD_TILE = PS_THREADS * PS_MSD_ITEMS;
+    constexpr int PS_LSD_ITEMS = 8, PS_LSD_MINB = 4, PS_LSD_TILE = PS_THREADS * PS_LSD_ITEMS;
 
     /// bucket geometry of one segmented launch (kernel parameter, 2 KB)
     struct ps_table
@@ -421,7 +427,8 @@ namespace ipkgpu
     // max-merge + CSR by k-mer over sorted PACKED records (see merge.cuh for the semantics); tiles cut at bucket boundaries
     // -----------------------------------------------------------------------------------------------------------------
     constexpr int MP_THREADS = 256;
-    constexpr int MP_ITEMS = 12;
+    constexpr int MP_ITEMS = 8;
+    constexpr int MP_MINB = 6;
     constexpr int MP_TILE = MP_THREADS * MP_ITEMS;
     constexpr int MP_WARPS = MP_THREADS / 32;
 
@@ -438,7 +445,7 @@ namespace ipkgpu
         uint32_t epoch, n_tiles;
     };
 
-    __global__ void __launch_bounds__(MP_THREADS, 4) mg_merge_packed(const __grid_constant__ mergep_args A, const __grid_constant__ ps_table T)
+    __global__ void __launch_bounds__(MP_THREADS, MP_MINB) mg_merge_packed(const __grid_constant__ mergep_args A, const __grid_constant__ ps_table T)
     {
         __shared__ uint64_t sk[MP_TILE + 1];            // sk[0] = the record before the tile (same bucket)
         __shared__ uint32_t s_cnt[2][MP_ITEMS][MP_WARPS];
@@ -629,7 +636,7 @@ namespace ipkgpu
     {
         const uint32_t nr = uint32_t(ctx->runs_n);
         const size_t a8 = (size_t(nr) * 8 + 255) & ~size_t(255), a4 = (size_t(nr + 1) * 4 + 255) & ~size_t(255);
-        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_TILE));
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_MSD_TILE));
         ctx->reserve(ctx->runs_scratch, 2 * a8 + 5 * a4 + size_t(n_tiles) * 4);
         char* base = ctx->runs_scratch.as<char>();
         uint64_t* ka = reinterpret_cast<uint64_t*>(base); uint64_t* kb = reinterpret_cast<uint64_t*>(base + a8);
@@ -643,7 +650,7 @@ namespace ipkgpu
         exclusive_scan_u32(ctx, cnt, lstart, nr, ctx->scan_tmp);
         uint32_t* tile_first = lstart + a4 / 4;
         IPK_LAUNCH(ctx, "ps_runs_tile_first", uint64_t(n_tiles) * 80,
-                   ps_runs_tile_first<<<div_up<uint32_t>(n_tiles, 256), 256, 0, ctx->stream>>>(lstart, nr, n_tiles, PS_TILE, tile_first));
+                   ps_runs_tile_first<<<div_up<uint32_t>(n_tiles, 256), 256, 0, ctx->stream>>>(lstart, nr, n_tiles, PS_MSD_TILE, tile_first));
         return ps_runs{ lstart, off, tile_first, nr };
     }
 
@@ -663,14 +670,14 @@ namespace ipkgpu
                             const uint32_t* d_base, const ps_dest& D, bool peers, const ps_runs& Rn)
     {
         if (n == 0) return;
-        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_TILE));
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_MSD_TILE));
         ps_reserve_status(ctx, n_tiles);
         uint32_t* ticket = ctx->hist.as<uint32_t>() + RS_MAX_PASSES * RS_RADIX + 15;
         IPK_CUDA(cudaMemsetAsync(ticket, 0, 4, ctx->stream));
         ps_table none;
         memset(&none, 0, sizeof none);
-        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(true);
-        auto kern = Rn.lstart ? ps_sweep<PS_THREADS, PS_ITEMS, true, 2, true> : ps_sweep<PS_THREADS, PS_ITEMS, true, 2, false>;
+        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_MSD_ITEMS>(true);
+        auto kern = Rn.lstart ? ps_sweep<PS_THREADS, PS_MSD_ITEMS, true, PS_MSD_MINB, true> : ps_sweep<PS_THREADS, PS_MSD_ITEMS, true, PS_MSD_MINB, false>;
         IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         IPK_LAUNCH(ctx, peers ? "ps_msd_scatter_peers" : "ps_msd_pack", n * 20 + uint64_t(n_tiles) * RS_RADIX * 8,
                    kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(keys, vals, nullptr, d_base, n, low_bits, 0, ctx->rs_status.as<uint64_t>(), ticket,
@@ -686,7 +693,7 @@ namespace ipkgpu
         const uint32_t passes = div_up<uint32_t>(low_bits - skip_bits, 8);
         const uint64_t n = uint64_t(T.start[d1]) - T.start[d0];
         if (n == 0 || passes == 0) return false;
-        ps_fill_tiles(T, d0, d1, PS_TILE);
+        ps_fill_tiles(T, d0, d1, PS_LSD_TILE);
         const uint32_t n_tiles = T.tile_first[d1];
         ps_reserve_status(ctx, n_tiles);
         const size_t hist_words = size_t(PS_BUCKETS) * passes * RS_RADIX;
@@ -706,8 +713,8 @@ namespace ipkgpu
         memset(&none, 0, sizeof none);
         ps_runs no_runs;
         memset(&no_runs, 0, sizeof no_runs);
-        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_ITEMS>(false);
-        auto kern = ps_sweep<PS_THREADS, PS_ITEMS, false, 2>;
+        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS>(false);
+        auto kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB>;
         IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         bool in1 = false;
         for (uint32_t p = 0; p < passes; ++p)

@@ -12,6 +12,7 @@
 #include <thread>
 #include <vector>
 #include <unistd.h>
+#include <sys/mman.h>
 
 namespace
 {
@@ -148,10 +149,35 @@ namespace
         return flush();
     }
 
+    /// output positions [q0, q1) formatted straight into the mapped file at `dst`
+    void format_range(unsigned char* dst, const source& S, uint64_t q0, uint64_t q1)
+    {
+        for (uint64_t q = q0; q < q1; ++q)
+        {
+            const ipkhost_db* db = S.db(q);
+            const uint64_t i = S.at(q);
+            const uint64_t a = db->offsets[i], n = entries_of(db, i);
+            memcpy(dst, &db->keys[i], 8); memcpy(dst + 8, &db->fv[i], 4); memcpy(dst + 12, &n, 8);
+            dst += 20;
+            const float* sc = db->score + a;
+            if (db->branch16)
+            {
+                const uint16_t* br = db->branch16 + a;
+                for (uint64_t j = 0; j < n; ++j) { const uint32_t b = br[j]; memcpy(dst + 8 * j, &b, 4); memcpy(dst + 8 * j + 4, &sc[j], 4); }
+            }
+            else
+            {
+                const uint32_t* br = db->branch + a;
+                for (uint64_t j = 0; j < n; ++j) { memcpy(dst + 8 * j, &br[j], 4); memcpy(dst + 8 * j + 4, &sc[j], 4); }
+            }
+            dst += 8 * n;
+        }
+    }
+
     /// header + all records of `S` (n_kmers output positions, n_entries entries in total) with T threads
     int write_all(const char* path, const ipkhost_db* header, const source& S, uint64_t n_kmers, uint64_t n_entries, int n_threads)
     {
-        FILE* f = fopen(path, "wb");
+        FILE* f = fopen(path, "w+b");           // read-write: the records are written through a shared mapping
         if (!f) return IPKHOST_EIO;
         uint64_t header_bytes = 0;
         {
@@ -182,9 +208,27 @@ namespace
         const int fd = fileno(f);
         std::vector<char> ok(T, 1);
         std::vector<std::thread> th;
-        for (unsigned t = 0; t < T; ++t)
-            th.emplace_back([&, t] { ok[t] = write_range(fd, S, cut[t], cut[t + 1], header_bytes + at[t]) ? 1 : 0; });
-        for (auto& x : th) x.join();
+        // Buffered writes to ONE file serialize on its inode lock, whatever the number of threads (measured: 3.3 GB/s on tmpfs
+        // with 16 threads).  The file is therefore sized up front and mapped, and every thread formats its run straight into the
+        // mapping: page faults are per page and run in parallel, and the private blocks are gone.  Files that cannot be mapped
+        // (pipes, some network mounts) take the pwrite path.
+        void* map = MAP_FAILED;
+        if (total && ftruncate(fd, off_t(header_bytes + total)) == 0)
+            map = mmap(nullptr, size_t(header_bytes + total), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        if (map != MAP_FAILED)
+        {
+            unsigned char* base = static_cast<unsigned char*>(map) + header_bytes;
+            for (unsigned t = 0; t < T; ++t)
+                th.emplace_back([&, t] { format_range(base + at[t], S, cut[t], cut[t + 1]); });
+            for (auto& x : th) x.join();
+            if (munmap(map, size_t(header_bytes + total)) != 0) ok[0] = 0;
+        }
+        else
+        {
+            for (unsigned t = 0; t < T; ++t)
+                th.emplace_back([&, t] { ok[t] = write_range(fd, S, cut[t], cut[t + 1], header_bytes + at[t]) ? 1 : 0; });
+            for (auto& x : th) x.join();
+        }
         bool good = true;
         for (char c : ok) good = good && c;
         good = fclose(f) == 0 && good;

@@ -47,6 +47,8 @@ namespace
         int filter = IPKGPU_FILTER_MIF0;
         uint32_t node_count = 0;
         int device = 0, threads = 0, verbosity = 1;
+        std::string logp_f32;              // --logp-f32 FILE --width W: the matrices as raw float32 [node][site][state] in node-map order (benchmarks: no text to parse)
+        uint32_t width = 0;
         std::string boundary_file;         // --boundary-list FILE: the entries that depend on which side of +-band the threshold falls
         float boundary_band = 1e-5f;
         std::vector<int> devices;          // --devices 0,1,...: one rank per device, the multi-GPU build of include/ipkgpu.h
@@ -110,6 +112,8 @@ namespace
             else if (a == "-j" || a == "--num-threads") o.threads = atoi(need(i));
             else if (a == "-v" || a == "--verbosity") o.verbosity = atoi(need(i));
             else if (a == "--dump") o.dump = true;
+            else if (a == "--logp-f32") o.logp_f32 = need(i);
+            else if (a == "--width") o.width = uint32_t(atoll(need(i)));
             else if (a == "--boundary-list") o.boundary_file = need(i);
             else if (a == "--boundary-band") o.boundary_band = float(atof(need(i)));
             // parsed and ignored: they steer raxml-ng / the alignment reduction (upstream), or nothing at all in the reference build
@@ -130,6 +134,8 @@ namespace
             else usage(("unknown option " + a).c_str());
         }
         if (o.states != "dna" && o.states != "aa") usage("--states must be dna or aa");
+        if (!o.logp_f32.empty() && (o.node_map.empty() || o.width == 0)) usage("--logp-f32 needs --node-map and --width");
+        if (!o.logp_f32.empty()) o.ar_probs = o.logp_f32;
         const bool reference_mode = o.ar_probs.empty() && o.node_map.empty();
         if (reference_mode)
         {
@@ -363,19 +369,34 @@ int main(int argc, char** argv)
 
         // ---- posteriors
         auto t0 = std::chrono::steady_clock::now();
-        ipkhost_ar* ar = nullptr;
-        if (ipkhost_ar_open(ar_probs.c_str(), sigma, o.threads, &ar) != IPKHOST_OK) throw std::runtime_error(ipkhost_last_error());
-        const uint32_t width = ipkhost_ar_width(ar);
-        std::vector<const char*> label_ptrs;
-        for (auto& s : labels) label_ptrs.push_back(s.c_str());
-        // page-locked, so that the library uploads in node chunks under its first kernels
+        uint32_t width = o.width;
         void* logp_mem = nullptr;
-        if (ipkgpu_host_alloc(o.device, size_t(labels.size()) * width * sigma * sizeof(float), &logp_mem) != IPKGPU_OK)
-            throw std::runtime_error("cannot allocate page-locked memory for the posteriors (no CUDA device?)");
-        std::unique_ptr<float, void (*)(float*)> logp(static_cast<float*>(logp_mem), [](float* p) { ipkgpu_host_free(p); });
-        if (ipkhost_ar_read_nodes(ar, label_ptrs.data(), uint32_t(labels.size()), logp.get()) != IPKHOST_OK)
-            throw std::runtime_error(ipkhost_last_error());
-        ipkhost_ar_close(ar);
+        std::unique_ptr<float, void (*)(float*)> logp(nullptr, [](float* p) { ipkgpu_host_free(p); });
+        if (!o.logp_f32.empty())
+        {
+            const size_t bytes = size_t(labels.size()) * width * sigma * sizeof(float);
+            if (ipkgpu_host_alloc(o.device, bytes, &logp_mem) != IPKGPU_OK)
+                throw std::runtime_error("cannot allocate page-locked memory for the posteriors (no CUDA device?)");
+            logp.reset(static_cast<float*>(logp_mem));
+            FILE* f = fopen(o.logp_f32.c_str(), "rb");
+            if (!f || fread(logp.get(), 1, bytes, f) != bytes) { if (f) fclose(f); throw std::runtime_error("cannot read " + std::to_string(bytes) + " bytes from " + o.logp_f32); }
+            fclose(f);
+        }
+        else
+        {
+            ipkhost_ar* ar = nullptr;
+            if (ipkhost_ar_open(ar_probs.c_str(), sigma, o.threads, &ar) != IPKHOST_OK) throw std::runtime_error(ipkhost_last_error());
+            width = ipkhost_ar_width(ar);
+            std::vector<const char*> label_ptrs;
+            for (auto& s : labels) label_ptrs.push_back(s.c_str());
+            // page-locked, so that the library uploads in node chunks under its first kernels
+            if (ipkgpu_host_alloc(o.device, size_t(labels.size()) * width * sigma * sizeof(float), &logp_mem) != IPKGPU_OK)
+                throw std::runtime_error("cannot allocate page-locked memory for the posteriors (no CUDA device?)");
+            logp.reset(static_cast<float*>(logp_mem));
+            if (ipkhost_ar_read_nodes(ar, label_ptrs.data(), uint32_t(labels.size()), logp.get()) != IPKHOST_OK)
+                throw std::runtime_error(ipkhost_last_error());
+            ipkhost_ar_close(ar);
+        }
         fprintf(stderr, "Loaded %zu ghost-node matrices x %u sites x %u states in %.3f s\n", labels.size(), width, sigma, seconds_since(t0));
 
         // ---- the device path

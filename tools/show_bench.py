@@ -13,3 +13,4 @@ for f in sys.argv[1:]:
     if d.get("cpu_baseline"): print("  cpu", d["cpu_baseline"]["value"], d["cpu_baseline"]["cores"], d["cpu_baseline"]["kind"], "|", d["cpu_baseline"].get("parity"))
     if d.get("digest"): print("  digest", d["digest"].get("check"), d["digest"].get("entries_xor"))
     print("  roofline", d.get("roofline"))
+    if d.get("e2e_file"): print("  file", d["e2e_file"])
