@@ -113,6 +113,7 @@ struct ipkgpu_ctx
     std::vector<ipc_mapping> ipc_open;  // peers' receive buffers mapped into this process
     std::vector<ipc_mapping> ipc_slots; // ... one per peer rank for the packed exchange: a changed handle replaces the mapping (ipkgpu_open_peer_slot)
     uint32_t s1_key_bits = 0;          // k * bits of the stage-1 build
+    ipkgpu::dbuf recv_old2;            // (the score buffer of the pair exchange, same rule)
     ipkgpu::dbuf recv_old;             // a receive buffer that was outgrown: freed one exchange later, once no peer maps it any more
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;

@@ -131,6 +131,8 @@ namespace
         if (in->k * in->bits > 63) fail(IPKGPU_EINVAL, "k * bits = %u does not fit the 64-bit k-mer key", in->k * in->bits);
         if (in->filter != IPKGPU_FILTER_MIF0 && in->filter != IPKGPU_FILTER_RANDOM) fail(IPKGPU_EINVAL, "unknown filter %d", in->filter);
         if (uint64_t(in->n_nodes) * (uint64_t(in->width) + 1) > 0xffffffffull) fail(IPKGPU_EINVAL, "n_nodes * width too large");
+        // k1a_colmax reads a DNA column as one float4
+        if (in->sigma == 4 && in->n_nodes && (reinterpret_cast<uintptr_t>(in->logp) & 15) != 0) fail(IPKGPU_EINVAL, "logp must be 16-byte aligned for 4 states");
     }
 
     struct stage_timer
@@ -1432,7 +1434,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
                             &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
-                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old };
+                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old, &ctx->recv_old2 };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto& m : ctx->ipc_slots) if (m.ptr) cudaIpcCloseMemHandle(m.ptr);
@@ -1741,8 +1743,15 @@ int ipkgpu_recv_buffers(ipkgpu_ctx* ctx, uint64_t n_records, uint64_t** d_keys, 
         if (!d_keys || !d_scores) fail(IPKGPU_EINVAL, "output pointer is null");
         static_assert(sizeof(cudaIpcMemHandle_t) == IPKGPU_IPC_HANDLE_BYTES, "IPC handle size");
         // peers hold mappings of these allocations: grow rarely (25 % head room) so that handles stay valid across builds
-        if (n_records * 8 + 8 > ctx->recv_keys.cap) ctx->reserve(ctx->recv_keys, (n_records + n_records / 4) * 8 + 8);
-        if (n_records * 4 + 4 > ctx->recv_scores.cap) ctx->reserve(ctx->recv_scores, (n_records + n_records / 4) * 4 + 4);
+        // (a buffer that is outgrown stays alive for one more exchange: peers that still map it re-open on the changed handle first)
+        if (n_records * 8 + 8 > ctx->recv_keys.cap || n_records * 4 + 4 > ctx->recv_scores.cap)
+        {
+            ctx->release(ctx->recv_old); ctx->release(ctx->recv_old2);
+            ctx->recv_old = ctx->recv_keys; ctx->recv_old2 = ctx->recv_scores;
+            ctx->recv_keys = dbuf(); ctx->recv_scores = dbuf();
+            ctx->reserve(ctx->recv_keys, (n_records + n_records / 4) * 8 + 8);
+            ctx->reserve(ctx->recv_scores, (n_records + n_records / 4) * 4 + 4);
+        }
         *d_keys = ctx->recv_keys.as<uint64_t>();
         *d_scores = ctx->recv_scores.as<float>();
         if (handle_keys)
@@ -1785,6 +1794,7 @@ int ipkgpu_stage1_scatter(ipkgpu_ctx* ctx, uint32_t n_parts, uint64_t* const* pe
         if (!peer_keys || !peer_scores || !base_offsets) fail(IPKGPU_EINVAL, "null argument");
         const uint64_t n = ctx->s1_n;
         if (n == 0) return;
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed one shard's 2^32-1 limit", (unsigned long long)n);
         rs_peer_table PT;
         memset(&PT, 0, sizeof PT);
         uint32_t base[RS_RADIX];

@@ -29,10 +29,22 @@ namespace ipkgpu
     // Tile shapes of the two sweeps and of the merge, from an A/B of builds on one box (profiles/r03n_ab_shapes.txt; ms per step on
     // cfg3): MSD pass 384x16 @2 CTAs/SM 16.7, 384x12 @3 15.4, 512x12 @2 15.8; LSD passes (two) 384x16 @2 29.9, 384x8 @4 29.0, 512x8 @2
     // 33.5; merge 256x12 @4 12.05, 256x8 @6 11.4, 256x16 @3 12.9.  All within 8 %: the kernels are bound by per-record work, not by
-    // occupancy.
+    // occupancy.  With the look-back after the shared-memory scatter (r03q_ab_lookback.txt): LSD 384x8 @4 26.7, 384x12 @3 26.0,
+    // 384x16 @2 27.6; polling 2 / 4 / 8 predecessors at a time 27.3 / 26.7 / 26.7; sleeping 0 / 64 / 200 ns in the spin: no difference.
     constexpr int PS_THREADS = 384;
     constexpr int PS_MSD_ITEMS = 12, PS_MSD_MINB = 3, PS_MSD_TILE = PS_THREADS * PS_MSD_ITEMS;
-    constexpr int PS_LSD_ITEMS = 8, PS_LSD_MINB = 4, PS_LSD_TILE = PS_THREADS * PS_LSD_ITEMS;
+#ifndef IPK_LSD_ITEMS
+#define IPK_LSD_ITEMS 12
+#define IPK_LSD_MINB 3
+#endif
+#ifndef IPK_PS_POLL
+#define IPK_PS_POLL 4
+#endif
+#ifndef IPK_PS_SLEEP
+#define IPK_PS_SLEEP 64
+#endif
+    constexpr int PS_LSD_ITEMS = IPK_LSD_ITEMS, PS_LSD_MINB = IPK_LSD_MINB, PS_LSD_TILE = PS_THREADS * PS_LSD_ITEMS;
+    constexpr int PS_POLL = IPK_PS_POLL;
 
     /// bucket geometry of one segmented launch (kernel parameter, 2 KB)
     struct ps_table
@@ -285,39 +297,11 @@ namespace ipkgpu
             if (lane < 8) S.misc[lane] = winc - w;
         }
         __syncthreads();
-        if (is_digit)
-        {
-            const uint32_t ex_local = S.misc[warp] + inc - cnt;
-            uint32_t before = 0;
-            if (!first_of_chain)
-            {
-                // the chain ends at the first tile of the bucket (MSD: of the launch), which published an inclusive word.
-                // Four predecessors are polled at a time: their loads overlap, and a walk over LOCAL words costs one
-                // memory latency per four tiles instead of one per tile (ncu r03c: a quarter of the stall samples sat here).
-                const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
-                uint32_t left = chain_pos;                      // predecessors in the chain, nearest first
-                bool done = false;
-                while (!done)
-                {
-                    uint64_t w[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) w[j] = uint32_t(j) < left ? p[-int64_t(j) * RS_RADIX] : 0ull;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                    {
-                        if (done || uint32_t(j) >= left) break;
-                        if (uint32_t(w[j] >> 34) != epoch || ((w[j] >> 32) & 3) == 0) { left -= j; p -= int64_t(j) * RS_RADIX; goto again; }
-                        before += uint32_t(w[j]);
-                        if (((w[j] >> 32) & 3) == RS_FLAG_INCL) done = true;
-                    }
-                    if (!done) { left -= 4; p -= 4 * int64_t(RS_RADIX); }
-                again:;
-                }
-                *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
-            }
-            S.dbase[tid] = ex_local;
-            S.goff[tid] = dbase_g[tid] + before - ex_local;
-        }
+        // The records are placed into the tile's digit order in shared memory FIRST: that only needs the local scan, and it
+        // gives the preceding tiles time to publish before the look-back below starts walking (ncu r03p: 30 % of the
+        // instructions the kernel executed were polls of words that were not there yet).
+        const uint32_t ex_local = is_digit ? S.misc[warp] + inc - cnt : 0u;
+        if (is_digit) S.dbase[tid] = ex_local;
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i)
@@ -330,6 +314,40 @@ namespace ipkgpu
                 S.sk[pos] = rec[i];
                 if (MSD) S.sd[pos] = uint8_t(d);
             }
+        }
+        if (is_digit)
+        {
+            uint32_t before = 0;
+            if (!first_of_chain)
+            {
+                // the chain ends at the first tile of the bucket (MSD: of the launch), which published an inclusive word.
+                // Four predecessors are polled at a time: their loads overlap, and a walk over LOCAL words costs one
+                // memory latency per four tiles instead of one per tile; a word that is not there yet is waited for with a
+                // short sleep instead of a hot spin.
+                const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
+                uint32_t left = chain_pos;                      // predecessors in the chain, nearest first
+                bool done = false;
+                while (!done)
+                {
+                    uint64_t w[PS_POLL];
+#pragma unroll
+                    for (int j = 0; j < PS_POLL; ++j) w[j] = uint32_t(j) < left ? p[-int64_t(j) * RS_RADIX] : 0ull;
+                    int used = 0;
+#pragma unroll
+                    for (int j = 0; j < PS_POLL; ++j)
+                    {
+                        if (done || uint32_t(j) >= left || used != j) continue;
+                        if (uint32_t(w[j] >> 34) != epoch || ((w[j] >> 32) & 3) == 0) continue;      // not published yet: stop consuming here
+                        before += uint32_t(w[j]);
+                        used = j + 1;
+                        if (((w[j] >> 32) & 3) == RS_FLAG_INCL) done = true;
+                    }
+                    left -= used; p -= int64_t(used) * RS_RADIX;
+                    if (IPK_PS_SLEEP > 0 && !done && used < PS_POLL) __nanosleep(IPK_PS_SLEEP);
+                }
+                *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
+            }
+            S.goff[tid] = dbase_g[tid] + before - ex_local;
         }
         __syncthreads();
 #pragma unroll
