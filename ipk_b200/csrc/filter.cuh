@@ -40,7 +40,8 @@ namespace ipkgpu
     // ----------------------------------------------------------------------------------------------------------
     constexpr int MIF_THREADS = 256;
     constexpr int MIF_CHUNK = 1024;          // entries per CTA chunk (k-mers are assigned by their first entry)
-    constexpr int MIF_LONG = 16;             // k-mers with at least this many entries are summed by a warp (fixed lane order)
+    constexpr int MIF_LONG = 16;             // k-mers with at least this many entries are summed by 8 lanes (fixed lane order) ...
+    constexpr int MIF_WIDE = 256;            // ... and from this many on by a whole warp
     constexpr int MIF_CAP = 2048;            // entries a CTA can stage; longer runs take the streaming path
     constexpr size_t MIF_SMEM = size_t(MIF_CAP) * 8 + size_t(MIF_CAP) * 4 + size_t(MIF_CHUNK + 2) * 4;
 
@@ -79,9 +80,16 @@ namespace ipkgpu
         return float(__dsub_rn(__dsub_rn(__dmul_rn(ss, __dsub_rn(l, C.Hc)), A), __dmul_rn(rest, C.tlog)));
     }
 
+    /// the constants of a build, evaluated once on the host (the two log2 calls per THREAD were 17 % of the kernel's instructions, ncu r03p)
+    inline mif0_consts mif0_make_consts(float threshold, uint32_t total_num_groups)
+    {
+        const double thr = double(threshold);
+        return mif0_consts{ thr, std::log2(double(total_num_groups)), double(total_num_groups), thr * std::log2(thr) };
+    }
+
     __global__ void __launch_bounds__(MIF_THREADS) k4_mif0(const uint64_t* __restrict__ offs, const float* __restrict__ scores,
-                                                           const uint32_t* __restrict__ chunk_first, uint32_t total_num_groups,
-                                                           float threshold, float* __restrict__ fv, const mif_log2_entry* __restrict__ log2_tab)
+                                                           const uint32_t* __restrict__ chunk_first, const __grid_constant__ mif0_consts C,
+                                                           float* __restrict__ fv, const mif_log2_entry* __restrict__ log2_tab)
     {
         __shared__ mif_log2_entry s_tab[MIF_LOG2_BUCKETS];
         extern __shared__ __align__(16) unsigned char mif_smem[];
@@ -95,8 +103,6 @@ namespace ipkgpu
         const uint32_t nk = q1 - q0;
         const uint64_t e0 = offs[q0], e1 = offs[q1];
         const uint64_t span = e1 - e0;
-        const double thr = double(threshold);
-        const mif0_consts C{ thr, log2(double(total_num_groups)), double(total_num_groups), thr * log2(thr) };
         const int lane = tid & 31, warp = tid >> 5;
         constexpr int MIF_WARPS = MIF_THREADS / 32;
         const unsigned full = 0xffffffffu;
@@ -119,10 +125,26 @@ namespace ipkgpu
                 for (uint32_t i = a; i < b; ++i) { S = __dadd_rn(S, double(sx[i])); A = __dadd_rn(A, st[i]); }       // stored order (filter.cpp:78-82)
                 fv[q0 + j] = mif0_value(S, A, b - a, C, s_tab);
             }
+            // MIF_LONG .. MIF_WIDE - 1 entries: 8 lanes, lane l adds entries l, l + 8, ..., then the xor butterfly over 4, 2, 1
+            {
+                const int gl = tid & 7;
+                const unsigned gmask = 0xffu << (lane & ~7);
+                for (uint32_t j = tid >> 3; j < nk; j += MIF_THREADS / 8)
+                {
+                    const uint32_t a = koff[j], b = koff[j + 1];
+                    if (b - a < uint32_t(MIF_LONG) || b - a >= uint32_t(MIF_WIDE)) continue;      // uniform within the 8 lanes
+                    double S = 0, A = 0;
+                    for (uint32_t i = a + gl; i < b; i += 8) { S = __dadd_rn(S, double(sx[i])); A = __dadd_rn(A, st[i]); }
+#pragma unroll
+                    for (int o = 4; o >= 1; o >>= 1) { S = __dadd_rn(S, shfl_xor_f64(gmask, S, o)); A = __dadd_rn(A, shfl_xor_f64(gmask, A, o)); }
+                    if (gl == 0) fv[q0 + j] = mif0_value(S, A, b - a, C, s_tab);
+                }
+            }
+            // MIF_WIDE entries and more: a warp, lane l adds entries l, l + 32, ..., butterfly over 16 .. 1
             for (uint32_t j = warp; j < nk; j += MIF_WARPS)
             {
                 const uint32_t a = koff[j], b = koff[j + 1];
-                if (b - a < uint32_t(MIF_LONG)) continue;
+                if (b - a < uint32_t(MIF_WIDE)) continue;
                 double S = 0, A = 0;
                 for (uint32_t i = a + lane; i < b; i += 32) { S = __dadd_rn(S, double(sx[i])); A = __dadd_rn(A, st[i]); }
 #pragma unroll
@@ -139,11 +161,15 @@ namespace ipkgpu
             double S = 0, A = 0;
             if (b - a >= uint64_t(MIF_LONG))
             {
-                for (uint64_t i = a + lane; i < b; i += 32)
-                {
-                    const double x = double(logscore_to_score(scores[i]));
-                    S = __dadd_rn(S, x); A = __dadd_rn(A, mif_xlog2x(x, s_tab));
-                }
+                // the association of the staged path: 8 summing lanes below MIF_WIDE entries (the other lanes add exact zeros
+                // in the first two butterfly steps), 32 from there on
+                const int width = b - a >= uint64_t(MIF_WIDE) ? 32 : 8;
+                if (lane < width)
+                    for (uint64_t i = a + lane; i < b; i += width)
+                    {
+                        const double x = double(logscore_to_score(scores[i]));
+                        S = __dadd_rn(S, x); A = __dadd_rn(A, mif_xlog2x(x, s_tab));
+                    }
 #pragma unroll
                 for (int o = 16; o >= 1; o >>= 1) { S = __dadd_rn(S, shfl_xor_f64(full, S, o)); A = __dadd_rn(A, shfl_xor_f64(full, A, o)); }
             }

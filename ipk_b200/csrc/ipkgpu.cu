@@ -1173,7 +1173,7 @@ namespace
                 IPK_CUDA(cudaFuncSetAttribute(k4_mif0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(MIF_SMEM)));
                 IPK_LAUNCH(ctx, "k4_mif0", n_kmers * 12 + n_entries * 4,
                            k4_mif0<<<uint32_t(n_chunks), MIF_THREADS, MIF_SMEM, ctx->stream>>>(ctx->kmer_offs.as<uint64_t>(), ctx->ent_score.as<float>(),
-                                                                                        ctx->mif_chunks.as<uint32_t>(), sp.total_num_groups, sp.threshold, ctx->fv.as<float>(),
+                                                                                        ctx->mif_chunks.as<uint32_t>(), mif0_make_consts(sp.threshold, sp.total_num_groups), ctx->fv.as<float>(),
                                                                                         ctx->mif_tab.as<mif_log2_entry>()));
             }
             else
