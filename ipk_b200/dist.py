@@ -242,7 +242,15 @@ class SharedArena:
         from . import capi
         self.cap_entries, self.cap_kmers = int(cap_entries), int(cap_kmers)
         self.nbytes, self.offsets = capi.result_arena_layout(self.cap_entries, self.cap_kmers)
-        self.shm = shared_memory.SharedMemory(name=name, create=create, size=self.nbytes if create else 0)
+        if create:
+            try:
+                self.shm = shared_memory.SharedMemory(name=name, create=True, size=self.nbytes)
+            except FileExistsError:                    # left behind by a run that died: replace it
+                stale = shared_memory.SharedMemory(name=name, create=False)
+                stale.close(); stale.unlink()
+                self.shm = shared_memory.SharedMemory(name=name, create=True, size=self.nbytes)
+        else:
+            self.shm = shared_memory.SharedMemory(name=name, create=False)
         self.buf = np.frombuffer(self.shm.buf, dtype=np.uint8, count=self.nbytes)
         self.owner, self.registered = create, False
 
