@@ -133,6 +133,25 @@ def cpu_build_sample(wl, seed, b0, b1, threads, keep_db=False):
     return db.n_entries, db.n_emitted, dt, kind
 
 
+def cpu_stage3(db, wl):
+    """the CPU arm's serialization (db_builder.cpp:297-332: one save_phylo_kmer per k-mer, a single thread) of its sample
+    database, timed the way the B200 arm's file leg is: records -> file closed on /dev/shm.  Reported beside the build time,
+    not added to it (the build metric of both arms ends before serialization)."""
+    import tempfile
+    from ipk_b200 import hostlib
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+    path = os.path.join(base, f"ipkb200_cpu_stage3_{os.getpid()}.ipk")
+    try:
+        t = time.perf_counter()
+        hostlib.write_ipk(path, db.keys, db.fv, db.offsets, db.branch, db.score, wl.k, wl.omega, "DNA" if wl.sigma == 4 else "Proteins", threads=1)
+        dt = time.perf_counter() - t
+        size = os.path.getsize(path)
+        return {"seconds": round(dt, 3), "file_bytes": size, "gbs": round(size / dt * 1e-9, 2), "threads": 1}
+    finally:
+        if os.path.exists(path):
+            os.remove(path)
+
+
 def cpu_sample_size(wl, seed, threads, target_s, forced=0):
     """branch groups in the bounded sample: probe with one group per thread, scale to ~target_s seconds"""
     if forced:
@@ -153,6 +172,7 @@ def cpu_baseline(wl, seed, target_s=15.0, forced=0, gpu_check=None):
            "sample": f"branch groups [0,{nb}) of {wl.n_branches} ({2 * nb} ghost matrices, {2 * nb * (wl.width - wl.k + 1)} windows): "
                      f"{n_entries} entries, {n_emitted} emitted in {dt:.2f} s; OpenMP over branch groups "
                      f"(the loop db_builder.cpp:602-605 once marked parallel), in-RAM stages 1+2, no serialization"}
+    out["stage3"] = cpu_stage3(db, wl)
     if gpu_check is not None:
         out["parity"] = gpu_check(nb, db)
     return out
@@ -222,7 +242,7 @@ def file_leg(ctx, inp_host, h_logp, node_branch, wl, n_entries, n_kmers):
         db = hostlib.HostDb(b"DNA" if wl.sigma == 4 else b"Proteins", b"", 0, None, None, wl.k, wl.omega, res.n_kmers, res.n_entries,
                             C.cast(res.keys, C.POINTER(C.c_uint64)), C.cast(res.fv, C.POINTER(C.c_float)), C.cast(res.offsets, C.POINTER(C.c_uint64)),
                             C.cast(res.counts, C.POINTER(C.c_uint32)), C.cast(res.branch, C.POINTER(C.c_uint32)), C.cast(res.score, C.POINTER(C.c_float)),
-                            C.cast(res.branch16, C.POINTER(C.c_uint16)))
+                            C.cast(res.branch16, C.POINTER(C.c_uint16)), None)
         rc = lib.ipkhost_write_ipk_mt(path.encode(), C.byref(db), 0)
         t2 = time.perf_counter()
         if rc != 0:
@@ -475,6 +495,17 @@ def run_b200(args):
                     "algo_bytes_per_launch": top["bytes"] // max(top["launches"], 1),
                     "ms_per_launch": round(top["ms"] / max(top["launches"], 1), 4),
                     "share_of_step": round(top["ms"] / max(ms_dev, 1e-9), 4)}
+        if top["kernel"].startswith("k2_"):
+            roofline["note"] = ("the enumeration is bound by instruction issue and shared-memory latency (ncu: 56 % issue slots, DRAM 7 %), "
+                                "not by HBM: its bytes are the record write; `roofline_hbm_kernel` is the largest memory-bound kernel")
+        hbm = [r for r in rows if r["kernel"].startswith(("ps_", "rs_onesweep", "mg_"))]
+        if hbm:
+            h0 = hbm[0]
+            roofline_hbm = {"kernel": h0["kernel"], "achieved": round(h0["bytes"] / max(h0["ms"], 1e-9) * 1e-6, 1), "peak": peak, "unit": "GB/s",
+                            "frac": round(h0["bytes"] / max(h0["ms"], 1e-9) * 1e-6 / peak, 4), "launches_per_step": h0["launches"] // max(args.steps, 1),
+                            "ms_per_launch": round(h0["ms"] / max(h0["launches"], 1), 4), "share_of_step": round(h0["ms"] / max(ms_dev, 1e-9), 4)}
+        else:
+            roofline_hbm = None
     # whole-path roofline as north_star defines it: emitted-plus-sorted bytes over HBM vs all-to-all bytes over NVLink
     passes = int(st["sort_passes"])
     exch_bytes_per_record = float(exch_info.get("bytes_per_record", 12))     # 8: packed records; 12: (u64 composite key, f32 score)
@@ -508,7 +539,7 @@ def run_b200(args):
             "host": "rank processes bound to the CPUs next to their GPU (NVML affinity)" if numa_bound else "unbound",
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "build_time_s": ms_e2e / args.steps * 1e-3},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "roofline_hbm_kernel": roofline_hbm if rows else None,
             "path_roofline": {"algo_bytes_per_step": int(path_bytes), "t_hbm_ms": round(t_hbm * 1e3, 3), "t_nvlink_ms": round(t_nvl * 1e3, 3),
                               "frac": round(t_bound / (ms_dev / args.steps * 1e-3), 4), "nvlink_peak_gbs": NVLINK_GBS,
                               "bound": "nvlink" if t_nvl > t_hbm else "hbm"},

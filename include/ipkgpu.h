@@ -135,6 +135,16 @@ int  ipkgpu_kernel_profile_get(const ipkgpu_ctx* ctx, uint32_t index, char* name
 int  ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, ipkgpu_result* out);
 void ipkgpu_free_result(ipkgpu_ctx* ctx, ipkgpu_result* res);
 
+/* KEEP_POSITIONS builds (the reference's `ipk-aa-pos` binary: ipk::put of ipk/src/branch_group.cpp:72-86, entries
+ * {branch, score, position}, db_builder.cpp:655-690).  While switched on, ipkgpu_build also records, per (k-mer, branch) entry,
+ * the alignment position (window start) of the FIRST window in processing order -- the group's ghost nodes one after the
+ * other, windows ascending -- that reached the entry's score (the strict `<` of put keeps the first maximum).
+ * ipkgpu_result_positions hands back the array that runs parallel to ipkgpu_result.branch / score of the last build (same
+ * memory space, same order; NULL when the last build kept none).  The path is the reference's rarely used variant and is
+ * built for clarity, not speed (positions.cuh); 16-bit branches, streamed parts and the multi-GPU stages do not apply. */
+int  ipkgpu_set_keep_positions(ipkgpu_ctx* ctx, int on);
+int  ipkgpu_result_positions(ipkgpu_ctx* ctx, const uint32_t** positions, int32_t* on_device);
+
 /* Order-independent digest of the database the last ipkgpu_build / ipkgpu_stage2 of ctx produced (it is still resident
  * on the device whatever result mode was asked for).  No reference counterpart -- the reference compares databases entry by
  * entry (tools/src/diff.cpp:129-295); the digest does the same for builds that never share a memory: sums (mod 2^64) and

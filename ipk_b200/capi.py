@@ -133,6 +133,10 @@ def load() -> C.CDLL:
     lib.ipkgpu_build.restype = C.c_int
     lib.ipkgpu_result_digest.argtypes = [C.c_void_p, C.c_float, C.c_float, P(Digest)]
     lib.ipkgpu_result_digest.restype = C.c_int
+    lib.ipkgpu_set_keep_positions.argtypes = [C.c_void_p, C.c_int]
+    lib.ipkgpu_set_keep_positions.restype = C.c_int
+    lib.ipkgpu_result_positions.argtypes = [C.c_void_p, P(C.c_void_p), P(C.c_int32)]
+    lib.ipkgpu_result_positions.restype = C.c_int
     lib.ipkgpu_boundary_list.argtypes = [C.c_void_p, P(Input), C.c_float, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_uint64)]
     lib.ipkgpu_boundary_list.restype = C.c_int
     lib.ipkgpu_free_result.argtypes = [C.c_void_p, P(Result)]
@@ -372,6 +376,19 @@ class Context:
         d = Digest()
         self._check(self._lib.ipkgpu_result_digest(self._h, log_threshold, band, C.byref(d)))
         return d.as_dict()
+
+    def set_keep_positions(self, on: bool = True) -> None:
+        """KEEP_POSITIONS builds (ipk-aa-pos): every entry also carries the alignment position of the first window that reached its score"""
+        self._check(self._lib.ipkgpu_set_keep_positions(self._h, 1 if on else 0))
+
+    def result_positions(self, n_entries: int):
+        """positions parallel to the last HOST result's branch / score arrays (numpy copy), or None when the build kept none"""
+        p = C.c_void_p(0)
+        dev = C.c_int32(0)
+        self._check(self._lib.ipkgpu_result_positions(self._h, C.byref(p), C.byref(dev)))
+        if not p.value or dev.value:
+            return None
+        return _view(p.value, n_entries, np.uint32).copy()
 
     def boundary_list(self, inp: Input, band: float = 1e-5, cap: int = 1 << 20):
         """(k-mer, branch) entries whose presence or score flips when the threshold moves by less than `band`:

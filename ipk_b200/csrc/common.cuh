@@ -117,6 +117,13 @@ struct ipkgpu_ctx
     ipkgpu::dbuf recv_old;             // a receive buffer that was outgrown: freed one exchange later, once no peer maps it any more
     uint64_t* s1_keys = nullptr;       // the records ipkgpu_stage1_partition buckets: u_keys (merged) or keys_a (raw)
     uint32_t* s1_scores = nullptr;
+    // KEEP_POSITIONS builds (positions.cuh; ipkgpu_set_keep_positions)
+    bool keep_positions = false;
+    ipkgpu::dbuf ent_pos, out_pos, pos_flags, node_rank;
+    ipkgpu::hbuf h_pos;
+    const uint32_t* res_perm = nullptr;             // k-mer order of the last result (fv order -> index in key order), device
+    const uint32_t* res_pos = nullptr;              // positions aligned with the last result's entries (host or device like the result), or null
+    int res_pos_on_device = 0;
     uint64_t res_n_kmers = 0, res_n_entries = 0;      // the CSR the last build / stage 2 left in kmer_keys / kmer_offs / ent_* / fv
     bool res_valid = false;
     uint64_t hint_side = 0;            // ... and of its side stream

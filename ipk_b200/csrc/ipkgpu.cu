@@ -13,6 +13,7 @@
 #include "packed_sort.cuh"
 #include "filter.cuh"
 #include "digest.cuh"
+#include "positions.cuh"
 
 #include <cmath>
 #include <numeric>
@@ -479,7 +480,7 @@ namespace
         merge_out r;
         const uint64_t n = n_main + n_side;          // the kernel walks the merge of the two sorted streams
         if (n == 0) return r;
-        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed the 2^32-1 limit of one merge", (unsigned long long)n);
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed the 2^32-1 limit of one merge on one device: split the build over devices (ipk-b200 --devices, key shards stay below the limit)", (unsigned long long)n);
         const uint32_t tiles = uint32_t(div_up<uint64_t>(n, MG_TILE));
         // single pass: the outputs are sized by their upper bounds (records <= n, k-mers <= min(n, 2^key_bits))
         const uint64_t n_cap = std::max(n_total, ent_base + n);
@@ -862,7 +863,7 @@ namespace
                           bool want_csr, ipkgpu_stats* st, stage_timer& tm, bool raw = false, int result_mode = 0)
     {
         stage1_out o;
-        ctx->res_valid = false;
+        ctx->res_valid = false; ctx->res_pos = nullptr;
         o.n_groups = uint32_t(T.group_branch.size());
         const uint32_t key_bits = in->k * in->bits;
         if (key_bits + group_bits > 64) fail(IPKGPU_EINVAL, "k*bits + group bits = %u exceeds 64", key_bits + group_bits);
@@ -1097,7 +1098,7 @@ namespace
     void finish_from_csr(ipkgpu_ctx* ctx, uint64_t n_kmers, uint64_t n_entries, const stage2_params& sp, int result_on_device,
                          ipkgpu_result* out, stage_timer& tm)
     {
-        if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard", (unsigned long long)n_entries);
+        if (n_entries > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu entries exceed the 2^32-1 limit of one device shard: split the build over more devices (ipk-b200 --devices)", (unsigned long long)n_entries);
         ctx->hint_kmers = n_kmers;
         ipkgpu_stats& st = out->stats;
         const bool on_device = (result_on_device & 1) != 0, indexed = (result_on_device & 2) != 0;
@@ -1189,6 +1190,7 @@ namespace
             const bool in_b = radix_sort_pairs(ctx, ctx->ord_keys_a.as<uint64_t>(), ctx->ord_vals_a.as<uint32_t>(), ctx->ord_keys_b.as<uint64_t>(),
                                                ctx->ord_vals_b.as<uint32_t>(), n_kmers, 32, ctx->hist, ctx->scan_tmp);
             const uint32_t* perm = in_b ? ctx->ord_vals_b.as<uint32_t>() : ctx->ord_vals_a.as<uint32_t>();
+            ctx->res_perm = perm;
             // K6
             IPK_LAUNCH(ctx, "k6_gather_heads", n_kmers * 44,
                        k6_gather_heads<<<grid, 256, 0, ctx->stream>>>(perm, ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->fv.as<float>(),
@@ -1268,7 +1270,10 @@ namespace
     void run_stage2(ipkgpu_ctx* ctx, uint64_t* keys, float* scores, uint64_t n, bool group_ordered, const stage2_params& sp,
                     int result_on_device, ipkgpu_result* out, stage_timer& tm)
     {
-        ctx->res_valid = false;
+        ctx->res_valid = false; ctx->res_pos = nullptr;
+        if (n > 0xffffffffull)
+            fail(IPKGPU_EINVAL, "%llu unique (k-mer, branch) records exceed the 2^32-1 limit of one device's regroup sort (about 51 GB of records, near the "
+                 "memory bound of the device anyway): split the build over devices (ipk-b200 --devices; every key shard has its own limit)", (unsigned long long)n);
         const size_t e0 = tm.mark();
         const uint64_t* sk = keys;
         const float* sv = scores;
@@ -1321,6 +1326,125 @@ namespace
         finish_from_csr(ctx, m.n_kmers, m.n_records, sp, result_on_device, out, tm);
         out->stats.ms_sort += tm.ms(e0, e1);
         out->stats.ms_merge += tm.ms(e1, e2);
+    }
+
+    /// The KEEP_POSITIONS build (positions.cuh): enumeration with per-record (node, window), sequence numbers below the group
+    /// field, pair sort on (k-mer, group), one thread per run for the first maximum, then the common filter / order / hand-over.
+    void run_build_positions(ipkgpu_ctx* ctx, const ipkgpu_input* in, const group_tables& T, int result_mode, ipkgpu_result* out, stage_timer& tm)
+    {
+        ipkgpu_stats& st = out->stats;
+        const uint32_t key_bits = in->k * in->bits, n_groups = uint32_t(T.group_branch.size()), group_bits = ceil_log2(n_groups);
+        const uint32_t nwin = in->width >= in->k ? in->width - in->k + 1 : 0;
+        uint32_t max_rank = 0;
+        std::vector<uint32_t> node_rank(in->n_nodes, 0);
+        for (uint32_t g = 0; g < n_groups; ++g)
+            for (uint32_t s = T.group_first_slot[g]; s < T.group_first_slot[g + 1]; ++s)
+            {
+                node_rank[T.node_order[s]] = s - T.group_first_slot[g];           // processing order inside the group (db_builder.cpp:642)
+                max_rank = std::max(max_rank, s - T.group_first_slot[g]);
+            }
+        const uint32_t seq_bits = ceil_log2(uint64_t(max_rank + 1) * std::max<uint32_t>(nwin, 1));
+        if (key_bits + group_bits + seq_bits > 64) fail(IPKGPU_EINVAL, "k*bits %u + group bits %u + position bits %u exceed 64", key_bits, group_bits, seq_bits);
+        const stage2_params sp{ group_bits, key_bits, in->total_num_groups, in->threshold, in->filter };
+        ctx->res_valid = false; ctx->res_pos = nullptr;
+        ctx->reserve(ctx->counters, 128);
+        const size_t eh = tm.mark();
+        const float* d_logp = stage_inputs(ctx, in, T, &st);
+        ctx->reserve(ctx->node_rank, size_t(in->n_nodes) * 4 + 4);
+        IPK_CUDA(cudaMemcpyAsync(ctx->node_rank.p, node_rank.data(), size_t(in->n_nodes) * 4, cudaMemcpyHostToDevice, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));                       // node_rank is a local vector
+        const size_t e0 = tm.mark();
+        run_best_prefix(ctx, d_logp, in);
+        const size_t e1 = tm.mark();
+        uint64_t n = 0;
+        if (in->n_nodes && nwin)
+        {
+            const enum_program P = make_enum_program(int(in->k));
+            uint64_t cap = std::max<uint64_t>(1 << 20, ctx->hint_emitted ? ctx->hint_emitted + ctx->hint_emitted / 16 : 32ull * in->n_nodes * nwin);
+            for (int attempt = 0; attempt < 2; ++attempt)
+            {
+                ctx->reserve(ctx->keys_a, cap * 8 + 8); ctx->reserve(ctx->vals_a, cap * 4 + 4);
+                ctx->reserve(ctx->dbg_node, cap * 4 + 4); ctx->reserve(ctx->dbg_win, cap * 4 + 4);
+                IPK_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 128, ctx->stream));
+                enum_launch L{ 0, in->n_nodes, 0, 0, cap, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<float>(),
+                               ctx->dbg_node.as<uint32_t>(), ctx->dbg_win.as<uint32_t>(), true };
+                launch_enumerate(ctx, d_logp, in, P, L, false);
+                n = read_u64(ctx, ctx->counters.p);
+                st.enum_launches++;
+                if (n <= cap) break;
+                if (attempt == 1) fail(IPKGPU_ECUDA, "the enumeration emitted %llu records into a buffer sized for %llu by its own count", (unsigned long long)n, (unsigned long long)cap);
+                cap = n;
+            }
+            ctx->hint_emitted = n;
+        }
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu records exceed the 2^32-1 limit of a KEEP_POSITIONS build", (unsigned long long)n);
+        st.n_emitted = n;
+        const size_t e2 = tm.mark();
+        uint64_t n_entries = 0, n_kmers = 0;
+        size_t e3 = e2;
+        if (n)
+        {
+            const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(n, 256), uint64_t(ctx->num_sms) * 32));
+            IPK_LAUNCH(ctx, "kp_compose", n * 24, kp_compose<<<grid, 256, 0, ctx->stream>>>(ctx->keys_a.as<uint64_t>(), ctx->dbg_node.as<uint32_t>(), ctx->dbg_win.as<uint32_t>(),
+                                                                                         ctx->node_group.as<uint32_t>(), ctx->node_rank.as<uint32_t>(), n, group_bits, seq_bits, nwin));
+            ctx->reserve(ctx->keys_b, n * 8 + 8); ctx->reserve(ctx->vals_b, n * 4 + 4);
+            uint32_t passes = 0;
+            const bool in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(), n,
+                                               key_bits + group_bits, ctx->hist, ctx->scan_tmp, &passes, seq_bits);
+            st.sort_passes = passes;
+            e3 = tm.mark();
+            const uint64_t* sk = in_b ? ctx->keys_b.as<uint64_t>() : ctx->keys_a.as<uint64_t>();
+            const float* sv = in_b ? ctx->vals_b.as<float>() : ctx->vals_a.as<float>();
+            // flags and their scans live in one scratch: head_e, idx_e, head_k, idx_k
+            ctx->reserve(ctx->pos_flags, n * 16 + 64);
+            uint32_t* head_e = ctx->pos_flags.as<uint32_t>(); uint32_t* idx_e = head_e + n; uint32_t* head_k = idx_e + n; uint32_t* idx_k = head_k + n;
+            IPK_LAUNCH(ctx, "kp_flags", n * 16, kp_flags<<<grid, 256, 0, ctx->stream>>>(sk, n, group_bits, seq_bits, head_e, head_k));
+            unsigned long long* totals = ctx->counters.as<unsigned long long>() + 2;
+            exclusive_scan_u32(ctx, head_e, idx_e, n, ctx->scan_tmp, totals);
+            exclusive_scan_u32(ctx, head_k, idx_k, n, ctx->scan_tmp, totals + 1);
+            uint64_t h[2];
+            IPK_CUDA(cudaMemcpyAsync(h, totals, 16, cudaMemcpyDeviceToHost, ctx->stream));
+            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+            n_entries = h[0]; n_kmers = h[1];
+            ctx->reserve(ctx->kmer_keys, n_kmers * 8 + 8); ctx->reserve(ctx->kmer_offs, (n_kmers + 1) * 8);
+            ctx->reserve(ctx->ent_branch, n_entries * 4 + 4); ctx->reserve(ctx->ent_score, n_entries * 4 + 4); ctx->reserve(ctx->ent_pos, n_entries * 4 + 4);
+            IPK_LAUNCH(ctx, "kp_write", n * 12 + n_entries * 12 + n_kmers * 16,
+                       kp_write<<<grid, 256, 0, ctx->stream>>>(sk, sv, n, group_bits, seq_bits, nwin, head_e, idx_e, head_k, idx_k, ctx->group_branch.as<uint32_t>(),
+                                                               ctx->kmer_keys.as<uint64_t>(), ctx->kmer_offs.as<uint64_t>(), ctx->ent_branch.as<uint32_t>(),
+                                                               ctx->ent_score.as<float>(), ctx->ent_pos.as<uint32_t>()));
+            IPK_CUDA(cudaMemcpyAsync(ctx->kmer_offs.as<uint64_t>() + n_kmers, &n_entries, 8, cudaMemcpyHostToDevice, ctx->stream));
+            IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        }
+        else
+        {
+            ctx->reserve(ctx->kmer_offs, 8);
+            IPK_CUDA(cudaMemsetAsync(ctx->kmer_offs.p, 0, 8, ctx->stream));
+        }
+        const size_t e4 = tm.mark();
+        const int mode = result_mode & 3;                                    // 16-bit branches / streaming do not apply here
+        finish_from_csr(ctx, n_kmers, n_entries, sp, mode, out, tm);
+        // the positions follow their entries: in place for indexed results, gathered by the same k-mer order otherwise
+        const bool on_device = (mode & 1) != 0, indexed = (mode & 2) != 0;
+        const uint32_t* d_pos = ctx->ent_pos.as<uint32_t>();
+        if (!indexed && n_kmers)
+        {
+            ctx->reserve(ctx->out_pos, n_entries * 4 + 4);
+            const uint32_t ggrid = uint32_t(div_up<uint64_t>(n_kmers * 8, 256));
+            IPK_LAUNCH(ctx, "kp_gather_pos", n_entries * 8, kp_gather_pos<8><<<ggrid, 256, 0, ctx->stream>>>(ctx->res_perm, ctx->kmer_offs.as<uint64_t>(), ctx->out_offs.as<uint64_t>(),
+                                                                                                           n_kmers, ctx->ent_pos.as<uint32_t>(), ctx->out_pos.as<uint32_t>()));
+            d_pos = ctx->out_pos.as<uint32_t>();
+        }
+        if (on_device) ctx->res_pos = n_entries ? d_pos : nullptr;
+        else
+        {
+            ctx->reserve_host(ctx->h_pos, n_entries * 4 + 4);
+            if (n_entries) IPK_CUDA(cudaMemcpyAsync(ctx->h_pos.p, d_pos, n_entries * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            st.d2h_bytes += n_entries * 4;
+            ctx->res_pos = n_entries ? ctx->h_pos.as<uint32_t>() : nullptr;
+        }
+        ctx->res_pos_on_device = on_device ? 1 : 0;
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+        st.ms_h2d = tm.ms(eh, e0); st.ms_prefix = tm.ms(e0, e1); st.ms_enumerate = tm.ms(e1, e2); st.ms_sort = tm.ms(e2, e3); st.ms_merge = tm.ms(e3, e4);
     }
 
     template<class F> int guarded(ipkgpu_ctx* ctx, F&& f)
@@ -1434,13 +1558,13 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
                             &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
-                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old, &ctx->recv_old2 };
+                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old, &ctx->recv_old2, &ctx->ent_pos, &ctx->out_pos, &ctx->pos_flags, &ctx->node_rank };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto& m : ctx->ipc_slots) if (m.ptr) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_slots.clear();
     for (auto* b : all) ctx->release(*b);
-    ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score, &ctx->h_cnt };
+    ipkgpu::hbuf* hall[] = { &ctx->h_small, &ctx->h_keys, &ctx->h_fv, &ctx->h_offs, &ctx->h_branch, &ctx->h_score, &ctx->h_cnt, &ctx->h_pos };
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->ev_merged) { cudaEventDestroy(ctx->ev_merged); cudaEventDestroy(ctx->ev_copied); }
     for (auto* b : hall) if (b->p && !b->external) ipkgpu::pinned_free(b->p);
@@ -1517,6 +1641,17 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         ipkgpu_stats& st = out->stats;
         st.n_windows = in->width >= in->k ? uint64_t(in->n_nodes) * (in->width - in->k + 1) : 0;
         st.n_groups = n_groups;
+        if (ctx->keep_positions)
+        {
+            run_build_positions(ctx, in, T, result_on_device, out, tm);
+            const size_t t1p = tm.mark();
+            IPK_CUDA(cudaEventSynchronize(ctx->event(t1p)));
+            st.ms_total = tm.ms(t0, t1p);
+            st.kernel_launches = ctx->launches;
+            st.n_tiles = ctx->last_tiles; st.n_deferred_tiles = ctx->last_deferred_tiles;
+            return;
+        }
+        ctx->res_pos = nullptr;
         const stage1_out s1 = run_stage1(ctx, in, T, 0, group_bits, true, &st, tm, false, result_on_device);
         st.n_emitted = s1.n_emitted;
         st.sort_passes = s1.sort_passes;
@@ -1531,6 +1666,21 @@ int ipkgpu_build(ipkgpu_ctx* ctx, const ipkgpu_input* in, int result_on_device, 
         st.kernel_launches = ctx->launches;
         st.n_tiles = ctx->last_tiles; st.n_deferred_tiles = ctx->last_deferred_tiles;
     });
+}
+
+int ipkgpu_set_keep_positions(ipkgpu_ctx* ctx, int on)
+{
+    if (!ctx) return IPKGPU_EINVAL;
+    ctx->keep_positions = on != 0;
+    return IPKGPU_OK;
+}
+
+int ipkgpu_result_positions(ipkgpu_ctx* ctx, const uint32_t** positions, int32_t* on_device)
+{
+    if (!ctx || !positions) return IPKGPU_EINVAL;
+    *positions = ctx->res_valid ? ctx->res_pos : nullptr;
+    if (on_device) *on_device = ctx->res_pos_on_device;
+    return IPKGPU_OK;
 }
 
 int ipkgpu_result_digest(ipkgpu_ctx* ctx, float log_threshold, float band, ipkgpu_digest* out)
@@ -2037,7 +2187,7 @@ int ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_sta
         if (n && !ps_eligible(key_bits, group_bits, n)) fail(IPKGPU_EINVAL, "records do not fit the packed form");
         if (n * 8 > ctx->recv_keys.cap) fail(IPKGPU_EINVAL, "%llu records exceed the receive buffer (ipkgpu_recv_packed)", (unsigned long long)n);
         memset(out, 0, sizeof *out);
-        ctx->res_valid = false;
+        ctx->res_valid = false; ctx->res_pos = nullptr;
         stage_timer tm(ctx);
         const size_t t0 = tm.mark();
         ctx->reserve(ctx->group_branch, size_t(n_groups_total) * 4 + 4);

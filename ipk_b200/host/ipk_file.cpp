@@ -66,7 +66,7 @@ struct ipkhost_db_file
     std::vector<uint64_t> index_num_nodes, keys, offsets;
     std::vector<double> index_len;
     std::vector<float> fv, score;
-    std::vector<uint32_t> branch;
+    std::vector<uint32_t> branch, position;
 };
 
 namespace
@@ -98,6 +98,7 @@ namespace
     }
 
     inline uint64_t entries_of(const ipkhost_db* db, uint64_t q) { return db->counts ? db->counts[q] : db->offsets[q + 1] - db->offsets[q]; }
+    inline size_t entry_bytes(const ipkhost_db* db) { return db->position ? 10 : 8; }
 
     /// where the k-mer at output position q lives: one database, or k-mer order_index[q] of shard order_shard[q]
     struct source
@@ -137,12 +138,17 @@ namespace
             fill += 20;
             for (uint64_t e = a; e < a + n;)
             {
-                if (fill + 8 > BLOCK && !flush()) return false;
-                const uint64_t room = (BLOCK - fill) / 8, m = std::min<uint64_t>(room, a + n - e);
+                if (fill + 16 > BLOCK && !flush()) return false;
+                const size_t eb = entry_bytes(db);
+                const uint64_t room = (BLOCK - fill) / eb, m = std::min<uint64_t>(room, a + n - e);
                 unsigned char* o = buf.data() + fill;
-                if (db->branch16) for (uint64_t j = 0; j < m; ++j) { const uint32_t b = db->branch16[e + j]; memcpy(o + 8 * j, &b, 4); memcpy(o + 8 * j + 4, &db->score[e + j], 4); }
-                else for (uint64_t j = 0; j < m; ++j) { memcpy(o + 8 * j, &db->branch[e + j], 4); memcpy(o + 8 * j + 4, &db->score[e + j], 4); }
-                fill += size_t(m) * 8;
+                for (uint64_t j = 0; j < m; ++j)
+                {
+                    const uint32_t b = db->branch16 ? uint32_t(db->branch16[e + j]) : db->branch[e + j];
+                    memcpy(o + eb * j, &b, 4); memcpy(o + eb * j + 4, &db->score[e + j], 4);
+                    if (db->position) { const uint16_t p16 = uint16_t(db->position[e + j]); memcpy(o + eb * j + 8, &p16, 2); }
+                }
+                fill += size_t(m) * eb;
                 e += m;
             }
         }
@@ -160,6 +166,18 @@ namespace
             memcpy(dst, &db->keys[i], 8); memcpy(dst + 8, &db->fv[i], 4); memcpy(dst + 12, &n, 8);
             dst += 20;
             const float* sc = db->score + a;
+            if (db->position)
+            {
+                // KEEP_POSITIONS entries: {branch u32, score f32, position u16} (i2l::phylo_kmer::pos_type; UNVERIFIED like the rest)
+                for (uint64_t j = 0; j < n; ++j)
+                {
+                    const uint32_t b = db->branch16 ? uint32_t(db->branch16[a + j]) : db->branch[a + j];
+                    const uint16_t p16 = uint16_t(db->position[a + j]);
+                    memcpy(dst + 10 * j, &b, 4); memcpy(dst + 10 * j + 4, &sc[j], 4); memcpy(dst + 10 * j + 8, &p16, 2);
+                }
+                dst += 10 * n;
+                continue;
+            }
             if (db->branch16)
             {
                 const uint16_t* br = db->branch16 + a;
@@ -193,7 +211,8 @@ namespace
         // into runs of about equal bytes, one thread formats and pwrites each run at its prefix-summed offset
         unsigned T = n_threads > 0 ? unsigned(n_threads) : std::max(1u, std::thread::hardware_concurrency());
         T = unsigned(std::min<uint64_t>(T, std::max<uint64_t>(1, n_kmers / 4096)));
-        const uint64_t total = n_kmers * 20 + n_entries * 8;
+        const size_t eb = entry_bytes(S.dbs);
+        const uint64_t total = n_kmers * 20 + n_entries * eb;
         std::vector<uint64_t> cut(T + 1, n_kmers), at(T + 1, total);
         cut[0] = 0; at[0] = 0;
         {
@@ -201,7 +220,7 @@ namespace
             for (uint64_t q = 0; q < n_kmers && next < T; ++q)
             {
                 while (next < T && acc >= total / T * next) { cut[next] = q; at[next] = acc; ++next; }
-                acc += 20 + 8 * entries_of(S.db(q), S.at(q));
+                acc += 20 + eb * entries_of(S.db(q), S.at(q));
             }
             // cuts never reached (the last k-mers are long) stay at the end: empty ranges
         }
@@ -389,6 +408,19 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
     if (!r.ok || n_kmers > (1ull << 40) || n_entries > (1ull << 40)) { fclose(f); delete d; return IPKHOST_EFORMAT; }
     d->keys.resize(n_kmers); d->fv.resize(n_kmers); d->offsets.resize(n_kmers + 1);
     d->branch.resize(n_entries); d->score.resize(n_entries);
+    // entries with positions are 10 bytes instead of 8: the header does not say which (i2l: a property of the binary that wrote
+    // the file), the length of the file does
+    bool with_pos = false;
+    {
+        const long here = ftell(f);
+        if (here >= 0 && fseek(f, 0, SEEK_END) == 0)
+        {
+            const long end = ftell(f);
+            with_pos = n_entries && uint64_t(end - here) == n_kmers * 20 + n_entries * 10;
+            fseek(f, here, SEEK_SET);
+        }
+    }
+    if (with_pos) d->position.resize(n_entries);
     uint64_t e = 0;
     for (uint64_t q = 0; q < n_kmers && r.ok; ++q)
     {
@@ -397,7 +429,11 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
         const uint64_t n = r.get<uint64_t>();
         d->offsets[q] = e;
         if (!r.ok || e + n > n_entries) { r.ok = false; break; }
-        for (uint64_t i = 0; i < n; ++i, ++e) { d->branch[e] = r.get<uint32_t>(); d->score[e] = r.get<float>(); }
+        for (uint64_t i = 0; i < n; ++i, ++e)
+        {
+            d->branch[e] = r.get<uint32_t>(); d->score[e] = r.get<float>();
+            if (with_pos) d->position[e] = r.get<uint16_t>();
+        }
     }
     d->offsets[n_kmers] = e;
     fclose(f);
@@ -414,6 +450,7 @@ int ipkhost_read_ipk(const char* path, ipkhost_db_file** out, ipkhost_db* view)
     view->branch = d->branch.data(); view->score = d->score.data();
     view->counts = nullptr;
     view->branch16 = nullptr;
+    view->position = with_pos ? d->position.data() : nullptr;
     *out = d;
     return IPKHOST_OK;
 }

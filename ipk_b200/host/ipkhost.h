@@ -87,6 +87,8 @@ typedef struct ipkhost_db
     const uint32_t* branch;                    /* [n_entries], or NULL when branch16 is set */
     const float* score;                        /* [n_entries] */
     const uint16_t* branch16;                  /* NULL, or the branch ids as 16-bit values (ipkgpu's IPKGPU_RESULT_BRANCH16) */
+    const uint32_t* position;                  /* NULL, or [n_entries] alignment positions of a KEEP_POSITIONS build (ipk-aa-pos): entries
+                                                * are then written as { u32 branch; f32 score; u16 position } (pos_type; UNVERIFIED(i2l)) */
 } ipkhost_db;
 
 int  ipkhost_write_ipk(const char* path, const ipkhost_db* db);                 /* all cores */

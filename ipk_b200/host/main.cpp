@@ -53,7 +53,7 @@ namespace
         float boundary_band = 1e-5f;
         std::vector<int> devices;          // --devices 0,1,...: one rank per device, the multi-GPU build of include/ipkgpu.h
         int ghosts = 0;                    // 0 both, 1 inner only, 2 outer only
-        bool dump = false, use_unrooted = false, ar_only = false, merge_branches = false;
+        bool dump = false, use_unrooted = false, ar_only = false, merge_branches = false, keep_positions = false;
     };
 
     [[noreturn]] void usage(const char* why)
@@ -75,7 +75,7 @@ namespace
             std::string self = argc ? argv[0] : "";
             const size_t slash = self.find_last_of('/');
             if (slash != std::string::npos) self = self.substr(slash + 1);
-            if (self.find("-pos") != std::string::npos) { fprintf(stderr, "ipk-b200: --keep-positions builds are not supported\n"); exit(1); }
+            o.keep_positions = self.find("-pos") != std::string::npos;       // ipk-aa-pos: the KEEP_POSITIONS binary (ipk/CMakeLists.txt; ipk.py:275-283)
             o.states = self.find("aa") != std::string::npos ? "aa" : "dna";
         }
         auto need = [&](int& i) -> const char* { if (i + 1 >= argc) usage((std::string("missing value for ") + argv[i]).c_str()); return argv[++i]; };
@@ -98,6 +98,7 @@ namespace
             else if (a == "--use-unrooted") o.use_unrooted = true;
             else if (a == "--ar-only") o.ar_only = true;
             else if (a == "--merge-branches") o.merge_branches = true;
+            else if (a == "--keep-positions") o.keep_positions = true;
             else if (a == "--node-count") o.node_count = uint32_t(atoll(need(i)));
             else if (a == "-w" || a == "--workdir") o.workdir = need(i);
             else if (a == "-o" || a == "--output") o.output = need(i);
@@ -146,7 +147,9 @@ namespace
         }
         else if (o.ar_probs.empty() || o.node_map.empty()) usage("--ar-probs and --node-map go together");
         // main.cpp:31-37 (check_parameters): ipk-dna / ipk-aa refuse it with exactly this message; only the KEEP_POSITIONS binary takes it
-        if (o.merge_branches) { fprintf(stderr, "Exception: --merge-branches is only supported for IPK compiled with the KEEP_POSITIONS flag.\n"); exit(1); }
+        if (o.merge_branches && !o.keep_positions) { fprintf(stderr, "Exception: --merge-branches is only supported for IPK compiled with the KEEP_POSITIONS flag.\n"); exit(1); }
+        // (with positions the reference accepts the flag and then never reads it: db_builder.cpp stores _merge_branches and that is all)
+        if (o.keep_positions && o.devices.size() > 1) { fprintf(stderr, "Exception: a KEEP_POSITIONS build runs on one device\n"); exit(1); }
         if (o.output.empty()) o.output = o.workdir + "/DB.ipk";         // command_line.cpp:259-263
         return o;
     }
@@ -460,6 +463,7 @@ int main(int argc, char** argv)
         in.total_num_groups = node_count;
         in.filter = o.filter;
         ipkgpu_result res;
+        if (o.keep_positions) ipkgpu_set_keep_positions(ctx, 1);
         if (ipkgpu_build(ctx, &in, IPKGPU_RESULT_HOST_INDEXED | IPKGPU_RESULT_BRANCH16, &res) != IPKGPU_OK)
         {
             const std::string msg = ipkgpu_last_error(ctx);
@@ -475,6 +479,12 @@ int main(int argc, char** argv)
         ipkhost_db db = header;
         db.n_kmers = res.n_kmers; db.n_entries = res.n_entries;
         db.keys = res.keys; db.fv = res.fv; db.offsets = res.offsets; db.counts = res.counts; db.branch = res.branch; db.branch16 = res.branch16; db.score = res.score;
+        if (o.keep_positions)
+        {
+            int32_t pos_on_device = 0;
+            ipkgpu_result_positions(ctx, &db.position, &pos_on_device);
+            if (res.n_entries && (!db.position || pos_on_device)) throw std::runtime_error("the build kept no positions");
+        }
         if (ipkhost_write_ipk_mt(o.output.c_str(), &db, o.threads) != IPKHOST_OK) throw std::runtime_error("cannot write " + o.output);
         fprintf(stderr, "Wrote %s in %.3f s %s\n", o.output.c_str(), seconds_since(t0), layout_note);
         if (o.dump)

@@ -18,7 +18,7 @@ class HostDb(C.Structure):
                 ("kmer_size", C.c_uint64), ("omega", C.c_float), ("n_kmers", C.c_uint64), ("n_entries", C.c_uint64),
                 ("keys", C.POINTER(C.c_uint64)), ("fv", C.POINTER(C.c_float)), ("offsets", C.POINTER(C.c_uint64)),
                 ("counts", C.POINTER(C.c_uint32)), ("branch", C.POINTER(C.c_uint32)), ("score", C.POINTER(C.c_float)),
-                ("branch16", C.POINTER(C.c_uint16))]
+                ("branch16", C.POINTER(C.c_uint16)), ("position", C.POINTER(C.c_uint32))]
 
 
 _lib = None
@@ -124,8 +124,9 @@ def plan(newick: str, ar_tree: str | None = None, ghosts: str = "both", use_unro
 
 
 def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega: float, sequence_type: str = "DNA",
-              tree: str = "", index_num_nodes=None, index_len=None, threads: int = 0) -> None:
+              tree: str = "", index_num_nodes=None, index_len=None, threads: int = 0, position=None) -> None:
     keys = np.ascontiguousarray(keys, np.uint64); fv = np.ascontiguousarray(fv, np.float32)
+    pos = np.ascontiguousarray(position, np.uint32) if position is not None else None
     offsets = np.ascontiguousarray(offsets, np.uint64)
     branch = np.ascontiguousarray(branch, np.uint32); score = np.ascontiguousarray(score, np.float32)
     inn = np.ascontiguousarray(index_num_nodes if index_num_nodes is not None else [], np.uint64)
@@ -134,7 +135,7 @@ def write_ipk(path: str, keys, fv, offsets, branch, score, kmer_size: int, omega
                 il.ctypes.data_as(C.POINTER(C.c_double)), kmer_size, omega, len(keys), len(branch),
                 keys.ctypes.data_as(C.POINTER(C.c_uint64)), fv.ctypes.data_as(C.POINTER(C.c_float)),
                 offsets.ctypes.data_as(C.POINTER(C.c_uint64)), None, branch.ctypes.data_as(C.POINTER(C.c_uint32)),
-                score.ctypes.data_as(C.POINTER(C.c_float)), None)
+                score.ctypes.data_as(C.POINTER(C.c_float)), None, pos.ctypes.data_as(C.POINTER(C.c_uint32)) if pos is not None else None)
     rc = load().ipkhost_write_ipk_mt(path.encode(), C.byref(db), threads)
     if rc != 0:
         raise HostError(rc, "cannot write " + path)
@@ -153,7 +154,7 @@ def read_ipk(path: str) -> dict:
         return dict(sequence_type=v.sequence_type.decode(), tree=v.tree.decode(), kmer_size=int(v.kmer_size), omega=float(v.omega),
                     index_num_nodes=arr(v.index_num_nodes, ni), index_len=arr(v.index_subtree_branch_length, ni),
                     keys=arr(v.keys, nk), fv=arr(v.fv, nk), offsets=np.ctypeslib.as_array(v.offsets, (nk + 1,)).copy(),
-                    branch=arr(v.branch, ne), score=arr(v.score, ne))
+                    branch=arr(v.branch, ne), score=arr(v.score, ne), position=arr(v.position, ne) if v.position else None)
     finally:
         lib.ipkhost_free_ipk(h)
 
@@ -172,7 +173,7 @@ def _host_db(d, keep: list) -> HostDb:
     ptr = lambda a, t: a.ctypes.data_as(C.POINTER(t)) if a is not None else None
     n_entries = len(score) if score is not None else 0
     return HostDb(b"", b"", 0, None, None, 0, 0.0, len(keys), n_entries, ptr(keys, C.c_uint64), ptr(fv, C.c_float), ptr(offsets, C.c_uint64),
-                  ptr(counts, C.c_uint32), ptr(branch, C.c_uint32), ptr(score, C.c_float), ptr(b16, C.c_uint16))
+                  ptr(counts, C.c_uint32), ptr(branch, C.c_uint32), ptr(score, C.c_float), ptr(b16, C.c_uint16), None)
 
 
 def merge_order(shards, threads: int = 0):
@@ -217,7 +218,7 @@ def write_ipk_sharded(path: str, shards, kmer_size: int, omega: float, sequence_
     inn = np.ascontiguousarray(index_num_nodes if index_num_nodes is not None else [], np.uint64)
     il = np.ascontiguousarray(index_len if index_len is not None else [], np.float64)
     header = HostDb(sequence_type.encode(), tree.encode(), len(inn), inn.ctypes.data_as(C.POINTER(C.c_uint64)), il.ctypes.data_as(C.POINTER(C.c_double)),
-                    kmer_size, omega, 0, 0, None, None, None, None, None, None, None)
+                    kmer_size, omega, 0, 0, None, None, None, None, None, None, None, None)
     rc = load().ipkhost_write_ipk_sharded(path.encode(), C.byref(header), len(shards), views, sh.ctypes.data, ix.ctypes.data, threads)
     if rc != 0:
         raise HostError(rc, "cannot write " + path)

@@ -202,6 +202,75 @@ def test_boundary_list_matches_oracle(ctx, k):
     assert ctx.result_digest(lthr, band)["n_boundary_above"] >= int(absent.sum()) - n      # (a lower bound; just exercises the counter)
 
 
+def _positions_oracle(logp, nb, sigma, bits, k, lthr):
+    """ipk::put under KEEP_POSITIONS (ipk/src/branch_group.cpp:72-86; db_builder.cpp:642-690) restated over the oracle's
+    per-window emission: a group's ghost nodes one after the other, windows ascending, `if (it->second.score < kmer.score)`
+    -- the FIRST window that reaches the maximum keeps its position.  -> {(key, branch): (score bits, position)}"""
+    out = {}
+    order = []
+    for b in nb:
+        if int(b) not in order:
+            order.append(int(b))
+    for b in order:
+        best = {}
+        for n in np.where(nb == b)[0]:
+            w, key, sc = O.enumerate_node(logp[n], sigma, bits, k, lthr, cap=1 << 20)
+            o = np.argsort(w, kind="stable")
+            for wi, ki, si in zip(w[o], key[o], sc[o]):
+                cur = best.get(int(ki))
+                if cur is None or cur[0] < si:
+                    best[int(ki)] = (np.float32(si), int(wi))
+        for ki, (si, wi) in best.items():
+            out[(ki, b)] = (int(np.float32(si).view(np.uint32)), wi)
+    return out
+
+
+@pytest.mark.parametrize("case", ["dna_ties", "aa"])
+@pytest.mark.parametrize("indexed", [False, True])
+def test_keep_positions_build(case, indexed):
+    """ipkgpu_set_keep_positions (the reference's ipk-aa-pos variant): same database as the plain build, and every entry's
+    position is the first window (in processing order) that reached its score"""
+    from ipk_b200 import capi as libipkgpu
+    if case == "dna_ties":
+        sigma, bits, k, omega, W, n_taxa = 4, 2, 5, 1.5, 90, 5
+        rng = np.random.default_rng(12)
+        n_nodes = 2 * (2 * n_taxa - 2)
+        logp = _threshold_columns(rng, n_nodes, W, k, omega)        # runs of identical column values: equal scores at several windows
+        nb = np.repeat(np.arange(n_nodes // 2, dtype=np.uint32), 2)
+        nb[[2, 3]] = nb[[3, 2]]                                      # ... and interleaved groups
+    else:
+        sigma, bits, k, omega, W, n_taxa = 20, 5, 3, 1.5, 50, 4
+        logp, nb = _synth(n_taxa, W, sigma)
+    thr, lthr = _thr(omega, sigma, k)
+    T = 2 * n_taxa - 1
+    want_db = O.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0, 4)
+    want = _positions_oracle(logp, nb, sigma, bits, k, lthr)
+    assert len(want) == want_db.n_entries
+    with libipkgpu.Context(0) as c:
+        c.set_keep_positions(True)
+        inp, keep = libipkgpu.make_input(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+        res = c.build_raw(inp, result_on_device=False, indexed=indexed)
+        pos = c.result_positions(int(res.n_entries))
+        got = libipkgpu.Context.to_db(res)
+        assert pos is not None and len(pos) == got.n_entries
+        if indexed:      # to_db gathered the entries into filter-value order; do the same to the positions
+            nk = int(res.n_kmers)
+            start = libipkgpu._view(res.offsets, nk, np.uint64).astype(np.int64)
+            cnt = libipkgpu._view(res.counts, nk, np.uint32).astype(np.int64)
+            pos = pos[np.repeat(start - got.offsets[:-1].astype(np.int64), cnt) + np.arange(int(cnt.sum()))]
+        assert_db_equal(got, want_db)
+        keys = np.repeat(got.keys, np.diff(got.offsets.astype(np.int64)))
+        have = {(int(a), int(b)): (int(s), int(p)) for a, b, s, p in zip(keys, got.branch, got.score.view(np.uint32), pos)}
+        assert have == want
+        if case == "dna_ties":
+            # the fixture does contain ties that a "last maximum" or "any maximum" rule would resolve differently
+            assert sum(1 for v in want.values() if v[1] > 0) > 10
+        c.set_keep_positions(False)
+        plain = c.build(logp, nb, W, sigma, bits, k, lthr, thr, T, 0)
+        assert c.result_positions(plain.n_entries) is None
+        assert_db_equal(plain, want_db)
+
+
 def test_build_interleaved_groups_and_singletons(ctx):
     """ghost nodes of one branch need not be adjacent; a branch may have one ghost only (--inner-only/--outer-only)"""
     logp, nb = _synth(10, 150, 4)

@@ -189,6 +189,29 @@ def test_db_tools_diff_and_dump(tmp_path):
     assert r.returncode == 1 and "Exception" in r.stderr
 
 
+def test_ipk_round_trip_with_positions(tmp_path):
+    """KEEP_POSITIONS databases (ipk-aa-pos): entries are {branch, score, position}; the reader tells the two layouts apart by
+    the length of the file"""
+    from ipk_b200 import hostlib
+    rng = np.random.default_rng(19)
+    nk = 3000
+    cnt = rng.integers(1, 7, nk)
+    offsets = np.concatenate(([0], np.cumsum(cnt))).astype(np.uint64)
+    ne = int(offsets[-1])
+    keys = rng.permutation(1 << 15)[:nk].astype(np.uint64)
+    fv = np.sort(rng.random(nk).astype(np.float32))
+    branch = rng.integers(0, 300, ne).astype(np.uint32)
+    score = (-5 * rng.random(ne)).astype(np.float32)
+    pos = rng.integers(0, 800, ne).astype(np.uint32)
+    a, b = str(tmp_path / "pos.ipk"), str(tmp_path / "plain.ipk")
+    hostlib.write_ipk(a, keys, fv, offsets, branch, score, 6, 1.5, "Proteins", "(a:1,b:2);", position=pos, threads=3)
+    hostlib.write_ipk(b, keys, fv, offsets, branch, score, 6, 1.5, "Proteins", "(a:1,b:2);")
+    assert os.path.getsize(a) - os.path.getsize(b) == 2 * ne
+    d = hostlib.read_ipk(a)
+    assert np.array_equal(d["position"], pos) and np.array_equal(d["branch"], branch) and np.array_equal(d["score"], score)
+    assert hostlib.read_ipk(b)["position"] is None
+
+
 def test_ipk_writer_threads_agree(tmp_path):
     """the multi-threaded writer (runs of k-mers at prefix-summed offsets) produces the bytes of the single-threaded one"""
     from ipk_b200 import hostlib
@@ -494,3 +517,33 @@ def test_exchange_plan_arithmetic():
             assert spans[0][0] == 0 and spans[-1][1] == load[o] and all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             start = plans[o][2]
             assert start[256] == load[o] and all(int(start[d + 1]) - int(start[d]) == (int(total[d]) if owner[d] == o else 0) for d in range(256))
+
+
+@pytest.mark.gpu
+def test_ipk_aa_pos_executable(tmp_path):
+    """`ipk-aa-pos` (the KEEP_POSITIONS binary of the reference, picked by name): AR file + node map -> DB.ipk whose entries carry
+    the position of the first window that reached their score (branch_group.cpp:72-86)"""
+    import oraclelib as O
+    from test_gpu_parity import _positions_oracle
+    from ipk_b200 import hostlib, capi, synth
+    n_taxa, W, sigma, k, omega = 4, 50, 20, 3, 1.5
+    logp, nb = synth.posteriors(n_taxa, W, sigma, seed=5)
+    order = "RHKDESTNQCGPAILMFWYV"
+    probs = np.power(10.0, logp.astype(np.float64))[:, :, [order.index(c) for c in AA_RAXML]]
+    labels = [f"Node{i + 1}" for i in range(len(nb))]
+    tsv, nmap, out = str(tmp_path / "ar.raxml.ancestralProbs"), str(tmp_path / "node_map.tsv"), str(tmp_path / "DB.ipk")
+    write_tsv(tsv, probs, labels, sigma)
+    with open(nmap, "w") as f:
+        f.write("".join(f"{lab}\t{int(b)}\n" for lab, b in zip(labels, nb)))
+    exe = os.path.join(os.path.dirname(hostlib.EXE_PATH), "ipk-aa-pos")
+    r = subprocess.run([exe, "--ar-probs", tsv, "--node-map", nmap, "-k", str(k), "--omega", str(omega), "--mif0", "-o", out,
+                        "--node-count", str(2 * n_taxa - 1), "--merge-branches"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    d = hostlib.read_ipk(out)
+    assert d["sequence_type"] == "Proteins" and d["position"] is not None
+    _, parsed = hostlib.read_ar(tsv, sigma, labels)
+    thr, lthr = capi.score_threshold(omega, sigma, k)
+    want = _positions_oracle(parsed, nb, sigma, 5, k, lthr)
+    keys = np.repeat(d["keys"], np.diff(d["offsets"].astype(np.int64)))
+    have = {(int(a), int(b)): (int(s), int(p)) for a, b, s, p in zip(keys, d["branch"], d["score"].view(np.uint32), d["position"])}
+    assert have == want and len(want) > 100
