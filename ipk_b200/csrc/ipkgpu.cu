@@ -911,7 +911,7 @@ namespace
         // commits of the join kernel recorded as runs of one branch group each: read in group order by the first pass of the
         // packed sort they spare it every pass on the group bits (packed_sort.cuh)
         static const bool runs_off = getenv("IPKGPU_RUNS") && atoi(getenv("IPKGPU_RUNS")) == 0;
-        L.want_runs = !runs_off && !ordered && (raw || want_csr) && key_bits >= 8 && key_bits + (raw ? group_bits : all_bits) - 8 <= 32;
+        L.want_runs = !runs_off && !ordered && (raw || want_csr);
         ctx->runs_n = 0;
         ctx->runs_valid = L.want_runs;
         uint64_t side_cap = 0;
@@ -1037,8 +1037,18 @@ namespace
                 continue;
             }
             uint32_t passes = 0;
+            bool in_b;
+            if (single && !use_side && first_valid && !raw && ctx->runs_valid && ctx->runs_n > 0 && b.n <= 0xffffffffull && bbits > 0)
+            {
+                // records that do not pack: ONE copy of the emission into group order through the run index (packed_sort.cuh), then a
+                // stable sort on the k-mer bits alone
+                ps_gather_in_group_order(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(), b.n, bbits);
+                in_b = !radix_sort_pairs(ctx, ctx->keys_b.as<uint64_t>(), ctx->vals_b.as<uint32_t>(), ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(),
+                                         b.n, key_bits, ctx->hist, ctx->scan_tmp, &passes, bbits);
+            }
+            else
             // ordered main stream: stable sort on the k-mer bits only (bit_begin = width of the group field)
-            const bool in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
+            in_b = radix_sort_pairs(ctx, ctx->keys_a.as<uint64_t>(), ctx->vals_a.as<uint32_t>(), ctx->keys_b.as<uint64_t>(),
                                                ctx->vals_b.as<uint32_t>(), b.n, use_side ? key_bits : key_bits + bbits, ctx->hist, ctx->scan_tmp,
                                                &passes, use_side ? bbits : 0);
             o.sort_passes += passes;

@@ -678,6 +678,43 @@ namespace ipkgpu
         return ps_runs{ lstart, off, tile_first, nr };
     }
 
+    /// The emission copied into branch-group order through the run index (tiles of PS_MSD_TILE logical positions): for
+    /// records that do not pack (amino acids) the pair sort then only has the k-mer bits to sort, stably -- one 24-byte copy
+    /// instead of the passes on the group bits.
+    __global__ void __launch_bounds__(PS_THREADS) ps_gather_runs(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint64_t n,
+                                                                 const __grid_constant__ ps_runs R)
+    {
+        __shared__ uint32_t s_rs[PS_RUN_WIN + 1], s_ro[PS_RUN_WIN];
+        const uint32_t tile = blockIdx.x, tid = threadIdx.x;
+        const uint64_t tile_base = uint64_t(tile) * PS_MSD_TILE;
+        const uint32_t tile_n = uint32_t(min(uint64_t(PS_MSD_TILE), n - tile_base));
+        const uint32_t first = R.tile_first[tile];
+        if (tid <= uint32_t(PS_RUN_WIN))
+        {
+            const uint32_t r = first + tid;
+            s_rs[tid] = r <= R.n_runs ? R.lstart[r] : 0xffffffffu;
+            if (tid < uint32_t(PS_RUN_WIN)) s_ro[tid] = r < R.n_runs ? R.off[r] : 0u;
+        }
+        __syncthreads();
+        ps_run_cursor c;
+        c.init(s_rs, s_ro);
+        for (uint32_t li = tid; li < tile_n; li += PS_THREADS)
+        {
+            const uint32_t L = uint32_t(tile_base) + li;
+            const uint32_t p = c.map(L, s_rs, s_ro, R, first);
+            keys_out[L] = keys_in[p];
+            vals_out[L] = vals_in[p];
+        }
+    }
+
+    inline void ps_gather_in_group_order(ipkgpu_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t n, uint32_t group_bits)
+    {
+        const ps_runs Rn = ps_order_runs(ctx, n, group_bits);
+        const uint32_t n_tiles = uint32_t(div_up<uint64_t>(n, PS_MSD_TILE));
+        IPK_LAUNCH(ctx, "ps_gather_runs", n * 24, ps_gather_runs<<<n_tiles, PS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, n, Rn));
+    }
+
     /// top-byte histogram of the composite keys -> hist[0..256) (device, in ctx->hist) ; not yet scanned
     inline void ps_top_histogram(ipkgpu_ctx* ctx, const uint64_t* keys, uint64_t n, uint32_t low_bits)
     {
