@@ -292,7 +292,9 @@ namespace
             for (auto& p : ctx->levels) v.push_back({ p.first, p.second });
             return v;
         }
-        if (in->sigma <= 4) return { { 3072, 128 }, { 12288, 128 }, { 0, 128 }, { 0, 16 }, { 0, 1 } };
+        // (the first retry takes the 1.3 % of cfg3's tiles whose lists overflow 3072 elements: with a 12288-element pool they ran at
+        // 2 CTAs/SM for 2.6 ms, with 4608 at 4 CTAs/SM for 1.5 ms -- profiles/r03w_sweep_levels.txt)
+        if (in->sigma <= 4) return { { 3072, 128 }, { 4608, 128 }, { 12288, 128 }, { 0, 128 }, { 0, 16 }, { 0, 1 } };
         return { { 20000, 128 }, { 0, 128 }, { 0, 16 }, { 0, 1 } };
     }
 
@@ -393,7 +395,8 @@ namespace
                 if (smem > 227 * 1024) fail(IPKGPU_EINVAL, "join kernel needs %zu bytes of shared memory", smem);
                 const uint64_t lvl_in_bytes = level == 0 ? in_bytes : lvl_grid * uint64_t(width + in->k) * (in->sigma + 1) * 4;
                 // (the retries of deferred items are their own launch class in the kernel profile: a few thousand CTAs against half a million)
-                const char* const kname = level == 0 ? "k2_join" : "k2_join_retry";
+                static const char* const level_names[] = { "k2_join", "k2_join_retry1", "k2_join_retry2", "k2_join_retry3", "k2_join_retry4" };
+                const char* const kname = level_names[std::min<size_t>(level, 4)];
                 if (L.debug)
                 {
                     IPK_CUDA(cudaFuncSetAttribute(k2_join<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
