@@ -264,6 +264,25 @@ int  ipkgpu_stage2(ipkgpu_ctx* ctx, uint64_t* d_keys, float* d_scores, uint64_t 
                    float threshold, uint32_t total_num_groups, int32_t filter, int32_t chunks_group_ordered,
                    int result_on_device, ipkgpu_result* out);
 
+/* ---- allocation-free entry point ---------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * ipkgpu_best_prefix_noalloc = the two kernels of ipkgpu_best_prefix (column maxima, then the sequential fp32 prefix
+ * sums of matrix::preprocess) on DEVICE arrays of the caller: d_logp[n_nodes][width][sigma] in, d_B[n_nodes][width+1]
+ * out, both on `device`, work ordered on `stream` (a cudaStream_t of that device, NULL = its default stream).  The call
+ * returns once the kernels are queued: synchronize the stream before reading d_B.  Same bits as ipkgpu_best_prefix.
+ * It needs no context and calls no cudaMalloc / cudaFree / allocating routine: the column maxima between the two
+ * kernels live in a file-scope __device__ array of IPKGPU_NOALLOC_MAX_COLUMNS floats (16 MiB) that every GPU using
+ * this library holds until the process exits.  n_nodes * width > IPKGPU_NOALLOC_MAX_COLUMNS is IPKGPU_EINVAL.
+ * Every call on a device shares that array (each call overwrites the part it reads, nothing needs clearing): calls that
+ * overlap on one GPU -- two streams, two threads -- race; order them on one stream.  With sigma == 4, d_logp must be
+ * 16-byte aligned.  The message of the calling thread's last failure: ipkgpu_noalloc_last_error(). */
+#define IPKGPU_NOALLOC_MAX_COLUMNS (1u << 22)
+int  ipkgpu_best_prefix_noalloc(int device, void* stream, const float* d_logp, uint32_t n_nodes, uint32_t width, uint32_t sigma,
+                                float* d_B);
+const char* ipkgpu_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -184,6 +184,10 @@ def load() -> C.CDLL:
     lib.ipkgpu_result_arena_layout.restype = C.c_size_t
     lib.ipkgpu_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, P(C.c_float), P(C.c_float)]
     lib.ipkgpu_score_threshold.restype = None
+    lib.ipkgpu_best_prefix_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+    lib.ipkgpu_best_prefix_noalloc.restype = C.c_int
+    lib.ipkgpu_noalloc_last_error.argtypes = []
+    lib.ipkgpu_noalloc_last_error.restype = C.c_char_p
     _lib = lib
     return lib
 
@@ -193,6 +197,17 @@ def result_arena_layout(cap_entries: int, cap_kmers: int) -> tuple[int, list[int
     off = (C.c_size_t * 6)()
     total = load().ipkgpu_result_arena_layout(cap_entries, cap_kmers, off)
     return int(total), [int(o) for o in off]
+
+
+NOALLOC_MAX_COLUMNS = 1 << 22          # IPKGPU_NOALLOC_MAX_COLUMNS
+
+
+def best_prefix_noalloc(device: int, stream: int, d_logp: int, n_nodes: int, width: int, sigma: int, d_B: int) -> None:
+    """ipkgpu_best_prefix_noalloc: DEVICE addresses in and out, work queued on `stream` (0 = default stream); allocates nothing"""
+    lib = load()
+    rc = lib.ipkgpu_best_prefix_noalloc(device, stream or None, d_logp or None, n_nodes, width, sigma, d_B or None)
+    if rc != 0:
+        raise IpkGpuError(rc, (lib.ipkgpu_noalloc_last_error() or b"").decode())
 
 
 def exchange_plan(n_parts: int, rank: int, counts: np.ndarray):

@@ -2246,3 +2246,117 @@ int ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_sta
 }
 
 }   // extern "C"
+
+// ---- allocation-free entry point (include/ipkgpu.h: no reference counterpart) ---------
+//
+// The column maxima between k1a_colmax and k1b_prefix live in a file-scope device array instead of the context's workspace.
+// In host code `g_noalloc_colmax` is only the host-side stand-in of the symbol: the device address comes from
+// cudaGetSymbolAddress, taken once per device with that device current, and only that pointer is given to the kernels.
+static __device__ __align__(256) float g_noalloc_colmax[IPKGPU_NOALLOC_MAX_COLUMNS];
+
+namespace
+{
+    constexpr int NOALLOC_MAX_DEVICES = 64;
+    struct noalloc_device { float* colmax = nullptr; int num_sms = 0; bool ready = false; };
+    noalloc_device g_noalloc_dev[NOALLOC_MAX_DEVICES];
+    std::mutex g_noalloc_mutex;
+    thread_local char g_noalloc_error[256] = "";
+
+    int noalloc_fail(int code, const char* fmt, ...)
+    {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(g_noalloc_error, sizeof g_noalloc_error, fmt, ap);
+        va_end(ap);
+        return code;
+    }
+
+    /// current device for the scope of one call; the caller's device is put back on the way out
+    struct noalloc_device_scope
+    {
+        int prev = -1;
+        bool switched = false;
+        cudaError_t enter(int device)
+        {
+            cudaError_t e = cudaGetDevice(&prev);
+            if (e != cudaSuccess) return e;
+            if (prev != device) { e = cudaSetDevice(device); switched = e == cudaSuccess; }
+            return e;
+        }
+        ~noalloc_device_scope() { if (switched) cudaSetDevice(prev); }
+    };
+
+    /// set-up of one device (its device current): address of the scratch symbol there, SM count for the grid
+    int noalloc_setup(int device, noalloc_device** out)
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        noalloc_device& d = g_noalloc_dev[device];
+        if (!d.ready)
+        {
+            cudaDeviceProp prop;
+            cudaError_t e = cudaGetDeviceProperties(&prop, device);
+            if (e != cudaSuccess) { cudaGetLastError(); return noalloc_fail(IPKGPU_ECUDA, "cudaGetDeviceProperties(%d): %s", device, cudaGetErrorString(e)); }
+            if (prop.major != 10) return noalloc_fail(IPKGPU_ENODEV, "device %d is sm_%d%d, not sm_100 (this library is built for sm_100a only)", device, prop.major, prop.minor);
+            float* p = nullptr;
+            e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_colmax);
+            if (e != cudaSuccess || !p) { cudaGetLastError(); return noalloc_fail(IPKGPU_ECUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", device, cudaGetErrorString(e)); }
+            d.colmax = p;
+            d.num_sms = prop.multiProcessorCount;
+            d.ready = true;
+        }
+        *out = &d;
+        return IPKGPU_OK;
+    }
+
+    bool noalloc_on_device(const void* p, int device)
+    {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+        return (a.type == cudaMemoryTypeDevice && a.device == device) || a.type == cudaMemoryTypeManaged;
+    }
+}
+
+extern "C" {
+
+const char* ipkgpu_noalloc_last_error(void) { return g_noalloc_error; }
+
+int ipkgpu_best_prefix_noalloc(int device, void* stream, const float* d_logp, uint32_t n_nodes, uint32_t width, uint32_t sigma, float* d_B)
+{
+    using namespace ipkgpu;
+    g_noalloc_error[0] = 0;
+    if (sigma < 2 || sigma > 32) return noalloc_fail(IPKGPU_EINVAL, "sigma = %u outside [2, 32]", sigma);
+    const uint64_t cols = uint64_t(n_nodes) * width;
+    if (cols > IPKGPU_NOALLOC_MAX_COLUMNS)
+        return noalloc_fail(IPKGPU_EINVAL, "n_nodes * width = %llu exceeds the static scratch of %u columns (IPKGPU_NOALLOC_MAX_COLUMNS); use ipkgpu_best_prefix",
+                            (unsigned long long)cols, IPKGPU_NOALLOC_MAX_COLUMNS);
+    if (n_nodes == 0) return IPKGPU_OK;
+    if (!d_B || (cols && !d_logp)) return noalloc_fail(IPKGPU_EINVAL, "d_logp / d_B is null");
+    if (sigma == 4 && (reinterpret_cast<uintptr_t>(d_logp) & 15) != 0) return noalloc_fail(IPKGPU_EINVAL, "d_logp must be 16-byte aligned for 4 states");
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) { cudaGetLastError(); return noalloc_fail(IPKGPU_ENODEV, "no CUDA device: %s", e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"); }
+    if (device < 0 || device >= n_dev || device >= NOALLOC_MAX_DEVICES) return noalloc_fail(IPKGPU_EINVAL, "device ordinal %d out of range", device);
+
+    noalloc_device_scope scope;
+    e = scope.enter(device);
+    if (e != cudaSuccess) { cudaGetLastError(); return noalloc_fail(IPKGPU_ECUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e)); }
+    noalloc_device* dev = nullptr;
+    if (const int rc = noalloc_setup(device, &dev)) return rc;
+    if ((cols && !noalloc_on_device(d_logp, device)) || !noalloc_on_device(d_B, device))
+        return noalloc_fail(IPKGPU_EINVAL, "d_logp / d_B must be device memory of device %d", device);
+
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (cols)
+    {
+        const uint32_t grid = uint32_t(std::min<uint64_t>(div_up<uint64_t>(cols, 256), uint64_t(dev->num_sms) * 16));
+        k1a_colmax<<<grid, 256, 0, s>>>(d_logp, dev->colmax, n_nodes, width, sigma);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return noalloc_fail(IPKGPU_ECUDA, "k1a_colmax launch: %s", cudaGetErrorString(e));
+    }
+    k1b_prefix<<<div_up<uint32_t>(n_nodes, 64), 64, 0, s>>>(dev->colmax, d_B, n_nodes, width);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return noalloc_fail(IPKGPU_ECUDA, "k1b_prefix launch: %s", cudaGetErrorString(e));
+    return IPKGPU_OK;
+}
+
+}   // extern "C"
