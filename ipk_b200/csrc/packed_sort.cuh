@@ -37,6 +37,15 @@ namespace ipkgpu
 #define IPK_LSD_ITEMS 12
 #define IPK_LSD_MINB 3
 #endif
+#ifndef IPK_PS_RANKB
+#define IPK_PS_RANKB 12         // items whose matches are issued back to back (r04f: 0 / 4 / 6 / 12 -> LSD passes 26.0 / 24.7 / 24.7 / 23.9 ms)
+#endif
+#ifndef IPK_PS_PREFETCH
+#define IPK_PS_PREFETCH 0          // tiles ahead whose records a tile asks the L2 for (0 = off; r04g: 512 / 1024 / 2048 ahead made the LSD passes 0.7 - 1.6 ms SLOWER)
+#endif
+#ifndef IPK_MP_PREFETCH
+#define IPK_MP_PREFETCH 1024     // r04g: merge 11.54 ms without, 10.76 / 11.07 / 11.48 with 1024 / 2048 / 4096 tiles ahead
+#endif
 #ifndef IPK_PS_POLL
 #define IPK_PS_POLL 4
 #endif
@@ -45,6 +54,17 @@ namespace ipkgpu
 #endif
     constexpr int PS_LSD_ITEMS = IPK_LSD_ITEMS, PS_LSD_MINB = IPK_LSD_MINB, PS_LSD_TILE = PS_THREADS * PS_LSD_ITEMS;
     constexpr int PS_POLL = IPK_PS_POLL;
+
+    /// asks the L2 for records [first, first + count) of `base` (one bulk prefetch; SASS: UBLKPF): a tile that starts a tile
+    /// lifetime later then loads from L2 instead of waiting for DRAM
+    __device__ __forceinline__ void ps_prefetch_l2(const uint64_t* base, uint64_t first, uint64_t end, uint32_t count)
+    {
+        if (first >= end) return;
+        const uint64_t lo = first & ~1ull;                                       // 16-byte aligned start
+        const uint64_t hi = min(end, first + count) & ~1ull;                    // whole 16-byte units only
+        if (hi <= lo) return;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + lo), "r"(uint32_t((hi - lo) * 8)) : "memory");
+    }
 
     /// bucket geometry of one segmented launch (kernel parameter, 2 KB)
     struct ps_table
@@ -109,29 +129,29 @@ namespace ipkgpu
         return lo;
     }
 
-    template<int THREADS, int ITEMS> constexpr size_t ps_smem_bytes(bool digits) { return size_t(THREADS / 32) * RS_RADIX * 4 + 2 * RS_RADIX * 4 + 64 + size_t(THREADS) * ITEMS * (digits ? 9 : 8); }
+    template<int THREADS, int ITEMS, int RADIX = RS_RADIX> constexpr size_t ps_smem_bytes(bool digits) { return size_t(THREADS / 32) * RADIX * 4 + 2 * RADIX * 4 + 64 + size_t(THREADS) * ITEMS * (digits ? 9 : 8); }
 
     // -----------------------------------------------------------------------------------------------------------------
     // Ranking core shared by the two sweeps: the tile's items in (warp, round, lane) order carry a digit each; afterwards
     // pos[i] = position of item i in the tile's digit-sorted order, dbase / goff as in rs_onesweep.
     // -----------------------------------------------------------------------------------------------------------------
-    template<int THREADS, int ITEMS>
+    template<int THREADS, int ITEMS, int RADIX>
     struct ps_smem_view
     {
         uint64_t* sk;                       // [TILE] staged records
-        uint32_t (*wh)[RS_RADIX];           // [WARPS][256]
-        uint32_t* dbase;                    // [256]
-        uint32_t* goff;                     // [256]
+        uint32_t (*wh)[RADIX];              // [WARPS][RADIX]
+        uint32_t* dbase;                    // [RADIX]
+        uint32_t* goff;                     // [RADIX]
         uint32_t* misc;                     // [16]
         uint8_t* sd;                        // [TILE] staged digits (MSD pass only)
         __device__ explicit ps_smem_view(unsigned char* raw)
         {
             constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
             sk = reinterpret_cast<uint64_t*>(raw);
-            wh = reinterpret_cast<uint32_t (*)[RS_RADIX]>(sk + TILE);
-            dbase = &wh[0][0] + WARPS * RS_RADIX;
-            goff = dbase + RS_RADIX;
-            misc = goff + RS_RADIX;
+            wh = reinterpret_cast<uint32_t (*)[RADIX]>(sk + TILE);
+            dbase = &wh[0][0] + WARPS * RADIX;
+            goff = dbase + RADIX;
+            misc = goff + RADIX;
             sd = reinterpret_cast<uint8_t*>(misc + 16);
         }
     };
@@ -139,7 +159,9 @@ namespace ipkgpu
     /// One pass over one tile.  MSD = true: (keys_in, vals_in) pairs -> packed records, digit = top byte of the composite key,
     /// destination per digit from D, tiles are plain runs of THREADS * ITEMS pairs.  MSD = false: packed -> packed, digit =
     /// byte `shift / 8` of the record, tiles cut at bucket boundaries (T), digit bases per bucket.
-    template<int THREADS, int ITEMS, bool MSD, int MINB, bool RUNS = false>
+    /// BITS = width of the digit (LSD passes of 4 .. 8 bits: everything that is per digit -- the counters' reset and scan,
+    /// the status words, the look-back -- shrinks with the radix, the per-record work does not).
+    template<int THREADS, int ITEMS, bool MSD, int MINB, bool RUNS = false, int BITS = 8>
     __global__ void __launch_bounds__(THREADS, MINB) ps_sweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                               uint64_t* __restrict__ out, const uint32_t* __restrict__ digit_base, uint64_t n,
                                                               uint32_t shift /* MSD: low_bits; else: bit of the record where the digit starts */,
@@ -149,9 +171,11 @@ namespace ipkgpu
                                                               const __grid_constant__ ps_runs R)
     {
         constexpr int WARPS = THREADS / 32, TILE = THREADS * ITEMS;
-        static_assert(THREADS >= RS_RADIX && THREADS % 32 == 0 && ITEMS % 4 == 0, "tile shape");
+        constexpr int RADIX = 1 << BITS, DWARPS = RADIX >= 32 ? RADIX / 32 : 1;        // DWARPS: warps that hold one digit per lane
+        constexpr uint32_t DMASK = RADIX - 1;
+        static_assert(THREADS >= RADIX && THREADS % 32 == 0 && ITEMS % 4 == 0 && BITS >= 1 && BITS <= 8 && (!MSD || BITS == 8), "tile shape");
         extern __shared__ __align__(16) unsigned char ps_smem[];
-        const ps_smem_view<THREADS, ITEMS> S(ps_smem);
+        const ps_smem_view<THREADS, ITEMS, RADIX> S(ps_smem);
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const unsigned full = 0xffffffffu;
         if (tid == 0)
@@ -160,7 +184,7 @@ namespace ipkgpu
             S.misc[15] = t;
             if (!MSD) S.misc[14] = ps_bucket_of_tile(T, t);
         }
-        for (int i = tid; i < WARPS * RS_RADIX; i += THREADS) (&S.wh[0][0])[i] = 0;
+        for (int i = tid; i < WARPS * RADIX; i += THREADS) (&S.wh[0][0])[i] = 0;
         __syncthreads();
         const uint32_t tile = S.misc[15];
         uint64_t tile_base;
@@ -183,6 +207,8 @@ namespace ipkgpu
             first_of_chain = lt == 0;
             chain_pos = lt;
             dbase_g = digit_base + size_t(b) * base_stride;
+            // (bucket boundaries shift the tiles ahead by less than a tile each: close enough for a prefetch)
+            if (IPK_PS_PREFETCH > 0 && tid == 32) ps_prefetch_l2(keys_in, tile_base + uint64_t(IPK_PS_PREFETCH) * TILE, T.start[T.d1], TILE);
         }
 
         uint64_t rec[ITEMS];
@@ -250,29 +276,44 @@ namespace ipkgpu
             {
                 const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
                 rec[i] = li < tile_n ? keys_in[tile_base + li] : 0ull;
-                dpk[i / 4] |= (uint32_t(rec[i] >> shift) & 0xffu) << (8 * (i & 3));
+                dpk[i / 4] |= (uint32_t(rec[i] >> shift) & DMASK) << (8 * (i & 3));
             }
         }
+        // The matches of a batch of items are issued back to back (MATCH has a long latency and does not depend on the
+        // counters); then, item by item, every lane reads its digit's warp counter and the lowest lane of each digit adds the
+        // digit's count to it (no leader election, no shuffle).
+        const unsigned lt_mask = (1u << lane) - 1;
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i)
+        for (int i0 = 0; i0 < ITEMS; i0 += IPK_PS_RANKB)
         {
-            const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
-            const bool valid = li < tile_n;
-            const uint32_t d = valid ? (dpk[i / 4] >> (8 * (i & 3))) & 0xffu : RS_RADIX;
-            const unsigned peers = __match_any_sync(full, d);
-            const int leader = __ffs(peers) - 1;
-            uint32_t old = 0;
-            if (lane == leader && valid)
+            unsigned pe[IPK_PS_RANKB];
+#pragma unroll
+            for (int j = 0; j < IPK_PS_RANKB; ++j)
             {
-                old = S.wh[warp][d];
-                S.wh[warp][d] = old + __popc(peers);
+                const int i = i0 + j;
+                if (i >= ITEMS) continue;
+                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                const uint32_t d = li < tile_n ? (dpk[i / 4] >> (8 * (i & 3))) & 0xffu : uint32_t(RADIX);
+                pe[j] = __match_any_sync(full, d);
             }
-            old = __shfl_sync(full, old, leader);
-            rkp[i / 2] |= ((old + __popc(peers & ((1u << lane) - 1))) & 0xffffu) << (16 * (i & 1));
-            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < IPK_PS_RANKB; ++j)
+            {
+                const int i = i0 + j;
+                if (i >= ITEMS) continue;
+                const uint32_t li = warp * (32 * ITEMS) + i * 32 + lane;
+                const bool valid = li < tile_n;
+                const uint32_t d = (dpk[i / 4] >> (8 * (i & 3))) & 0xffu;
+                const unsigned below = pe[j] & lt_mask;
+                const uint32_t old = valid ? S.wh[warp][d] : 0u;
+                __syncwarp();
+                if (valid && below == 0) S.wh[warp][d] = old + __popc(pe[j]);
+                __syncwarp();
+                rkp[i / 2] |= ((old + __popc(below)) & 0xffffu) << (16 * (i & 1));
+            }
         }
         __syncthreads();
-        const bool is_digit = tid < RS_RADIX;
+        const bool is_digit = tid < RADIX;
         uint32_t cnt = 0;
         if (is_digit)
         {
@@ -284,17 +325,17 @@ namespace ipkgpu
                 cnt += t;
             }
         }
-        uint64_t* my_status = status + uint64_t(tile) * RS_RADIX + (is_digit ? tid : 0);
+        uint64_t* my_status = status + uint64_t(tile) * RADIX + (is_digit ? tid : 0);
         if (is_digit)
             *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, first_of_chain ? RS_FLAG_INCL : RS_FLAG_LOCAL, cnt);
-        const uint32_t inc = warp_incl_scan(cnt, lane);
-        if (is_digit && lane == 31) S.misc[warp] = inc;
+        const uint32_t inc = warp_incl_scan(cnt, lane);                 // (cnt = 0 in the lanes beyond the radix)
+        if (warp < DWARPS && lane == 31) S.misc[warp] = inc;
         __syncthreads();
         if (warp == 0)
         {
-            const uint32_t w = lane < 8 ? S.misc[lane] : 0;
+            const uint32_t w = lane < DWARPS ? S.misc[lane] : 0;
             const uint32_t winc = warp_incl_scan(w, lane);
-            if (lane < 8) S.misc[lane] = winc - w;
+            if (lane < DWARPS) S.misc[lane] = winc - w;
         }
         __syncthreads();
         // The records are placed into the tile's digit order in shared memory FIRST: that only needs the local scan, and it
@@ -324,14 +365,14 @@ namespace ipkgpu
                 // Four predecessors are polled at a time: their loads overlap, and a walk over LOCAL words costs one
                 // memory latency per four tiles instead of one per tile; a word that is not there yet is waited for with a
                 // short sleep instead of a hot spin.
-                const volatile uint64_t* p = status + uint64_t(tile - 1) * RS_RADIX + tid;
+                const volatile uint64_t* p = status + uint64_t(tile - 1) * RADIX + tid;
                 uint32_t left = chain_pos;                      // predecessors in the chain, nearest first
                 bool done = false;
                 while (!done)
                 {
                     uint64_t w[PS_POLL];
 #pragma unroll
-                    for (int j = 0; j < PS_POLL; ++j) w[j] = uint32_t(j) < left ? p[-int64_t(j) * RS_RADIX] : 0ull;
+                    for (int j = 0; j < PS_POLL; ++j) w[j] = uint32_t(j) < left ? p[-int64_t(j) * RADIX] : 0ull;
                     int used = 0;
 #pragma unroll
                     for (int j = 0; j < PS_POLL; ++j)
@@ -342,7 +383,7 @@ namespace ipkgpu
                         used = j + 1;
                         if (((w[j] >> 32) & 3) == RS_FLAG_INCL) done = true;
                     }
-                    left -= used; p -= int64_t(used) * RS_RADIX;
+                    left -= used; p -= int64_t(used) * RADIX;
                     if (IPK_PS_SLEEP > 0 && !done && used < PS_POLL) __nanosleep(IPK_PS_SLEEP);
                 }
                 *reinterpret_cast<volatile uint64_t*>(my_status) = rs_status(epoch, RS_FLAG_INCL, before + cnt);
@@ -364,11 +405,34 @@ namespace ipkgpu
                 }
                 else
                 {
-                    const uint32_t d = uint32_t(r >> shift) & 0xffu;
+                    const uint32_t d = uint32_t(r >> shift) & DMASK;
                     out[S.goff[d] + q] = r;
                 }
             }
         }
+    }
+
+    /// Digit widths of the LSD passes over `total` key bits: as few passes as 8-bit digits need, the bits spread evenly over
+    /// them (12 bits = 6 + 6, not 8 + 4: the per-digit work of a pass -- counters, status words, look-back -- goes with
+    /// 2^width).  IPKGPU_LSD_WIDTHS="8,4" overrides (tuning).
+    inline uint32_t ps_pass_widths(uint32_t total, uint32_t* width /*[8]*/)
+    {
+        uint32_t passes = div_up<uint32_t>(total, 8);
+        if (const char* e = getenv("IPKGPU_LSD_WIDTHS"))
+        {
+            uint32_t w[8], nw = 0, sum = 0;
+            for (const char* q = e; *q && nw < 8;)
+            {
+                const uint32_t v = uint32_t(strtoul(q, const_cast<char**>(&q), 10));
+                if (v < 1 || v > 8) { nw = 0; break; }
+                w[nw++] = v; sum += v;
+                if (*q == ',') ++q;
+            }
+            if (nw && sum >= total) { for (uint32_t i = 0; i < nw; ++i) width[i] = w[i]; return nw; }
+        }
+        uint32_t left = total;
+        for (uint32_t p = 0; p < passes; ++p) { width[p] = div_up<uint32_t>(left, passes - p); left -= width[p]; }
+        return passes;
     }
 
     /// Digit histograms of every LSD pass and bucket from ONE read of the packed records: hist[b][p][d] += ...
@@ -376,7 +440,7 @@ namespace ipkgpu
     /// whenever it crosses a bucket boundary.
     constexpr int PS_HIST_THREADS = 256;
     constexpr int PS_HIST_ITEMS = 16;
-    __global__ void __launch_bounds__(PS_HIST_THREADS) ps_seg_hist(const uint64_t* __restrict__ recs, uint32_t n_passes, uint32_t skip_bits, uint64_t chunk,
+    __global__ void __launch_bounds__(PS_HIST_THREADS) ps_seg_hist(const uint64_t* __restrict__ recs, uint32_t n_passes, uint64_t pass_shift, uint64_t pass_bits, uint64_t chunk,
                                                                   uint32_t* __restrict__ hist, const __grid_constant__ ps_table T)
     {
         extern __shared__ uint32_t ps_sh[];              // [2 copies][n_passes][256]
@@ -414,8 +478,9 @@ namespace ipkgpu
                     const uint64_t idx = base + uint64_t(i) * PS_HIST_THREADS + threadIdx.x;
                     if (idx < seg_end)
                     {
-                        const uint32_t kk = uint32_t(r[i] >> 32) >> skip_bits;
-                        for (uint32_t p = 0; p < n_passes; ++p) atomicAdd(&mine[p * RS_RADIX + ((kk >> (8 * p)) & 0xffu)], 1u);
+                        const uint32_t kk = uint32_t(r[i] >> 32);
+                        for (uint32_t p = 0; p < n_passes; ++p)           // pass p: bits [shift_p, shift_p + bits_p) of the key field
+                            atomicAdd(&mine[p * RS_RADIX + ((kk >> uint32_t((pass_shift >> (8 * p)) & 0xff)) & ((1u << uint32_t((pass_bits >> (8 * p)) & 0xff)) - 1))], 1u);
                     }
                 }
             }
@@ -483,6 +548,7 @@ namespace ipkgpu
         const uint64_t base = uint64_t(T.start[bucket]) + uint64_t(lt) * MP_TILE, bucket_end = T.start[bucket + 1];
         const uint32_t tile_n = uint32_t(min(uint64_t(MP_TILE), bucket_end - base));
         const bool first_in_bucket = lt == 0;
+        if (IPK_MP_PREFETCH > 0 && tid == 32) ps_prefetch_l2(A.recs, base + uint64_t(IPK_MP_PREFETCH) * MP_TILE, T.start[T.d1], MP_TILE);
         {
             const uint64_t* __restrict__ g = A.recs + base;
             uint64_t r[MP_ITEMS];
@@ -751,9 +817,13 @@ namespace ipkgpu
     /// emission in group order): the passes start above them.
     inline bool ps_sort_buckets(ipkgpu_ctx* ctx, uint64_t* p0, uint64_t* p1, ps_table& T, uint32_t d0, uint32_t d1, uint32_t low_bits, uint32_t skip_bits = 0)
     {
-        const uint32_t passes = div_up<uint32_t>(low_bits - skip_bits, 8);
+        if (low_bits <= skip_bits) return false;
+        uint32_t width[8];
+        const uint32_t passes = ps_pass_widths(low_bits - skip_bits, width);
         const uint64_t n = uint64_t(T.start[d1]) - T.start[d0];
         if (n == 0 || passes == 0) return false;
+        uint64_t pass_shift = 0, pass_bits = 0;
+        for (uint32_t p = 0, at = skip_bits; p < passes; at += width[p], ++p) { pass_shift |= uint64_t(at) << (8 * p); pass_bits |= uint64_t(width[p]) << (8 * p); }
         ps_fill_tiles(T, d0, d1, PS_LSD_TILE);
         const uint32_t n_tiles = T.tile_first[d1];
         ps_reserve_status(ctx, n_tiles);
@@ -767,22 +837,34 @@ namespace ipkgpu
         uint64_t chunk = div_up<uint64_t>(n, hgrid);
         chunk = div_up<uint64_t>(chunk, PS_HIST_THREADS * PS_HIST_ITEMS) * (PS_HIST_THREADS * PS_HIST_ITEMS);
         IPK_LAUNCH(ctx, "ps_seg_hist", n * 8,
-                   ps_seg_hist<<<uint32_t(div_up<uint64_t>(n, chunk)), PS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(p0, passes, skip_bits, chunk, hist, T));
+                   ps_seg_hist<<<uint32_t(div_up<uint64_t>(n, chunk)), PS_HIST_THREADS, 2 * passes * RS_RADIX * 4, ctx->stream>>>(p0, passes, pass_shift, pass_bits, chunk, hist, T));
         IPK_LAUNCH(ctx, "ps_seg_scan", uint64_t(d1 - d0) * passes * 2048,
                    ps_seg_scan<<<dim3(passes, d1 - d0), RS_RADIX, 0, ctx->stream>>>(hist, passes, T));
         ps_dest none;
         memset(&none, 0, sizeof none);
         ps_runs no_runs;
         memset(&no_runs, 0, sizeof no_runs);
-        constexpr size_t smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS>(false);
-        auto kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB>;
-        IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         bool in1 = false;
         for (uint32_t p = 0; p < passes; ++p)
         {
-            IPK_LAUNCH(ctx, "ps_sweep", n * 16 + uint64_t(n_tiles) * RS_RADIX * 8,
-                       kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(in1 ? p1 : p0, nullptr, in1 ? p0 : p1, hist + size_t(p) * RS_RADIX, n, 32 + skip_bits + 8 * p,
-                                                                        passes * RS_RADIX, ctx->rs_status.as<uint64_t>(), tickets + p, rs_next_epoch(ctx), T, none, no_runs));
+            // digits narrower than 4 bits run as 4-bit digits: the bits above the key field of a packed record are zero
+            const uint32_t bits = std::max<uint32_t>(width[p], 4);
+            void (*kern)(const uint64_t*, const uint32_t*, uint64_t*, const uint32_t*, uint64_t, uint32_t, uint32_t, uint64_t*, uint32_t*, uint32_t, const ps_table, const ps_dest,
+                         const ps_runs) = nullptr;
+            size_t smem = 0;
+            switch (bits)
+            {
+            case 4: kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB, false, 4>; smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS, 16>(false); break;
+            case 5: kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB, false, 5>; smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS, 32>(false); break;
+            case 6: kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB, false, 6>; smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS, 64>(false); break;
+            case 7: kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB, false, 7>; smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS, 128>(false); break;
+            default: kern = ps_sweep<PS_THREADS, PS_LSD_ITEMS, false, PS_LSD_MINB, false, 8>; smem = ps_smem_bytes<PS_THREADS, PS_LSD_ITEMS, 256>(false); break;
+            }
+            IPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            IPK_LAUNCH(ctx, "ps_sweep", n * 16 + uint64_t(n_tiles) * (1u << bits) * 8,
+                       kern<<<n_tiles, PS_THREADS, smem, ctx->stream>>>(in1 ? p1 : p0, nullptr, in1 ? p0 : p1, hist + size_t(p) * RS_RADIX, n,
+                                                                        32 + uint32_t((pass_shift >> (8 * p)) & 0xff), passes * RS_RADIX, ctx->rs_status.as<uint64_t>(),
+                                                                        tickets + p, rs_next_epoch(ctx), T, none, no_runs));
             in1 = !in1;
         }
         return in1;
