@@ -22,7 +22,10 @@
 
 namespace ipkgpu
 {
-    constexpr int ENUM_THREADS = 128;        // windows per CTA tile
+#ifndef IPK_ENUM_THREADS
+#define IPK_ENUM_THREADS 128
+#endif
+    constexpr int ENUM_THREADS = IPK_ENUM_THREADS;        // windows per CTA tile
     constexpr int ENUM_WARPS = ENUM_THREADS / 32;
     constexpr int MAX_K = 32;
     constexpr int STAGE_CAP = 96;            // per-warp staging records; flushed when fewer than 32 slots remain
