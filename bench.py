@@ -265,6 +265,17 @@ def file_leg(ctx, inp_host, h_logp, node_branch, wl, n_entries, n_kmers):
         out["one_shot"] = {"wall_s": round(t1 - t0, 3), "returncode": r.returncode, "file_bytes": os.path.getsize(path) if os.path.exists(path) else 0,
                            "log": [l_ for l_ in r.stderr.splitlines() if l_.startswith(("Loaded", "Built", "Wrote", "Exception"))],
                            "what": "ipk-b200 --logp-f32 ... -o DB.ipk: process start to exit, posteriors and database on " + base}
+        # the same executable over several devices (ranks = threads, shards merged while serializing): IPK_ONE_SHOT_DEVICES=0,1
+        devs = os.environ.get("IPK_ONE_SHOT_DEVICES")
+        if devs and r.returncode == 0:
+            path2 = os.path.join(d, "DB_multi.ipk")
+            argv2 = argv[:-1] + [path2, "--devices", devs]
+            t0 = time.perf_counter()
+            r2 = subprocess.run(argv2, capture_output=True, text=True)
+            t1 = time.perf_counter()
+            same = r2.returncode == 0 and subprocess.run(["cmp", "-s", path, path2]).returncode == 0
+            out["one_shot_devices"] = {"devices": devs, "wall_s": round(t1 - t0, 3), "returncode": r2.returncode, "byte_equal_to_one_device": same,
+                                       "log": [l_ for l_ in r2.stderr.splitlines() if l_.startswith(("Loaded", "Built", "Wrote", "Exception"))]}
     finally:
         shutil.rmtree(d, ignore_errors=True)
     return out

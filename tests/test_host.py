@@ -448,6 +448,16 @@ def test_reference_command_line_end_to_end(ghosts, tmp_path):
     r = subprocess.run(argv3, capture_output=True, text=True)
     assert r.returncode == 0 and "on 3 devices" in r.stderr, r.stderr
     assert open(tmp_path / "DB3.ipk", "rb").read() == open(tmp_path / "DB.ipk", "rb").read()
+    # ... and over distinct devices where the box has them (direct peer access between the ranks' buffers)
+    import torch
+    n_dev = torch.cuda.device_count()
+    if n_dev >= 2:
+        devs = ",".join(str(i) for i in range(min(n_dev, 4)))
+        argvn = argv + ["--devices", devs]
+        argvn[argvn.index("-o") + 1] = str(tmp_path / "DBn.ipk")
+        r = subprocess.run(argvn, capture_output=True, text=True)
+        assert r.returncode == 0 and f"on {min(n_dev, 4)} devices" in r.stderr, r.stderr
+        assert open(tmp_path / "DBn.ipk", "rb").read() == open(tmp_path / "DB.ipk", "rb").read()
 
 
 def _random_shards(rng, n_shards, n_kmers_each, with_ties=True):
