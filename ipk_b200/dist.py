@@ -161,7 +161,8 @@ def packed_exchange(ctx, device, group=None):
     rp, handle = ctx.recv_packed(max(n_recv, 1))
     h_all = [torch.zeros(64, dtype=torch.uint8, device=device) for _ in range(world)]
     dist.all_gather(h_all, torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(device), group=group)
-    peers = [rp if r == rank else ctx.open_peer_slot(r, bytes(h_all[r].cpu().numpy().tobytes())) for r in range(world)]
+    handles = torch.stack(h_all).cpu().numpy()           # one device -> host copy for all ranks' handles
+    peers = [rp if r == rank else ctx.open_peer_slot(r, handles[r].tobytes()) for r in range(world)]
     ordered = ctx.stage1_scatter_packed(peers, owner, base)        # returns once this rank's stores have completed
     flag = torch.tensor([1 if ordered else 0], dtype=torch.int32, device=device)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)       # the barrier: every rank's stores have landed; and the AND of the flags
