@@ -342,11 +342,11 @@ def run_b200(args):
                          n_received_rank0=int(info.get("n_received", 0)))
         if host and arenas:
             # the end-to-end build ends with ONE database in rank 0's memory: the shards (mapped in place) + their N-way merge order
-            t_m = time.perf_counter()
-            got = ipkdist.gather_database(res, arenas, dev)
+            got = ipkdist.gather_database(res, arenas, dev, ctx=None if os.environ.get("IPK_HOST_MERGE") else ctx,
+                                          key_ranges=str(info.get("exchange", "")).startswith("packed"), key_bits=key_bits)
             if got is not None:
                 merged["shards"], merged["order"] = got
-                merged["ms_merge_order"] = (time.perf_counter() - t_m) * 1e3
+                merged["ms_merge_order"] = ipkdist.LAST_MERGE_ORDER_MS
         st = res.stats.as_dict()
         st1 = info["stage1"]
         for k_ in ("n_windows", "n_emitted", "ms_h2d", "ms_prefix", "ms_enumerate", "h2d_bytes"):
@@ -414,6 +414,8 @@ def run_b200(args):
         dist.barrier()
         for r in range(world):
             arenas[r] = mine if r == rank else (ipkdist.SharedArena(f"ipkb200_{tag}_{r}", caps[r][0], caps[r][1], create=False) if rank == 0 else None)
+            if rank == 0 and r != rank:
+                arenas[r].register_heads()          # rank 0 uploads every shard's filter values for the merge order
     step(True)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -536,7 +538,8 @@ def run_b200(args):
         if len(osh) != n_kmers or not np.all(fv_m[1:] >= fv_m[:-1]) or not np.all(key_m[1:][tie] > key_m[:-1][tie]):
             raise SystemExit("bench.py: the N-way merge order of the shards is not ascending in (filter value, key)")
         host_check = (f"{world} shards mapped into rank 0 (shared page-locked arenas), host digest == device digest, N-way merge order over "
-                      f"{len(osh)} k-mers in {merged.get('ms_merge_order', 0.0):.1f} ms (inside the timed region)")
+                      f"{len(osh)} k-mers in {merged.get('ms_merge_order', 0.0):.1f} ms "
+                      f"({'host cores' if os.environ.get('IPK_HOST_MERGE') else 'ipkgpu_merge_order on rank 0'}; inside the timed region)")
     path_bytes = sum(r["bytes"] for r in rows) / max(args.steps, 1)
     t_hbm = path_bytes / (peak * 1e9)                     # `rows` are rank 0's own kernels: its share of the path already
     t_nvl = (exch_bytes_per_record * sent_remote / world) / (NVLINK_GBS * 1e9) if world > 1 else 0.0

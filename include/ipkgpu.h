@@ -253,6 +253,17 @@ int  ipkgpu_stage2_packed(ipkgpu_ctx* ctx, uint64_t n, const uint64_t* bucket_st
 size_t ipkgpu_result_arena_layout(uint64_t cap_entries, uint64_t cap_kmers, size_t* offsets /*[6] or NULL*/);
 int  ipkgpu_set_result_arena(ipkgpu_ctx* ctx, void* base, uint64_t cap_entries, uint64_t cap_kmers);
 
+/* The N-way merge of merge_stage2 (db_builder.cpp:392-458) over the k-mer heads, on the device: shard s holds n_kmers[s]
+ * k-mers in ascending (filter value, key) -- HOST arrays fv[s] / keys[s] (page-locked ones copy fastest) -- and the k-mer at
+ * merged position i is k-mer out_index[i] of shard out_shard[i] (host arrays of sum(n_kmers) elements; entries stay where
+ * they are).  The order-preserving 32-bit images of all filter values are sorted stably with their positions as payload.
+ * key_ranges != 0 promises that shard s holds smaller keys than shard s + 1 (what the packed exchange's k-mer-range owners
+ * produce): equal filter values then fall in key order by stability alone and `keys` may be NULL; otherwise the positions are
+ * first put into key order by LSD passes on the low key_bits bits of the keys.  Same order as ipkhost_merge_order
+ * (ipk_b200/host/ipkhost.h), which stays the host-only form; <= 256 shards, < 2^32 k-mers in all. */
+int  ipkgpu_merge_order(ipkgpu_ctx* ctx, uint32_t n_shards, const float* const* fv, const uint64_t* const* keys, const uint64_t* n_kmers,
+                        int32_t key_ranges, uint32_t key_bits, uint8_t* out_shard, uint32_t* out_index);
+
 /* Stage 2 of one rank: DEVICE records (composite keys as above, unique) -> regroup sort -> CSR by k-mer -> filter
  * values -> order (equal composite keys are merged by maximum score).  d_keys/d_scores are overwritten (one side of the sort's ping-pong).
  * chunks_group_ordered != 0 promises that the records are a concatenation of chunks in ascending group ranges, each

@@ -184,6 +184,8 @@ def load() -> C.CDLL:
     lib.ipkgpu_result_arena_layout.restype = C.c_size_t
     lib.ipkgpu_score_threshold.argtypes = [C.c_float, C.c_uint32, C.c_uint32, P(C.c_float), P(C.c_float)]
     lib.ipkgpu_score_threshold.restype = None
+    lib.ipkgpu_merge_order.argtypes = [C.c_void_p, C.c_uint32, P(C.c_void_p), P(C.c_void_p), P(C.c_uint64), C.c_int32, C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.ipkgpu_merge_order.restype = C.c_int
     lib.ipkgpu_best_prefix_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     lib.ipkgpu_best_prefix_noalloc.restype = C.c_int
     lib.ipkgpu_noalloc_last_error.argtypes = []
@@ -334,6 +336,7 @@ class Context:
 
     def close(self):
         if self._h:
+            self._free_merge_order_staging()
             self._lib.ipkgpu_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -544,6 +547,35 @@ class Context:
                                                    group_branch.ctypes.data, int(group_branch.shape[0]), key_bits, threshold, total_num_groups, filter,
                                                    mode, C.byref(res)))
         return res
+
+    def merge_order(self, shards, key_ranges: bool, key_bits: int = 64):
+        """ipkgpu_merge_order over shard objects with .keys / .fv host arrays (numpy): -> (shard[u8], index[u32]) per merged k-mer"""
+        n = len(shards)
+        fvs = [np.ascontiguousarray(d.fv, np.float32) for d in shards]
+        kys = [np.ascontiguousarray(d.keys, np.uint64) for d in shards]
+        cnt = (C.c_uint64 * n)(*[len(f) for f in fvs])
+        pf = (C.c_void_p * n)(*[f.ctypes.data for f in fvs])
+        pk = (C.c_void_p * n)(*[k.ctypes.data for k in kys])
+        total = sum(len(f) for f in fvs)
+        # the order comes back into page-locked memory kept with the context (views are valid until the next call / close())
+        need = total * 5 + 64
+        if getattr(self, "_mo_cap", 0) < need:
+            self._free_merge_order_staging()
+            p = C.c_void_p(0)
+            rc = self._lib.ipkgpu_host_alloc(self.device, need + need // 8, C.byref(p))
+            if rc != 0 or not p.value:
+                raise IpkGpuError(rc, "ipkgpu_host_alloc failed")
+            self._mo_pin, self._mo_cap = p, need + need // 8
+        base = self._mo_pin.value
+        out_index = np.ctypeslib.as_array((C.c_uint32 * max(total, 1)).from_address(base))[:total]
+        out_shard = np.ctypeslib.as_array((C.c_uint8 * max(total, 1)).from_address(base + 4 * total))[:total]
+        self._check(self._lib.ipkgpu_merge_order(self._h, n, pf, pk, cnt, 1 if key_ranges else 0, key_bits, out_shard.ctypes.data, out_index.ctypes.data))
+        return out_shard, out_index
+
+    def _free_merge_order_staging(self):
+        if getattr(self, "_mo_pin", None):
+            self._lib.ipkgpu_host_free(self._mo_pin)
+        self._mo_pin, self._mo_cap = None, 0
 
     def set_result_arena(self, base, cap_entries: int, cap_kmers: int) -> None:
         """host results go to the caller's page-locked arena (e.g. shared memory another process maps); base None resets"""

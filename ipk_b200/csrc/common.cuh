@@ -105,6 +105,7 @@ struct ipkgpu_ctx
     ipkgpu::dbuf u_keys, u_scores;                 // unique (kmer,group) records, composite keys
     ipkgpu::dbuf kmer_keys, kmer_offs, ent_branch, ent_score, fv, ord_keys_a, ord_keys_b, ord_vals_a, ord_vals_b;
     ipkgpu::dbuf out_keys, out_fv, out_offs, out_branch, out_score, out_cnt;
+    ipkgpu::dbuf mo_buf;                           // ipkgpu_merge_order: filter values, sort ping-pong and the split order of all shards
     // stage-1 state kept for ipkgpu_stage1_partition
     uint64_t s1_n = 0;
     uint32_t s1_group_bits = 0;

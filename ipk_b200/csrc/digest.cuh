@@ -72,6 +72,40 @@ namespace ipkgpu
         }
     }
 
+    // ---- the N-way merge order of key shards (merge_stage2, ipk/src/db_builder.cpp:392-458) as one stable sort ---------------
+    /// keys[i] = ascending-sortable image of fv[src], vals[i] = src, with src = perm[i] (or i without a permutation)
+    __global__ void __launch_bounds__(256) k9_image_keys(const float* __restrict__ fv, const uint32_t* __restrict__ perm, uint64_t n,
+                                                         uint64_t* __restrict__ okeys, uint32_t* __restrict__ ovals)
+    {
+        const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        if (i >= n) return;
+        const uint32_t src = perm ? perm[i] : uint32_t(i);
+        const uint32_t b = __float_as_uint(fv[src]);
+        okeys[i] = b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
+        ovals[i] = src;
+    }
+
+    __global__ void __launch_bounds__(256) k9_iota(uint32_t* __restrict__ v, uint64_t n)
+    {
+        const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        if (i < n) v[i] = uint32_t(i);
+    }
+
+    struct mo_table { uint64_t prefix[257]; uint32_t n_shards; };
+
+    /// global position (shards laid end to end) -> (shard, index inside the shard)
+    __global__ void __launch_bounds__(256) k9_split_positions(const uint32_t* __restrict__ g, uint64_t n, const __grid_constant__ mo_table T,
+                                                              uint8_t* __restrict__ shard, uint32_t* __restrict__ index)
+    {
+        const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+        if (i >= n) return;
+        const uint64_t p = g[i];
+        uint32_t lo = 0, hi = T.n_shards;              // last s with prefix[s] <= p
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (T.prefix[mid] <= p) lo = mid; else hi = mid; }
+        shard[i] = uint8_t(lo);
+        index[i] = uint32_t(p - T.prefix[lo]);
+    }
+
     /// Boundary cases (BASELINE.json: k-mers whose score lies within a band of the threshold are listed separately): the
     /// unique (k-mer, group) records of a build at threshold - band (`loose`, sorted by composite key) against those of a
     /// build at threshold + band (`tight`, a subset as a set of keys).  A loose record that the tight build lacks, or holds

@@ -1569,7 +1569,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->block_counts, &ctx->block_offs, &ctx->rs_status, &ctx->mg_status, &ctx->mif_chunks, &ctx->dbg_node, &ctx->dbg_win, &ctx->deferred, &ctx->deferred2, &ctx->u_keys, &ctx->u_scores,
                             &ctx->kmer_keys, &ctx->kmer_offs, &ctx->ent_branch, &ctx->ent_score, &ctx->fv, &ctx->ord_keys_a, &ctx->ord_keys_b,
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
-                            &ctx->out_score, &ctx->out_cnt, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
+                            &ctx->out_score, &ctx->out_cnt, &ctx->mo_buf, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
                             &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
                             &ctx->runs, &ctx->runs_scratch, &ctx->recv_old, &ctx->recv_old2, &ctx->ent_pos, &ctx->out_pos, &ctx->pos_flags, &ctx->node_rank };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
@@ -1585,6 +1585,65 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
     for (auto e : ctx->ev_h2d) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+int ipkgpu_merge_order(ipkgpu_ctx* ctx, uint32_t n_shards, const float* const* fv, const uint64_t* const* keys, const uint64_t* n_kmers,
+                       int32_t key_ranges, uint32_t key_bits, uint8_t* out_shard, uint32_t* out_index)
+{
+    return guarded(ctx, [&] {
+        if (n_shards < 1 || n_shards > 256) fail(IPKGPU_EINVAL, "n_shards = %u outside [1, 256]", n_shards);
+        if (!fv || !n_kmers || (!key_ranges && !keys)) fail(IPKGPU_EINVAL, "fv / keys / n_kmers is null");
+        if (!key_ranges && (key_bits < 1 || key_bits > 64)) fail(IPKGPU_EINVAL, "key_bits = %u outside [1, 64]", key_bits);
+        mo_table T;
+        memset(&T, 0, sizeof T);
+        T.n_shards = n_shards;
+        for (uint32_t s = 0; s < n_shards; ++s)
+        {
+            if (n_kmers[s] && (!fv[s] || (!key_ranges && !keys[s]))) fail(IPKGPU_EINVAL, "shard %u: array is null", s);
+            T.prefix[s + 1] = T.prefix[s] + n_kmers[s];
+        }
+        for (uint32_t s = n_shards + 1; s <= 256; ++s) T.prefix[s] = T.prefix[n_shards];
+        const uint64_t n = T.prefix[n_shards];
+        if (n == 0) return;
+        if (n > 0xffffffffull) fail(IPKGPU_EINVAL, "%llu k-mers over all shards: the merge order indexes them with 32 bits", (unsigned long long)n);
+        if (!out_shard || !out_index) fail(IPKGPU_EINVAL, "output pointer is null");
+        // one allocation: fv | keys a | keys b | vals a | vals b | shard | index
+        const uint64_t n8 = (n + 31) & ~31ull;
+        ctx->reserve(ctx->mo_buf, n8 * (4 + 8 + 8 + 4 + 4 + 4 + 1) + 256);
+        unsigned char* base = ctx->mo_buf.as<unsigned char>();
+        uint64_t* ka = reinterpret_cast<uint64_t*>(base);
+        uint64_t* kb = ka + n8;
+        float* d_fv = reinterpret_cast<float*>(kb + n8);
+        uint32_t* va = reinterpret_cast<uint32_t*>(d_fv + n8);
+        uint32_t* vb = va + n8;
+        uint32_t* d_index = vb + n8;
+        uint8_t* d_shard = reinterpret_cast<uint8_t*>(d_index + n8);
+        for (uint32_t s = 0; s < n_shards; ++s)
+            if (n_kmers[s]) IPK_CUDA(cudaMemcpyAsync(d_fv + T.prefix[s], fv[s], n_kmers[s] * 4, cudaMemcpyHostToDevice, ctx->stream));
+        const uint32_t grid = uint32_t(div_up<uint64_t>(n, 256));
+        const uint32_t* perm = nullptr;
+        uint64_t *k0 = ka, *k1 = kb;                  // where the image keys go / the other side of the ping-pong
+        uint32_t *v0 = va, *v1 = vb;
+        if (!key_ranges)
+        {
+            // shards with interleaved key sets: ties between equal filter values must fall in key order, so the positions are
+            // put into key order first (stable LSD passes on the key bits), then sorted stably on the filter values
+            for (uint32_t s = 0; s < n_shards; ++s)
+                if (n_kmers[s]) IPK_CUDA(cudaMemcpyAsync(ka + T.prefix[s], keys[s], n_kmers[s] * 8, cudaMemcpyHostToDevice, ctx->stream));
+            IPK_LAUNCH(ctx, "k9_iota", n * 4, k9_iota<<<grid, 256, 0, ctx->stream>>>(va, n));
+            const bool in_b = radix_sort_pairs(ctx, ka, va, kb, vb, n, key_bits, ctx->hist, ctx->scan_tmp);
+            perm = in_b ? vb : va;
+            if (!in_b) { k0 = kb; k1 = ka; v0 = vb; v1 = va; }
+        }
+        IPK_LAUNCH(ctx, "k9_image_keys", n * 20, k9_image_keys<<<grid, 256, 0, ctx->stream>>>(d_fv, perm, n, k0, v0));
+        // key-range shards (the packed exchange): shard s holds smaller keys than shard s + 1 and is itself in (fv, key) order,
+        // so the stable sort on the filter values alone leaves equal values in key order
+        const bool in_1 = radix_sort_pairs(ctx, k0, v0, k1, v1, n, 32, ctx->hist, ctx->scan_tmp);
+        IPK_LAUNCH(ctx, "k9_split_positions", n * 9, k9_split_positions<<<grid, 256, 0, ctx->stream>>>(in_1 ? v1 : v0, n, T, d_shard, d_index));
+        IPK_CUDA(cudaMemcpyAsync(out_index, d_index, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaMemcpyAsync(out_shard, d_shard, n, cudaMemcpyDeviceToHost, ctx->stream));
+        IPK_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
 }
 
 const char* ipkgpu_last_error(const ipkgpu_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }

@@ -265,6 +265,16 @@ class SharedArena:
             raise RuntimeError(f"cudaHostRegister of the shared arena failed: {rc}")
         self.registered = True
 
+    def register_heads(self):
+        """page-lock only the k-mer heads (keys and filter values): what a process that attaches needs pinned for
+        ipkgpu_merge_order to read them at the full PCIe rate"""
+        lo = (self.address + self.offsets[2]) & ~4095
+        hi = (self.address + self.offsets[4] + 4095) & ~4095
+        rc = torch.cuda.cudart().cudaHostRegister(lo, hi - lo, 0)
+        if int(rc) != 0:
+            raise RuntimeError(f"cudaHostRegister of the shared arena's heads failed: {rc}")
+        self.heads_registered = lo
+
     def shard(self, n_kmers: int, n_entries: int, branch16: bool):
         """the arrays of a finished indexed host result, viewed in place"""
         from types import SimpleNamespace
@@ -279,6 +289,9 @@ class SharedArena:
         if self.registered:
             torch.cuda.cudart().cudaHostUnregister(self.address)
             self.registered = False
+        if getattr(self, "heads_registered", None):
+            torch.cuda.cudart().cudaHostUnregister(self.heads_registered)
+            self.heads_registered = None
         self.buf = None
         try:
             self.shm.close()
@@ -288,10 +301,14 @@ class SharedArena:
             pass
 
 
-def gather_database(res, arenas, device, group=None, threads: int = 0):
+LAST_MERGE_ORDER_MS = 0.0
+
+
+def gather_database(res, arenas, device, group=None, threads: int = 0, ctx=None, key_ranges: bool = False, key_bits: int = 64):
     """After sharded_build with host results in shared arenas: rank 0 learns every shard's sizes (one tiny all-gather) and
     merges the k-mer heads of all shards by (filter value, key) -- the N-way merge of merge_stage2 (db_builder.cpp:392-458),
-    natively (hostlib.merge_order).  Returns on rank 0 (shards, (order_shard, order_index)): the whole database in rank 0's
+    on rank 0's device when a context is given (ipkgpu_merge_order), else natively on the host cores (hostlib.merge_order).
+    key_ranges: the shards are ascending k-mer ranges (the packed exchange).  Returns on rank 0 (shards, (order_shard, order_index)): the whole database in rank 0's
     address space, k-mer i of the build = k-mer order_index[i] of shards[order_shard[i]]; None elsewhere."""
     from . import hostlib
     world, rank = dist.get_world_size(group), dist.get_rank(group)
@@ -302,4 +319,14 @@ def gather_database(res, arenas, device, group=None, threads: int = 0):
         return None
     sizes = [[int(x) for x in r.cpu().tolist()] for r in rows]
     shards = [arenas[r].shard(sizes[r][0], sizes[r][1], bool(sizes[r][2])) for r in range(world)]
-    return shards, hostlib.merge_order(shards, threads)
+    import time
+    global LAST_MERGE_ORDER_MS
+    t0 = time.perf_counter()
+    if ctx is not None and hasattr(ctx, "merge_order") and torch.device(device).type == "cuda":
+        # the same order from one stable device sort of the filter values (ipkgpu_merge_order): the heads go up from the
+        # page-locked arenas, (shard, index) per merged k-mer comes back
+        order = ctx.merge_order(shards, key_ranges, key_bits)
+    else:
+        order = hostlib.merge_order(shards, threads)
+    LAST_MERGE_ORDER_MS = (time.perf_counter() - t0) * 1e3          # the order alone, without the wait for the other ranks' copies
+    return shards, order

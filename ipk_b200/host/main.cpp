@@ -435,8 +435,17 @@ int main(int argc, char** argv)
             t0 = std::chrono::steady_clock::now();
             std::vector<uint8_t> order_shard(n_kmers);
             std::vector<uint32_t> order_index(n_kmers);
-            if (ipkhost_merge_order(uint32_t(views.size()), views.data(), o.threads, order_shard.data(), order_index.data()) != IPKHOST_OK)
-                throw std::runtime_error("cannot merge the shards");
+            // the shards are ascending k-mer ranges (packed exchange): one stable device sort of the filter values gives the order
+            // (ipkgpu_merge_order on the first device)
+            {
+                std::vector<const float*> fvs(views.size());
+                std::vector<const uint64_t*> kys(views.size());
+                std::vector<uint64_t> cnt(views.size());
+                for (size_t r = 0; r < views.size(); ++r) { fvs[r] = views[r].fv; kys[r] = views[r].keys; cnt[r] = views[r].n_kmers; }
+                if (ipkgpu_merge_order(shards[0].ctx, uint32_t(views.size()), fvs.data(), kys.data(), cnt.data(), 1, o.k * bits,
+                                       order_shard.data(), order_index.data()) != IPKGPU_OK)
+                    throw std::runtime_error(std::string("cannot merge the shards: ") + ipkgpu_last_error(shards[0].ctx));
+            }
             if (ipkhost_write_ipk_sharded(o.output.c_str(), &header, uint32_t(views.size()), views.data(), order_shard.data(), order_index.data(), o.threads) != IPKHOST_OK)
                 throw std::runtime_error("cannot write " + o.output);
             fprintf(stderr, "Wrote %s in %.3f s %s\n", o.output.c_str(), seconds_since(t0), layout_note);

@@ -708,3 +708,38 @@ def test_workload_sample_matches_oracle(ctx, mode, name):
     got = ctx.build(logp, nb, w.width, w.sigma, w.bits, w.k, lthr, thr, w.n_tree_nodes, 0)
     assert got.stats["n_emitted"] == want.n_emitted
     assert_db_equal(got, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("key_ranges", [True, False])
+@pytest.mark.parametrize("n_shards", [1, 3, 8])
+def test_device_merge_order_equals_host_merge_order(ctx, key_ranges, n_shards):
+    """ipkgpu_merge_order (one stable device sort of the filter values) against ipkhost_merge_order (the N-way merge of
+    merge_stage2, db_builder.cpp:392-458, on the host cores): same (shard, index) per merged k-mer, ties and signed zeros included"""
+    from types import SimpleNamespace
+    from ipk_b200 import hostlib
+    rng = np.random.default_rng(11 + n_shards)
+    per = 5000
+    keys_all = rng.permutation(1 << 22)[: n_shards * per].astype(np.uint64)
+    if key_ranges:
+        keys_all = np.sort(keys_all)                      # shard s = the s-th contiguous key range (k-mer-range owners)
+    shards = []
+    for s in range(n_shards):
+        keys = keys_all[s * per:(s + 1) * per]
+        fv = rng.normal(size=per).astype(np.float32)
+        fv[rng.integers(0, per, per // 8)] = np.float32(0.125)       # equal filter values inside and across shards
+        fv[:4] = [-0.0, 0.0, -1.5, np.float32(-3.0e38)]
+        img = fv.view(np.uint32).astype(np.int64)
+        o = np.lexsort((keys, np.where(img >> 31, img ^ 0xffffffff, img ^ 0x80000000)))     # the order the device leaves a shard in
+        keys, fv = keys[o], fv[o]
+        cnt = np.ones(per, np.int64)
+        offsets = np.concatenate(([0], np.cumsum(cnt))).astype(np.uint64)
+        shards.append(SimpleNamespace(keys=keys, fv=fv, offsets=offsets, counts=None, branch=np.zeros(per, np.uint32), score=np.zeros(per, np.float32), branch16=None))
+    want_s, want_i = hostlib.merge_order(shards)
+    got_s, got_i = ctx.merge_order(shards, key_ranges, 22)
+    got_s, got_i = got_s.copy(), got_i.copy()            # (views of the context's staging, overwritten by the next call)
+    assert np.array_equal(got_s, want_s) and np.array_equal(got_i, want_i)
+    if not key_ranges and n_shards > 1:
+        # and the promise matters: without it the tie order of interleaved key sets needs the keys
+        bad_s, bad_i = ctx.merge_order(shards, True, 22)
+        assert not (np.array_equal(bad_s, want_s) and np.array_equal(bad_i, want_i))
