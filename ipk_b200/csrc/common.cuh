@@ -10,6 +10,7 @@
 #include <utility>
 #include <cstdlib>
 #include <algorithm>
+#include <chrono>
 #include "../../include/ipkgpu.h"
 
 namespace ipkgpu
@@ -198,8 +199,12 @@ struct ipkgpu_ctx
         if (b.p) { cudaFree(b.p); dev_bytes -= b.cap; b.p = nullptr; b.cap = 0; }
         // round up a little so that slowly growing inputs do not realloc on every call
         size_t want = bytes + bytes / 16 + 256;
+        static const bool trace = getenv("IPKGPU_TRACE") != nullptr;
+        const auto t_0 = std::chrono::steady_clock::now();
         cudaError_t e = cudaMalloc(&b.p, want);
         if (e != cudaSuccess) { want = bytes; e = cudaMalloc(&b.p, want); }
+        if (trace && want >= (size_t(64) << 20))
+            fprintf(stderr, "[ipkgpu] cudaMalloc %.2f GB: %.1f ms\n", double(want) * 1e-9, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_0).count());
         if (e != cudaSuccess)
         {
             cudaGetLastError();

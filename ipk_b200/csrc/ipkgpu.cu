@@ -15,6 +15,7 @@
 #include "digest.cuh"
 #include "positions.cuh"
 
+#include <chrono>
 #include <cmath>
 #include <numeric>
 #include <unordered_map>
@@ -43,6 +44,8 @@ namespace ipkgpu
             {
                 char* q = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(base) + HUGE - 1) & ~uintptr_t(HUGE - 1));
                 madvise(q, len, MADV_HUGEPAGE);
+                static const bool trace = getenv("IPKGPU_TRACE") != nullptr;          // where a cold build's host time goes (stderr)
+                const auto t_0 = std::chrono::steady_clock::now();
                 const unsigned T = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
                 std::vector<std::thread> th;
                 for (unsigned t = 0; t < T; ++t)
@@ -51,7 +54,13 @@ namespace ipkgpu
                         for (size_t o = lo; o < hi; o += 4096) q[o] = 0;
                     });
                 for (auto& x : th) x.join();
-                if (cudaHostRegister(q, len, cudaHostRegisterPortable) == cudaSuccess)
+                const auto t_1 = std::chrono::steady_clock::now();
+                const cudaError_t reg = cudaHostRegister(q, len, cudaHostRegisterPortable);
+                if (trace)
+                    fprintf(stderr, "[ipkgpu] pinned_alloc %.2f GB: touch %.1f ms, cudaHostRegister %.1f ms\n", double(len) * 1e-9,
+                            std::chrono::duration<double, std::milli>(t_1 - t_0).count(),
+                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_1).count());
+                if (reg == cudaSuccess)
                 {
                     std::lock_guard<std::mutex> l(g_pin_mutex);
                     g_pin_maps[q] = { base, len + HUGE };
