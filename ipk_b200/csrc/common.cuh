@@ -99,6 +99,8 @@ struct ipkgpu_ctx
     uint32_t small_list = 64;          // join kernel: longest list its owner thread fills and sorts alone (env IPKGPU_SMALL_LIST)
     uint32_t pool_cap = 0;             // list-pool capacity of the join kernel in elements; 0 = default per alphabet
     uint64_t last_tiles = 0, last_deferred_tiles = 0;   // of the current call
+    ipkgpu::dbuf join_hist;            // per-SM partial top-byte histograms of the join kernel's emission (enum_args::top_hist)
+    bool top_hist_on = false;          // ... counted by the current enumeration (valid as long as runs_valid is)
     ipkgpu::dbuf runs, runs_scratch;   // commits of the join kernel (enumerate.cuh: emit_run) and their group-ordered index (packed_sort.cuh)
     uint64_t runs_n = 0;               // runs recorded by the current enumeration
     bool runs_valid = false;           // ... and whether they cover every emitted record (join kernel only, nothing deferred to the depth-first kernel)

@@ -171,6 +171,9 @@ namespace ipkgpu
         emit_run* runs;               // join kernel: one entry per committing item (null: not recorded) ...
         unsigned long long* run_counter;   // ... their number so far
         uint32_t run_cap;
+        uint32_t* top_hist;           // join kernel: [JOIN_HIST_SLOTS][256] counts of the emitted records by the top byte of their k-mer (null: not
+                                      // counted) -- the histogram the first pass of the merge sort needs, taken where the records are made
+        uint32_t top_shift;           // ... that byte = (key of the root's left element) >> top_shift
         uint32_t group_min;           // join kernel: lists of at least this many elements are built by a lane group
         uint32_t small_list;          // join kernel: lists up to this length are filled and sorted by their owner thread
     };

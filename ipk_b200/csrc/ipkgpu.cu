@@ -284,7 +284,7 @@ namespace
     uint32_t max_pool_cap(const ipkgpu_input* in, int n_fam)
     {
         const size_t fixed = make_join_layout(int(in->k), int(in->sigma), n_fam, 0).total;
-        const size_t avail = size_t(226) * 1024 > fixed ? size_t(226) * 1024 - fixed : 0;
+        const size_t avail = size_t(225) * 1024 > fixed ? size_t(225) * 1024 - fixed : 0;      // (227 KB per CTA less the kernel's 1.5 KB of static shared memory)
         return uint32_t(std::min<size_t>(avail / 8, 65000));
     }
 
@@ -398,6 +398,11 @@ namespace
                     A.runs = ctx->runs.as<emit_run>();
                     A.run_counter = counters + 5;
                     A.run_cap = uint32_t(std::min<uint64_t>(ctx->runs.cap / sizeof(emit_run), 0xffffffffull));
+                    if (ctx->top_hist_on)
+                    {
+                        A.top_hist = ctx->join_hist.as<uint32_t>();
+                        A.top_shift = uint32_t(J.root_hl) * in->bits - 8;
+                    }
                 }
                 IPK_CUDA(cudaMemsetAsync(A.counter + 1, 0, 8, ctx->stream));
                 const size_t smem = make_join_layout(int(in->k), int(in->sigma), J.n_fam, A.pool_cap).total;
@@ -792,7 +797,8 @@ namespace
         ps_runs Rn;
         memset(&Rn, 0, sizeof Rn);
         if (use_runs) Rn = ps_order_runs(ctx, n, gbits);          // (uses ctx->hist as sort scratch: before the top histogram)
-        ps_top_histogram(ctx, ka, n, low_bits);
+        if (use_runs && ctx->top_hist_on) ps_top_histogram_from_join(ctx);
+        else ps_top_histogram(ctx, ka, n, low_bits);
         IPK_LAUNCH(ctx, "rs_scan_hist", 2048, rs_scan_hist<<<1, RS_RADIX, 0, ctx->stream>>>(ctx->hist.as<uint32_t>()));
         IPK_CUDA(cudaMemcpyAsync(T.start, ctx->hist.p, RS_RADIX * 4, cudaMemcpyDeviceToHost, ctx->stream));
         ps_dest D;
@@ -926,6 +932,19 @@ namespace
         L.want_runs = !runs_off && !ordered && (raw || want_csr);
         ctx->runs_n = 0;
         ctx->runs_valid = L.want_runs;
+        // the join kernel also counts its records by the top byte of their k-mer (the histogram of the merge sort's first pass)
+        // when that byte lies inside the root's left half and the counters fit the memory of the list thresholds
+        {
+            static const bool off = getenv("IPKGPU_JOIN_HIST") && atoi(getenv("IPKGPU_JOIN_HIST")) == 0;
+            const int NCP_ = (ENUM_THREADS + int(in->k) - 1 + 3) & ~3;
+            ctx->top_hist_on = !off && L.want_runs && in->k >= 2 && (in->k / 2) * in->bits >= 8 && in->k * in->bits + L.group_bits <= 40 &&
+                               size_t(make_join_program(int(in->k)).n_fam) * NCP_ * 4 >= 1024;
+            if (ctx->top_hist_on)
+            {
+                ctx->reserve(ctx->join_hist, size_t(JOIN_HIST_SLOTS) * 256 * 4);
+                IPK_CUDA(cudaMemsetAsync(ctx->join_hist.p, 0, size_t(JOIN_HIST_SLOTS) * 256 * 4, ctx->stream));
+            }
+        }
         uint64_t side_cap = 0;
         if (ordered)
         {
@@ -1580,7 +1599,7 @@ void ipkgpu_destroy(ipkgpu_ctx* ctx)
                             &ctx->ord_vals_a, &ctx->ord_vals_b, &ctx->out_keys, &ctx->out_fv, &ctx->out_offs, &ctx->out_branch,
                             &ctx->out_score, &ctx->out_cnt, &ctx->mo_buf, &ctx->recv_keys, &ctx->recv_scores, &ctx->peer_base, &ctx->mif_tab, &ctx->tile_status,
                             &ctx->side_keys_a, &ctx->side_keys_b, &ctx->side_vals_a, &ctx->side_vals_b, &ctx->mg_split, &ctx->ps_hist,
-                            &ctx->runs, &ctx->runs_scratch, &ctx->recv_old, &ctx->recv_old2, &ctx->ent_pos, &ctx->out_pos, &ctx->pos_flags, &ctx->node_rank };
+                            &ctx->runs, &ctx->runs_scratch, &ctx->join_hist, &ctx->recv_old, &ctx->recv_old2, &ctx->ent_pos, &ctx->out_pos, &ctx->pos_flags, &ctx->node_rank };
     for (auto& m : ctx->ipc_open) cudaIpcCloseMemHandle(m.ptr);
     ctx->ipc_open.clear();
     for (auto& m : ctx->ipc_slots) if (m.ptr) cudaIpcCloseMemHandle(m.ptr);
@@ -2134,7 +2153,8 @@ int ipkgpu_stage1_bucket_counts(ipkgpu_ctx* ctx, uint64_t* counts)
         if (!ps_eligible(ctx->s1_key_bits, ctx->s1_group_bits, n))
             fail(IPKGPU_EINVAL, "packed exchange needs k*bits >= 8, k*bits + group bits - 8 <= 32 and fewer than 2^32 records per rank (have %u + %u bits, %llu records)",
                  ctx->s1_key_bits, ctx->s1_group_bits, (unsigned long long)n);
-        ps_top_histogram(ctx, ctx->s1_keys, n, ctx->s1_key_bits + ctx->s1_group_bits - 8);
+        if (ctx->runs_valid && ctx->top_hist_on && ctx->runs_n > 0) ps_top_histogram_from_join(ctx);
+        else ps_top_histogram(ctx, ctx->s1_keys, n, ctx->s1_key_bits + ctx->s1_group_bits - 8);
         uint32_t h[PS_BUCKETS];
         IPK_CUDA(cudaMemcpyAsync(h, ctx->hist.p, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         IPK_CUDA(cudaStreamSynchronize(ctx->stream));

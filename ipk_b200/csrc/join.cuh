@@ -165,6 +165,7 @@ namespace ipkgpu
     // threads of a k2_join CTA: one per window of the tile (ENUM_THREADS) plus one warp, so that the tile's
     // ENUM_THREADS + k - 1 columns (k <= 33) are covered by ONE pass of every per-column loop (phase clocks r01m: the second
     // pass over the last k - 1 columns cost as much latency as the first)
+    constexpr int JOIN_HIST_SLOTS = 256;     // partial top-byte histograms of the emission, one per SM id (mod 256)
     constexpr int JOIN_THREADS = ENUM_THREADS + 32;
     constexpr int JOIN_WARPS = JOIN_THREADS / 32;
 #ifndef IPK_JOIN_GROUP
@@ -438,6 +439,7 @@ namespace ipkgpu
         __shared__ uint32_t s_defer, s_qn[2], s_bh[32], s_nwork, s_nheavy;
         __shared__ int s_lo, s_hi;                           // pool cursors: bottom end grows up, top end grows down
         __shared__ uint32_t s_wsum[2][JOIN_WARPS];
+        __shared__ uint32_t s_hist[256];                     // the tile's records by the top byte of their k-mer (enum_args::top_hist)
 
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int k = P.k, sigma = int(A.sigma), bits = int(A.bits);
@@ -475,6 +477,8 @@ namespace ipkgpu
             s_merge[tid] = uint32_t(P.merges[tid].id) | uint32_t(P.merges[tid].left) << 8;
         }
         if (tid == 0) { s_lo = 0; s_hi = int(A.pool_cap); s_defer = 0; s_qn[0] = 0; s_qn[1] = 0; }
+        if (!DEBUG && A.top_hist)
+            for (int i = tid; i < 256; i += JOIN_THREADS) s_hist[i] = 0;
         stage_tile(A, node, s0, ncols, NCP, raw, bs, sval, sidx, &mbar, JOIN_THREADS);
 
         // ---- eps of every tree node for this thread's window (pk_compute.cpp:54-55; window.cpp:69-72) ---------------
@@ -770,8 +774,11 @@ namespace ipkgpu
                 const uint32_t ex_s = __shfl_sync(full, excl, s);
                 if (act)
                 {
-                    const float sa = el_score(pool[la_s + (rho - ex_s)]);
-                    atomicAdd(&wbase[(tid & ~31) + s], uint32_t(row_length(pool + lb_s, l0_s, sa, eps0)));
+                    const unsigned long long ea = pool[la_s + (rho - ex_s)];
+                    const uint32_t len = uint32_t(row_length(pool + lb_s, l0_s, el_score(ea), eps0));
+                    atomicAdd(&wbase[(tid & ~31) + s], len);
+                    // the records of this row share the top byte of their k-mer: it lies in the left element's key
+                    if (!DEBUG && A.top_hist && len) atomicAdd(&s_hist[el_key(ea) >> A.top_shift], len);
                 }
             }
             __syncwarp();
@@ -790,6 +797,16 @@ namespace ipkgpu
             return;
         }
 
+        if (!DEBUG && A.top_hist)
+        {
+            // the tile will emit what it counted: one RED per non-empty bin into the partial histogram of this SM (the slots keep
+            // the contention per address low); the first pass of the merge sort then needs no pass over the keys for it
+            uint32_t smid;
+            asm("mov.u32 %0, %%smid;" : "=r"(smid));
+            uint32_t* const g = A.top_hist + size_t(smid & (JOIN_HIST_SLOTS - 1)) * 256;
+            for (int i = tid; i < 256; i += JOIN_THREADS)
+                if (const uint32_t v = s_hist[i]) atomicAdd(g + i, v);
+        }
         IPK_PHASE(13);
         // ---- exclusive scans over the tile's windows: output offsets and row offsets ----------------------------------
         {

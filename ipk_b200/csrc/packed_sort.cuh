@@ -791,6 +791,23 @@ namespace ipkgpu
         IPK_LAUNCH(ctx, "rs_hist", n * 8, rs_hist_bits<<<hgrid, RS_HIST_THREADS, 2 * RS_RADIX * 4, ctx->stream>>>(keys, n, low_bits, 8, 1, ctx->hist.as<uint32_t>()));
     }
 
+    /// hist[d] = sum over the slots of partial[slot][d]: the join kernel's per-SM counts of the emission by top k-mer byte
+    __global__ void __launch_bounds__(RS_RADIX) ps_reduce_top_hist(const uint32_t* __restrict__ partial, uint32_t slots, uint32_t* __restrict__ hist)
+    {
+        uint32_t s = 0;
+        for (uint32_t i = 0; i < slots; ++i) s += partial[size_t(i) * RS_RADIX + threadIdx.x];
+        hist[threadIdx.x] = s;
+    }
+
+    /// the top-byte histogram from the join kernel's own counts (enum_args::top_hist) instead of a pass over the keys
+    inline void ps_top_histogram_from_join(ipkgpu_ctx* ctx)
+    {
+        ctx->reserve(ctx->hist, (RS_MAX_PASSES * RS_RADIX + 16) * 4);
+        IPK_CUDA(cudaMemsetAsync(ctx->hist.p, 0, (RS_MAX_PASSES * RS_RADIX + 16) * 4, ctx->stream));
+        IPK_LAUNCH(ctx, "ps_reduce_top_hist", uint64_t(JOIN_HIST_SLOTS) * RS_RADIX * 4,
+                   ps_reduce_top_hist<<<1, RS_RADIX, 0, ctx->stream>>>(ctx->join_hist.as<uint32_t>(), JOIN_HIST_SLOTS, ctx->hist.as<uint32_t>()));
+    }
+
     /// MSD pass: n (key, score) pairs -> packed records in D's buffers; d_base[256] (device) = where this rank's records of
     /// each bucket start inside the owner's buffer.  Uses tickets[15] of ctx->hist.
     inline void ps_msd_pack(ipkgpu_ctx* ctx, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint32_t low_bits,
