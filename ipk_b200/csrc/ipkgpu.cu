@@ -57,6 +57,25 @@ namespace ipkgpu
                 const auto t_1 = std::chrono::steady_clock::now();
                 const cudaError_t reg = cudaHostRegister(q, len, cudaHostRegisterPortable);
                 if (trace)
+                {
+                    // how much of the mapping the kernel backed with huge pages (smaps of the VMA that holds q)
+                    double huge_kb = -1.0, size_kb = 0.0;
+                    if (FILE* f = fopen("/proc/self/smaps", "r"))
+                    {
+                        char line[256];
+                        bool mine = false;
+                        while (fgets(line, sizeof line, f))
+                        {
+                            unsigned long lo = 0, hi = 0;
+                            if (sscanf(line, "%lx-%lx ", &lo, &hi) == 2 && strchr(line, '-') && !strstr(line, "kB")) mine = uintptr_t(q) >= lo && uintptr_t(q) < hi;
+                            else if (mine && !strncmp(line, "Size:", 5)) size_kb = atof(line + 5);
+                            else if (mine && !strncmp(line, "AnonHugePages:", 14)) { huge_kb = atof(line + 14); break; }
+                        }
+                        fclose(f);
+                    }
+                    fprintf(stderr, "[ipkgpu] pinned_alloc: %.0f of %.0f MB of the mapping are huge pages\n", huge_kb / 1024.0, size_kb / 1024.0);
+                }
+                if (trace)
                     fprintf(stderr, "[ipkgpu] pinned_alloc %.2f GB: touch %.1f ms, cudaHostRegister %.1f ms\n", double(len) * 1e-9,
                             std::chrono::duration<double, std::milli>(t_1 - t_0).count(),
                             std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_1).count());
